@@ -1,0 +1,323 @@
+#!/usr/bin/env python
+"""Headline benchmark: decode tokens/s (and prefill tokens/s) of the layer-sharded pipeline on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+One "step" = one decode step of the whole pipeline over the batch (one new token per sequence).
+N=1 : BASELINE.json configs[1]  -- TinyLlama-1.1B bf16, batch 1, 512-token prompt, one stage on one B200.
+N>1 : BASELINE.json configs[2]  -- Llama-3-8B bf16 layer-sharded over N stages (one rank per GPU), batch 16 per
+      micro-batch, N micro-batches in flight, hidden-state hand-off over NCCL send/recv (NVLink).
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle pipeline (the reference itself emits no
+tokens) on the host cores for the same metric / config.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "distributed-llms_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+METRIC = "decode_tokens_per_sec"
+UNIT = "tokens/s"
+
+
+# ------------------------------------------------------------------------------------------------------
+# helpers
+# ------------------------------------------------------------------------------------------------------
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "measured"
+    return 6650.0, 1590.0, "fallback"  # B200_PROFILING.md fallback figures
+
+
+def stage_bytes_per_step(hf: dict, n_layers: int, has_head: bool, batch: int, ctx: float, esz: int = 2) -> float:
+    """Algorithmic HBM bytes of one decode step of one stage: every weight of the stage once,
+    the K and V of every cached token once (+ lm_head on the last stage).  Norm weights, biases and
+    activations (< 0.1 %) are left out."""
+    d = hf.get("hidden_size", hf.get("n_embd"))
+    H = hf.get("num_attention_heads", hf.get("n_head"))
+    KV = hf.get("num_key_value_heads", H)
+    hd = hf.get("head_dim") or d // H
+    ffn = hf.get("intermediate_size", hf.get("n_inner") or 4 * d)
+    g = 2 if hf["model_type"] == "gpt2" else 3
+    w = d * H * hd + 2 * d * KV * hd + H * hd * d + g * d * ffn
+    kv = batch * ctx * 2 * KV * hd
+    total = n_layers * (w + kv) * esz
+    if has_head:
+        total += hf["vocab_size"] * d * esz
+    return float(total)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx, self.proc, self.path = gpu_index, None, f"/tmp/dllm_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.idx), "-lms", "100"],
+                                         stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for n, v in zip(names, f[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            os.remove(self.path)
+        except Exception:
+            pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+WORKLOADS = {
+    # name: (model, batch per micro-batch, prompt length)
+    "tinyllama-1.1b": ("tinyllama-1.1b", 1, 512),
+    "llama3-8b": ("llama3-8b", 16, 512),
+    "gpt2-small": ("gpt2-small", 1, 16),
+}
+
+
+# ------------------------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the oracle pipeline on the host cores
+# ------------------------------------------------------------------------------------------------------
+
+def cpu_pipeline_tokens_per_sec(model: str, batch: int, prompt_len: int, steps: int, warmup: int,
+                                n_stages: int = 1, budget_s: float = 150.0):
+    """Time `steps` greedy decode steps of the CPU oracle pipeline (fp32 math on the seeded random-init
+    weights, all host threads) after a `prompt_len`-token prefill.  Returns (tokens/s, description, cores)."""
+    from oracle.shard_oracle import NAMED_CONFIGS, build_pipeline, make_prompts, make_state_dict, pipeline_step
+    cfg = NAMED_CONFIGS[model]
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    depth = cfg.n_layers
+    note = ""
+    if cfg.n_layers * (cfg.hidden * cfg.hidden * 2 + 3 * cfg.hidden * cfg.ffn) * 4 > 24e9:
+        depth = 4  # 8B+ in fp32 does not fit a bounded CPU sample: time 4 layers, scale per layer
+        note = f"; {depth} of {cfg.n_layers} layers timed, per-layer time extrapolated"
+        cfg = type(cfg)(**{**cfg.__dict__, "n_layers": depth})
+    sd = make_state_dict(cfg, 1234, torch.float32)
+    stages = build_pipeline(cfg, sd, min(n_stages, cfg.n_layers), torch.float32, max_context=prompt_len + warmup + steps + 8)
+    prompts = make_prompts(cfg.vocab, batch, prompt_len, seed=7)
+    with torch.no_grad():
+        out = pipeline_step(stages, {"input_ids": prompts})
+        tok = out["next_token"]
+        for _ in range(warmup):
+            tok = pipeline_step(stages, {"input_ids": tok[:, None]})["next_token"]
+        t0 = time.perf_counter()
+        done = 0
+        for _ in range(steps):
+            tok = pipeline_step(stages, {"input_ids": tok[:, None]})["next_token"]
+            done += 1
+            if time.perf_counter() - t0 > budget_s:
+                break
+        dt = time.perf_counter() - t0
+    scale = NAMED_CONFIGS[model].n_layers / depth
+    tps = batch * done / (dt * scale)
+    desc = (f"{model} fp32 CPU oracle pipeline ({n_stages} stage(s)), batch {batch}, {prompt_len}-token prompt, "
+            f"{done} decode steps timed after {warmup} warm-up{note}")
+    return tps, desc, cores, dt / done * 1e3 * scale, done
+
+
+def run_reference(args) -> int:
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    model, batch, prompt = WORKLOADS[args.workload or ("tinyllama-1.1b" if args.gpus == 1 else "llama3-8b")]
+    steps = args.steps if args.steps > 0 else 16
+    warm = args.warmup if args.warmup >= 0 else 3
+    tps, desc, cores, ms, done = cpu_pipeline_tokens_per_sec(model, batch, prompt, steps, warm, n_stages=max(1, args.gpus))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
+        "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{model} decode, batch {batch}, {prompt}-token prompt", "stages": max(1, args.gpus)},
+        "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
+        "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "the reference as shipped emits no tokens (BASELINE.md 1); this is its CPU restatement (oracle/)",
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------------
+# our arm, one GPU
+# ------------------------------------------------------------------------------------------------------
+
+def run_single(args) -> int:
+    from src.engine import cabi
+    from src.model import random_init
+    from src.worker.node import ModelShard
+
+    model, batch, prompt_len = WORKLOADS[args.workload or "tinyllama-1.1b"]
+    if args.batch:
+        batch = args.batch
+    K = args.steps if args.steps > 0 else 256
+    W = args.warmup if args.warmup >= 0 else 8
+    W = max(W, 3)
+    hf = random_init.NAMED_CONFIGS[model]
+    L = hf.get("num_hidden_layers", hf.get("n_layer"))
+    torch.cuda.set_device(0)
+    dev = "cuda:0"
+    params = random_init.random_stage_parameters(hf, range(L), True, True, 1234, torch.bfloat16, device=dev)
+    max_ctx = prompt_len + 2 * (W + K) + 16
+    shard = ModelShard(0, params, config=hf, max_rows=max(128, batch), max_seqs=batch, max_context=max_ctx, page_size=64)
+    shard.to_device()
+    ex = shard.executor
+    g = torch.Generator().manual_seed(7)
+    prompts = torch.randint(0, hf["vocab_size"], (batch, prompt_len), generator=g)
+    hbm_peak, _, peak_kind = load_peaks()
+
+    # ---- prefill (warm once, then timed) ----
+    out = shard.compute({"input_ids": prompts})
+    torch.cuda.synchronize()
+    shard.reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = shard.compute({"input_ids": prompts})
+    e1.record()
+    torch.cuda.synchronize()
+    prefill_ms = e0.elapsed_time(e1)
+
+    # ---- decode, device-resident (value) ----
+    shard.decode_loop(batch, W)
+    torch.cuda.synchronize()
+    launches0 = cabi.kernel_launch_count()
+    sampler = ClockSampler(0)
+    sampler.start()
+    torch.cuda.synchronize()
+    e0.record()
+    toks = shard.decode_loop(batch, K)
+    e1.record()
+    torch.cuda.synchronize()
+    dec_ms = e0.elapsed_time(e1)
+    launches = cabi.kernel_launch_count() - launches0
+    value = batch * K / (dec_ms * 1e-3)
+    ctx_mid = prompt_len + W + K / 2.0
+
+    # ---- decode, end to end through the C ABI with host buffers (e2e) ----
+    seqs = list(range(batch))
+    cur = prompt_len + W + K  # tokens cached per sequence so far
+    ids_h = toks[:, -1].to(torch.int32).cpu().pin_memory()
+    pos_h = torch.full((batch,), cur, dtype=torch.int32).pin_memory()
+    seq_h = torch.arange(batch, dtype=torch.int32).pin_memory()
+    nxt_h = torch.zeros(batch, dtype=torch.int32).pin_memory()
+    for s in seqs:
+        ex.reserve(s, cur + W + K + 1)
+    stream = torch.cuda.current_stream()
+
+    def host_step():
+        ex.step_host(ids_h, pos_h, seq_h, next_token_out=nxt_h)
+        stream.synchronize()  # the host needs the token before it can issue the next step
+        ids_h.copy_(nxt_h)
+        pos_h.add_(1)
+
+    for _ in range(W):
+        host_step()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        host_step()
+    e1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    e2e_ms = e0.elapsed_time(e1)
+    e2e = batch * K / (e2e_ms * 1e-3)
+
+    # ---- roofline of the decode step (one graph replay = one launch of the whole stage) ----
+    algo = stage_bytes_per_step(hf, L, True, batch, ctx_mid)
+    step_s = dec_ms * 1e-3 / K
+    achieved = algo / step_s / 1e9
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": None, "peak_kind": peak_kind, "kernel": "decode step (CUDA graph of the stage's fused GEMV/attention kernels)",
+                "algorithmic_bytes_per_launch": algo}
+
+    # ---- CPU baseline on the host cores (bounded sample) ----
+    cpu = None
+    if not args.no_cpu_baseline:
+        tps, desc, cores, _, _ = cpu_pipeline_tokens_per_sec(model, batch, prompt_len, 8, 1, 1, budget_s=40.0)
+        cpu = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": K, "warmup": W,
+        "ms_per_step": dec_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": f"{model} decode, batch {batch}, {prompt_len}-token prompt, 1 stage", "model": model,
+                   "batch": batch, "prompt_len": prompt_len, "stages": 1, "weights": "random-init (HF default init, seed 1234)",
+                   "l2": "inputs larger than L2: every step streams the stage's weights (>= 2 GB) from HBM"},
+        "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 3 * 4 * batch, "d2h_bytes_per_step": 4 * batch,
+                "ms_per_step": e2e_ms / K},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "prefill": {"tokens_per_sec": batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
+                    "note": "chunked prefill through the decode kernels (no tensor-core GEMM yet)"},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def main() -> int:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=-1)
+    ap.add_argument("--warmup", type=int, default=-1)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, choices=[None, *WORKLOADS])
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    if not torch.cuda.is_available():
+        print(json.dumps({"error": "no CUDA device: the shard forward has no CPU path"}))
+        return 1
+    if args.gpus <= 1:
+        return run_single(args)
+    from bench_pipeline import run_pipeline  # multi-GPU arm
+    return run_pipeline(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

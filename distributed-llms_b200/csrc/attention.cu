@@ -1,0 +1,161 @@
+// Split-K flash-decoding attention over the paged KV cache.
+//
+// grid = (n_splits, H, R): one CTA owns one query head of one row and one slice of that row's
+// context.  Its four warps walk the slice token by token (lanes across head_dim, online softmax in
+// fp32), merge through shared memory and write an un-normalised partial (o, m, l) to scratch.  The
+// last CTA to finish a (row, head) -- found with an atomic ticket -- combines the splits and writes the
+// normalised output, so the step needs one launch and the scratch counters end up zero again.
+//
+// Rounding follows HF eager attention (HF:llama/modeling_llama.py:212-219): the score is rounded to
+// the activation dtype after the dot product and again after scaling; probabilities stay fp32 here
+// (HF rounds them to bf16 before P@V -- documented difference, below bf16 output resolution).
+#include <float.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace dllm {
+
+constexpr int kAttnThreads = 128;
+constexpr int kAttnWarps = kAttnThreads / 32;
+
+template <typename T, int HD>
+__global__ void __launch_bounds__(kAttnThreads) attn_decode_splitk_kernel(const AttnParams p) {
+    using D = DT<T>;
+    constexpr int EPL = HD / 32;  // elements of head_dim per lane
+    const int split = blockIdx.x, h = blockIdx.y, r = blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits;
+    const int kvh = h / (H / KV);
+    const int len = p.positions[r] + 1;
+    const int seq = p.seq_ids[r];
+    const int chunk = (len + S - 1) / S;
+    const int t0 = split * chunk;
+    const int t1 = min(len, t0 + chunk);
+    const float scale = rsqrtf((float)HD);
+    const int page_mask = (1 << p.kv.page_shift) - 1;
+    const int32_t* bt = p.kv.block_table + (size_t)seq * p.kv.pages_per_seq;
+    const T* kpool = static_cast<const T*>(p.kv.kpool);
+    const T* vpool = static_cast<const T*>(p.kv.vpool);
+
+    float q[EPL];
+    {
+        const T* qp = static_cast<const T*>(p.q) + ((size_t)r * H + h) * HD + lane * EPL;
+#pragma unroll
+        for (int e = 0; e < EPL; ++e) q[e] = D::to_f(qp[e]);
+    }
+
+    float m = -FLT_MAX, l = 0.f, o[EPL];
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) o[e] = 0.f;
+
+    constexpr int UN = 4;  // tokens in flight per warp
+    for (int tb = t0 + warp * UN; tb < t1; tb += kAttnWarps * UN) {
+        float kf[UN][EPL], vf[UN][EPL];
+#pragma unroll
+        for (int u = 0; u < UN; ++u) {
+            const int t = tb + u;
+            if (t < t1) {
+                const int page = bt[t >> p.kv.page_shift];
+                const size_t base = ((((size_t)page * KV + kvh) << p.kv.page_shift) + (t & page_mask)) * HD + lane * EPL;
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) {
+                    kf[u][e] = D::to_f(kpool[base + e]);
+                    vf[u][e] = D::to_f(vpool[base + e]);
+                }
+            } else {
+#pragma unroll
+                for (int e = 0; e < EPL; ++e) kf[u][e] = vf[u][e] = 0.f;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < UN; ++u) {
+            if (tb + u >= t1) break;  // warp-uniform
+            float d = 0.f;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) d = fmaf(q[e], kf[u][e], d);
+            d = warp_sum(d);
+            const float s = D::rnd(D::rnd(d) * scale);
+            const float mn = fmaxf(m, s);
+            const float corr = expf(m - mn);
+            const float pe = expf(s - mn);
+            l = l * corr + pe;
+#pragma unroll
+            for (int e = 0; e < EPL; ++e) o[e] = fmaf(pe, vf[u][e], o[e] * corr);
+            m = mn;
+        }
+    }
+
+    // merge the four warps
+    __shared__ float sm_m[kAttnWarps], sm_l[kAttnWarps];
+    __shared__ float sm_o[kAttnWarps][HD];
+    __shared__ int s_last;
+    if (lane == 0) {
+        sm_m[warp] = m;
+        sm_l[warp] = l;
+    }
+#pragma unroll
+    for (int e = 0; e < EPL; ++e) sm_o[warp][lane * EPL + e] = o[e];
+    __syncthreads();
+    float M = -FLT_MAX;
+#pragma unroll
+    for (int w = 0; w < kAttnWarps; ++w) M = fmaxf(M, sm_m[w]);
+    const size_t pidx = ((size_t)r * H + h) * S + split;
+    if (threadIdx.x < HD) {
+        float acc = 0.f;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) acc += sm_o[w][threadIdx.x] * expf(sm_m[w] - M);
+        p.part_o[pidx * HD + threadIdx.x] = acc;
+    }
+    if (threadIdx.x == 0) {
+        float L = 0.f;
+#pragma unroll
+        for (int w = 0; w < kAttnWarps; ++w) L += sm_l[w] * expf(sm_m[w] - M);
+        p.part_ml[pidx * 2 + 0] = M;  // -FLT_MAX marks an empty split (L == 0)
+        p.part_ml[pidx * 2 + 1] = L;
+    }
+
+    // last CTA of this (row, head) combines the splits
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned ticket = atomicAdd(p.counters + (size_t)r * H + h, 1u);
+        s_last = (ticket == (unsigned)S - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    const size_t pb = ((size_t)r * H + h) * S;
+    float Mg = -FLT_MAX;
+    for (int s = 0; s < S; ++s) Mg = fmaxf(Mg, __ldcg(p.part_ml + (pb + s) * 2));
+    float Lg = 0.f;
+    for (int s = 0; s < S; ++s)
+        Lg += __ldcg(p.part_ml + (pb + s) * 2 + 1) * expf(__ldcg(p.part_ml + (pb + s) * 2) - Mg);
+    if (threadIdx.x < HD) {
+        float acc = 0.f;
+        for (int s = 0; s < S; ++s)
+            acc += __ldcg(p.part_o + (pb + s) * HD + threadIdx.x) * expf(__ldcg(p.part_ml + (pb + s) * 2) - Mg);
+        static_cast<T*>(p.out)[((size_t)r * H + h) * HD + threadIdx.x] = D::from_f(acc / Lg);
+    }
+    if (threadIdx.x == 0) p.counters[(size_t)r * H + h] = 0u;
+}
+
+template <typename T>
+static cudaError_t launch_t(const AttnParams& p, cudaStream_t s) {
+    dim3 grid(p.n_splits, p.n_heads, p.n_rows);
+    switch (p.head_dim) {
+        case 32: attn_decode_splitk_kernel<T, 32><<<grid, kAttnThreads, 0, s>>>(p); break;
+        case 64: attn_decode_splitk_kernel<T, 64><<<grid, kAttnThreads, 0, s>>>(p); break;
+        case 128: attn_decode_splitk_kernel<T, 128><<<grid, kAttnThreads, 0, s>>>(p); break;
+        default: return cudaErrorInvalidValue;
+    }
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_attn_decode(int dtype, const AttnParams& p, cudaStream_t s) {
+    if (p.n_rows <= 0 || p.n_splits <= 0 || p.n_heads % p.n_kv_heads != 0) return cudaErrorInvalidValue;
+    return dtype == 0 ? launch_t<bf16>(p, s) : launch_t<float>(p, s);
+}
+
+}  // namespace dllm

@@ -1,0 +1,94 @@
+// Internal launcher interface between the shard runtime / C ABI and the sm_100a kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dllm {
+
+enum NormKind { NORM_NONE = 0, NORM_RMS = 1, NORM_LAYER = 2 };
+enum EpiKind { EPI_RESIDUAL = 0, EPI_QKV = 1, EPI_GATEUP = 2, EPI_FC_GELU = 3, EPI_LOGITS = 4 };
+
+// Where a (sequence slot, position) lives in the paged KV pools of one layer.
+//   pool layout: [num_pages][KV][page_size][hd]; block_table: [max_seqs][pages_per_seq]
+struct PagedKV {
+    void* kpool;
+    void* vpool;
+    const int32_t* block_table;
+    int32_t pages_per_seq;
+    int32_t page_shift;  // log2(page_size)
+};
+
+// One fused decode GEMV launch: prologue (stage + normalise the rows), y = W x, epilogue.
+struct GemvParams {
+    // rows
+    const void* x;           // [*, K]   input rows (residual stream / attention output / activation)
+    const int32_t* row_map;  // optional gather: logical row r reads x[row_map[r]]
+    int32_t n_rows;          // R
+    int32_t K;
+    // prologue
+    int32_t norm;            // NormKind
+    const void* norm_w;
+    const void* norm_b;
+    float eps;
+    // weights: up to three [n_i, K] matrices handled by one launch
+    const void* w[3];
+    const void* b[3];
+    int32_t n[3];            // rows of each matrix
+    // epilogue
+    int32_t epi;             // EpiKind
+    void* y;                 // RESIDUAL: [R, n0] (in/out); QKV: q [R, H*hd]; GATEUP/FC: act [R, ffn]
+    int32_t accumulate;      // RESIDUAL: y += ...
+    // QKV
+    int32_t n_heads, n_kv_heads, head_dim, rope;
+    const float* rope_cos;
+    const float* rope_sin;
+    const int32_t* positions;
+    const int32_t* seq_ids;
+    PagedKV kv;
+    // LOGITS
+    float* logits;           // [R, n0] fp32 or null
+    float* arg_val;          // [grid, R] scratch
+    int32_t* arg_idx;        // [grid, R] scratch
+    uint32_t* counter;       // 1 counter, zero before the launch, left zero
+    int32_t* next_token;     // [R] or null
+};
+
+struct AttnParams {
+    const void* q;           // [R, H, hd]
+    PagedKV kv;
+    const int32_t* positions;
+    const int32_t* seq_ids;
+    int32_t n_rows, n_heads, n_kv_heads, head_dim, n_splits;
+    float* part_o;           // [R, H, S, hd]
+    float* part_ml;          // [R, H, S, 2]
+    uint32_t* counters;      // [R, H], zero before the launch, left zero
+    void* out;               // [R, H*hd]
+};
+
+struct EmbedParams {
+    const int32_t* ids;
+    const int32_t* positions;
+    const void* wte;
+    const void* wpe;         // null unless GPT-2
+    void* out;               // [R, d]
+    int32_t n_rows, hidden, vocab;
+};
+
+// Each returns cudaGetLastError() of its launch.  dtype: 0 = bf16, 1 = fp32.
+cudaError_t gemv_init_device();  // once per device, outside stream capture
+cudaError_t launch_gemv(int dtype, const GemvParams& p, int num_sms, cudaStream_t s);
+int gemv_grid_size(int dtype, const GemvParams& p, int num_sms);  // grid launch_gemv will use (sizes arg scratch)
+cudaError_t launch_attn_decode(int dtype, const AttnParams& p, cudaStream_t s);
+cudaError_t launch_embed(int dtype, const EmbedParams& p, cudaStream_t s);
+cudaError_t launch_decode_begin(int32_t* ids, int32_t* positions, int32_t* seq_ids, const int32_t* next_token,
+                                const int32_t* logit_rows, int32_t n, int32_t* step_ctr, cudaStream_t s);
+cudaError_t launch_advance(int32_t* ids, int32_t* positions, const int32_t* next_token, int32_t* tok_ring,
+                           int32_t* step_ctr, int32_t n_rows, cudaStream_t s);
+cudaError_t launch_legacy_matmul(const float* in, const float* param, float* out, int m, int k, int n,
+                                 cudaStream_t s);
+
+void count_launch(unsigned long long n = 1);
+unsigned long long launch_count();
+
+}  // namespace dllm

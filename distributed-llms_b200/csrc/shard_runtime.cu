@@ -1,0 +1,537 @@
+// The shard runtime behind the C ABI (include/dllm_b200.h): one handle = one pipeline stage
+// (reference: one `ModelShard`, src/worker/node.py:13-32).  It owns the stage's paged KV cache, block
+// table, activation and scratch buffers; it binds (does not own) the caller's weights; it turns a
+// forward call into a CUDA-graph replay of the fused decode kernels.
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/dllm_b200.h"
+#include "kernels.h"
+
+using namespace dllm;
+
+// ---- error plumbing ------------------------------------------------------------------------------
+
+static thread_local std::string g_err;
+
+static int fail(const std::string& msg) {
+    g_err = msg;
+    return 1;
+}
+
+#define CUDA_TRY(expr)                                                                             \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess)                                                                     \
+            return fail(std::string(#expr) + ": " + cudaGetErrorName(_e) + " (" + cudaGetErrorString(_e) + ")"); \
+    } while (0)
+
+extern "C" const char* dllm_last_error(void) { return g_err.c_str(); }
+extern "C" int dllm_abi_version(void) { return DLLM_ABI_VERSION; }
+extern "C" int dllm_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+extern "C" unsigned long long dllm_kernel_launch_count(void) { return launch_count(); }
+
+static int ensure_device_ready() {
+    // per-device one-time kernel attribute set-up
+    static bool ready[64] = {false};
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 64 && ready[dev]) return 0;
+    CUDA_TRY(gemv_init_device());
+    if (dev < 64) ready[dev] = true;
+    return 0;
+}
+
+// ---- the handle -----------------------------------------------------------------------------------
+
+struct GraphEntry {
+    cudaGraphExec_t exec = nullptr;
+    unsigned long long kernels = 0;
+};
+
+struct dllm_shard {
+    dllm_shard_config cfg;
+    std::vector<dllm_layer_weights> layers;
+    dllm_io_weights io;
+    int device = 0, num_sms = 148;
+    size_t esz = 2;
+    // device memory
+    char* arena = nullptr;
+    size_t arena_bytes = 0;
+    void* h = nullptr;         // residual stream [max_rows, d]
+    void* qbuf = nullptr;      // [max_rows, H*hd]
+    void* attn_out = nullptr;  // [max_rows, H*hd]
+    void* act = nullptr;       // [max_rows, ffn]
+    int32_t *ids = nullptr, *pos = nullptr, *seq = nullptr, *logit_rows = nullptr, *arange = nullptr;
+    int32_t *next_tok = nullptr, *block_table = nullptr, *tok_ring = nullptr, *step_ctr = nullptr;
+    float* logits = nullptr;   // [max_logit_rows, V]
+    float *part_o = nullptr, *part_ml = nullptr, *arg_val = nullptr;
+    int32_t* arg_idx = nullptr;
+    uint32_t *attn_counters = nullptr, *arg_counter = nullptr;
+    std::vector<void*> kpool, vpool;
+    // geometry
+    int pages_per_seq = 0, page_shift = 0, num_pages = 0, max_logit_rows = 0, arg_grid_cap = 0;
+    long max_partials = 0;
+    size_t tok_ring_cap = 0;
+    // host-side KV bookkeeping
+    std::vector<int32_t> free_pages;
+    std::vector<std::vector<int32_t>> seq_pages;
+    int32_t* h_bt_row = nullptr;  // pinned staging, one block-table row per slot
+    // graphs
+    std::map<unsigned long long, GraphEntry> graphs;
+    cudaStream_t cap_stream = nullptr;
+};
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int pick_splits(const dllm_shard* s, int n_rows) {
+    const int H = s->cfg.n_heads;
+    const long target = 8L * s->num_sms;
+    long S = (target + (long)n_rows * H - 1) / ((long)n_rows * H);
+    const long cap_ctx = (s->cfg.max_context + 15) / 16;
+    if (S > cap_ctx) S = cap_ctx;
+    if (S > 64) S = 64;
+    while (S > 1 && (long)n_rows * H * S > s->max_partials) --S;
+    if (S < 1) S = 1;
+    return (int)S;
+}
+
+extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_weights* layers,
+                                 const dllm_io_weights* io, dllm_shard** out) {
+    if (!cfg || !out || (cfg->n_layers > 0 && !layers) || !io) return fail("dllm_shard_create: null argument");
+    *out = nullptr;
+    const dllm_shard_config& c = *cfg;
+    if (c.dtype != DLLM_DTYPE_BF16 && c.dtype != DLLM_DTYPE_F32) return fail("dllm_shard_create: bad dtype");
+    if (c.arch < DLLM_ARCH_GPT2 || c.arch > DLLM_ARCH_QWEN2) return fail("dllm_shard_create: bad arch");
+    if (c.head_dim != 32 && c.head_dim != 64 && c.head_dim != 128)
+        return fail("dllm_shard_create: head_dim must be 32, 64 or 128");
+    if (c.n_heads <= 0 || c.n_kv_heads <= 0 || c.n_heads % c.n_kv_heads != 0)
+        return fail("dllm_shard_create: n_heads must be a positive multiple of n_kv_heads");
+    const int vec = c.dtype == DLLM_DTYPE_BF16 ? 8 : 4;
+    if (c.hidden % vec || c.ffn % vec || (c.n_heads * c.head_dim) % vec)
+        return fail("dllm_shard_create: hidden, ffn and H*hd must be multiples of the 16-byte vector width");
+    if (c.page_size < 8 || (c.page_size & (c.page_size - 1))) return fail("dllm_shard_create: page_size must be a power of two >= 8");
+    if (c.max_rows <= 0 || c.max_seqs <= 0 || c.max_context <= 0) return fail("dllm_shard_create: max_rows/max_seqs/max_context must be positive");
+    if (c.has_embed && !io->wte) return fail("dllm_shard_create: has_embed but wte is null");
+    if (c.has_head && (!io->lm_head || !io->final_norm_w)) return fail("dllm_shard_create: has_head but lm_head/final_norm_w is null");
+    if (c.arch != DLLM_ARCH_GPT2 && c.n_layers > 0 && (!io->rope_cos || !io->rope_sin))
+        return fail("dllm_shard_create: rope tables missing");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail("dllm_shard_create: no CUDA device (this library has no CPU path)");
+    }
+    if (ensure_device_ready()) return 1;
+
+    dllm_shard* s = new dllm_shard();
+    s->cfg = c;
+    s->layers.assign(layers, layers + c.n_layers);
+    s->io = *io;
+    s->esz = c.dtype == DLLM_DTYPE_BF16 ? 2 : 4;
+    cudaGetDevice(&s->device);
+    cudaDeviceGetAttribute(&s->num_sms, cudaDevAttrMultiProcessorCount, s->device);
+    s->pages_per_seq = (c.max_context + c.page_size - 1) / c.page_size;
+    while ((1 << s->page_shift) < c.page_size) ++s->page_shift;
+    s->num_pages = c.num_pages > 0 ? c.num_pages : c.max_seqs * s->pages_per_seq;
+    s->max_logit_rows = c.has_head ? c.max_rows : 0;
+    s->max_partials = (long)c.max_rows * c.n_heads + 16L * s->num_sms;
+    s->arg_grid_cap = s->num_sms * 4 + 8;
+    s->tok_ring_cap = 1u << 20;
+
+    // carve one arena
+    const size_t Hd = (size_t)c.n_heads * c.head_dim;
+    struct Item { void** p; size_t bytes; };
+    std::vector<Item> items;
+    auto add = [&](void* pp, size_t bytes) { items.push_back({(void**)pp, align_up(bytes ? bytes : 16, 256)}); };
+    add(&s->h, (size_t)c.max_rows * c.hidden * s->esz);
+    add(&s->qbuf, (size_t)c.max_rows * Hd * s->esz);
+    add(&s->attn_out, (size_t)c.max_rows * Hd * s->esz);
+    add(&s->act, (size_t)c.max_rows * c.ffn * s->esz);
+    add(&s->ids, (size_t)c.max_rows * 4);
+    add(&s->pos, (size_t)c.max_rows * 4);
+    add(&s->seq, (size_t)c.max_rows * 4);
+    add(&s->logit_rows, (size_t)c.max_rows * 4);
+    add(&s->arange, (size_t)c.max_rows * 4);
+    add(&s->next_tok, (size_t)c.max_rows * 4);
+    add(&s->block_table, (size_t)c.max_seqs * s->pages_per_seq * 4);
+    add(&s->tok_ring, c.has_head && c.has_embed ? s->tok_ring_cap * 4 : 0);
+    add(&s->step_ctr, 4);
+    add(&s->logits, (size_t)s->max_logit_rows * c.vocab * 4);
+    add(&s->part_o, (size_t)s->max_partials * c.head_dim * 4);
+    add(&s->part_ml, (size_t)s->max_partials * 2 * 4);
+    add(&s->arg_val, (size_t)s->arg_grid_cap * c.max_rows * 4);
+    add(&s->arg_idx, (size_t)s->arg_grid_cap * c.max_rows * 4);
+    add(&s->attn_counters, (size_t)c.max_rows * c.n_heads * 4);
+    add(&s->arg_counter, 4);
+    const size_t kv_layer = (size_t)s->num_pages * c.n_kv_heads * c.page_size * c.head_dim * s->esz;
+    s->kpool.resize(c.n_layers);
+    s->vpool.resize(c.n_layers);
+    for (int l = 0; l < c.n_layers; ++l) {
+        add(&s->kpool[l], kv_layer);
+        add(&s->vpool[l], kv_layer);
+    }
+    size_t total = 0;
+    for (auto& it : items) total += it.bytes;
+    cudaError_t e = cudaMalloc((void**)&s->arena, total);
+    if (e != cudaSuccess) {
+        delete s;
+        char buf[160];
+        snprintf(buf, sizeof buf, "dllm_shard_create: cudaMalloc of %zu bytes failed: %s", total, cudaGetErrorString(e));
+        cudaGetLastError();
+        return fail(buf);
+    }
+    s->arena_bytes = total;
+    size_t off = 0;
+    for (auto& it : items) {
+        *it.p = s->arena + off;
+        off += it.bytes;
+    }
+    // zero everything that is not KV (counters must start at zero); KV pages are written before they are read
+    const size_t head_bytes = (size_t)((char*)(c.n_layers ? s->kpool[0] : (void*)(s->arena + total)) - s->arena);
+    e = cudaMemset(s->arena, 0, head_bytes);
+    if (e == cudaSuccess) e = cudaMemset(s->block_table, 0xff, (size_t)c.max_seqs * s->pages_per_seq * 4);  // -1
+    std::vector<int32_t> ar(c.max_rows);
+    for (int i = 0; i < c.max_rows; ++i) ar[i] = i;
+    if (e == cudaSuccess) e = cudaMemcpy(s->arange, ar.data(), ar.size() * 4, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&s->h_bt_row, (size_t)c.max_seqs * s->pages_per_seq * 4);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) {
+        std::string m = std::string("dllm_shard_create: ") + cudaGetErrorString(e);
+        cudaGetLastError();
+        dllm_shard_destroy(s);
+        return fail(m);
+    }
+    memset(s->h_bt_row, 0xff, (size_t)c.max_seqs * s->pages_per_seq * 4);
+    s->free_pages.resize(s->num_pages);
+    for (int i = 0; i < s->num_pages; ++i) s->free_pages[i] = s->num_pages - 1 - i;  // pop_back hands out 0,1,2,...
+    s->seq_pages.resize(c.max_seqs);
+    *out = s;
+    return 0;
+}
+
+extern "C" int dllm_shard_destroy(dllm_shard* s) {
+    if (!s) return 0;
+    cudaSetDevice(s->device);
+    cudaDeviceSynchronize();
+    for (auto& kv : s->graphs)
+        if (kv.second.exec) cudaGraphExecDestroy(kv.second.exec);
+    if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
+    if (s->h_bt_row) cudaFreeHost(s->h_bt_row);
+    if (s->arena) cudaFree(s->arena);
+    cudaGetLastError();
+    delete s;
+    return 0;
+}
+
+extern "C" size_t dllm_shard_device_bytes(const dllm_shard* s) { return s ? s->arena_bytes : 0; }
+
+// ---- KV pages ---------------------------------------------------------------------------------------
+
+extern "C" int dllm_shard_kv_reserve(dllm_shard* s, int32_t seq_id, int32_t n_tokens, void* stream) {
+    if (!s) return fail("dllm_shard_kv_reserve: null shard");
+    if (seq_id < 0 || seq_id >= s->cfg.max_seqs) return fail("dllm_shard_kv_reserve: seq_id out of range");
+    if (n_tokens < 0 || n_tokens > s->cfg.max_context) return fail("dllm_shard_kv_reserve: n_tokens exceeds max_context");
+    auto& pages = s->seq_pages[seq_id];
+    const int need = (n_tokens + s->cfg.page_size - 1) / s->cfg.page_size;
+    if ((int)pages.size() >= need) return 0;
+    if ((int)(need - pages.size()) > (int)s->free_pages.size()) return fail("dllm_shard_kv_reserve: KV page pool exhausted");
+    int32_t* row = s->h_bt_row + (size_t)seq_id * s->pages_per_seq;
+    const size_t first = pages.size();
+    while ((int)pages.size() < need) {
+        const int32_t pg = s->free_pages.back();
+        s->free_pages.pop_back();
+        row[pages.size()] = pg;
+        pages.push_back(pg);
+    }
+    CUDA_TRY(cudaMemcpyAsync(s->block_table + (size_t)seq_id * s->pages_per_seq + first, row + first,
+                             (pages.size() - first) * 4, cudaMemcpyHostToDevice, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int dllm_shard_kv_release(dllm_shard* s, int32_t seq_id) {
+    if (!s) return fail("dllm_shard_kv_release: null shard");
+    if (seq_id >= s->cfg.max_seqs) return fail("dllm_shard_kv_release: seq_id out of range");
+    const int lo = seq_id < 0 ? 0 : seq_id, hi = seq_id < 0 ? s->cfg.max_seqs : seq_id + 1;
+    for (int q = lo; q < hi; ++q) {
+        auto& pages = s->seq_pages[q];
+        while (!pages.empty()) {
+            s->free_pages.push_back(pages.back());
+            pages.pop_back();
+        }
+    }
+    // block-table rows keep their stale ids: a slot is always re-reserved before it is used again
+    return 0;
+}
+
+extern "C" int dllm_shard_kv_free_pages(const dllm_shard* s) { return s ? (int)s->free_pages.size() : 0; }
+
+// ---- kernel sequence of one stage step -------------------------------------------------------------
+
+// Enqueue this stage's kernels for n_rows rows already staged in the handle's buffers.
+static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advance, cudaStream_t st) {
+    const dllm_shard_config& c = s->cfg;
+    const int dt = c.dtype;
+    const bool gpt2 = c.arch == DLLM_ARCH_GPT2;
+    const int norm = gpt2 ? NORM_LAYER : NORM_RMS;
+    const int Hd = c.n_heads * c.head_dim;
+    if (c.has_embed) {
+        EmbedParams e{};
+        e.ids = s->ids; e.positions = s->pos; e.wte = s->io.wte; e.wpe = gpt2 ? s->io.wpe : nullptr;
+        e.out = s->h; e.n_rows = n_rows; e.hidden = c.hidden; e.vocab = c.vocab;
+        CUDA_TRY(launch_embed(dt, e, st));
+    }
+    const int splits = pick_splits(s, n_rows);
+    for (int l = 0; l < c.n_layers; ++l) {
+        const dllm_layer_weights& w = s->layers[l];
+        PagedKV kv{s->kpool[l], s->vpool[l], s->block_table, s->pages_per_seq, s->page_shift};
+        {   // K1: norm -> QKV -> bias -> rope -> paged append
+            GemvParams p{};
+            p.x = s->h; p.n_rows = n_rows; p.K = c.hidden;
+            p.norm = norm; p.norm_w = w.norm1_w; p.norm_b = w.norm1_b; p.eps = c.norm_eps;
+            p.w[0] = w.wq; p.w[1] = w.wk; p.w[2] = w.wv; p.b[0] = w.bq; p.b[1] = w.bk; p.b[2] = w.bv;
+            p.n[0] = Hd; p.n[1] = p.n[2] = c.n_kv_heads * c.head_dim;
+            p.epi = EPI_QKV; p.y = s->qbuf;
+            p.n_heads = c.n_heads; p.n_kv_heads = c.n_kv_heads; p.head_dim = c.head_dim; p.rope = !gpt2;
+            p.rope_cos = s->io.rope_cos; p.rope_sin = s->io.rope_sin;
+            p.positions = s->pos; p.seq_ids = s->seq; p.kv = kv;
+            CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
+        }
+        {   // K2: split-K flash decoding
+            AttnParams a{};
+            a.q = s->qbuf; a.kv = kv; a.positions = s->pos; a.seq_ids = s->seq;
+            a.n_rows = n_rows; a.n_heads = c.n_heads; a.n_kv_heads = c.n_kv_heads; a.head_dim = c.head_dim;
+            a.n_splits = splits; a.part_o = s->part_o; a.part_ml = s->part_ml; a.counters = s->attn_counters;
+            a.out = s->attn_out;
+            CUDA_TRY(launch_attn_decode(dt, a, st));
+        }
+        {   // K3: o-proj + residual
+            GemvParams p{};
+            p.x = s->attn_out; p.n_rows = n_rows; p.K = Hd; p.norm = NORM_NONE;
+            p.w[0] = w.wo; p.b[0] = w.bo; p.n[0] = c.hidden;
+            p.epi = EPI_RESIDUAL; p.y = s->h; p.accumulate = 1;
+            CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
+        }
+        {   // K4: norm -> gate/up -> SiLU*up   |   norm -> fc -> gelu_new
+            GemvParams p{};
+            p.x = s->h; p.n_rows = n_rows; p.K = c.hidden;
+            p.norm = norm; p.norm_w = w.norm2_w; p.norm_b = w.norm2_b; p.eps = c.norm_eps;
+            if (gpt2) { p.w[0] = w.w_up; p.b[0] = w.b_up; p.n[0] = c.ffn; p.epi = EPI_FC_GELU; }
+            else { p.w[0] = w.w_gate; p.w[1] = w.w_up; p.n[0] = p.n[1] = c.ffn; p.epi = EPI_GATEUP; }
+            p.y = s->act;
+            CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
+        }
+        {   // K5: down-proj + residual
+            GemvParams p{};
+            p.x = s->act; p.n_rows = n_rows; p.K = c.ffn; p.norm = NORM_NONE;
+            p.w[0] = w.w_down; p.b[0] = w.b_down; p.n[0] = c.hidden;
+            p.epi = EPI_RESIDUAL; p.y = s->h; p.accumulate = 1;
+            CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
+        }
+    }
+    if (c.has_head && n_logit_rows > 0) {   // K6: final norm -> lm_head -> argmax
+        GemvParams p{};
+        p.x = s->h; p.row_map = s->logit_rows; p.n_rows = n_logit_rows; p.K = c.hidden;
+        p.norm = norm; p.norm_w = s->io.final_norm_w; p.norm_b = s->io.final_norm_b; p.eps = c.norm_eps;
+        p.w[0] = s->io.lm_head; p.n[0] = c.vocab; p.epi = EPI_LOGITS;
+        p.logits = s->logits; p.arg_val = s->arg_val; p.arg_idx = s->arg_idx; p.counter = s->arg_counter;
+        p.next_token = s->next_tok;
+        if (gemv_grid_size(dt, p, s->num_sms) > s->arg_grid_cap) return fail("internal: argmax scratch too small");
+        CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
+    }
+    if (advance) CUDA_TRY(launch_advance(s->ids, s->pos, s->next_tok, s->tok_ring, s->step_ctr, n_rows, st));
+    return 0;
+}
+
+// Replay (capturing on first use) the graph of one step; large row counts launch directly.
+static int run_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advance, cudaStream_t st) {
+    constexpr int kGraphMaxRows = 64;
+    if (n_rows > kGraphMaxRows) return enqueue_step(s, n_rows, n_logit_rows, advance, st);
+    const unsigned long long key = ((unsigned long long)n_rows << 32) | ((unsigned long long)n_logit_rows << 1) | (advance ? 1 : 0);
+    auto it = s->graphs.find(key);
+    if (it == s->graphs.end()) {
+        cudaGraph_t graph = nullptr;
+        const unsigned long long before = launch_count();
+        CUDA_TRY(cudaStreamBeginCapture(s->cap_stream, cudaStreamCaptureModeThreadLocal));
+        const int rc = enqueue_step(s, n_rows, n_logit_rows, advance, s->cap_stream);
+        const cudaError_t ce = cudaStreamEndCapture(s->cap_stream, &graph);
+        if (rc) {
+            if (graph) cudaGraphDestroy(graph);
+            cudaGetLastError();
+            return rc;
+        }
+        CUDA_TRY(ce);
+        GraphEntry ge;
+        ge.kernels = launch_count() - before;
+        count_launch(0ULL - ge.kernels);  // capture enqueued nothing; replays are what count
+        const cudaError_t ie = cudaGraphInstantiate(&ge.exec, graph, 0);
+        cudaGraphDestroy(graph);
+        CUDA_TRY(ie);
+        it = s->graphs.emplace(key, ge).first;
+    }
+    CUDA_TRY(cudaGraphLaunch(it->second.exec, st));
+    count_launch(it->second.kernels);
+    return 0;
+}
+
+// ---- the hot path ------------------------------------------------------------------------------------
+
+extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_t* positions,
+                                  const int32_t* seq_ids, int32_t n_rows, void* hidden_out,
+                                  const int32_t* logit_rows, int32_t n_logit_rows, float* logits_out,
+                                  int32_t* next_token_out, void* stream) {
+    if (!s) return fail("dllm_shard_forward: null shard");
+    if (!input || !positions || !seq_ids) return fail("dllm_shard_forward: input, positions and seq_ids are required");
+    const dllm_shard_config& c = s->cfg;
+    if (n_rows <= 0 || n_rows > c.max_rows) return fail("dllm_shard_forward: n_rows out of range (max_rows)");
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = -1;
+    cudaGetDevice(&dev);
+    if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
+    if (c.has_embed) CUDA_TRY(cudaMemcpyAsync(s->ids, input, (size_t)n_rows * 4, cudaMemcpyDefault, st));
+    else CUDA_TRY(cudaMemcpyAsync(s->h, input, (size_t)n_rows * c.hidden * s->esz, cudaMemcpyDefault, st));
+    CUDA_TRY(cudaMemcpyAsync(s->pos, positions, (size_t)n_rows * 4, cudaMemcpyDefault, st));
+    CUDA_TRY(cudaMemcpyAsync(s->seq, seq_ids, (size_t)n_rows * 4, cudaMemcpyDefault, st));
+    int nl = 0;
+    if (c.has_head) {
+        if (logit_rows) {
+            if (n_logit_rows <= 0 || n_logit_rows > n_rows) return fail("dllm_shard_forward: n_logit_rows out of range");
+            nl = n_logit_rows;
+            CUDA_TRY(cudaMemcpyAsync(s->logit_rows, logit_rows, (size_t)nl * 4, cudaMemcpyDefault, st));
+        } else {
+            nl = n_rows;
+            CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    if (run_step(s, n_rows, nl, false, st)) return 1;
+    if (hidden_out) CUDA_TRY(cudaMemcpyAsync(hidden_out, s->h, (size_t)n_rows * c.hidden * s->esz, cudaMemcpyDefault, st));
+    if (c.has_head && logits_out)
+        CUDA_TRY(cudaMemcpyAsync(logits_out, s->logits, (size_t)nl * c.vocab * 4, cudaMemcpyDefault, st));
+    if (c.has_head && next_token_out)
+        CUDA_TRY(cudaMemcpyAsync(next_token_out, s->next_tok, (size_t)nl * 4, cudaMemcpyDefault, st));
+    return 0;
+}
+
+extern "C" int dllm_shard_decode_loop(dllm_shard* s, int32_t n_rows, int32_t n_steps, int32_t* tokens_out,
+                                      void* stream) {
+    if (!s) return fail("dllm_shard_decode_loop: null shard");
+    const dllm_shard_config& c = s->cfg;
+    if (!c.has_embed || !c.has_head) return fail("dllm_shard_decode_loop: the shard must own both the embedding and the head");
+    if (n_rows <= 0 || n_rows > c.max_rows || n_rows > 1024) return fail("dllm_shard_decode_loop: n_rows out of range");
+    if (n_steps <= 0 || (size_t)n_steps * n_rows > s->tok_ring_cap) return fail("dllm_shard_decode_loop: n_steps out of range");
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = -1;
+    cudaGetDevice(&dev);
+    if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(launch_decode_begin(s->ids, s->pos, s->seq, s->next_tok, s->logit_rows, n_rows, s->step_ctr, st));
+    CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)n_rows * 4, cudaMemcpyDeviceToDevice, st));
+    for (int i = 0; i < n_steps; ++i)
+        if (run_step(s, n_rows, n_rows, true, st)) return 1;
+    if (tokens_out)
+        CUDA_TRY(cudaMemcpyAsync(tokens_out, s->tok_ring, (size_t)n_steps * n_rows * 4, cudaMemcpyDefault, st));
+    return 0;
+}
+
+// ---- hand-off ---------------------------------------------------------------------------------------
+
+extern "C" int dllm_handoff_peer_copy(void* dst_ptr, int dst_device, const void* src_ptr, int src_device,
+                                      size_t bytes, void* stream) {
+    if (!dst_ptr || !src_ptr) return fail("dllm_handoff_peer_copy: null pointer");
+    if (bytes == 0) return 0;
+    if (dst_device == src_device) {
+        CUDA_TRY(cudaMemcpyAsync(dst_ptr, src_ptr, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+        return 0;
+    }
+    int can = 0;
+    CUDA_TRY(cudaDeviceCanAccessPeer(&can, src_device, dst_device));
+    if (can) {
+        int cur = 0;
+        cudaGetDevice(&cur);
+        cudaSetDevice(src_device);
+        cudaError_t e = cudaDeviceEnablePeerAccess(dst_device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+            cudaSetDevice(cur);
+            CUDA_TRY(e);
+        }
+        cudaGetLastError();
+        cudaSetDevice(cur);
+    }
+    CUDA_TRY(cudaMemcpyPeerAsync(dst_ptr, dst_device, src_ptr, src_device, bytes, (cudaStream_t)stream));
+    return 0;
+}
+
+// ---- single operators ----------------------------------------------------------------------------------
+
+extern "C" int dllm_op_gemv(int32_t dtype, const void* d_x, const void* d_w, const void* d_bias, void* d_y,
+                            int32_t n_rows, int32_t n_out, int32_t k, int32_t accumulate, void* stream) {
+    if (dtype != DLLM_DTYPE_BF16 && dtype != DLLM_DTYPE_F32) return fail("dllm_op_gemv: bad dtype");
+    if (!d_x || !d_w || !d_y || n_rows <= 0 || n_out <= 0 || k <= 0) return fail("dllm_op_gemv: bad argument");
+    if (dllm_device_count() == 0) return fail("dllm_op_gemv: no CUDA device (this library has no CPU path)");
+    if (k % (dtype == DLLM_DTYPE_BF16 ? 8 : 4)) return fail("dllm_op_gemv: k must be a multiple of the 16-byte vector width");
+    if (ensure_device_ready()) return 1;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    GemvParams p{};
+    p.x = d_x; p.n_rows = n_rows; p.K = k; p.norm = NORM_NONE;
+    p.w[0] = d_w; p.b[0] = d_bias; p.n[0] = n_out; p.epi = EPI_RESIDUAL; p.y = d_y; p.accumulate = accumulate;
+    CUDA_TRY(launch_gemv(dtype, p, sms, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" size_t dllm_op_decode_attention_scratch_bytes(int32_t n_rows, int32_t n_heads, int32_t head_dim,
+                                                         int32_t n_splits) {
+    const size_t rh = (size_t)n_rows * n_heads;
+    return align_up(rh * 4, 256) + align_up(rh * n_splits * 2 * 4, 256) + align_up(rh * n_splits * head_dim * 4, 256);
+}
+
+extern "C" int dllm_op_decode_attention(int32_t dtype, const void* d_q, const void* d_kpool, const void* d_vpool,
+                                        const int32_t* d_block_table, int32_t pages_per_seq, int32_t page_size,
+                                        const int32_t* d_positions, const int32_t* d_seq_ids, int32_t n_rows,
+                                        int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t n_splits,
+                                        void* d_scratch, void* d_out, void* stream) {
+    if (dtype != DLLM_DTYPE_BF16 && dtype != DLLM_DTYPE_F32) return fail("dllm_op_decode_attention: bad dtype");
+    if (!d_q || !d_kpool || !d_vpool || !d_block_table || !d_positions || !d_seq_ids || !d_scratch || !d_out)
+        return fail("dllm_op_decode_attention: null pointer");
+    if (n_rows <= 0 || n_splits <= 0 || n_heads <= 0 || n_kv_heads <= 0 || n_heads % n_kv_heads)
+        return fail("dllm_op_decode_attention: bad shape");
+    if (head_dim != 32 && head_dim != 64 && head_dim != 128) return fail("dllm_op_decode_attention: head_dim must be 32, 64 or 128");
+    if (page_size < 8 || (page_size & (page_size - 1))) return fail("dllm_op_decode_attention: page_size must be a power of two >= 8");
+    if (dllm_device_count() == 0) return fail("dllm_op_decode_attention: no CUDA device (this library has no CPU path)");
+    const size_t rh = (size_t)n_rows * n_heads;
+    char* base = static_cast<char*>(d_scratch);
+    AttnParams a{};
+    a.counters = reinterpret_cast<uint32_t*>(base);
+    a.part_ml = reinterpret_cast<float*>(base + align_up(rh * 4, 256));
+    a.part_o = reinterpret_cast<float*>(base + align_up(rh * 4, 256) + align_up(rh * n_splits * 2 * 4, 256));
+    a.q = d_q;
+    a.kv.kpool = const_cast<void*>(d_kpool);
+    a.kv.vpool = const_cast<void*>(d_vpool);
+    a.kv.block_table = d_block_table;
+    a.kv.pages_per_seq = pages_per_seq;
+    a.kv.page_shift = 0;
+    while ((1 << a.kv.page_shift) < page_size) ++a.kv.page_shift;
+    a.positions = d_positions; a.seq_ids = d_seq_ids;
+    a.n_rows = n_rows; a.n_heads = n_heads; a.n_kv_heads = n_kv_heads; a.head_dim = head_dim; a.n_splits = n_splits;
+    a.out = d_out;
+    CUDA_TRY(launch_attn_decode(dtype, a, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int dllm_op_legacy_matmul(const float* d_in, const float* d_param, float* d_out, int32_t m, int32_t k,
+                                     int32_t n, void* stream) {
+    if (!d_in || !d_param || !d_out) return fail("dllm_op_legacy_matmul: null pointer");
+    if (dllm_device_count() == 0) return fail("dllm_op_legacy_matmul: no CUDA device (this library has no CPU path)");
+    CUDA_TRY(launch_legacy_matmul(d_in, d_param, d_out, m, k, n, (cudaStream_t)stream));
+    return 0;
+}

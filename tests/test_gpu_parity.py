@@ -1,0 +1,323 @@
+"""GPU: the CUDA path (through the C ABI) against the CPU oracle and the golden fixtures.
+
+Tolerances are the north star's: fp32 logits within 1e-4 relative, bf16 within 1e-2 relative (relative to the
+largest |logit| of the step), greedy token ids identical.  Integer outputs (token ids) are compared exactly.
+"""
+import os
+
+import pytest
+import torch
+
+from oracle.shard_oracle import (ShardModelConfig, build_pipeline, greedy_generate, make_prompts, make_state_dict,
+                                 split_state_dict)
+from src.engine import cabi
+from src.model import random_init
+from src.worker.node import ModelShard, WorkerNode
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+TOL = {torch.float32: 1e-4, torch.bfloat16: 1e-2}
+
+
+def rel_err(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ---- single operators -------------------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("rows,n_out,k", [(1, 64, 256), (1, 257, 2048), (3, 50, 768), (5, 33, 5632), (1, 2, 8), (16, 96, 512)])
+def test_gemv_matches_fp32_reference(dtype, rows, n_out, k):
+    g = torch.Generator().manual_seed(rows * 1000 + n_out)
+    x = torch.randn(rows, k, generator=g).to(dtype)
+    w = (torch.randn(n_out, k, generator=g) * 0.05).to(dtype)
+    b = torch.randn(n_out, generator=g).to(dtype)
+    y0 = torch.randn(rows, n_out, generator=g).to(dtype)
+    ref = x.float() @ w.float().t() + b.float()
+    ref_acc = ref.to(dtype).float() + y0.float()
+    xd, wd, bd = x.cuda(), w.cuda(), b.cuda()
+    code = cabi.DTYPE_F32 if dtype == torch.float32 else cabi.DTYPE_BF16
+    y = torch.empty(rows, n_out, dtype=dtype, device="cuda")
+    cabi.check(cabi.lib().dllm_op_gemv(code, xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), y.data_ptr(), rows, n_out, k, 0, stream()))
+    ya = y0.cuda()
+    cabi.check(cabi.lib().dllm_op_gemv(code, xd.data_ptr(), wd.data_ptr(), bd.data_ptr(), ya.data_ptr(), rows, n_out, k, 1, stream()))
+    torch.cuda.synchronize()
+    tol = 2e-5 if dtype == torch.float32 else 1e-2
+    assert rel_err(y, ref) < tol
+    assert rel_err(ya, ref_acc) < tol
+
+
+def test_gemv_rejects_bad_k():
+    x = torch.zeros(1, 12, device="cuda", dtype=torch.bfloat16)
+    rc = cabi.lib().dllm_op_gemv(0, x.data_ptr(), x.data_ptr(), None, x.data_ptr(), 1, 1, 12, 0, stream())
+    assert rc != 0 and b"multiple" in cabi.lib().dllm_last_error()
+
+
+def _paged_kv(lens, KV, hd, page, dtype, gen):
+    """Random K/V for sequences of the given lengths, scattered over shuffled pages."""
+    pps = (max(lens) + page - 1) // page
+    n_pages = pps * len(lens) + 3
+    perm = torch.randperm(n_pages, generator=gen)
+    kpool = torch.zeros(n_pages, KV, page, hd)
+    vpool = torch.zeros(n_pages, KV, page, hd)
+    bt = torch.full((len(lens), pps), -1, dtype=torch.int32)
+    ks, vs, nxt = [], [], 0
+    for s, n in enumerate(lens):
+        k = torch.randn(n, KV, hd, generator=gen).to(dtype).float()
+        v = torch.randn(n, KV, hd, generator=gen).to(dtype).float()
+        ks.append(k); vs.append(v)
+        for p in range((n + page - 1) // page):
+            pg = int(perm[nxt]); nxt += 1
+            bt[s, p] = pg
+            t0, t1 = p * page, min(n, (p + 1) * page)
+            kpool[pg, :, : t1 - t0] = k[t0:t1].transpose(0, 1)
+            vpool[pg, :, : t1 - t0] = v[t0:t1].transpose(0, 1)
+    return kpool.to(dtype), vpool.to(dtype), bt, ks, vs, pps
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("H,KV,hd,splits,lens", [(4, 2, 64, 3, [5, 70]), (8, 1, 128, 8, [200, 1, 33]), (4, 4, 32, 1, [17]),
+                                                 (32, 4, 64, 16, [512]), (5, 1, 64, 64, [40, 41])])
+def test_decode_attention_matches_reference(dtype, H, KV, hd, splits, lens):
+    gen = torch.Generator().manual_seed(H * 100 + hd)
+    page = 16
+    kpool, vpool, bt, ks, vs, pps = _paged_kv(lens, KV, hd, page, dtype, gen)
+    R = len(lens)
+    q = torch.randn(R, H, hd, generator=gen).to(dtype)
+    pos = torch.tensor([n - 1 for n in lens], dtype=torch.int32)
+    seq = torch.arange(R, dtype=torch.int32)
+    ref = torch.empty(R, H * hd)
+    G = H // KV
+    rnd = (lambda t: t.to(dtype).float())
+    for r in range(R):
+        K = ks[r].repeat_interleave(G, dim=1)
+        V = vs[r].repeat_interleave(G, dim=1)
+        sc = rnd(rnd(torch.einsum("hd,chd->hc", q[r].float(), K)) * hd ** -0.5)
+        ref[r] = torch.einsum("hc,chd->hd", torch.softmax(sc, -1), V).reshape(-1)
+    code = cabi.DTYPE_F32 if dtype == torch.float32 else cabi.DTYPE_BF16
+    L = cabi.lib()
+    scratch = torch.zeros(L.dllm_op_decode_attention_scratch_bytes(R, H, hd, splits), dtype=torch.uint8, device="cuda")
+    out = torch.empty(R, H * hd, dtype=dtype, device="cuda")
+    args = [t.cuda() for t in (q, kpool, vpool, bt, pos, seq)]
+    for _ in range(2):  # second call checks that the counters were left at zero
+        out.zero_()
+        cabi.check(L.dllm_op_decode_attention(code, args[0].data_ptr(), args[1].data_ptr(), args[2].data_ptr(), args[3].data_ptr(),
+                                              pps, page, args[4].data_ptr(), args[5].data_ptr(), R, H, KV, hd, splits,
+                                              scratch.data_ptr(), out.data_ptr(), stream()))
+        torch.cuda.synchronize()
+        assert rel_err(out, ref) < (2e-5 if dtype == torch.float32 else 1e-2)
+
+
+def test_placeholder_matches_reference_golden():
+    """The reference's shipped `compute` (per-key matmul), through ModelShard on the GPU."""
+    g = torch.load(os.path.join(GOLD, "reference_placeholder.pt"), weights_only=True)
+    shard = ModelShard(1, {k: v.clone() for k, v in g["params"].items()})
+    shard.to_device()
+    out = shard.compute(g["inputs"])
+    assert set(out) == set(g["outputs"])
+    for k in out:
+        assert out[k].is_cuda and out[k].shape == g["outputs"][k].shape
+        assert rel_err(out[k], g["outputs"][k]) < 1e-5
+
+
+def test_reference_worker_tests_on_gpu():
+    """reference tests/worker/test_node.py:26-30, 87-112: shapes and the two-shard merge."""
+    shard = ModelShard(1, {"weight": torch.randn(3, 3)})
+    r = shard.compute({"weight": torch.randn(1, 3)})
+    assert "weight" in r and r["weight"].shape == (1, 3)
+    w = WorkerNode()
+    w.shards[1] = ModelShard(1, {"weight1": torch.randn(3, 3)})
+    w.shards[2] = ModelShard(2, {"weight2": torch.randn(3, 3)})
+    res = w.schedule_computation({"weight1": torch.randn(1, 3), "weight2": torch.randn(1, 3)}, [1, 2])
+    assert res["weight1"].shape == (1, 3) and res["weight2"].shape == (1, 3)
+
+
+# ---- the layer-shard pipeline ---------------------------------------------------------------------------------
+def gpu_stages(cfg: ShardModelConfig, sd, n_shards, dtype, **limits):
+    hf = cfg.to_hf_dict()
+    stages = []
+    for i, part in enumerate(split_state_dict(cfg, {k: v.to(dtype) for k, v in sd.items()}, n_shards)):
+        st = ModelShard(i, dict(part), config=hf, **limits)
+        st.to_device()
+        stages.append(st)
+    return stages
+
+
+def gpu_step(stages, inputs):
+    x = inputs
+    for st in stages:
+        x = st.compute(x)
+    return x
+
+
+def gpu_generate(stages, prompts, n_new):
+    for st in stages:
+        st.reset()
+    out = gpu_step(stages, {"input_ids": prompts})
+    toks, logits = [out["next_token"].cpu()], [out["logits"].cpu()]
+    for _ in range(n_new - 1):
+        out = gpu_step(stages, {"input_ids": toks[-1][:, None]})
+        toks.append(out["next_token"].cpu())
+        logits.append(out["logits"].cpu())
+    return torch.stack(toks, 1), torch.stack(logits, 1)
+
+
+@pytest.mark.parametrize("name", ["gpt2", "llama", "qwen2"])
+@pytest.mark.parametrize("tag,dtype", [("fp32", torch.float32), ("bf16", torch.bfloat16)])
+@pytest.mark.parametrize("shards", [1, 2, 3])
+def test_pipeline_matches_golden(name, tag, dtype, shards):
+    g = torch.load(os.path.join(GOLD, f"oracle_{name}_{tag}.pt"), weights_only=True)
+    cfg = ShardModelConfig.from_hf_dict(g["config"])
+    sd = make_state_dict(cfg, 1234, torch.float32, init="full")
+    stages = gpu_stages(cfg, sd, shards, dtype, max_rows=64, max_seqs=4, max_context=cfg.max_pos, page_size=8)
+    ids, lg = gpu_generate(stages, g["prompts"], g["tokens"].shape[1])
+    err = max(rel_err(lg[:, t], g["logits"][:, t]) for t in range(lg.shape[1]))
+    assert err < TOL[dtype], err
+    if dtype == torch.float32:
+        assert torch.equal(ids, g["tokens"])  # bit-identical greedy tokens
+        hf = torch.load(os.path.join(GOLD, f"hf_{name}.pt"), weights_only=True)
+        assert torch.equal(ids, hf["tokens"]) and rel_err(lg, hf["logits"]) < 1e-4  # and against HF itself
+    else:
+        # bf16: identical unless the oracle's own top-2 margin is within bf16 resolution of the logit scale
+        diff = ids != g["tokens"]
+        first = diff.float().cumsum(1).clamp(max=1)  # after the first flip the continuations diverge legitimately
+        for b, t in diff.nonzero().tolist():
+            if first[b, :t].sum() == 0:
+                assert float(g["margins"][b, t]) <= 2 ** -7 * float(g["logits"][b, t].abs().max()), (b, t)
+        assert int(diff[:, 0].sum()) == 0 or float(g["margins"][:, 0].min()) <= 2 ** -7 * float(g["logits"][:, 0].abs().max())
+
+
+@pytest.mark.parametrize("name", ["llama", "gpt2"])
+def test_boundary_hidden_state_matches_golden(name):
+    """The hand-off tile itself (stage 0 -> stage 1), fp32."""
+    g = torch.load(os.path.join(GOLD, f"oracle_{name}_fp32.pt"), weights_only=True)
+    cfg = ShardModelConfig.from_hf_dict(g["config"])
+    sd = make_state_dict(cfg, 1234, torch.float32, init="full")
+    st = gpu_stages(cfg, sd, 2, torch.float32, max_rows=64, max_seqs=4, max_context=cfg.max_pos, page_size=8)[0]
+    out = st.compute({"input_ids": g["prompts"]})
+    assert out["hidden_states"].shape == g["boundary_hidden"].shape
+    assert rel_err(out["hidden_states"], g["boundary_hidden"]) < 1e-4
+    assert out["positions"].tolist() == [list(range(g["prompts"].shape[1]))] * g["prompts"].shape[0]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_seeded_pipeline_against_live_oracle(dtype):
+    """Same seeded inputs through the oracle (CPU) and the CUDA path, GQA llama with 128-wide heads, 32 tokens."""
+    cfg = ShardModelConfig("llama", 512, 3, 4, 2, 128, 1024, 1000, 256, 1e-5, 500000.0)
+    sd = make_state_dict(cfg, 99, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, 3, 21, seed=5)
+    sdd = {k: v.to(dtype) for k, v in sd.items()}
+    o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 2, dtype), prompts, 32, record=True)
+    stages = gpu_stages(cfg, sd, 2, dtype, max_rows=64, max_seqs=4, max_context=128, page_size=16)
+    ids, lg = gpu_generate(stages, prompts, 32)
+    if dtype == torch.float32:
+        assert torch.equal(ids, o_ids)
+        assert rel_err(lg, o_lg) < 1e-4
+    else:
+        same_prefix = (ids == o_ids).long().cumprod(1).bool()  # compare logits while the token history agrees
+        for t in range(32):
+            rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
+            if rows.any():
+                assert rel_err(lg[rows, t], o_lg[rows, t]) < 1e-2
+        flips = (~same_prefix).float().argmax(1)
+        for b in range(ids.shape[0]):
+            if not same_prefix[b].all():
+                t = int(flips[b])
+                assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
+
+
+def test_decode_loop_equals_stepwise():
+    """Device-resident greedy loop == one forward call per token (token ids exact)."""
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, 2, 10, seed=2)
+    for dtype in (torch.float32, torch.bfloat16):
+        (st,) = gpu_stages(cfg, sd, 1, dtype, max_rows=32, max_seqs=2, max_context=128, page_size=16)
+        ids, _ = gpu_generate([st], prompts, 20)
+        st.reset()
+        first = st.compute({"input_ids": prompts})["next_token"].cpu()
+        rest = st.decode_loop(2, 19).cpu()
+        assert torch.equal(torch.cat([first[:, None], rest], 1), ids)
+
+
+def test_chunked_prefill_equals_single_call():
+    """max_rows smaller than the prompt -> chunked prefill; same logits (fp32 tolerance) and token."""
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, 2, 37, seed=2)
+    big = gpu_stages(cfg, sd, 2, torch.float32, max_rows=128, max_seqs=2, max_context=128, page_size=16)
+    small = gpu_stages(cfg, sd, 2, torch.float32, max_rows=10, max_seqs=2, max_context=128, page_size=16)
+    a, b = gpu_step(big, {"input_ids": prompts}), gpu_step(small, {"input_ids": prompts})
+    assert torch.equal(a["next_token"], b["next_token"]) and rel_err(a["logits"], b["logits"]) < 1e-5
+
+
+def test_ragged_batch_and_slot_reuse():
+    """Rows with different context lengths in one call; releasing a slot and reusing its pages."""
+    cfg = ShardModelConfig("qwen2", 256, 2, 8, 2, 32, 384, 300, 128, 1e-6, 1000000.0)
+    sd = make_state_dict(cfg, 8, torch.float32, init="full")
+    from oracle.shard_oracle import OracleShard
+    oracle = OracleShard(0, sd, cfg, max_context=64)
+    (st,) = gpu_stages(cfg, sd, 1, torch.float32, max_rows=32, max_seqs=3, max_context=64, page_size=8)
+    g = torch.Generator().manual_seed(4)
+    p0, p1 = torch.randint(0, 300, (1, 5), generator=g), torch.randint(0, 300, (1, 19), generator=g)
+    for s, p in ((0, p0), (2, p1)):
+        st.compute({"input_ids": p, "seq_ids": torch.tensor([s])})
+        oracle.compute({"input_ids": p, "seq_ids": torch.tensor([s])})
+    nxt = torch.tensor([[3], [8]])
+    got = st.compute({"input_ids": nxt, "seq_ids": torch.tensor([0, 2])})
+    want = oracle.compute({"input_ids": nxt, "seq_ids": torch.tensor([0, 2])})
+    assert torch.equal(got["next_token"].cpu(), want["next_token"]) and rel_err(got["logits"], want["logits"]) < 1e-4
+    free_before = cabi.lib().dllm_shard_kv_free_pages(st.executor._handle)
+    st.reset([2]); oracle.reset([2])
+    assert cabi.lib().dllm_shard_kv_free_pages(st.executor._handle) == free_before + 3  # 20 tokens / 8 per page
+    got = st.compute({"input_ids": p0, "seq_ids": torch.tensor([2])})
+    want = oracle.compute({"input_ids": p0, "seq_ids": torch.tensor([2])})
+    assert rel_err(got["logits"], want["logits"]) < 1e-4
+
+
+def test_limits_are_enforced():
+    cfg = ShardModelConfig("llama", 256, 1, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32)
+    (st,) = gpu_stages(cfg, sd, 1, torch.float32, max_rows=8, max_seqs=1, max_context=16, page_size=8)
+    with pytest.raises(ValueError):
+        st.compute({"input_ids": torch.zeros(1, 17, dtype=torch.long)})  # past max_context
+    with pytest.raises(ValueError):
+        st.compute({"input_ids": torch.zeros(1, 1, dtype=torch.long), "seq_ids": torch.tensor([1])})  # no such slot
+    with pytest.raises(KeyError):
+        gpu_stages(cfg, sd, 2, torch.float32, max_rows=8, max_seqs=1, max_context=16, page_size=8)[1].compute(
+            {"input_ids": torch.zeros(1, 1, dtype=torch.long)})  # stage 1 needs hidden_states
+
+
+# ---- full-size properties (BASELINE configs[1]: TinyLlama-1.1B bf16, 512-token prompt) ---------------------------
+def test_tinyllama_full_size_properties():
+    """No CPU oracle at this size in seconds, so check what must hold at any size:
+    (1) splitting the model into 2 stages does not change a single bit of the hand-off or the tokens,
+    (2) the device-resident loop reproduces step-by-step decoding exactly,
+    (3) a 512-token chunked prefill and token-by-token prefill agree within the bf16 tolerance."""
+    hf = random_init.NAMED_CONFIGS["tinyllama-1.1b"]
+    L = hf["num_hidden_layers"]
+    params = random_init.random_stage_parameters(hf, range(L), True, True, 1234, torch.bfloat16, device="cuda")
+    limits = dict(max_rows=128, max_seqs=1, max_context=640, page_size=64)
+    one = ModelShard(0, dict(params), config=hf, **limits); one.to_device()
+    keys0 = {k for k in params if k.startswith("embed") or (k.startswith("layers.") and int(k.split(".")[1]) < L // 2)}
+    s0 = ModelShard(0, {k: params[k] for k in keys0}, config=hf, **limits); s0.to_device()
+    s1 = ModelShard(1, {k: v for k, v in params.items() if k not in keys0}, config=hf, **limits); s1.to_device()
+    prompt = make_prompts(hf["vocab_size"], 1, 512, seed=7)
+    a = one.compute({"input_ids": prompt})
+    b = s1.compute(s0.compute({"input_ids": prompt}))
+    assert torch.equal(a["logits"], b["logits"]) and torch.equal(a["next_token"], b["next_token"])
+    loop = one.decode_loop(1, 31).cpu()
+    toks = [b["next_token"].cpu()]
+    for _ in range(31):
+        toks.append(s1.compute(s0.compute({"input_ids": toks[-1][:, None]}))["next_token"].cpu())
+    assert torch.equal(torch.stack(toks, 1)[:, 1:], loop)
+    one.reset()
+    for t in range(64):
+        step = one.compute({"input_ids": prompt[:, t:t + 1]})
+    one2 = ModelShard(0, dict(params), config=hf, **limits); one2.to_device()
+    chunk = one2.compute({"input_ids": prompt[:, :64]})
+    assert rel_err(step["logits"], chunk["logits"]) < 1e-2

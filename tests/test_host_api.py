@@ -1,0 +1,222 @@
+"""CPU: the reference-shaped host API (names, signatures, error behaviour) -- reads like the reference's own
+tests (reference tests/worker/test_node.py, tests/model/test_shard_manager.py, tests/network/test_protocol.py)."""
+import io
+import json
+import os
+import pickle
+import socket
+import threading
+from unittest.mock import MagicMock
+
+import pytest
+import torch
+
+from src.engine import cabi
+from src.engine.shard_exec import CONFIG_KEY, StageGeometry, decode_config, encode_config, rope_tables
+from src.model import random_init
+from src.model.shard_manager import ModelShardManager, contiguous_partition, partition_state_dict
+from src.network.protocol import HEADER_SIZE, MessageProtocol
+from src.worker.node import ModelShard, WorkerNode
+
+NO_GPU = not torch.cuda.is_available()
+
+
+# ---- ModelShard / WorkerNode surface (reference tests/worker/test_node.py) ----------------------------
+class TestModelShard:
+    def setup_method(self):
+        self.shard = ModelShard(1, {"weight": torch.randn(3, 3)})
+
+    def test_init(self):
+        assert self.shard.shard_id == 1 and list(self.shard.parameters) == ["weight"]
+        assert self.shard.device == ("cuda" if torch.cuda.is_available() else "cpu")
+
+    def test_to_device(self):
+        self.shard.to_device()
+        for p in self.shard.parameters.values():
+            assert p.device.type == self.shard.device
+
+    @pytest.mark.skipif(not NO_GPU, reason="loud-failure check for machines without CUDA")
+    def test_compute_without_gpu_fails_loudly(self):
+        with pytest.raises(cabi.DllmError, match="no CPU fallback"):
+            self.shard.compute({"weight": torch.randn(1, 3)})
+
+    def test_compute_ignores_unknown_keys(self):
+        assert self.shard.compute({"something_else": torch.randn(1, 3)}) == {}
+
+    def test_config_travels_with_parameters(self):
+        cfg = random_init.NAMED_CONFIGS["tinyllama-1.1b"]
+        shard = ModelShard(0, {CONFIG_KEY: encode_config(cfg)})
+        assert shard.config == cfg and decode_config(encode_config(cfg)) == cfg
+
+
+class TestWorkerNode:
+    def setup_method(self):
+        self.worker = WorkerNode()
+
+    def test_init(self):
+        w = self.worker
+        assert (w.host, w.port, w.master_address, w.shards, w.running) == ("0.0.0.0", 65433, None, {}, False)
+
+    def test_start_does_not_block_and_stop(self):
+        w = WorkerNode(host="127.0.0.1", port=0)
+        w.start()
+        assert w.running
+        w.stop()
+        assert not w.running
+
+    def test_load_and_unload_shard(self):
+        buf = io.BytesIO()
+        torch.save({"weight": torch.randn(3, 3)}, buf)
+        assert self.worker.load_shard(1, buf.getvalue()) is True
+        assert 1 in self.worker.shards
+        assert self.worker.load_shard(2, pickle.dumps({"weight": torch.randn(3, 3)})) is True  # the reference's codec
+        assert self.worker.load_shard(3, b"not a shard") is False
+        assert self.worker.unload_shard(1) is True and self.worker.unload_shard(1) is False
+        assert 1 not in self.worker.shards
+
+    def test_unknown_shard_raises_keyerror(self):
+        """reference tests/worker/test_node.py:114-123 expects KeyError after an unload."""
+        self.worker.shards[1] = ModelShard(1, {"weight": torch.randn(3, 3)})
+        self.worker.unload_shard(1)
+        with pytest.raises(KeyError):
+            self.worker.schedule_computation({"weight": torch.randn(1, 3)}, [1])
+
+
+# ---- shard files (reference tests/model/test_shard_manager.py) -------------------------------------------
+def _write_model(tmp_path, cfg, sd):
+    os.makedirs(tmp_path, exist_ok=True)
+    torch.save(sd, os.path.join(tmp_path, "pytorch_model.bin"))
+    with open(os.path.join(tmp_path, "config.json"), "w") as f:
+        json.dump(cfg, f)
+
+
+def test_shard_manager_reference_case(tmp_path):
+    d = str(tmp_path / "m")
+    _write_model(d, {"model_type": "test"}, {"weight1": torch.randn(3, 3), "weight2": torch.randn(3, 3)})
+    mgr = ModelShardManager(d, num_shards=2)
+    shard_dir = mgr.shard_model()
+    files = [f for f in os.listdir(shard_dir) if f.startswith("shard_") and f.endswith(".pt")]
+    assert len(files) == 2 and os.path.exists(os.path.join(shard_dir, "shard_info.json"))
+    paths = mgr.get_shard_paths()
+    assert len(paths) == 2 and all(p.startswith(d) for p in paths)
+    sd, cfg = ModelShardManager.reconstruct_model(paths, os.path.join(shard_dir, "config.json"))
+    assert "weight1" in sd and "weight2" in sd and cfg["model_type"] == "test"  # the reference loses both keys
+
+
+def test_shard_manager_contiguous_and_complete(tmp_path):
+    cfg = dict(model_type="llama", hidden_size=64, num_hidden_layers=5, num_attention_heads=2, num_key_value_heads=1,
+               intermediate_size=96, vocab_size=50, max_position_embeddings=32, rms_norm_eps=1e-5, rope_theta=1e4)
+    sd = random_init.random_stage_parameters(cfg, range(5), True, True, dtype=torch.float32)
+    prefixed = {("model." + k if k != "lm_head.weight" else k): v for k, v in sd.items()}  # LlamaForCausalLM keys
+    d = str(tmp_path / "llama")
+    _write_model(d, cfg, prefixed)
+    mgr = ModelShardManager(d, 3)
+    mgr.shard_model()
+    shards = [torch.load(p, weights_only=True) for p in mgr.get_shard_paths()]
+    layers = [sorted({int(k.split(".")[1]) for k in s if k.startswith("layers.")}) for s in shards]
+    assert layers == [[0, 1], [2, 3], [4]]  # contiguous (the reference would give [0,3],[1,4],[2])
+    assert "embed_tokens.weight" in shards[0] and "norm.weight" in shards[2] and "lm_head.weight" in shards[2]
+    assert all(decode_config(s[CONFIG_KEY]) == cfg for s in shards)
+    full, _ = ModelShardManager.reconstruct_model(mgr.get_shard_paths(), os.path.join(mgr.shard_dir, "config.json"))
+    assert set(full) == set(sd) and all(torch.equal(full[k], sd[k]) for k in sd)
+
+
+def test_tied_head_is_materialised_on_last_shard():
+    cfg = random_init.NAMED_CONFIGS["gpt2-small"] | {"n_embd": 32, "n_layer": 2, "n_head": 2, "n_inner": 64,
+                                                     "vocab_size": 40, "n_positions": 16}
+    sd = random_init.random_stage_parameters(cfg, range(2), True, True, dtype=torch.float32)
+    sd.pop("lm_head.weight")
+    parts = partition_state_dict({"transformer." + k: v for k, v in sd.items()}, 2)
+    assert torch.equal(parts[1]["lm_head.weight"], sd["wte.weight"]) and "wte.weight" in parts[0]
+
+
+def test_partition_matches_oracle_partition():
+    from oracle.shard_oracle import contiguous_partition as oracle_partition
+    for L, S in [(12, 2), (22, 4), (32, 8), (80, 8), (48, 4), (7, 3)]:
+        assert contiguous_partition(L, S) == oracle_partition(L, S)
+
+
+def test_random_init_matches_oracle_generator():
+    from oracle.shard_oracle import ShardModelConfig, make_state_dict
+    hf = dict(model_type="qwen2", hidden_size=64, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+              intermediate_size=96, vocab_size=50, max_position_embeddings=32, rms_norm_eps=1e-6, rope_theta=1e6)
+    ours = random_init.random_stage_parameters(hf, range(2), True, True, 1234, torch.float32, init="full")
+    ref = make_state_dict(ShardModelConfig.from_hf_dict(hf), 1234, torch.float32, init="full")
+    assert set(ours) == set(ref) and all(torch.equal(ours[k], ref[k]) for k in ref)
+
+
+def test_rope_tables_match_oracle():
+    from oracle.shard_oracle import ShardModelConfig, rope_tables as oracle_rope
+    cfg = ShardModelConfig("llama", 256, 1, 4, 2, 64, 64, 10, 128, 1e-5, 500000.0)
+    c, s = rope_tables(64, 500000.0, 128)
+    oc, os_ = oracle_rope(cfg, 128)
+    assert torch.equal(c, oc) and torch.equal(s, os_)
+
+
+def test_geometry_from_named_configs():
+    g = StageGeometry.from_hf(random_init.NAMED_CONFIGS["llama3-8b"])
+    assert (g.hidden, g.n_heads, g.n_kv_heads, g.head_dim, g.ffn, g.vocab) == (4096, 32, 8, 128, 14336, 128256)
+    g = StageGeometry.from_hf(random_init.NAMED_CONFIGS["gpt2-small"])
+    assert (g.model_type, g.head_dim, g.ffn, g.tie_head) == ("gpt2", 64, 3072, True)
+    with pytest.raises(ValueError):
+        StageGeometry.from_hf({"model_type": "opt"})
+
+
+# ---- wire protocol (reference tests/network/test_protocol.py) ---------------------------------------------
+class TestMessageProtocol:
+    def test_send_on_class_like_the_reference_tests(self):
+        sock = MagicMock()
+        assert MessageProtocol.send_message(sock, "TEST_COMMAND") is True
+        sock.sendall.assert_called()
+        sock = MagicMock()
+        assert MessageProtocol.send_message(sock, "TEST_COMMAND", payload=b"test_payload") is True
+        assert sock.sendall.call_count == 2
+
+    def test_tcp_round_trip(self):
+        a, b = socket.socketpair()
+        proto = MessageProtocol()
+        payload = os.urandom(300_000)
+        t = threading.Thread(target=lambda: proto.send_message(a, "RESULT", payload, {"task_id": "t1"}))
+        t.start()
+        header, got = proto.receive_message(b, timeout=10)
+        t.join()
+        assert header["command"] == "RESULT" and header["task_id"] == "t1" and got == payload
+        MessageProtocol.send_message(a, "HEARTBEAT", metadata={"timestamp": 1.0})
+        header, got = MessageProtocol.receive_message(b, timeout=10)
+        assert header["command"] == "HEARTBEAT" and got is None
+        a.close(); b.close()
+
+    def test_header_length_field_width(self):
+        sock = MagicMock()
+        MessageProtocol.send_message(sock, "X")
+        first = sock.sendall.call_args_list[0][0][0]
+        assert int(first[:HEADER_SIZE].decode().strip()) == len(first) - HEADER_SIZE
+
+    def test_timeout_bad_header_and_closed_connection(self):
+        sock = MagicMock()
+        sock.recv.side_effect = socket.timeout()
+        with pytest.raises(TimeoutError):
+            MessageProtocol.receive_message(sock)
+        sock = MagicMock()
+        sock.recv.side_effect = [b"invalid   ", b"header"]
+        with pytest.raises(ValueError):
+            MessageProtocol.receive_message(sock)
+        sock = MagicMock()
+        sock.recv.return_value = b""
+        with pytest.raises(ConnectionError):
+            MessageProtocol.receive_message(sock)
+
+    def test_zmq_router_dealer_round_trip(self):
+        zmq = pytest.importorskip("zmq")
+        ctx = zmq.Context.instance()
+        server, client = MessageProtocol(ctx), MessageProtocol(ctx)
+        router = server.setup_zmq_socket(zmq.ROUTER, "tcp://127.0.0.1:*")  # binds (the reference never did)
+        endpoint = router.getsockopt_string(zmq.LAST_ENDPOINT)
+        dealer = client.setup_zmq_socket(zmq.DEALER, endpoint)
+        assert client.send_message(dealer, "REGISTER", metadata={"capabilities": {"has_gpu": False}})
+        header, payload = server.receive_message(router, timeout=5)
+        assert header["command"] == "REGISTER" and payload is None and header["identity"]
+        assert server.send_message(router, "LOAD_SHARD", b"abc", {"identity": header["identity"], "shard_id": 3})
+        header, payload = client.receive_message(dealer, timeout=5)
+        assert header["command"] == "LOAD_SHARD" and header["shard_id"] == 3 and payload == b"abc"
+        router.close(); dealer.close()
