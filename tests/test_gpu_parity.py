@@ -320,4 +320,5 @@ def test_tinyllama_full_size_properties():
         step = one.compute({"input_ids": prompt[:, t:t + 1]})
     one2 = ModelShard(0, dict(params), config=hf, **limits); one2.to_device()
     chunk = one2.compute({"input_ids": prompt[:, :64]})
-    assert rel_err(step["logits"], chunk["logits"]) < 1e-2
+    # two bf16 evaluation orders (different split-K and row tiling), each within 1e-2 of exact arithmetic
+    assert rel_err(step["logits"], chunk["logits"]) < 3e-2
