@@ -1,0 +1,1143 @@
+// Persistent decode kernel for sm_100a: one cooperative launch runs `n_steps` whole decode steps of a
+// stage (embedding, every layer's phases, head, greedy argmax, token feedback) for 1-16 rows.
+//
+// Why: at batch 1 a layer of TinyLlama is 84 MB = 13 us of HBM time; with one kernel per fused op the
+// step was launch/latency-bound at 30 % of the HBM roofline (profiles/r1a_summary.md).  Here
+//   * one CTA per SM stays resident; phases are separated by a grid barrier (monotonic counter in L2);
+//   * weights are read from a packed copy (megakernel.h): every warp owns a ring of 4 KB stages filled by
+//     TMA bulk copies (cp.async.bulk + mbarrier complete_tx), one copy per stage.  A stage is refilled the
+//     moment the warp has consumed it and a warp's sequence of stages is static, so the ring runs ahead
+//     *across* phase barriers, layers and decode steps: HBM keeps streaming while the CTA waits;
+//   * the dot products run on the tensor cores as a swap-AB skinny GEMM (mma.sync m16n8k16: M = batch rows,
+//     N = the 8 weight rows of a panel), which removes the bf16->fp32 unpack / FMA instruction stream that
+//     made the first version issue-bound; accumulation is fp32;
+//   * warps of a CTA that share a panel split K; partials are summed in a fixed order in shared memory
+//     (deterministic), then one thread per (row pair, batch row) runs the fused epilogue;
+//   * activations (a few KB) move between phases through L2 (ld.global.cg); old K/V tiles are prefetched with
+//     cp.async before the barrier that precedes attention.
+// Rounding points are those of the per-op kernels in decode_gemv.cu / attention.cu.
+#include <float.h>
+#include <limits.h>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "megakernel.h"
+
+namespace dllm {
+
+namespace {
+
+constexpr int kThreads = MK_THREADS;
+constexpr int kWarps = MK_THREADS / 32;
+constexpr int kStageBytes = MK_STAGE_BYTES;
+constexpr int kStageK = MK_STAGE_K;
+constexpr int kTT = 64;     // tokens per attention tile
+constexpr int kMaxGq = 8;   // query heads per KV head handled by one CTA (one warp each)
+constexpr int kMaxSplits = MK_MAX_SPLITS;
+constexpr int kPartStride = 8 * MK_MAX_ROWS;  // floats per unit in the partial buffer: [8 panel rows][16 batch]
+
+// ---- PTX wrappers ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// A wait that can never be satisfied is a bug; trap instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    for (unsigned spins = 0; !mbar_try_wait(bar, parity); ++spins)
+        if (spins > (1u << 24)) __trap();
+}
+// TMA bulk copy global -> shared, completion counted in bytes on an mbarrier
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
+    return r;
+}
+// D += A(16x16, row) * B(16x8, col), bf16 inputs, fp32 accumulate
+__device__ __forceinline__ void mma_bf16(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0,
+                                         uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void red_release_add(unsigned* p, unsigned v) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ldcg_u4(const void* p) { return __ldcg(reinterpret_cast<const uint4*>(p)); }
+// positions / ids change between steps inside one launch: always read them from L2
+__device__ __forceinline__ int ldcg_i32(const int32_t* p) { return __ldcg(p); }
+
+// All CTAs of the (co-resident, cooperative) grid meet here.  `target` advances by gridDim.x per barrier.
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target) {
+    __syncthreads();
+    target += gridDim.x;
+    if (threadIdx.x == 0) {
+        // release: the CTA's earlier writes (ordered before by bar.sync) become visible before the arrival;
+        // acquire: nothing after the barrier is satisfied from stale data
+        red_release_add(bar, 1u);
+        for (unsigned spins = 0; ld_acquire_u32(bar) < target; ++spins)
+            if (spins > (1u << 26)) __trap();  // a lost arrival is a bug; do not hang the GPU
+    }
+    __syncthreads();
+}
+
+__device__ __forceinline__ uint4 pack8(const float (&in)[8]) {
+    uint4 r;
+    __nv_bfloat162 a = __floats2bfloat162_rn(in[0], in[1]);
+    __nv_bfloat162 b = __floats2bfloat162_rn(in[2], in[3]);
+    __nv_bfloat162 c = __floats2bfloat162_rn(in[4], in[5]);
+    __nv_bfloat162 d = __floats2bfloat162_rn(in[6], in[7]);
+    r.x = *reinterpret_cast<uint32_t*>(&a);
+    r.y = *reinterpret_cast<uint32_t*>(&b);
+    r.z = *reinterpret_cast<uint32_t*>(&c);
+    r.w = *reinterpret_cast<uint32_t*>(&d);
+    return r;
+}
+
+__device__ __forceinline__ float ldf(const void* p, int i) { return __bfloat162float(static_cast<const bf16*>(p)[i]); }
+__device__ __forceinline__ float silu_f(float g) { return g / (1.0f + expf(-g)); }
+__device__ __forceinline__ float gelu_new_f(float x) {
+    return 0.5f * x * (1.0f + tanhf(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+}
+
+struct ArgBest {
+    float val;
+    int idx;
+};
+__device__ __forceinline__ void arg_update(ArgBest& b, float v, int i) {
+    if (v > b.val || (v == b.val && i < b.idx)) {
+        b.val = v;
+        b.idx = i;
+    }
+}
+
+__device__ __forceinline__ bool is_weight_phase(int kind) {
+    return kind == MK_QKV || kind == MK_OPROJ || kind == MK_GATEUP || kind == MK_FC_GELU || kind == MK_DOWN ||
+           kind == MK_HEAD;
+}
+
+// Per-step constants every phase needs (positions do not change inside a step): cached in shared memory at
+// the start of the step so that epilogues and attention set-up have no dependent global loads.
+struct StepCache {
+    int pos[MK_MAX_ROWS];
+    int seq[MK_MAX_ROWS];
+    int page[MK_MAX_ROWS];   // KV page that holds position pos[r] of sequence seq[r]
+    int off[MK_MAX_ROWS];    // offset of pos[r] inside that page
+};
+
+// ---- a warp's static sequence of stages -------------------------------------------------------------------
+// Panel p belongs to CTA p % grid (local slot p / grid).  Inside the CTA the (slot, k-split) pairs are dealt
+// round-robin to the warps.  The issue side and the consume side walk the same sequence; the issue side is
+// `stages` entries ahead.
+struct WIter {
+    int step, ph, j, st, st_end;
+    // cached at seek time so that advancing by one stage needs no division and no phase-table lookup
+    const unsigned char* wp;
+    int n_panels, K, panel;
+};
+
+__device__ __forceinline__ int local_panels(const MkPhase& ph) {
+    const int c = blockIdx.x, G = gridDim.x;
+    return c < ph.n_panels ? (ph.n_panels - c + G - 1) / G : 0;
+}
+
+struct Ctx {
+    int n_steps, n_phases;
+    const MkPhase* phases;  // shared-memory copy
+    const int* units;       // shared: (panel slot, k-split) units this CTA owns in each phase (0 = not a weight phase)
+    int warp, lane;
+    uint32_t ring;          // shared address of this warp's stages
+    uint32_t full;          // shared address of this warp's mbarriers
+};
+
+__device__ __forceinline__ int ks_shift_of(int ks) { return ks == 1 ? 0 : (ks == 2 ? 1 : (ks == 4 ? 2 : 3)); }
+
+__device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
+    while (it.step < c.n_steps) {
+        while (it.ph < c.n_phases) {
+            const int idx = c.warp + kWarps * it.j;
+            if (idx < c.units[it.ph]) {
+                const MkPhase& ph = c.phases[it.ph];
+                const int sh = ks_shift_of(ph.ksplit);
+                const int slot = idx >> sh, s = idx & (ph.ksplit - 1);
+                it.st = (s * ph.n_stages) >> sh;
+                it.st_end = ((s + 1) * ph.n_stages) >> sh;
+                it.wp = static_cast<const unsigned char*>(ph.wp);
+                it.n_panels = ph.n_panels;
+                it.K = ph.K;
+                it.panel = blockIdx.x + gridDim.x * slot;
+                return;
+            }
+            ++it.ph;
+            it.j = 0;
+        }
+        it.ph = 0;
+        ++it.step;
+    }
+}
+
+__device__ __forceinline__ const unsigned char* stage_src(const Ctx& c, const WIter& it, uint32_t* bytes) {
+    return it.wp + mk_stage_offset(it.n_panels, it.K, it.panel, it.st, bytes);
+}
+
+__device__ __forceinline__ void issue_stage(const Ctx& c, const WIter& it, int slot) {
+    if (c.lane == 0) {
+        uint32_t bytes;
+        const unsigned char* src = stage_src(c, it, &bytes);
+        mbar_expect_tx(c.full + slot * 8, bytes);
+        bulk_g2s(c.ring + slot * kStageBytes, src, bytes, c.full + slot * 8);
+    }
+}
+
+__device__ __forceinline__ void witer_next(const Ctx& c, WIter& it) {
+    if (++it.st == it.st_end) {
+        ++it.j;
+        witer_seek(c, it);
+    }
+}
+
+// At the start of a phase every warp asks L2 for (up to `budget` bytes of) its units of the NEXT weight phase,
+// one prefetch instruction per unit (a unit is contiguous in the packed layout).  HBM then has work to do
+// during this phase's barrier, prologue, epilogue and attention, which the shared-memory ring alone (a few
+// microseconds of traffic) cannot cover.
+__device__ __forceinline__ void prefetch_next_phase(const Ctx& c, int step, int phi, int budget) {
+    if (c.lane != 0 || budget <= 0) return;
+    WIter it = {step, phi + 1, 0, 0, 0, nullptr, 0, 0, 0};
+    witer_seek(c, it);
+    const int ph0 = it.ph, step0 = it.step;
+    while (it.step < c.n_steps && it.ph == ph0 && it.step == step0 && budget > 0) {
+        uint32_t b0;
+        const unsigned char* src = it.wp + mk_stage_offset(it.n_panels, it.K, it.panel, it.st, &b0);
+        size_t bytes = (size_t)(it.st_end - it.st) * kStageBytes;
+        const size_t panel_left = (size_t)it.K * 16 - (size_t)it.st * kStageBytes;
+        if (bytes > panel_left) bytes = panel_left;
+        if (bytes > (size_t)budget) bytes = (size_t)budget & ~(size_t)15;
+        if (bytes >= 16)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"((uint32_t)bytes) : "memory");
+        budget -= (int)bytes;
+        ++it.j;
+        witer_seek(c, it);
+    }
+}
+
+// ---- prologues: build the phase's input rows in shared memory (bf16, row stride ldx) ------------------------
+
+// Rows of the residual stream / an activation -> shared memory, optionally normalised.  One row is shared by
+// 256 / 128 / 64 / 32 threads (1 / 2 / <=4 / more rows) so that a single row costs one batched L2 round trip.
+__device__ __forceinline__ void accum_stats(const uint4& v, float& s1, float& s2) {
+    float f[8];
+    unpack<bf16>(v, f);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        s1 += f[j];
+        s2 = fmaf(f[j], f[j], s2);
+    }
+}
+
+__device__ __forceinline__ uint4 norm_vec(const uint4& x, const uint4& w, const uint4& b, int norm, float mean, float rstd) {
+    float f[8], wf[8], bf[8];
+    unpack<bf16>(x, f);
+    unpack<bf16>(w, wf);
+    if (norm == NORM_RMS) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = wf[j] * bf16_round(f[j] * rstd);
+    } else {
+        unpack<bf16>(b, bf);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = fmaf((f[j] - mean) * rstd, wf[j], bf[j]);
+    }
+    return pack8(f);
+}
+
+__device__ __forceinline__ void stage_rows(const MkParams& p, const void* src, int K, int norm, const void* nw, const void* nb,
+                                           bf16* xs, int ldx, float* red) {
+    const int R = p.n_rows;
+    const int tpr = R == 1 ? 256 : (R == 2 ? 128 : (R <= 4 ? 64 : 32));
+    const int rows_par = kThreads / tpr, wpr = tpr >> 5;
+    const int sub = threadIdx.x / tpr, lt = threadIdx.x - sub * tpr;
+    const int warp = threadIdx.x >> 5;
+    const int stride = tpr * 8;
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (int r0 = 0; r0 < R; r0 += rows_par) {
+        const int r = r0 + sub;
+        const bool active = r < R && sub < rows_par;
+        const bf16* xr = static_cast<const bf16*>(src) + (size_t)(active ? r : 0) * K;
+        bf16* dst = xs + (size_t)(active ? r : 0) * ldx;
+        float s1 = 0.f, s2 = 0.f;
+        if (norm != NORM_NONE && K <= 4 * stride) {
+            // fast path (every decode shape of the BASELINE models): the whole row is held in registers by its
+            // threads; the activation and the norm weights are fetched together -- one L2 round trip in all
+            const int kb = lt * 8, k1 = kb + stride, k2 = kb + 2 * stride, k3 = kb + 3 * stride;
+            const bf16* wq = static_cast<const bf16*>(nw);
+            const bf16* bq = static_cast<const bf16*>(nb);
+            const bool a0 = active && kb < K, a1 = active && k1 < K, a2 = active && k2 < K, a3 = active && k3 < K;
+            uint4 v0 = z, v1 = z, v2 = z, v3 = z, w0 = z, w1 = z, w2 = z, w3 = z, b0 = z, b1 = z, b2 = z, b3 = z;
+            if (a0) { v0 = ldcg_u4(xr + kb); w0 = ld_u4(wq + kb); if (norm == NORM_LAYER) b0 = ld_u4(bq + kb); }
+            if (a1) { v1 = ldcg_u4(xr + k1); w1 = ld_u4(wq + k1); if (norm == NORM_LAYER) b1 = ld_u4(bq + k1); }
+            if (a2) { v2 = ldcg_u4(xr + k2); w2 = ld_u4(wq + k2); if (norm == NORM_LAYER) b2 = ld_u4(bq + k2); }
+            if (a3) { v3 = ldcg_u4(xr + k3); w3 = ld_u4(wq + k3); if (norm == NORM_LAYER) b3 = ld_u4(bq + k3); }
+            if (a0) accum_stats(v0, s1, s2);
+            if (a1) accum_stats(v1, s1, s2);
+            if (a2) accum_stats(v2, s1, s2);
+            if (a3) accum_stats(v3, s1, s2);
+            auto group_sum = [&](float a) {
+                a = warp_sum(a);
+                if (wpr > 1) {
+                    __syncthreads();
+                    if ((threadIdx.x & 31) == 0) red[warp] = a;
+                    __syncthreads();
+                    a = 0.f;
+                    if (sub < rows_par)
+                        for (int w = 0; w < wpr; ++w) a += red[sub * wpr + w];
+                }
+                return a;
+            };
+            float mean = 0.f, rstd;
+            if (norm == NORM_RMS) {
+                rstd = 1.0f / sqrtf(group_sum(s2) / (float)K + p.eps);
+            } else {
+                mean = group_sum(s1) / (float)K;
+                float sq = 0.f, f[8];
+                if (a0) { unpack<bf16>(v0, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq); }
+                if (a1) { unpack<bf16>(v1, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq); }
+                if (a2) { unpack<bf16>(v2, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq); }
+                if (a3) { unpack<bf16>(v3, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq); }
+                rstd = 1.0f / sqrtf(group_sum(sq) / (float)K + p.eps);
+            }
+            if (a0) *reinterpret_cast<uint4*>(dst + kb) = norm_vec(v0, w0, b0, norm, mean, rstd);
+            if (a1) *reinterpret_cast<uint4*>(dst + k1) = norm_vec(v1, w1, b1, norm, mean, rstd);
+            if (a2) *reinterpret_cast<uint4*>(dst + k2) = norm_vec(v2, w2, b2, norm, mean, rstd);
+            if (a3) *reinterpret_cast<uint4*>(dst + k3) = norm_vec(v3, w3, b3, norm, mean, rstd);
+            continue;
+        }
+        for (int kb = lt * 8; kb < K; kb += 4 * stride) {
+            // four loads in flight per thread, then the stores (explicit scalars: no local arrays)
+            const int k1 = kb + stride, k2 = kb + 2 * stride, k3 = kb + 3 * stride;
+            uint4 v0 = z, v1 = z, v2 = z, v3 = z;
+            if (active) {
+                v0 = ldcg_u4(xr + kb);
+                if (k1 < K) v1 = ldcg_u4(xr + k1);
+                if (k2 < K) v2 = ldcg_u4(xr + k2);
+                if (k3 < K) v3 = ldcg_u4(xr + k3);
+                *reinterpret_cast<uint4*>(dst + kb) = v0;
+                accum_stats(v0, s1, s2);
+                if (k1 < K) { *reinterpret_cast<uint4*>(dst + k1) = v1; accum_stats(v1, s1, s2); }
+                if (k2 < K) { *reinterpret_cast<uint4*>(dst + k2) = v2; accum_stats(v2, s1, s2); }
+                if (k3 < K) { *reinterpret_cast<uint4*>(dst + k3) = v3; accum_stats(v3, s1, s2); }
+            }
+        }
+        if (norm == NORM_NONE) continue;
+        // row statistics: warp shuffle, then across the row's warps through shared memory
+        float mean = 0.f, rstd;
+        {
+            float a = warp_sum(norm == NORM_RMS ? s2 : s1);
+            if (wpr > 1) {
+                __syncthreads();
+                if ((threadIdx.x & 31) == 0) red[warp] = a;
+                __syncthreads();
+                a = 0.f;
+                if (sub < rows_par)
+                    for (int w = 0; w < wpr; ++w) a += red[sub * wpr + w];
+            }
+            if (norm == NORM_RMS) rstd = 1.0f / sqrtf(a / (float)K + p.eps);  // HF LlamaRMSNorm: fp32 variance
+            else mean = a / (float)K;
+        }
+        if (norm == NORM_LAYER) {
+            float sq = 0.f;
+            if (active)
+                for (int k = lt * 8; k < K; k += stride) {
+                    float f[8];
+                    unpack<bf16>(*reinterpret_cast<const uint4*>(dst + k), f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq);
+                }
+            float a = warp_sum(sq);
+            if (wpr > 1) {
+                __syncthreads();
+                if ((threadIdx.x & 31) == 0) red[warp] = a;
+                __syncthreads();
+                a = 0.f;
+                if (sub < rows_par)
+                    for (int w = 0; w < wpr; ++w) a += red[sub * wpr + w];
+            }
+            rstd = 1.0f / sqrtf(a / (float)K + p.eps);
+        }
+        const bf16* wp = static_cast<const bf16*>(nw);
+        const bf16* bp = static_cast<const bf16*>(nb);
+        for (int kb = lt * 8; kb < K; kb += 2 * stride) {
+            const int k1 = kb + stride;
+            if (active) {
+                uint4 w0 = ld_u4(wp + kb), w1 = z, b0 = z, b1 = z;
+                if (k1 < K) w1 = ld_u4(wp + k1);
+                if (norm == NORM_LAYER) {
+                    b0 = ld_u4(bp + kb);
+                    if (k1 < K) b1 = ld_u4(bp + k1);
+                }
+                *reinterpret_cast<uint4*>(dst + kb) = norm_vec(*reinterpret_cast<const uint4*>(dst + kb), w0, b0, norm, mean, rstd);
+                if (k1 < K)
+                    *reinterpret_cast<uint4*>(dst + k1) = norm_vec(*reinterpret_cast<const uint4*>(dst + k1), w1, b1, norm, mean, rstd);
+            }
+        }
+    }
+}
+
+// OPROJ prologue: merge the split-K attention partials of every (row, head) into bf16 rows in shared memory.
+// Batched L2 round trips: the (m, l) pairs, then the partial outputs as 16-byte vectors, eight in flight per
+// thread; splits past the end of a row's context are skipped.  `sw` = 2*R*H*S floats of scratch.
+__device__ __forceinline__ int attn_active_splits(const MkParams& p, const StepCache& sc, int r) {
+    const int S = p.n_splits, len = sc.pos[r] + 1;
+    int chunk = (len + S - 1) / S;
+    chunk = (chunk + kTT - 1) / kTT * kTT;
+    return (len + chunk - 1) / chunk;
+}
+
+__device__ __forceinline__ float4 ldcg_f4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+__device__ __forceinline__ void stage_attn_combine(const MkParams& p, const StepCache& sc, bf16* xs, int ldx, float* sw) {
+    const int hd = p.head_dim, H = p.n_heads, S = p.n_splits, Hd = H * hd;
+    const int n_pairs = p.n_rows * H;
+    float* sm_w = sw;                 // [pair][S]  split maxima, then normalised weights
+    float* sm_l = sw + n_pairs * S;   // [pair][S]  split sums
+    for (int i = threadIdx.x; i < n_pairs * S; i += kThreads) {
+        const int pair = i / S, s2 = i - pair * S;
+        float2 ml = make_float2(-FLT_MAX, 0.f);
+        if (s2 < attn_active_splits(p, sc, pair / H)) ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml) + i);
+        sm_w[i] = ml.x;
+        sm_l[i] = ml.y;
+    }
+    __syncthreads();
+    for (int pair = threadIdx.x; pair < n_pairs; pair += kThreads) {
+        float Mg = -FLT_MAX, Lg = 0.f;
+        for (int s2 = 0; s2 < S; ++s2) Mg = fmaxf(Mg, sm_w[pair * S + s2]);
+        for (int s2 = 0; s2 < S; ++s2) {
+            const float w = expf(sm_w[pair * S + s2] - Mg);
+            Lg = fmaf(sm_l[pair * S + s2], w, Lg);
+            sm_w[pair * S + s2] = w;
+        }
+        const float inv = 1.0f / Lg;
+        for (int s2 = 0; s2 < S; ++s2) sm_w[pair * S + s2] *= inv;
+    }
+    __syncthreads();
+    const int vec_per_row = Hd >> 2;  // groups of four output elements
+    for (int idx = threadIdx.x; idx < p.n_rows * vec_per_row; idx += kThreads) {
+        const int r = idx / vec_per_row, c = (idx - r * vec_per_row) * 4, h = c / hd, e = c - h * hd;
+        const int pair = r * H + h;
+        const int ns = attn_active_splits(p, sc, r);
+        const float* po = p.part_o + (size_t)pair * S * hd + e;
+        const float* wg = sm_w + pair * S;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s0 = 0; s0 < ns; s0 += 8) {
+            float4 v0, v1, v2, v3, v4, v5, v6, v7;
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            v0 = ldcg_f4(po + (size_t)s0 * hd);
+            v1 = s0 + 1 < ns ? ldcg_f4(po + (size_t)(s0 + 1) * hd) : z4;
+            v2 = s0 + 2 < ns ? ldcg_f4(po + (size_t)(s0 + 2) * hd) : z4;
+            v3 = s0 + 3 < ns ? ldcg_f4(po + (size_t)(s0 + 3) * hd) : z4;
+            v4 = s0 + 4 < ns ? ldcg_f4(po + (size_t)(s0 + 4) * hd) : z4;
+            v5 = s0 + 5 < ns ? ldcg_f4(po + (size_t)(s0 + 5) * hd) : z4;
+            v6 = s0 + 6 < ns ? ldcg_f4(po + (size_t)(s0 + 6) * hd) : z4;
+            v7 = s0 + 7 < ns ? ldcg_f4(po + (size_t)(s0 + 7) * hd) : z4;
+#define DLLM_ACC4(V, I)                                    \
+    if (s0 + (I) < ns) {                                   \
+        const float w = wg[s0 + (I)];                      \
+        acc.x = fmaf((V).x, w, acc.x);                     \
+        acc.y = fmaf((V).y, w, acc.y);                     \
+        acc.z = fmaf((V).z, w, acc.z);                     \
+        acc.w = fmaf((V).w, w, acc.w);                     \
+    }
+            DLLM_ACC4(v0, 0) DLLM_ACC4(v1, 1) DLLM_ACC4(v2, 2) DLLM_ACC4(v3, 3)
+            DLLM_ACC4(v4, 4) DLLM_ACC4(v5, 5) DLLM_ACC4(v6, 6) DLLM_ACC4(v7, 7)
+#undef DLLM_ACC4
+        }
+        __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y), hi = __floats2bfloat162_rn(acc.z, acc.w);
+        uint2 out;
+        out.x = *reinterpret_cast<uint32_t*>(&lo);
+        out.y = *reinterpret_cast<uint32_t*>(&hi);
+        *reinterpret_cast<uint2*>(xs + (size_t)r * ldx + c) = out;
+    }
+}
+
+// ---- attention phase ------------------------------------------------------------------------------------
+
+struct AttnSmem {
+    bf16* k;      // [kTT][hd + 8]
+    bf16* v;      // [kTT][hd + 8]
+    float* s;     // [kMaxGq][kTT]
+    float* q;     // [kMaxGq][hd]
+};
+
+// cp.async the K and V rows of tokens [a, b) of (seq, kvh) into tile rows (token - tile0)
+__device__ __forceinline__ void attn_load_rows(const MkParams& p, const MkLayer& L, const AttnSmem& sm, const int* bt,
+                                               int kvh, int tile0, int a, int b) {
+    const int hd = p.head_dim, vecs = hd >> 3, ld = hd + 8;
+    const int mask = (1 << p.page_shift) - 1;
+    for (int i = threadIdx.x; i < (b - a) * vecs; i += kThreads) {
+        const int t = a + i / vecs, v = i % vecs;
+        const int page = bt[t >> p.page_shift];
+        const size_t base = ((((size_t)page * p.n_kv_heads + kvh) << p.page_shift) + (t & mask)) * hd + v * 8;
+        cp_async16(sm.k + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.kpool) + base);
+        cp_async16(sm.v + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.vpool) + base);
+    }
+}
+
+struct AttnUnit {
+    int r, kvh, split, seq, t0, t1;
+};
+
+__device__ __forceinline__ AttnUnit attn_unit(const MkParams& p, const StepCache& sc, int u) {
+    AttnUnit a;
+    const int S = p.n_splits, KV = p.n_kv_heads;
+    a.r = u / (KV * S);
+    a.kvh = (u / S) % KV;
+    a.split = u % S;
+    const int len = sc.pos[a.r] + 1;
+    a.seq = sc.seq[a.r];
+    int chunk = (len + S - 1) / S;
+    chunk = (chunk + kTT - 1) / kTT * kTT;  // whole tiles per split: no one-token tail tiles
+    a.t0 = min(len, a.split * chunk);
+    a.t1 = min(len, a.t0 + chunk);
+    return a;
+}
+
+// Tokens that may be written during this very step (any row of the same sequence) start here; everything
+// below is old and safe to prefetch before the barrier.
+__device__ __forceinline__ int attn_safe_end(const StepCache& sc, const AttnUnit& a) {
+    return sc.pos[a.r] - (MK_MAX_ROWS - 1);
+}
+
+__device__ __forceinline__ void attention_phase(const MkParams& p, const StepCache& sc, const int* sbt, const MkLayer& L, const AttnSmem& sm, bool prefetched) {
+    const int hd = p.head_dim, H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int epl = hd >> 5;  // output columns per lane: 1, 2 or 4
+    const float scale = rsqrtf((float)hd);
+    const int n_units = p.n_rows * KV * S;
+    bool first = true;
+    for (int u = blockIdx.x; u < n_units; u += gridDim.x, first = false) {
+        const AttnUnit a = attn_unit(p, sc, u);
+        if (a.t0 >= a.t1) continue;  // split past the end of the context: the merge never reads it
+        // q of the Gq heads of this KV head -> shared, fp32
+        for (int i = threadIdx.x; i < Gq * hd; i += kThreads)
+            sm.q[i] = __bfloat162float(__ldcg(static_cast<const bf16*>(p.q) + ((size_t)a.r * H + a.kvh * Gq) * hd + i));
+        float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};  // warp g owns head g: (m, l) and hd/32 columns per lane
+        for (int tile0 = a.t0; tile0 < a.t1; tile0 += kTT) {
+            const int tend = min(a.t1, tile0 + kTT), nt = tend - tile0;
+            int from = tile0;
+            if (first && prefetched && tile0 == a.t0) from = max(tile0, min(tend, attn_safe_end(sc, a)));
+            attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend);
+            cp_async_wait_all();
+            __syncthreads();
+            // scores: one (token, head) pair per thread-iteration; lanes walk tokens (padded rows: no conflicts)
+            for (int i = threadIdx.x; i < kTT * Gq; i += kThreads) {
+                const int t = i & (kTT - 1), g = i / kTT;
+                if (t < nt) {
+                    const bf16* kr = sm.k + (size_t)t * ld;
+                    const float* qg = sm.q + g * hd;
+                    float d0 = 0.f, d1 = 0.f;
+                    for (int e = 0; e < hd; e += 8) {
+                        float kf[8];
+                        unpack<bf16>(*reinterpret_cast<const uint4*>(kr + e), kf);
+                        const float4 q0 = *reinterpret_cast<const float4*>(qg + e);
+                        const float4 q1 = *reinterpret_cast<const float4*>(qg + e + 4);
+                        d0 = fmaf(kf[0], q0.x, d0); d1 = fmaf(kf[1], q0.y, d1); d0 = fmaf(kf[2], q0.z, d0); d1 = fmaf(kf[3], q0.w, d1);
+                        d0 = fmaf(kf[4], q1.x, d0); d1 = fmaf(kf[5], q1.y, d1); d0 = fmaf(kf[6], q1.z, d0); d1 = fmaf(kf[7], q1.w, d1);
+                    }
+                    sm.s[g * kTT + t] = bf16_round(bf16_round(d0 + d1) * scale);
+                }
+            }
+            __syncthreads();
+            if (warp < Gq) {  // online softmax + P.V for head `warp`
+                float* sg = sm.s + warp * kTT;
+                const float s0 = lane < nt ? sg[lane] : -FLT_MAX;
+                const float s1 = lane + 32 < nt ? sg[lane + 32] : -FLT_MAX;
+                const float mn = fmaxf(m, warp_max(fmaxf(s0, s1)));
+                const float p0 = lane < nt ? expf(s0 - mn) : 0.f;
+                const float p1 = lane + 32 < nt ? expf(s1 - mn) : 0.f;
+                const float corr = expf(m - mn);
+                l = l * corr + warp_sum(p0 + p1);
+                m = mn;
+                if (lane < nt) sg[lane] = p0;
+                if (lane + 32 < nt) sg[lane + 32] = p1;
+                __syncwarp();
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] *= corr;
+                if (epl == 2) {
+                    float oa0 = 0.f, oa1 = 0.f, ob0 = 0.f, ob1 = 0.f;  // two independent chains
+                    int t = 0;
+                    for (; t + 1 < nt; t += 2) {
+                        const uint32_t va = *reinterpret_cast<const uint32_t*>(sm.v + (size_t)t * ld + lane * 2);
+                        const uint32_t vb = *reinterpret_cast<const uint32_t*>(sm.v + (size_t)(t + 1) * ld + lane * 2);
+                        const float pa = sg[t], pb = sg[t + 1];
+                        oa0 = fmaf(pa, __uint_as_float(va << 16), oa0);
+                        oa1 = fmaf(pa, __uint_as_float(va & 0xffff0000u), oa1);
+                        ob0 = fmaf(pb, __uint_as_float(vb << 16), ob0);
+                        ob1 = fmaf(pb, __uint_as_float(vb & 0xffff0000u), ob1);
+                    }
+                    if (t < nt) {
+                        const uint32_t va = *reinterpret_cast<const uint32_t*>(sm.v + (size_t)t * ld + lane * 2);
+                        oa0 = fmaf(sg[t], __uint_as_float(va << 16), oa0);
+                        oa1 = fmaf(sg[t], __uint_as_float(va & 0xffff0000u), oa1);
+                    }
+                    o[0] += oa0 + ob0;
+                    o[1] += oa1 + ob1;
+                } else {
+                    for (int t = 0; t < nt; ++t) {
+                        const float pt = sg[t];
+                        const bf16* vr = sm.v + (size_t)t * ld + lane * epl;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e)
+                            if (e < epl) o[e] = fmaf(pt, __bfloat162float(vr[e]), o[e]);
+                    }
+                }
+            }
+            __syncthreads();  // tile buffers are reused
+        }
+        if (warp < Gq) {
+            const size_t pidx = ((size_t)a.r * H + a.kvh * Gq + warp) * S + a.split;
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+                if (e < epl) p.part_o[pidx * hd + lane * epl + e] = o[e];
+            if (lane == 0) {
+                p.part_ml[pidx * 2 + 0] = m;
+                p.part_ml[pidx * 2 + 1] = l;
+            }
+        }
+        __syncthreads();  // shared buffers are reused by the next unit
+    }
+}
+
+// ---- the kernel ----------------------------------------------------------------------------------------
+
+template <bool HI>  // HI: more than 8 batch rows (second half of the mma M dimension in use)
+__global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int ldx = p.k_max + 8;  // padded row stride of xs: rows land in different banks
+    // carve-up (mirrors mk_smem_bytes)
+    unsigned char* sp = smem;
+    MkPhase* phases = reinterpret_cast<MkPhase*>(sp);
+    sp += (size_t)((p.n_phases * sizeof(MkPhase) + 127) / 128) * 128;
+    const uint32_t full_all = smem_u32(sp);
+    sp += (size_t)((kWarps * p.stages * 8 + 127) / 128) * 128;
+    bf16* xs = reinterpret_cast<bf16*>(sp);
+    sp += (size_t)((p.n_rows * ldx * 2 + 127) / 128) * 128;
+    float* spart = reinterpret_cast<float*>(sp);
+    sp += (size_t)p.part_units * kPartStride * 4;
+    float* srope = reinterpret_cast<float*>(sp);  // [R][head_dim]: cos row then sin row of each batch row's position
+    sp += (size_t)p.n_rows * p.head_dim * 4;
+    int* sbt = reinterpret_cast<int*>(sp);        // [R][pages_per_seq]: block-table row of each batch row's sequence
+    sp += (size_t)((p.n_rows * p.pages_per_seq * 4 + 15) / 16) * 16;
+    AttnSmem at;
+    at.k = reinterpret_cast<bf16*>(sp);
+    sp += (size_t)kTT * (p.head_dim + 8) * 2;
+    at.v = reinterpret_cast<bf16*>(sp);
+    sp += (size_t)kTT * (p.head_dim + 8) * 2;
+    at.s = reinterpret_cast<float*>(sp);
+    sp += kMaxGq * kTT * 4;
+    at.q = reinterpret_cast<float*>(sp);
+    sp += kMaxGq * p.head_dim * 4;
+    sp = reinterpret_cast<unsigned char*>(((uintptr_t)sp + 127) & ~(uintptr_t)127);
+    const uint32_t ring_all = smem_u32(sp);
+
+    __shared__ StepCache sc;
+    __shared__ int s_units[MK_MAX_PHASES];
+    __shared__ float red[kWarps];
+    __shared__ float s_val[kWarps][MK_MAX_ROWS];
+    __shared__ int s_idx[kWarps][MK_MAX_ROWS];
+    __shared__ int s_last;
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t4 = lane & 3;  // mma fragment coordinates
+    const int R = p.n_rows;
+    int RP = 1;
+    while (RP < R) RP <<= 1;
+    for (int i = threadIdx.x; i < p.n_phases * (int)(sizeof(MkPhase) / 4); i += kThreads)
+        reinterpret_cast<uint32_t*>(phases)[i] = reinterpret_cast<const uint32_t*>(p.phases)[i];
+    for (int i = threadIdx.x; i < p.n_phases; i += kThreads) {
+        const MkPhase& q = p.phases[i];
+        s_units[i] = is_weight_phase(q.kind) ? local_panels(q) * q.ksplit : 0;
+    }
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kWarps * p.stages; ++i) mbar_init(full_all + i * 8, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    Ctx c;
+    c.n_steps = p.n_steps;
+    c.n_phases = p.n_phases;
+    c.phases = phases;
+    c.units = s_units;
+    c.warp = warp;
+    c.lane = lane;
+    c.ring = ring_all + warp * p.stages * kStageBytes;
+    c.full = full_all + warp * p.stages * 8;
+
+    // prime this warp's ring: the first `stages` entries of its static sequence
+    WIter prod = {0, 0, 0, 0, 0, nullptr, 0, 0, 0};
+    witer_seek(c, prod);
+    for (int i = 0; i < p.stages && prod.step < p.n_steps; ++i) {
+        issue_stage(c, prod, i);
+        witer_next(c, prod);
+    }
+    unsigned consumed = 0;  // stages this warp has consumed so far -> ring slot and mbarrier parity
+    unsigned bar_target = 0;
+    bool need_barrier = false;
+    // rows this lane feeds into the A fragment (rows >= R produce output rows nobody reads)
+    const uint32_t xrow_lo = smem_u32(xs) + (uint32_t)(min(g, R - 1) * ldx * 2);
+    const uint32_t xrow_hi = smem_u32(xs) + (uint32_t)(min(g + 8, R - 1) * ldx * 2);
+
+    for (int step = 0; step < p.n_steps; ++step) {
+        for (int phi = 0; phi < p.n_phases; ++phi) {
+            const MkPhase& ph = phases[phi];
+            const MkLayer* L = p.layers + ph.layer;
+            if (need_barrier) grid_barrier(p.barrier, bar_target);
+            need_barrier = true;
+            if (phi == 0) {
+                // positions / slots / KV page of every row, and the rotary rows of those positions
+                if ((int)threadIdx.x < R) {
+                    const int ps = ldcg_i32(p.pos + threadIdx.x), sq = ldcg_i32(p.seq + threadIdx.x);
+                    sc.pos[threadIdx.x] = ps;
+                    sc.seq[threadIdx.x] = sq;
+                    sc.page[threadIdx.x] = p.block_table[(size_t)sq * p.pages_per_seq + (ps >> p.page_shift)];
+                    sc.off[threadIdx.x] = ps & ((1 << p.page_shift) - 1);
+                }
+                for (int i = threadIdx.x; i < R * p.pages_per_seq; i += kThreads) {
+                    const int r = i / p.pages_per_seq;
+                    sbt[i] = p.block_table[(size_t)ldcg_i32(p.seq + r) * p.pages_per_seq + (i - r * p.pages_per_seq)];
+                }
+                if (p.rope) {
+                    const int half = p.head_dim >> 1;
+                    for (int i = threadIdx.x; i < R * p.head_dim; i += kThreads) {
+                        const int r = i / p.head_dim, e = i - r * p.head_dim;
+                        const int ps = ldcg_i32(p.pos + r);
+                        srope[i] = e < half ? p.rope_cos[(size_t)ps * half + e] : p.rope_sin[(size_t)ps * half + e - half];
+                    }
+                }
+                __syncthreads();
+            }
+            if (p.prefetch_kb > 0 && ph.kind != MK_ATTN) prefetch_next_phase(c, step, phi, p.prefetch_kb * 1024);
+            long long* tr = (p.trace && blockIdx.x == 0 && threadIdx.x == 0) ? p.trace + ((size_t)step * p.n_phases + phi) * 8 : nullptr;
+            if (tr) tr[0] = clock64();
+
+            if (ph.kind == MK_EMBED) {
+                // h[r] = wte[ids[r]] (+ wpe[pos[r]]), spread over the grid in 16-byte vectors
+                const int vecs = p.hidden >> 3;
+                for (int i = blockIdx.x * kThreads + threadIdx.x; i < R * vecs; i += gridDim.x * kThreads) {
+                    const int r = i / vecs, v = i - r * vecs;
+                    int id = ldcg_i32(p.ids + r);
+                    id = min(max(id, 0), p.vocab - 1);
+                    uint4 val = ld_u4(static_cast<const bf16*>(p.wte) + (size_t)id * p.hidden + v * 8);
+                    if (p.wpe) {
+                        float a[8], b[8];
+                        unpack<bf16>(val, a);
+                        unpack<bf16>(ld_u4(static_cast<const bf16*>(p.wpe) + (size_t)sc.pos[r] * p.hidden + v * 8), b);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) a[j] += b[j];
+                        val = pack8(a);
+                    }
+                    *reinterpret_cast<uint4*>(static_cast<bf16*>(p.h) + (size_t)r * p.hidden + v * 8) = val;
+                }
+                if (tr) tr[1] = tr[2] = tr[3] = clock64();
+                continue;
+            }
+            if (ph.kind == MK_ATTN) {
+                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true);
+                if (tr) tr[1] = tr[2] = tr[3] = clock64();
+                continue;
+            }
+
+            // ---- weight-streaming phase: prologue ----
+            if (ph.kind == MK_QKV) stage_rows(p, p.h, ph.K, p.norm, L->norm1_w, L->norm1_b, xs, ldx, red);
+            else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) stage_rows(p, p.h, ph.K, p.norm, L->norm2_w, L->norm2_b, xs, ldx, red);
+            else if (ph.kind == MK_HEAD) stage_rows(p, p.h, ph.K, p.norm, p.final_norm_w, p.final_norm_b, xs, ldx, red);
+            else if (ph.kind == MK_DOWN) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
+            else stage_attn_combine(p, sc, xs, ldx, reinterpret_cast<float*>(at.k));
+            __syncthreads();
+            if (tr) tr[1] = clock64();
+
+            // ---- main: this warp's (panel slot, k-split) units on the tensor cores ----
+            const int K = ph.K, ks = ph.ksplit, ns = ph.n_stages;
+            const int n_local = local_panels(ph);
+            // the epilogue of the residual phases needs the old residual: fetch this thread's first pair now,
+            // so that the L2 round trip overlaps the main loop
+            uint32_t old_pref = 0u;
+            if ((ph.kind == MK_OPROJ || ph.kind == MK_DOWN) && (int)threadIdx.x < n_local * 4 * RP) {
+                const int r = threadIdx.x & (RP - 1), pi = threadIdx.x / RP;
+                const int n = (blockIdx.x + gridDim.x * (pi >> 2)) * 8 + 2 * (pi & 3);
+                if (r < R && n < ph.n0)
+                    old_pref = __ldcg(reinterpret_cast<const uint32_t*>(static_cast<const bf16*>(p.h) + (size_t)r * ph.n0 + n));
+            }
+            const int ksh = ks_shift_of(ks);
+            const int n_units_cta = n_local * ks;
+            ArgBest best = {-FLT_MAX, INT_MAX};
+            // units are processed in rounds of `part_units` (a multiple of the warp count and of ks) so that the
+            // partial buffer stays small however many panels a CTA owns (the lm_head: ~100 per CTA)
+            for (int base = 0; base < n_units_cta; base += p.part_units) {
+            const int round_end = min(n_units_cta, base + p.part_units);
+            for (int idx = base + warp; idx < round_end; idx += kWarps) {
+                const int s = idx & (ks - 1);
+                const int sb = (s * ns) >> ksh, se = ((s + 1) * ns) >> ksh;
+                // four independent accumulator sets: the mma dependency chain of a stage is 4 long, not 16
+                float acc[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
+                float acc2[4] = {0.f, 0.f, 0.f, 0.f}, acc3[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int st = sb; st < se; ++st) {
+                    const unsigned slot = consumed % (unsigned)p.stages;
+                    long long tq0 = 0, tq1 = 0, tq2 = 0;
+                    if (tr) tq0 = clock64();
+                    mbar_wait(c.full + slot * 8, (consumed / (unsigned)p.stages) & 1u);
+                    if (tr) tq1 = clock64();
+                    const uint32_t sbase = c.ring + slot * kStageBytes + (uint32_t)(lane * 16);  // [32-k block][row g][chunk t4]
+                    const int k0 = st * kStageK;
+                    const int nkb = min(kStageK, K - k0) >> 5;  // 32-k blocks in this stage
+                    const uint32_t xlo = xrow_lo + (uint32_t)((k0 + t4 * 8) * 2);
+                    const uint32_t xhi = xrow_hi + (uint32_t)((k0 + t4 * 8) * 2);
+                    // lane (g, t4) holds 8 consecutive k of weight row g and of batch row g: two mma k-steps per block
+#define DLLM_MK_BLOCK2(KB)                                                                          \
+    {                                                                                               \
+        const uint4 wa = lds_u4(sbase + (KB) * 512), wb = lds_u4(sbase + (KB) * 512 + 512);         \
+        const uint4 xa = lds_u4(xlo + (KB) * 64), xb = lds_u4(xlo + (KB) * 64 + 64);                \
+        uint4 ha = make_uint4(0u, 0u, 0u, 0u), hb = ha;                                             \
+        if (HI) {                                                                                   \
+            ha = lds_u4(xhi + (KB) * 64);                                                           \
+            hb = lds_u4(xhi + (KB) * 64 + 64);                                                      \
+        }                                                                                           \
+        mma_bf16(acc, xa.x, ha.x, xa.y, ha.y, wa.x, wa.y);                                          \
+        mma_bf16(acc1, xa.z, ha.z, xa.w, ha.w, wa.z, wa.w);                                         \
+        mma_bf16(acc2, xb.x, hb.x, xb.y, hb.y, wb.x, wb.y);                                         \
+        mma_bf16(acc3, xb.z, hb.z, xb.w, hb.w, wb.z, wb.w);                                         \
+    }
+                    if (nkb == 8) {
+                        DLLM_MK_BLOCK2(0) DLLM_MK_BLOCK2(2) DLLM_MK_BLOCK2(4) DLLM_MK_BLOCK2(6)
+                    } else {
+                        int kb = 0;
+                        for (; kb + 1 < nkb; kb += 2) DLLM_MK_BLOCK2(kb)
+                        if (kb < nkb) {
+                            const uint4 wa = lds_u4(sbase + kb * 512);
+                            const uint4 xa = lds_u4(xlo + kb * 64);
+                            uint4 ha = make_uint4(0u, 0u, 0u, 0u);
+                            if (HI) ha = lds_u4(xhi + kb * 64);
+                            mma_bf16(acc, xa.x, ha.x, xa.y, ha.y, wa.x, wa.y);
+                            mma_bf16(acc1, xa.z, ha.z, xa.w, ha.w, wa.z, wa.w);
+                        }
+                    }
+                    __syncwarp();
+                    if (tr) tq2 = clock64();
+                    ++consumed;
+                    if (prod.step < p.n_steps) {  // refill the slot with the next stage of this warp's sequence
+                        issue_stage(c, prod, (int)slot);
+                        witer_next(c, prod);
+                    }
+                    if (tr) {
+                        const long long tq3 = clock64();
+                        tr[4] += tq1 - tq0;  // waiting for the stage
+                        tr[5] += tq2 - tq1;  // LDS + mma
+                        tr[6] += tq3 - tq2;  // refill issue + cursor advance
+                        tr[7] += 1;
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) acc[q] = (acc[q] + acc1[q]) + (acc2[q] + acc3[q]);
+                // C[batch g][panel rows 2*t4, 2*t4+1] (and batch g+8) -> partial buffer [idx][panel row][batch]
+                float* dstp = spart + (size_t)(idx - base) * kPartStride;
+                if (g < R) {
+                    dstp[(2 * t4) * MK_MAX_ROWS + g] = acc[0];
+                    dstp[(2 * t4 + 1) * MK_MAX_ROWS + g] = acc[1];
+                }
+                if (HI && g + 8 < R) {
+                    dstp[(2 * t4) * MK_MAX_ROWS + g + 8] = acc[2];
+                    dstp[(2 * t4 + 1) * MK_MAX_ROWS + g + 8] = acc[3];
+                }
+            }
+            __syncthreads();
+            if (tr) tr[2] = clock64();
+
+            // ---- epilogue: one thread per (local panel, row pair, batch row); k-splits summed in fixed order ----
+            const int slot0 = base >> ksh, n_slots = (round_end - base) >> ksh;
+            for (int o = threadIdx.x; o < n_slots * 4 * RP; o += kThreads) {
+                const int r = o & (RP - 1);
+                const int pi = o / RP, slot = slot0 + (pi >> 2), i = pi & 3;
+                if (r >= R) continue;
+                float v0 = 0.f, v1 = 0.f;
+                for (int s = 0; s < ks; ++s) {
+                    const float* src = spart + (size_t)((slot - slot0) * ks + s) * kPartStride;
+                    v0 += src[(2 * i) * MK_MAX_ROWS + r];
+                    v1 += src[(2 * i + 1) * MK_MAX_ROWS + r];
+                }
+                const int panel = blockIdx.x + gridDim.x * slot;
+                if (ph.kind == MK_QKV) {
+                    const int hd = p.head_dim, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
+                    const int ppb = half >> 2;  // panels per head
+                    const int head = panel / ppb, jj = (panel - head * ppb) * 4 + i;
+                    const int m = head < H ? 0 : (head < H + KV ? 1 : 2);
+                    const int hl = head - (m == 0 ? 0 : (m == 1 ? H : H + KV));
+                    const int row0 = hl * hd + jj;
+                    const void* bias = m == 0 ? L->bq : (m == 1 ? L->bk : L->bv);
+                    v0 = bf16_round(v0 + (bias ? ldf(bias, row0) : 0.f));
+                    v1 = bf16_round(v1 + (bias ? ldf(bias, row0 + half) : 0.f));
+                    if (p.rope && m != 2) {
+                        const float cs = bf16_round(srope[r * hd + jj]);
+                        const float sn = bf16_round(srope[r * hd + half + jj]);
+                        const float o0 = bf16_round(bf16_round(v0 * cs) + bf16_round(-v1 * sn));
+                        const float o1 = bf16_round(bf16_round(v1 * cs) + bf16_round(v0 * sn));
+                        v0 = o0;
+                        v1 = o1;
+                    }
+                    if (m == 0) {
+                        bf16* q = static_cast<bf16*>(p.q) + (size_t)r * H * hd + row0;
+                        q[0] = __float2bfloat16_rn(v0);
+                        q[half] = __float2bfloat16_rn(v1);
+                    } else {
+                        const int page = sc.page[r], off = sc.off[r];
+                        bf16* pool = static_cast<bf16*>(m == 1 ? L->kpool : L->vpool);
+                        bf16* dst = pool + ((((size_t)page * KV + hl) << p.page_shift) + off) * hd + jj;
+                        dst[0] = __float2bfloat16_rn(v0);
+                        dst[half] = __float2bfloat16_rn(v1);
+                    }
+                } else if (ph.kind == MK_GATEUP) {
+                    const int n = panel * 4 + i;
+                    const float gg = bf16_round(v0), uu = bf16_round(v1);
+                    static_cast<bf16*>(p.act)[(size_t)r * ph.n0 + n] = __float2bfloat16_rn(bf16_round(silu_f(gg)) * uu);
+                } else {
+                    const int n = panel * 8 + 2 * i;  // rows n, n+1
+                    if (n >= ph.n0) continue;
+                    const bool valid1 = n + 1 < ph.n0;
+                    if (ph.kind == MK_FC_GELU) {
+                        bf16* y = static_cast<bf16*>(p.act) + (size_t)r * ph.n0 + n;
+                        y[0] = __float2bfloat16_rn(gelu_new_f(bf16_round(v0 + (L->b_up ? ldf(L->b_up, n) : 0.f))));
+                        if (valid1) y[1] = __float2bfloat16_rn(gelu_new_f(bf16_round(v1 + (L->b_up ? ldf(L->b_up, n + 1) : 0.f))));
+                    } else if (ph.kind == MK_OPROJ || ph.kind == MK_DOWN) {
+                        const void* bias = ph.kind == MK_OPROJ ? L->bo : L->b_down;
+                        bf16* y = static_cast<bf16*>(p.h) + (size_t)r * ph.n0 + n;
+                        const uint32_t old = (o == (int)threadIdx.x && base == 0) ? old_pref : __ldcg(reinterpret_cast<const uint32_t*>(y));  // two bf16 of the residual
+                        v0 = bf16_round(v0 + (bias ? ldf(bias, n) : 0.f)) + __uint_as_float(old << 16);
+                        v1 = bf16_round(v1 + (bias ? ldf(bias, n + 1) : 0.f)) + __uint_as_float(old & 0xffff0000u);
+                        *reinterpret_cast<__nv_bfloat162*>(y) = __floats2bfloat162_rn(v0, v1);
+                    } else {  // MK_HEAD: logits in the model dtype, argmax = first index of the maximum
+                        v0 = bf16_round(v0);
+                        v1 = bf16_round(v1);
+                        if (p.logits) {
+                            float* lg = p.logits + (size_t)r * ph.n0 + n;
+                            lg[0] = v0;
+                            if (valid1) lg[1] = v1;
+                        }
+                        arg_update(best, v0, n);
+                        if (valid1) arg_update(best, v1, n + 1);
+                    }
+                }
+            }
+
+            __syncthreads();  // the partial buffer is reused by the next round
+            }  // rounds
+
+            if (ph.kind == MK_QKV && phi + 1 < p.n_phases && phases[phi + 1].kind == MK_ATTN) {
+                // prefetch the old K/V rows of this CTA's first attention tile before the barrier
+                const int n_units = R * p.n_kv_heads * p.n_splits;
+                if ((int)blockIdx.x < n_units) {
+                    const AttnUnit a = attn_unit(p, sc, blockIdx.x);
+                    const int tend = min(a.t1, a.t0 + kTT);
+                    const int upto = max(a.t0, min(tend, attn_safe_end(sc, a)));
+                    if (upto > a.t0) attn_load_rows(p, *L, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto);
+                }
+            }
+
+            if (tr) tr[3] = clock64();
+            if (ph.kind == MK_HEAD) {
+                // thread -> batch row (o & (RP-1)) is fixed: reduce over the lanes that share it, then warps, then CTAs
+                for (int off = RP; off < 32; off <<= 1) {
+                    const float ov = __shfl_xor_sync(0xffffffffu, best.val, off);
+                    const int oi = __shfl_xor_sync(0xffffffffu, best.idx, off);
+                    arg_update(best, ov, oi);
+                }
+                if (lane < RP && lane < MK_MAX_ROWS) {
+                    s_val[warp][lane] = best.val;
+                    s_idx[warp][lane] = best.idx;
+                }
+                __syncthreads();
+                if ((int)threadIdx.x < R) {
+                    ArgBest b = {-FLT_MAX, INT_MAX};
+                    for (int w = 0; w < kWarps; ++w) arg_update(b, s_val[w][threadIdx.x], s_idx[w][threadIdx.x]);
+                    p.arg_val[(size_t)blockIdx.x * R + threadIdx.x] = b.val;
+                    p.arg_idx[(size_t)blockIdx.x * R + threadIdx.x] = b.idx;
+                }
+                __threadfence();
+                __syncthreads();
+                if (threadIdx.x == 0) s_last = (atomicAdd(p.arg_counter, 1u) == gridDim.x - 1);
+                __syncthreads();
+                if (s_last) {
+                    __threadfence();
+                    for (int r = warp; r < R; r += kWarps) {
+                        ArgBest b = {-FLT_MAX, INT_MAX};
+                        for (int gi = lane; gi < (int)gridDim.x; gi += 32)
+                            arg_update(b, __ldcg(p.arg_val + (size_t)gi * R + r), __ldcg(p.arg_idx + (size_t)gi * R + r));
+#pragma unroll
+                        for (int off = 16; off > 0; off >>= 1) {
+                            const float ov = __shfl_xor_sync(0xffffffffu, b.val, off);
+                            const int oi = __shfl_xor_sync(0xffffffffu, b.idx, off);
+                            arg_update(b, ov, oi);
+                        }
+                        if (lane == 0) {
+                            p.next_token[r] = b.idx;
+                            if (p.advance) {
+                                p.ids[r] = b.idx;
+                                p.pos[r] = ldcg_i32(p.pos + r) + 1;
+                                p.tok_ring[(size_t)(p.tok_base + step) * R + r] = b.idx;
+                            }
+                        }
+                    }
+                    if (threadIdx.x == 0) *p.arg_counter = 0u;
+                    __threadfence();
+                }
+            }
+        }
+    }
+
+    // leave the barrier words at zero for the next launch: the last CTA out resets them
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(p.done, 1u) == gridDim.x - 1) {
+            *p.barrier = 0u;
+            *p.done = 0u;
+            __threadfence();
+        }
+    }
+}
+
+// ---- weight packer -----------------------------------------------------------------------------------------
+// dst[panel][k/8][row r][8]  <-  source row chosen by `kind` (see megakernel.h); rows past n0 are zero.
+__global__ void pack_panels_kernel(const PackJob j) {
+    const int kc_n = j.K >> 3;
+    const size_t total = (size_t)j.n_panels * kc_n * 8;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int r = (int)(i & 7);
+        const int kc = (int)((i >> 3) % kc_n);
+        const int panel = (int)(i / ((size_t)kc_n * 8));
+        const bf16* src = nullptr;
+        if (j.kind == MK_QKV) {
+            const int hd = j.head_dim, half = hd >> 1, ppb = half >> 2;
+            const int head = panel / ppb, jj = (panel - head * ppb) * 4 + (r >> 1) + (r & 1) * half;
+            const int m = head < j.n_heads ? 0 : (head < j.n_heads + j.n_kv_heads ? 1 : 2);
+            const int hl = head - (m == 0 ? 0 : (m == 1 ? j.n_heads : j.n_heads + j.n_kv_heads));
+            src = static_cast<const bf16*>(j.src[m]) + (size_t)(hl * hd + jj) * j.K;
+        } else if (j.kind == MK_GATEUP) {
+            src = static_cast<const bf16*>(j.src[r & 1]) + (size_t)(panel * 4 + (r >> 1)) * j.K;
+        } else {
+            const int row = panel * 8 + r;
+            if (row < j.n0) src = static_cast<const bf16*>(j.src[0]) + (size_t)row * j.K;
+        }
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (src) v = *reinterpret_cast<const uint4*>(src + (size_t)kc * 8);
+        uint32_t sbytes;
+        // inside a stage: [32-k block][row][4 chunks of 8 k]: the 32 lanes of a warp read 512 contiguous bytes
+        const size_t off = mk_stage_offset(j.n_panels, j.K, panel, kc >> 5, &sbytes) + (size_t)((kc & 31) >> 2) * 512 + r * 64 + (kc & 3) * 16;
+        *reinterpret_cast<uint4*>(static_cast<unsigned char*>(j.dst) + off) = v;
+    }
+}
+
+}  // namespace
+
+// ---- host side -------------------------------------------------------------------------------------------
+
+size_t mk_packed_bytes(int n_panels, int K) { return (size_t)n_panels * K * 16; }
+
+cudaError_t launch_pack(const PackJob& job, cudaStream_t st) {
+    if (job.K % 8 || job.n_panels <= 0) return cudaErrorInvalidValue;
+    pack_panels_kernel<<<1184, 256, 0, st>>>(job);
+    count_launch();
+    return cudaGetLastError();
+}
+
+size_t mk_smem_bytes(const MkParams& p, int stages) {
+    auto up = [](size_t v) { return (v + 127) / 128 * 128; };
+    size_t b = up((size_t)p.n_phases * sizeof(MkPhase));
+    b += up((size_t)kWarps * stages * 8);
+    b += up((size_t)p.n_rows * (p.k_max + 8) * 2);
+    b += (size_t)p.part_units * kPartStride * 4;
+    b += (size_t)p.n_rows * p.head_dim * 4;
+    b += (size_t)((p.n_rows * p.pages_per_seq * 4 + 15) / 16) * 16;
+    b += (size_t)2 * kTT * (p.head_dim + 8) * 2 + kMaxGq * kTT * 4 + (size_t)kMaxGq * p.head_dim * 4;
+    b = up(b) + 128;
+    b += (size_t)kWarps * stages * kStageBytes;
+    return b;
+}
+
+static int mk_pick_stages(const MkParams& p) {
+    for (int s = 6; s >= 2; --s)
+        if (mk_smem_bytes(p, s) <= (size_t)(227 * 1024 - 1536)) return s;
+    return 0;
+}
+
+template <bool HI>
+static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStream_t st) {
+    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;  // all CTAs co-resident: the grid barrier cannot deadlock
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI>, p);
+    count_launch();
+    return e;
+}
+
+cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStream_t st) {
+    MkParams p = p_in;
+    if (!mk_supported(p.n_rows, p.n_heads, p.n_kv_heads, p.head_dim)) return cudaErrorInvalidValue;
+    if (p.n_splits < 1 || p.n_splits > kMaxSplits || p.n_phases > MK_MAX_PHASES) return cudaErrorInvalidValue;
+    if ((size_t)p.n_rows * p.n_heads * p.n_splits * 8 > (size_t)2 * kTT * (p.head_dim + 8) * 2) return cudaErrorInvalidValue;  // merge scratch
+    p.stages = mk_pick_stages(p);
+    if (p.stages == 0) return cudaErrorInvalidValue;
+    const size_t smem = mk_smem_bytes(p, p.stages);
+    return p.n_rows > 8 ? mk_launch_t<true>(p, num_sms, smem, st) : mk_launch_t<false>(p, num_sms, smem, st);
+}
+
+int mk_max_splits(int n_rows, int n_heads, int head_dim) {
+    const size_t scratch = (size_t)2 * kTT * (head_dim + 8) * 2;  // the K/V tile buffers double as merge scratch
+    const long s = (long)(scratch / ((size_t)n_rows * n_heads * 8));
+    return (int)(s > kMaxSplits ? kMaxSplits : s);
+}
+
+bool mk_supported(int n_rows, int n_heads, int n_kv_heads, int head_dim) {
+    return n_rows >= 1 && n_rows <= MK_MAX_ROWS && n_heads % n_kv_heads == 0 && n_heads / n_kv_heads <= kMaxGq &&
+           (head_dim == 32 || head_dim == 64 || head_dim == 128);
+}
+
+}  // namespace dllm

@@ -1,0 +1,106 @@
+// Parameters of the persistent decode kernel (decode_megakernel.cu) and of the weight packer.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace dllm {
+
+constexpr int MK_THREADS = 384;
+constexpr int MK_STAGE_K = 256;                    // k-elements of one stage
+constexpr int MK_STAGE_BYTES = 8 * MK_STAGE_K * 2; // one stage = 8 weight rows x 256 k, bf16 = 4 KB
+constexpr int MK_MAX_ROWS = 16;
+constexpr int MK_MAX_SPLITS = 8;   // one batch of eight 16-byte loads per thread in the merge
+constexpr int MK_MAX_PHASES = 512;  // 5 per layer + 2: up to 102 layers per stage
+
+enum MkKind { MK_EMBED = 0, MK_QKV, MK_ATTN, MK_OPROJ, MK_GATEUP, MK_FC_GELU, MK_DOWN, MK_HEAD };
+
+// Weights are streamed from a packed copy owned by the shard handle:
+//   panel  = 8 weight rows; for the paired kinds (QKV rotary pairs, gate/up) rows (2i, 2i+1) of a panel are
+//            the two rows of pair i, so that one thread of the epilogue sees both
+//   layout = [panel][k / 32][row 0..7][32 elements]: every 256-k slice of a panel is 4 KB contiguous (one TMA
+//            bulk copy = one ring stage) and, inside a stage, the 16-byte chunks a warp reads per mma are
+//            512 contiguous bytes (bank-conflict free).  It is also the no-swizzle UMMA core-matrix order.
+struct MkPhase {
+    const void* wp;      // packed weights of this phase (null for EMBED / ATTN)
+    int32_t n_panels;
+    int32_t K;
+    int32_t n0;          // logical output rows (un-padded)
+    int16_t kind;        // MkKind
+    int16_t layer;
+    int16_t ksplit;      // warps of one CTA that share a panel (split along K, summed in fixed order)
+    int16_t n_stages;    // ceil(K / 256)
+};
+
+struct MkLayer {
+    const void *norm1_w, *norm1_b, *bq, *bk, *bv, *bo, *norm2_w, *norm2_b, *b_up, *b_down;
+    void *kpool, *vpool;
+};
+
+struct MkParams {
+    const MkPhase* phases;   // device array, n_phases entries = one decode step
+    const MkLayer* layers;   // device array
+    int32_t n_phases, n_steps, n_rows;
+    int32_t hidden, n_heads, n_kv_heads, head_dim, vocab, k_max;
+    int32_t norm, rope, stages, n_splits, advance, tok_base, part_units;
+    float eps;
+    void* h;                 // [R, d] residual stream
+    void* q;                 // [R, H*hd]
+    void* act;               // [R, ffn]
+    void* attn_out;          // [R, H*hd] merged attention output
+    unsigned* attn_counters; // [R, KV] tickets, zero between phases
+    float* part_o;           // [R, H, S, hd]
+    float* part_ml;          // [R, H, S, 2]
+    float* logits;           // [R, V] or null
+    float* arg_val;          // [grid, R]
+    int32_t* arg_idx;        // [grid, R]
+    int32_t* next_token;     // [R]
+    int32_t* ids;            // [R]
+    int32_t* pos;            // [R]
+    const int32_t* seq;      // [R]
+    int32_t* tok_ring;
+    const int32_t* block_table;
+    int32_t pages_per_seq, page_shift;
+    const void *wte, *wpe, *final_norm_w, *final_norm_b;
+    const float *rope_cos, *rope_sin;
+    unsigned *barrier, *done, *arg_counter;  // zero between launches
+    int32_t prefetch_kb;     // KB per warp of the NEXT phase pulled into L2 at each phase start (0 = off)
+    long long* trace;        // optional [n_steps][n_phases][4] SM-clock stamps of CTA 0 (debug, DLLM_MK_TRACE)
+};
+
+// Packed layout, panel-major: a panel's stages are consecutive, so any k-range of a panel (one warp unit) is
+// one contiguous run -- a single L2 prefetch instruction covers it.
+__host__ __device__ inline size_t mk_stage_offset(int n_panels, int K, int panel, int st, uint32_t* bytes) {
+    (void)n_panels;
+    const size_t panel_bytes = (size_t)K * 16;
+    const size_t off = (size_t)st * MK_STAGE_BYTES;
+    const size_t left = panel_bytes - off;
+    *bytes = (uint32_t)(left < (size_t)MK_STAGE_BYTES ? left : (size_t)MK_STAGE_BYTES);
+    return (size_t)panel * panel_bytes + off;
+}
+
+// geometry helpers shared by host and device
+__host__ __device__ inline int mk_ksplit(int n_panels, int n_stages, int grid) {
+    const int per_cta = (n_panels + grid - 1) / grid;
+    const int want = (MK_THREADS / 32 + per_cta - 1) / per_cta;  // enough units to keep every warp of the CTA busy
+    int ks = 1;
+    while (ks < want && ks < 8 && ks * 2 <= n_stages) ks *= 2;   // power of two: the kernel splits with shifts
+    return ks;
+}
+
+// packer: kind selects the row order (QKV pairs, gate/up pairs, plain)
+struct PackJob {
+    const void* src[3];   // QKV: wq, wk, wv;  GATEUP: gate, up;  else: w
+    void* dst;
+    int32_t kind, n_panels, K, n0;
+    int32_t n_heads, n_kv_heads, head_dim;
+};
+size_t mk_packed_bytes(int n_panels, int K);
+cudaError_t launch_pack(const PackJob& job, cudaStream_t st);
+
+bool mk_supported(int n_rows, int n_heads, int n_kv_heads, int head_dim);
+size_t mk_smem_bytes(const MkParams& p, int stages);
+int mk_max_splits(int n_rows, int n_heads, int head_dim);  // largest split count the combine scratch allows
+cudaError_t launch_decode_megakernel(const MkParams& p, int num_sms, cudaStream_t st);
+
+}  // namespace dllm

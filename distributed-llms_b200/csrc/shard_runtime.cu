@@ -5,12 +5,16 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <stdlib.h>
+
+#include <algorithm>
 #include <map>
 #include <string>
 #include <vector>
 
 #include "../../include/dllm_b200.h"
 #include "kernels.h"
+#include "megakernel.h"
 
 using namespace dllm;
 
@@ -79,6 +83,13 @@ struct dllm_shard {
     float *part_o = nullptr, *part_ml = nullptr, *arg_val = nullptr;
     int32_t* arg_idx = nullptr;
     uint32_t *attn_counters = nullptr, *arg_counter = nullptr;
+    // persistent decode kernel (bf16, <= 4 rows)
+    MkPhase* mk_phases = nullptr;
+    MkLayer* mk_layers = nullptr;
+    unsigned* mk_sync = nullptr;  // [0] barrier, [1] done, [2] argmax ticket
+    void* mk_packed = nullptr;    // streaming-layout copy of the weights (megakernel.h)
+    int mk_n_phases = 0, mk_k_max = 0, mk_part_units = 1;
+    bool mk_enabled = false, mk_packed_ok = false;
     std::vector<void*> kpool, vpool;
     // geometry
     int pages_per_seq = 0, page_shift = 0, num_pages = 0, max_logit_rows = 0, arg_grid_cap = 0;
@@ -174,6 +185,26 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->arg_idx, (size_t)s->arg_grid_cap * c.max_rows * 4);
     add(&s->attn_counters, (size_t)c.max_rows * c.n_heads * 4);
     add(&s->arg_counter, 4);
+    const int mk_phase_cap = 5 * c.n_layers + 2;
+    add(&s->mk_phases, (size_t)mk_phase_cap * sizeof(MkPhase));
+    add(&s->mk_layers, (size_t)(c.n_layers > 0 ? c.n_layers : 1) * sizeof(MkLayer));
+    add(&s->mk_sync, 16);
+    {   // the persistent decode kernel streams a packed copy of the weights (bf16, every K a multiple of 32)
+        const char* env = getenv("DLLM_MEGAKERNEL");
+        const int Hdd = c.n_heads * c.head_dim;
+        s->mk_packed_ok = c.dtype == DLLM_DTYPE_BF16 && c.n_layers > 0 && !(env && env[0] == '0') &&
+                          c.hidden % 32 == 0 && Hdd % 32 == 0 && c.ffn % 32 == 0 && c.n_heads / c.n_kv_heads <= 8;
+        size_t pb = 0;
+        if (s->mk_packed_ok) {
+            const bool g2 = c.arch == DLLM_ARCH_GPT2;
+            const size_t per_layer = align_up(mk_packed_bytes((c.n_heads + 2 * c.n_kv_heads) * (c.head_dim / 8), c.hidden), 256) +
+                                     align_up(mk_packed_bytes(c.hidden / 8, Hdd), 256) +
+                                     align_up(mk_packed_bytes(g2 ? c.ffn / 8 : c.ffn / 4, c.hidden), 256) +
+                                     align_up(mk_packed_bytes(c.hidden / 8, c.ffn), 256);
+            pb = per_layer * c.n_layers + (c.has_head ? align_up(mk_packed_bytes((c.vocab + 7) / 8, c.hidden), 256) : 0);
+        }
+        add(&s->mk_packed, pb);
+    }
     const size_t kv_layer = (size_t)s->num_pages * c.n_kv_heads * c.page_size * c.head_dim * s->esz;
     s->kpool.resize(c.n_layers);
     s->vpool.resize(c.n_layers);
@@ -213,6 +244,57 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
         return fail(m);
     }
     memset(s->h_bt_row, 0xff, (size_t)c.max_seqs * s->pages_per_seq * 4);
+    if (s->mk_packed_ok) {
+        // packed streaming copy of the weights + phase list of one decode step for the persistent kernel
+        const bool gpt2 = c.arch == DLLM_ARCH_GPT2;
+        const int Hd = c.n_heads * c.head_dim;
+        const int G = s->num_sms;
+        std::vector<MkPhase> ph;
+        std::vector<MkLayer> ly(c.n_layers > 0 ? c.n_layers : 1);
+        char* pk = (char*)s->mk_packed;
+        cudaError_t me = cudaSuccess;
+        int part_units = 1;
+        auto weight_phase = [&](int kind, int layer, int n_panels, int K, int n0, const void* w0, const void* w1, const void* w2) {
+            PackJob job{};
+            job.src[0] = w0; job.src[1] = w1; job.src[2] = w2;
+            job.dst = pk; job.kind = kind; job.n_panels = n_panels; job.K = K; job.n0 = n0;
+            job.n_heads = c.n_heads; job.n_kv_heads = c.n_kv_heads; job.head_dim = c.head_dim;
+            if (me == cudaSuccess) me = launch_pack(job, 0);
+            MkPhase q{};
+            q.wp = pk; q.n_panels = n_panels; q.K = K; q.n0 = n0; q.kind = (int16_t)kind; q.layer = (int16_t)layer;
+            q.n_stages = (int16_t)((K + MK_STAGE_K - 1) / MK_STAGE_K);
+            q.ksplit = (int16_t)mk_ksplit(n_panels, q.n_stages, G);
+            part_units = std::max(part_units, ((n_panels + G - 1) / G) * (int)q.ksplit);
+            ph.push_back(q);
+            pk += align_up(mk_packed_bytes(n_panels, K), 256);
+        };
+        auto plain_phase = [&](int kind, int layer) {
+            MkPhase q{};
+            q.kind = (int16_t)kind; q.layer = (int16_t)layer; q.ksplit = 1; q.n_stages = 1;
+            ph.push_back(q);
+        };
+        if (c.has_embed) plain_phase(MK_EMBED, 0);
+        for (int l = 0; l < c.n_layers; ++l) {
+            const dllm_layer_weights& w = s->layers[l];
+            ly[l] = MkLayer{w.norm1_w, w.norm1_b, w.bq, w.bk, w.bv, w.bo, w.norm2_w, w.norm2_b, w.b_up, w.b_down,
+                            s->kpool[l], s->vpool[l]};
+            weight_phase(MK_QKV, l, (c.n_heads + 2 * c.n_kv_heads) * (c.head_dim / 8), c.hidden, Hd, w.wq, w.wk, w.wv);
+            plain_phase(MK_ATTN, l);
+            weight_phase(MK_OPROJ, l, c.hidden / 8, Hd, c.hidden, w.wo, nullptr, nullptr);
+            if (gpt2) weight_phase(MK_FC_GELU, l, c.ffn / 8, c.hidden, c.ffn, w.w_up, nullptr, nullptr);
+            else weight_phase(MK_GATEUP, l, c.ffn / 4, c.hidden, c.ffn, w.w_gate, w.w_up, nullptr);
+            weight_phase(MK_DOWN, l, c.hidden / 8, c.ffn, c.hidden, w.w_down, nullptr, nullptr);
+        }
+        if (c.has_head) weight_phase(MK_HEAD, 0, (c.vocab + 7) / 8, c.hidden, c.vocab, s->io.lm_head, nullptr, nullptr);
+        s->mk_n_phases = (int)ph.size();
+        s->mk_part_units = std::min(part_units, 24);  // rounds of 24 units (multiple of the warp count and of every k-split)
+        s->mk_k_max = std::max(std::max(c.hidden, Hd), c.ffn);
+        if (me == cudaSuccess) me = cudaMemcpy(s->mk_phases, ph.data(), ph.size() * sizeof(MkPhase), cudaMemcpyHostToDevice);
+        if (me == cudaSuccess) me = cudaMemcpy(s->mk_layers, ly.data(), ly.size() * sizeof(MkLayer), cudaMemcpyHostToDevice);
+        if (me == cudaSuccess) me = cudaDeviceSynchronize();
+        s->mk_enabled = me == cudaSuccess;
+        cudaGetLastError();
+    }
     s->free_pages.resize(s->num_pages);
     for (int i = 0; i < s->num_pages; ++i) s->free_pages[i] = s->num_pages - 1 - i;  // pop_back hands out 0,1,2,...
     s->seq_pages.resize(c.max_seqs);
@@ -353,6 +435,76 @@ static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advanc
     return 0;
 }
 
+// One launch of the persistent decode kernel for `n_steps` steps (bf16, <= 4 rows, logits for every row).
+static bool mk_eligible(const dllm_shard* s, int n_rows, int n_logit_rows, bool identity_rows) {
+    if (!s->mk_enabled || !mk_supported(n_rows, s->cfg.n_heads, s->cfg.n_kv_heads, s->cfg.head_dim)) return false;
+    if (mk_max_splits(n_rows, s->cfg.n_heads, s->cfg.head_dim) < 1) return false;
+    {   // the rows' inputs must fit in shared memory next to at least two ring stages per warp
+        MkParams q{};
+        q.n_phases = s->mk_n_phases; q.n_rows = n_rows; q.k_max = s->mk_k_max; q.part_units = s->mk_part_units;
+        q.head_dim = s->cfg.head_dim; q.pages_per_seq = s->pages_per_seq;
+        if (mk_smem_bytes(q, 2) > (size_t)(227 * 1024 - 1536)) return false;
+    }
+    if (s->cfg.has_head && !(identity_rows && n_logit_rows == n_rows)) return false;
+    return true;
+}
+
+static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, cudaStream_t st) {
+    const dllm_shard_config& c = s->cfg;
+    MkParams p{};
+    p.phases = s->mk_phases; p.layers = s->mk_layers; p.n_phases = s->mk_n_phases;
+    p.n_steps = n_steps; p.n_rows = n_rows;
+    p.hidden = c.hidden; p.n_heads = c.n_heads; p.n_kv_heads = c.n_kv_heads; p.head_dim = c.head_dim;
+    p.vocab = c.vocab; p.k_max = s->mk_k_max;
+    p.norm = c.arch == DLLM_ARCH_GPT2 ? NORM_LAYER : NORM_RMS; p.rope = c.arch != DLLM_ARCH_GPT2;
+    long S = (s->num_sms + (long)n_rows * c.n_kv_heads - 1) / ((long)n_rows * c.n_kv_heads);
+    const long s_cap = mk_max_splits(n_rows, c.n_heads, c.head_dim);
+    if (S > s_cap) S = s_cap;
+    while (S > 1 && (long)n_rows * c.n_heads * S > s->max_partials) --S;
+    if (const char* e = getenv("DLLM_MK_SPLITS")) { long v = atol(e); if (v >= 1 && v <= s_cap && (long)n_rows * c.n_heads * v <= s->max_partials) S = v; }
+    p.part_units = s->mk_part_units;
+    p.attn_out = s->attn_out; p.attn_counters = s->attn_counters;
+    p.prefetch_kb = 32;
+    if (const char* e = getenv("DLLM_MK_PREFETCH_KB")) { long v = atol(e); if (v >= 0 && v <= 1024) p.prefetch_kb = (int)v; }
+    p.n_splits = (int)S; p.advance = advance ? 1 : 0; p.tok_base = 0; p.eps = c.norm_eps;
+    p.h = s->h; p.q = s->qbuf; p.act = s->act; p.part_o = s->part_o; p.part_ml = s->part_ml;
+    p.logits = c.has_head ? s->logits : nullptr; p.arg_val = s->arg_val; p.arg_idx = s->arg_idx;
+    p.next_token = s->next_tok; p.ids = s->ids; p.pos = s->pos; p.seq = s->seq; p.tok_ring = s->tok_ring;
+    p.block_table = s->block_table; p.pages_per_seq = s->pages_per_seq; p.page_shift = s->page_shift;
+    p.wte = s->io.wte; p.wpe = c.arch == DLLM_ARCH_GPT2 ? s->io.wpe : nullptr;
+    p.final_norm_w = s->io.final_norm_w; p.final_norm_b = s->io.final_norm_b;
+    p.rope_cos = s->io.rope_cos; p.rope_sin = s->io.rope_sin;
+    p.barrier = s->mk_sync; p.done = s->mk_sync + 1; p.arg_counter = s->mk_sync + 2;
+    if (s->num_sms > s->arg_grid_cap) return fail("internal: argmax scratch too small for the persistent kernel");
+    const char* trace_path = getenv("DLLM_MK_TRACE");
+    long long* d_trace = nullptr;
+    const size_t trace_n = (size_t)n_steps * s->mk_n_phases * 8;
+    if (trace_path && n_steps > 1) {  // debug: per-phase SM-clock stamps of CTA 0, dumped after a device sync
+        CUDA_TRY(cudaMalloc((void**)&d_trace, trace_n * 8));
+        CUDA_TRY(cudaMemsetAsync(d_trace, 0, trace_n * 8, st));
+        p.trace = d_trace;
+    }
+    CUDA_TRY(launch_decode_megakernel(p, s->num_sms, st));
+    if (d_trace) {
+        std::vector<long long> h(trace_n);
+        CUDA_TRY(cudaStreamSynchronize(st));
+        CUDA_TRY(cudaMemcpy(h.data(), d_trace, trace_n * 8, cudaMemcpyDeviceToHost));
+        cudaFree(d_trace);
+        std::vector<MkPhase> ph(s->mk_n_phases);
+        CUDA_TRY(cudaMemcpy(ph.data(), s->mk_phases, ph.size() * sizeof(MkPhase), cudaMemcpyDeviceToHost));
+        if (FILE* f = fopen(trace_path, "w")) {
+            fprintf(f, "step,phase,kind,layer,t_start,t_prologue,t_main,t_epilogue,c_wait,c_mma,c_issue,n_stages\n");
+            for (int i = 0; i < n_steps; ++i)
+                for (int j = 0; j < s->mk_n_phases; ++j) {
+                    const long long* t = &h[((size_t)i * s->mk_n_phases + j) * 8];
+                    fprintf(f, "%d,%d,%d,%d,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld\n", i, j, (int)ph[j].kind, (int)ph[j].layer, t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7]);
+                }
+            fclose(f);
+        }
+    }
+    return 0;
+}
+
 // Replay (capturing on first use) the graph of one step; large row counts launch directly.
 static int run_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advance, cudaStream_t st) {
     constexpr int kGraphMaxRows = 64;
@@ -413,7 +565,11 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
             CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
         }
     }
-    if (run_step(s, n_rows, nl, false, st)) return 1;
+    if (mk_eligible(s, n_rows, nl, logit_rows == nullptr)) {
+        if (run_megakernel(s, n_rows, 1, false, st)) return 1;
+    } else if (run_step(s, n_rows, nl, false, st)) {
+        return 1;
+    }
     if (hidden_out) CUDA_TRY(cudaMemcpyAsync(hidden_out, s->h, (size_t)n_rows * c.hidden * s->esz, cudaMemcpyDefault, st));
     if (c.has_head && logits_out)
         CUDA_TRY(cudaMemcpyAsync(logits_out, s->logits, (size_t)nl * c.vocab * 4, cudaMemcpyDefault, st));
@@ -435,8 +591,12 @@ extern "C" int dllm_shard_decode_loop(dllm_shard* s, int32_t n_rows, int32_t n_s
     if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
     CUDA_TRY(launch_decode_begin(s->ids, s->pos, s->seq, s->next_tok, s->logit_rows, n_rows, s->step_ctr, st));
     CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)n_rows * 4, cudaMemcpyDeviceToDevice, st));
-    for (int i = 0; i < n_steps; ++i)
-        if (run_step(s, n_rows, n_rows, true, st)) return 1;
+    if (mk_eligible(s, n_rows, n_rows, true)) {
+        if (run_megakernel(s, n_rows, n_steps, true, st)) return 1;
+    } else {
+        for (int i = 0; i < n_steps; ++i)
+            if (run_step(s, n_rows, n_rows, true, st)) return 1;
+    }
     if (tokens_out)
         CUDA_TRY(cudaMemcpyAsync(tokens_out, s->tok_ring, (size_t)n_steps * n_rows * 4, cudaMemcpyDefault, st));
     return 0;

@@ -261,12 +261,13 @@ class ShardExecutor:
                 if hidden_out is not None:
                     hc = hidden_out if n == T else torch.empty(B, n, g.hidden, dtype=self.dtype, device=self.device)
                 lr = None
-                if self.has_head and last and want_logits:
+                emit = self.has_head and last and want_logits
+                if emit and n > 1:  # logits of the last position of every row (n == 1: every row, the default)
                     lr = (torch.arange(B, dtype=torch.int32) * n + (n - 1)).contiguous()
                 cabi.check(L.dllm_shard_forward(
                     self._handle, xc.data_ptr(), pc.data_ptr(), sc.data_ptr(), B * n, _ptr(hc),
                     _ptr(lr), B if lr is not None else 0,
-                    _ptr(logits) if lr is not None else None, _ptr(next_tok) if lr is not None else None, st))
+                    _ptr(logits) if emit else None, _ptr(next_tok) if emit else None, st))
                 if hc is not None and hc is not hidden_out:
                     hidden_out[:, t0:t1] = hc
         self._last_seqs = [int(v) for v in seq_host]

@@ -24,6 +24,16 @@ def rel_err(a, b):
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 
+def bf16_logits_close(a, b):
+    """North-star bf16 tolerance (1e-2 relative to the largest |logit|), floored at two bf16 output ulps at that
+    scale: HF returns logits rounded to bf16, and with max|logit| < 1.6 one part in 100 is *less* than two
+    quanta of the compared values themselves, so a pure 1e-2 test would fail on output rounding alone."""
+    a, b = a.float().cpu(), b.float().cpu()
+    scale = float(b.abs().max())
+    ulp = 2.0 ** (torch.floor(torch.log2(torch.tensor(scale))).item() - 7)
+    return float((a - b).abs().max()) <= max(1e-2 * scale, 2 * ulp)
+
+
 def stream():
     return torch.cuda.current_stream().cuda_stream
 
@@ -175,8 +185,15 @@ def test_pipeline_matches_golden(name, tag, dtype, shards):
     sd = make_state_dict(cfg, 1234, torch.float32, init="full")
     stages = gpu_stages(cfg, sd, shards, dtype, max_rows=64, max_seqs=4, max_context=cfg.max_pos, page_size=8)
     ids, lg = gpu_generate(stages, g["prompts"], g["tokens"].shape[1])
-    err = max(rel_err(lg[:, t], g["logits"][:, t]) for t in range(lg.shape[1]))
-    assert err < TOL[dtype], err
+    if dtype == torch.float32:
+        err = max(rel_err(lg[:, t], g["logits"][:, t]) for t in range(lg.shape[1]))
+        assert err < TOL[dtype], err
+    else:
+        same = (ids == g["tokens"]).long().cumprod(1).bool()  # logits are comparable while the histories agree
+        for t in range(lg.shape[1]):
+            rows = same[:, t - 1] if t else torch.ones(ids.shape[0], dtype=torch.bool)
+            if rows.any():
+                assert bf16_logits_close(lg[rows, t], g["logits"][rows, t]), t
     if dtype == torch.float32:
         assert torch.equal(ids, g["tokens"])  # bit-identical greedy tokens
         hf = torch.load(os.path.join(GOLD, f"hf_{name}.pt"), weights_only=True)
@@ -222,7 +239,7 @@ def test_seeded_pipeline_against_live_oracle(dtype):
         for t in range(32):
             rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
             if rows.any():
-                assert rel_err(lg[rows, t], o_lg[rows, t]) < 1e-2
+                assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
         flips = (~same_prefix).float().argmax(1)
         for b in range(ids.shape[0]):
             if not same_prefix[b].all():
