@@ -10,7 +10,9 @@
 // the activation dtype after the dot product and again after scaling; probabilities stay fp32 here
 // (HF rounds them to bf16 before P@V -- documented difference, below bf16 output resolution).
 #include <float.h>
+#include <stdio.h>
 
+#include "../../include/dllm_b200.h"
 #include "common.cuh"
 #include "kernels.h"
 
@@ -159,3 +161,107 @@ cudaError_t launch_attn_decode(int dtype, const AttnParams& p, cudaStream_t s) {
 }
 
 }  // namespace dllm
+
+// ---- split-K attention without any allocation -------------------------------------------------------------
+//
+// dllm_op_decode_attention() needs a scratch buffer from its caller.  Some callers have no way to get one:
+// a host process that handed the whole GPU to its own memory pool (a foreign cudaMalloc fails there), or a
+// stage thread that must never stall the other stages sharing the device (cudaMalloc synchronises it).
+// For them the same kernel runs on a fixed scratch area that is part of the library image.
+//
+// The area is one file-scope __device__ array.  Each GPU that loads the library keeps its own copy of it until
+// the process exits.  In host code the name of the array is only a stand-in -- it is not a device address --
+// so the address is looked up once per device with cudaGetSymbolAddress(), while that device is current, and
+// that pointer is what the kernel receives.
+static __device__ __align__(256) unsigned char g_static_attn_scratch[DLLM_STATIC_ATTN_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
+
+size_t round_up_256(size_t v) { return (v + 255) / 256 * 256; }
+}  // namespace
+
+extern "C" int dllm_op_decode_attention_static(int32_t dtype, const void* d_q, const void* d_kpool, const void* d_vpool,
+                                               const int32_t* d_block_table, int32_t pages_per_seq, int32_t page_size,
+                                               const int32_t* d_positions, const int32_t* d_seq_ids, int32_t n_rows,
+                                               int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t n_splits,
+                                               void* d_out, void* stream) {
+    using dllm::set_last_error;
+    if (dtype != DLLM_DTYPE_BF16 && dtype != DLLM_DTYPE_F32) return set_last_error("dllm_op_decode_attention_static: bad dtype");
+    if (!d_q || !d_kpool || !d_vpool || !d_block_table || !d_positions || !d_seq_ids || !d_out)
+        return set_last_error("dllm_op_decode_attention_static: null pointer");
+    if (n_rows <= 0 || n_splits <= 0 || n_heads <= 0 || n_kv_heads <= 0 || n_heads % n_kv_heads)
+        return set_last_error("dllm_op_decode_attention_static: bad shape");
+    if (head_dim != 32 && head_dim != 64 && head_dim != 128)
+        return set_last_error("dllm_op_decode_attention_static: head_dim must be 32, 64 or 128");
+    if (page_size < 8 || (page_size & (page_size - 1)))
+        return set_last_error("dllm_op_decode_attention_static: page_size must be a power of two >= 8");
+    // same carve-up as dllm_op_decode_attention_scratch_bytes(): tickets | (m, l) pairs | partial outputs
+    const size_t rh = (size_t)n_rows * n_heads;
+    const size_t ticket_bytes = round_up_256(rh * 4);
+    const size_t ml_bytes = round_up_256(rh * n_splits * 2 * 4);
+    const size_t need = ticket_bytes + ml_bytes + round_up_256(rh * n_splits * head_dim * 4);
+    if (need > (size_t)DLLM_STATIC_ATTN_SCRATCH_BYTES) {
+        char msg[256];
+        snprintf(msg, sizeof msg,
+                 "dllm_op_decode_attention_static: this shape needs %zu bytes of scratch but the built-in area holds %d; "
+                 "use fewer splits or rows, or call dllm_op_decode_attention with your own buffer",
+                 need, (int)DLLM_STATIC_ATTN_SCRATCH_BYTES);
+        return set_last_error(msg);
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+        cudaGetLastError();
+        return set_last_error("dllm_op_decode_attention_static: no usable CUDA device (this library has no CPU path)");
+    }
+    if (!g_static_scratch_ptr[dev]) {
+        // first call on this device: resolve the device address of the array (see the note above)
+        void* ptr = nullptr;
+        e = cudaGetSymbolAddress((void**)&ptr, g_static_attn_scratch);
+        if (e != cudaSuccess || !ptr) {
+            cudaGetLastError();
+            char msg[200];
+            snprintf(msg, sizeof msg, "dllm_op_decode_attention_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return set_last_error(msg);
+        }
+        g_static_scratch_ptr[dev] = ptr;
+    }
+    char* base = static_cast<char*>(g_static_scratch_ptr[dev]);
+    cudaStream_t st = (cudaStream_t)stream;
+    // The area still holds whatever the previous call left.  Only the tickets have to start at zero; the
+    // partials are fully rewritten before they are read.
+    e = cudaMemsetAsync(base, 0, ticket_bytes, st);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return set_last_error("dllm_op_decode_attention_static: clearing the ticket counters failed");
+    }
+    dllm::AttnParams a{};
+    a.counters = reinterpret_cast<uint32_t*>(base);
+    a.part_ml = reinterpret_cast<float*>(base + ticket_bytes);
+    a.part_o = reinterpret_cast<float*>(base + ticket_bytes + ml_bytes);
+    a.q = d_q;
+    a.kv.kpool = const_cast<void*>(d_kpool);
+    a.kv.vpool = const_cast<void*>(d_vpool);
+    a.kv.block_table = d_block_table;
+    a.kv.pages_per_seq = pages_per_seq;
+    a.kv.page_shift = 0;
+    while ((1 << a.kv.page_shift) < page_size) ++a.kv.page_shift;
+    a.positions = d_positions;
+    a.seq_ids = d_seq_ids;
+    a.n_rows = n_rows;
+    a.n_heads = n_heads;
+    a.n_kv_heads = n_kv_heads;
+    a.head_dim = head_dim;
+    a.n_splits = n_splits;
+    a.out = d_out;
+    e = dllm::launch_attn_decode(dtype, a, st);
+    if (e != cudaSuccess) {
+        char msg[200];
+        snprintf(msg, sizeof msg, "dllm_op_decode_attention_static: launch failed: %s", cudaGetErrorString(e));
+        return set_last_error(msg);
+    }
+    return 0;
+}
+

@@ -88,6 +88,7 @@ cudaError_t launch_advance(int32_t* ids, int32_t* positions, const int32_t* next
 cudaError_t launch_legacy_matmul(const float* in, const float* param, float* out, int m, int k, int n,
                                  cudaStream_t s);
 
+int set_last_error(const char* msg);  // stores the message dllm_last_error() returns; always returns 1
 void count_launch(unsigned long long n = 1);
 unsigned long long launch_count();
 

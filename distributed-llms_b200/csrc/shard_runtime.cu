@@ -27,6 +27,8 @@ static int fail(const std::string& msg) {
     return 1;
 }
 
+int dllm::set_last_error(const char* msg) { return fail(msg ? msg : ""); }
+
 #define CUDA_TRY(expr)                                                                             \
     do {                                                                                           \
         cudaError_t _e = (expr);                                                                   \

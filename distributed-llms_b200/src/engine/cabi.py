@@ -58,6 +58,8 @@ SIGNATURES = {
     "dllm_op_decode_attention_scratch_bytes": (_sz, [_i32, _i32, _i32, _i32]),
     "dllm_op_decode_attention": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32,
                                            _i32, _vp, _vp, _vp]),
+    "dllm_op_decode_attention_static": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32,
+                                                  _i32, _vp, _vp]),
     "dllm_op_legacy_matmul": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
 }
 

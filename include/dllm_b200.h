@@ -191,6 +191,27 @@ DLLM_API int dllm_op_decode_attention(int32_t dtype, const void* d_q, const void
                              int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t n_splits,
                              void* d_scratch, void* d_out, void* stream);
 
+/* No counterpart in the reference.  The same split-K attention as dllm_op_decode_attention, for callers that
+ * cannot hand over a scratch buffer because they cannot allocate device memory at this point: a process whose
+ * own memory pool already owns the whole GPU (a cudaMalloc from outside the pool fails), or a stage thread that
+ * may not stall the other stages on the device (cudaMalloc synchronises it).  The scratch is a fixed area of
+ * DLLM_STATIC_ATTN_SCRATCH_BYTES inside the library image; every GPU that loads the library holds its own copy
+ * until the process exits.  Nothing is allocated or freed by this call.
+ *   - Shapes that need more than the area (tickets + (m,l) pairs + partial outputs, i.e. roughly
+ *     n_rows * n_heads * n_splits * (head_dim + 2) * 4 bytes) are refused with an error that names both sizes.
+ *   - The first call on a device looks up the device address of the area; make that first call outside any
+ *     stream capture.
+ *   - All calls share the one area and it keeps the last call's contents; the call clears the part that must
+ *     start at zero on `stream`.  Two calls that overlap on the GPU (different streams or threads) race on it:
+ *     serialise them.
+ * Arguments are those of dllm_op_decode_attention without d_scratch; inputs and output stay the caller's. */
+#define DLLM_STATIC_ATTN_SCRATCH_BYTES (4 * 1024 * 1024)
+DLLM_API int dllm_op_decode_attention_static(int32_t dtype, const void* d_q, const void* d_kpool, const void* d_vpool,
+                                    const int32_t* d_block_table, int32_t pages_per_seq, int32_t page_size,
+                                    const int32_t* d_positions, const int32_t* d_seq_ids, int32_t n_rows,
+                                    int32_t n_heads, int32_t n_kv_heads, int32_t head_dim, int32_t n_splits,
+                                    void* d_out, void* stream);
+
 /* The reference's shipped placeholder, kept so that its own tests run on the GPU: fp32
  * out[m, n] = sum_k in[m, k] * param[k, n] (`torch.matmul(inputs[key], parameters[key])`,
  * reference src/worker/node.py:31). Device pointers. */
