@@ -1,0 +1,69 @@
+"""Stage-to-stage hand-off of the hidden-state tile: the data plane that replaces pickled tensors over
+`MessageProtocol.send_message / receive_message` (reference src/network/protocol.py:38-129; reference
+src/worker/node.py:224,236 pickles whole tensor dicts) inside one NVLink box.
+
+One process per GPU; adjacent pipeline stages exchange the bf16 `[B, T, d]` tile with NCCL send/recv over NVLink
+(8 KiB ... 20 MiB) and the last stage returns `[B]` int32 token ids to the first.  KV never
+moves; positions and sequence ids are implied by the schedule both sides run.  On a machine without GPUs the
+same code runs over gloo with CPU tensors (tests of the host logic).
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+import torch.distributed as dist
+
+
+def init_stage_group(backend: Optional[str] = None) -> tuple[int, int]:
+    """Join the process group torchrun set up (RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT).  Returns (rank, world)."""
+    if not dist.is_initialized():
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        dist.init_process_group(backend=backend, rank=int(os.environ.get("RANK", "0")),
+                                world_size=int(os.environ.get("WORLD_SIZE", "1")))
+    return dist.get_rank(), dist.get_world_size()
+
+
+class StageLink:
+    """Point-to-point links of one pipeline stage: previous stage, next stage, and the token ring
+    (last stage -> first stage).
+
+    Sends are asynchronous (`isend`): a stage never blocks in a send while its neighbour is itself blocked in a
+    send to it -- with blocking sends the ring (stage 0 -> 1 -> ... -> S-1 -> 0) deadlocks as soon as more than
+    one micro-batch is in flight.  The token ring uses its own process group (its own NCCL communicator and
+    stream), so that a token waiting for stage 0 never holds up the hidden-state traffic behind it."""
+
+    def __init__(self, rank: int, world: int, make_ring_group: bool = True):
+        self.rank, self.world = rank, world
+        self.prev = rank - 1 if rank > 0 else None
+        self.next = rank + 1 if rank < world - 1 else None
+        self.is_first, self.is_last = rank == 0, rank == world - 1
+        self.ring_group = None
+        if make_ring_group and world > 1 and dist.is_initialized():
+            self.ring_group = dist.new_group(ranks=list(range(world)))  # collective: every rank constructs a link
+
+    # hidden-state tile ------------------------------------------------------------------------------
+    def send_hidden(self, tile: torch.Tensor):
+        """Returns the pending work (wait on it before overwriting `tile`), or None."""
+        return dist.isend(tile, dst=self.next) if self.next is not None else None
+
+    def recv_hidden(self, buf: torch.Tensor) -> torch.Tensor:
+        if self.prev is not None:
+            dist.recv(buf, src=self.prev)
+        return buf
+
+    # token ring -------------------------------------------------------------------------------------
+    def send_tokens(self, tokens: torch.Tensor):
+        """Last stage -> first stage (no-op for a single-stage pipeline)."""
+        if self.is_last and self.world > 1:
+            return dist.isend(tokens, dst=0, group=self.ring_group)
+        return None
+
+    def recv_tokens(self, buf: torch.Tensor) -> torch.Tensor:
+        if self.is_first and self.world > 1:
+            dist.recv(buf, src=self.world - 1, group=self.ring_group)
+        return buf
