@@ -1,0 +1,307 @@
+"""Master side of the drop-in: `MasterNode` with the reference's surface (reference src/master/node.py:14-277) --
+`start / stop / initialize_model / assign_shards / distribute_shards / run_inference` -- plus what the reference's
+master lacks for the hot path to produce tokens:
+
+  * a *scheduler* that drives the stages in pipeline order (stage 0 only gets the request; each worker chains its
+    own shards; the hand-off of one worker becomes the input of the next) instead of broadcasting the same
+    payload to every worker (reference :256-269);
+  * a decode loop (prefill, then `max_new_tokens` steps) and a *sampler* (greedy argmax; optional temperature /
+    top-k) -- the reference returns the first RESULT's raw bytes (:117-138, :208-211);
+  * a blocking wait per task instead of polling a shared queue every 100 ms (:127-138).
+
+This is the control-plane route: hidden states between workers travel through the master over ZeroMQ, which is what
+the reference's topology allows (a star).  Inside one NVLink box the data plane bypasses it: stages exchange
+tiles directly (src/network/handoff.py, src/engine/pipeline.py).
+"""
+from __future__ import annotations
+
+import json
+import os
+import pickle
+import threading
+import time
+from queue import Empty, Queue
+from typing import Any, Dict, List, Optional, Sequence, Union
+
+import torch
+
+try:
+    import zmq
+except Exception:  # pragma: no cover
+    zmq = None
+
+from ..model.shard_manager import ModelShardManager
+from ..network.protocol import MessageProtocol
+
+
+class GreedySampler:
+    """The sampler the reference's master never had.  Greedy = first index of the maximum (torch.argmax)."""
+
+    def __init__(self, temperature: float = 0.0, top_k: int = 0, seed: int = 0):
+        self.temperature, self.top_k = temperature, top_k
+        self.gen = torch.Generator().manual_seed(seed)
+
+    def __call__(self, logits: torch.Tensor) -> torch.Tensor:
+        if self.temperature <= 0.0:
+            return torch.argmax(logits, dim=-1)
+        l = logits.float().cpu() / self.temperature
+        if self.top_k > 0:
+            kth = torch.topk(l, min(self.top_k, l.shape[-1]), dim=-1).values[..., -1:]
+            l = l.masked_fill(l < kth, float("-inf"))
+        return torch.multinomial(torch.softmax(l, dim=-1), 1, generator=self.gen).squeeze(-1)
+
+
+class MasterNode:
+    def __init__(self, host: str = "0.0.0.0", port: int = 65432):
+        self.host = host
+        self.port = port
+        self.workers: Dict[str, Dict[str, Any]] = {}  # worker_id -> info (identity, capabilities, last_heartbeat, ...)
+        self.model_path = None
+        self.tokenizer = None
+        self.shard_manager: Optional[ModelShardManager] = None
+        self.shard_assignments: Dict[str, List[int]] = {}
+        self.running = False
+        self.server_socket = None
+        self.task_queue: Queue = Queue()
+        self.result_queue: Queue = Queue()            # kept for API parity; results are delivered per task below
+        self.zmq_context = zmq.Context.instance() if zmq is not None else None
+        self.sampler = GreedySampler()
+        self._protocol: Optional[MessageProtocol] = None
+        self._send_lock = threading.Lock()            # one ROUTER socket, several sender threads
+        self._workers_lock = threading.Lock()
+        self._replies: Dict[str, Queue] = {}          # task_id -> queue of (header, payload) from workers
+        self._finished: Dict[str, Queue] = {}         # task_id -> final result for run_inference()
+        self._loaded = threading.Condition()
+        self._loaded_shards: set = set()
+        self.heartbeat_timeout = 30.0
+
+    # ---- life cycle (reference :29-52) -------------------------------------------------------------------
+    def start(self):
+        self._protocol = MessageProtocol(zmq_context=self.zmq_context)
+        self.server_socket = self._protocol.setup_zmq_socket(zmq.ROUTER, f"tcp://{self.host}:{self.port}")  # binds
+        if self.port == 0:
+            self.port = int(self.server_socket.getsockopt_string(zmq.LAST_ENDPOINT).rsplit(":", 1)[1])
+        self.running = True
+        print(f"Master node listening on {self.host}:{self.port}")
+        self.accept_thread = threading.Thread(target=self._accept_connections, daemon=True)
+        self.accept_thread.start()
+        self.task_thread = threading.Thread(target=self._process_tasks, daemon=True)
+        self.task_thread.start()
+
+    def stop(self):
+        self.running = False
+        time.sleep(0.05)
+        if self.server_socket is not None:
+            self.server_socket.close()
+            self.server_socket = None
+
+    # ---- model preparation (reference :54-82) ---------------------------------------------------------------
+    def initialize_model(self, model_id: str, num_shards: int, cache_dir: str = "./models"):
+        """`model_id`: a local directory (config.json + pytorch_model.bin / model.safetensors), `random:<name>` for a
+        seeded random-init checkpoint of a known architecture (no network needed), or a Hub id (needs a network)."""
+        if model_id.startswith("random:"):
+            self.model_path = self._materialise_random(model_id[len("random:"):], cache_dir)
+        elif os.path.exists(model_id):
+            self.model_path = model_id
+        else:
+            from ..model.downloader import download_model
+            print(f"Downloading model {model_id}...")
+            self.model_path = download_model(model_id, cache_dir=cache_dir)
+        try:  # the tokenizer is optional: prompts may be given as token ids
+            from transformers import AutoTokenizer
+            self.tokenizer = AutoTokenizer.from_pretrained(self.model_path)
+        except Exception:
+            self.tokenizer = None
+        print(f"Sharding model into {num_shards} parts...")
+        self.shard_manager = ModelShardManager(self.model_path, num_shards)
+        return self.shard_manager.shard_model()
+
+    @staticmethod
+    def _materialise_random(name: str, cache_dir: str, seed: int = 1234, dtype: torch.dtype = torch.bfloat16) -> str:
+        from ..model import random_init
+        cfg = random_init.NAMED_CONFIGS[name]
+        path = os.path.join(cache_dir, f"random-{name}")
+        os.makedirs(path, exist_ok=True)
+        if not os.path.exists(os.path.join(path, "pytorch_model.bin")):
+            L = cfg.get("num_hidden_layers", cfg.get("n_layer"))
+            sd = random_init.random_stage_parameters(cfg, range(L), True, True, seed, dtype)
+            if cfg.get("tie_word_embeddings", cfg["model_type"] == "gpt2"):
+                sd.pop("lm_head.weight", None)
+            torch.save(sd, os.path.join(path, "pytorch_model.bin"))
+            with open(os.path.join(path, "config.json"), "w") as f:
+                json.dump(cfg, f)
+        return path
+
+    # ---- placement (reference :84-115) -------------------------------------------------------------------------
+    def assign_shards(self):
+        """Shard i -> worker i (round-robin when there are more shards than workers; consecutive shards of one worker
+        stay in pipeline order)."""
+        with self._workers_lock:
+            workers = list(self.workers.keys())
+        if not workers:
+            raise ValueError("No workers connected")
+        num_shards = self.shard_manager.num_shards
+        self.shard_assignments = {}
+        for i in range(num_shards):
+            self.shard_assignments.setdefault(workers[i % len(workers)], []).append(i)
+        return self.shard_assignments
+
+    def distribute_shards(self, wait: bool = True, timeout: float = 600.0):
+        shard_paths = self.shard_manager.get_shard_paths()
+        wanted = set()
+        for worker_id, shard_ids in self.shard_assignments.items():
+            for shard_id in shard_ids:
+                self._send_shard(self.workers[worker_id], shard_id, shard_paths[shard_id])
+                wanted.add(shard_id)
+        if wait:
+            deadline = time.time() + timeout
+            with self._loaded:
+                while not wanted <= self._loaded_shards:
+                    left = deadline - time.time()
+                    if left <= 0:
+                        raise TimeoutError(f"workers did not confirm shards {sorted(wanted - self._loaded_shards)}")
+                    self._loaded.wait(left)
+
+    def _send_shard(self, worker, shard_id, shard_path):
+        print(f"Sending shard {shard_id} to worker")
+        with open(shard_path, "rb") as f:
+            shard_data = f.read()
+        self._send(worker, "LOAD_SHARD", shard_data, {"shard_id": shard_id})
+
+    def _send(self, worker, command, payload=None, metadata=None) -> bool:
+        md = dict(metadata or {})
+        md["identity"] = worker["identity"]
+        with self._send_lock:
+            return self._protocol.send_message(self.server_socket, command, payload, md)
+
+    # ---- inference (reference :117-138, :227-277) -----------------------------------------------------------------
+    def run_inference(self, input_text: Union[str, Sequence[int], torch.Tensor], timeout: int = 60,
+                      max_new_tokens: int = 32):
+        """Queue a request and wait for it.  Returns {"token_ids": [...], "text": str | None}."""
+        task_id = f"task_{int(time.time() * 1000)}_{threading.get_ident() & 0xffff}"
+        done: Queue = Queue()
+        self._finished[task_id] = done
+        self.task_queue.put((task_id, input_text, max_new_tokens))
+        try:
+            result = done.get(timeout=timeout)
+        except Empty:
+            raise TimeoutError(f"Inference timed out after {timeout} seconds")
+        finally:
+            self._finished.pop(task_id, None)
+        if isinstance(result, Exception):
+            raise result
+        return result
+
+    def _stage_order(self) -> List[tuple]:
+        """[(worker_id, [shard ids in pipeline order]), ...] sorted by the first shard a worker holds."""
+        order = sorted(((min(s), w, sorted(s)) for w, s in self.shard_assignments.items() if s))
+        flat = [i for _, _, s in order for i in s]
+        if flat != sorted(flat):
+            raise RuntimeError("shard assignment is not a pipeline: a worker holds non-consecutive shards")
+        return [(w, s) for _, w, s in order]
+
+    def _pipeline_step(self, task_id: str, inputs: Dict[str, torch.Tensor], reset: bool, timeout: float) -> Dict[str, torch.Tensor]:
+        """One pass through all stages: each worker's RESULT (the hand-off) is forwarded to the next worker."""
+        x = inputs
+        for worker_id, shard_ids in self._stage_order():
+            worker = self.workers[worker_id]
+            self._send(worker, "RUN_INFERENCE", pickle.dumps(x), {"task_id": task_id, "shard_ids": shard_ids, "reset": reset})
+            try:
+                header, payload = self._replies[task_id].get(timeout=timeout)
+            except Empty:
+                raise TimeoutError(f"worker {worker_id} did not answer")
+            if header.get("error"):
+                raise RuntimeError(f"worker {worker_id}: {header['error']}")
+            x = pickle.loads(payload)
+        return x
+
+    def _process_tasks(self):
+        while self.running:
+            try:
+                task_id, request, max_new = self.task_queue.get(block=True, timeout=0.2)
+            except Empty:
+                continue
+            done = self._finished.get(task_id)
+            self._replies[task_id] = Queue()
+            try:
+                if isinstance(request, str):
+                    if self.tokenizer is None:
+                        raise ValueError("no tokenizer is available: pass the prompt as token ids")
+                    ids = self.tokenizer(request, return_tensors="pt")["input_ids"].to(torch.int64)
+                else:
+                    ids = torch.as_tensor(request, dtype=torch.int64)
+                    if ids.dim() == 1:
+                        ids = ids[None, :]
+                if not self.shard_assignments:
+                    raise RuntimeError("no shard assignments: call assign_shards() / distribute_shards() first")
+                out = self._pipeline_step(task_id, {"input_ids": ids}, reset=True, timeout=60.0)   # prefill
+                tokens = [self.sampler(out["logits"]) if "logits" in out else out["next_token"]]
+                for _ in range(max_new - 1):                                                         # decode
+                    out = self._pipeline_step(task_id, {"input_ids": tokens[-1].reshape(-1, 1).to(torch.int64)},
+                                              reset=False, timeout=60.0)
+                    tokens.append(self.sampler(out["logits"]) if "logits" in out else out["next_token"])
+                token_ids = torch.stack([t.reshape(-1).cpu() for t in tokens], dim=1)
+                text = None
+                if self.tokenizer is not None:
+                    text = self.tokenizer.batch_decode(token_ids.tolist())
+                result = {"token_ids": token_ids.tolist(), "text": text}
+            except Exception as e:  # delivered to the caller instead of being printed and dropped (reference :240-242)
+                result = e
+            finally:
+                self._replies.pop(task_id, None)
+            if done is not None:
+                done.put(result)
+            self.result_queue.put((task_id, result))
+
+    # ---- worker messages (reference :140-211) ------------------------------------------------------------------------
+    def _accept_connections(self):
+        while self.running:
+            try:
+                header, payload = self._protocol.receive_message(self.server_socket, timeout=0.2)
+            except TimeoutError:
+                continue
+            except Exception as e:
+                if self.running:
+                    print(f"Error accepting connection: {e}")
+                continue
+            if not header:
+                continue
+            identity = header.get("identity", b"")
+            worker_id = identity.hex() or "worker"
+            with self._workers_lock:
+                if worker_id not in self.workers:
+                    print(f"New connection from {worker_id}")
+                    self.workers[worker_id] = {"identity": identity, "connected_time": time.time(),
+                                               "last_heartbeat": time.time(), "status": "connected"}
+            self._handle_worker_command(worker_id, header.get("command", ""), header, payload)
+
+    def _handle_worker_command(self, worker_id, command, header, payload):
+        if command == "REGISTER":
+            capabilities = header.get("capabilities", {})
+            self.workers[worker_id].update(capabilities)
+            print(f"Worker {worker_id} registered with capabilities: {capabilities}")
+        elif command == "HEARTBEAT":
+            self.workers[worker_id]["last_heartbeat"] = time.time()
+        elif command == "SHARD_LOADED":
+            shard_id = header.get("shard_id")
+            print(f"Worker {worker_id} loaded shard {shard_id}")
+            with self._loaded:
+                if header.get("ok", True):
+                    self._loaded_shards.add(shard_id)
+                self._loaded.notify_all()
+        elif command == "RESULT":
+            task_id = header.get("task_id")
+            q = self._replies.get(task_id)
+            if q is not None:
+                q.put((header, payload))
+
+    def evict_stale_workers(self) -> List[str]:
+        """Drop workers whose heartbeat is older than `heartbeat_timeout` (the reference records heartbeats and never
+        looks at them, :199-201)."""
+        now = time.time()
+        with self._workers_lock:
+            stale = [w for w, info in self.workers.items() if now - info["last_heartbeat"] > self.heartbeat_timeout]
+            for w in stale:
+                del self.workers[w]
+                self.shard_assignments.pop(w, None)
+        return stale

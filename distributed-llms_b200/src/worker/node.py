@@ -284,15 +284,19 @@ class WorkerNode:
         elif command in ("RUN_INFERENCE", "SCHEDULE_COMPUTATION"):
             task_id = header.get("task_id")
             shard_ids = header.get("shard_ids", [])
-            inputs = pickle.loads(payload)
-            if header.get("reset"):
-                for sid in shard_ids:
-                    if sid in self.shards:
-                        self.shards[sid].reset()
-            # `priority` (reference :244-251) is a constant sort key there, i.e. a no-op; kept as such
-            results = self.schedule_computation(inputs, [s for s in shard_ids if s in self.shards])
-            results = {k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in results.items()}
-            protocol.send_message(sock, "RESULT", payload=pickle.dumps(results), metadata={"task_id": task_id})
+            try:
+                inputs = pickle.loads(payload)
+                if header.get("reset"):
+                    for sid in shard_ids:
+                        if sid in self.shards:
+                            self.shards[sid].reset()
+                # `priority` (reference :244-251) is a constant sort key there, i.e. a no-op; kept as such
+                results = self.schedule_computation(inputs, [s for s in shard_ids if s in self.shards])
+                results = {k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in results.items()}
+                protocol.send_message(sock, "RESULT", payload=pickle.dumps(results), metadata={"task_id": task_id})
+            except Exception as e:  # the master's scheduler is waiting for this RESULT: tell it what went wrong
+                protocol.send_message(sock, "RESULT", payload=pickle.dumps({}),
+                                      metadata={"task_id": task_id, "error": f"{type(e).__name__}: {e}"})
 
     def _send_heartbeat(self):
         while self.running:

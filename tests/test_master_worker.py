@@ -1,0 +1,115 @@
+"""Master <-> workers over localhost ZeroMQ: registration, placement, shard shipping, heartbeat eviction (CPU), and --
+on a GPU -- BASELINE config[0] in miniature: a model split into 2 layer shards on a master + 2 localhost workers,
+greedy decode, tokens identical to the CPU oracle."""
+import json
+import os
+import time
+
+import pytest
+import torch
+
+from src.master.node import GreedySampler, MasterNode
+from src.model import random_init
+from src.worker.node import WorkerNode
+
+zmq = pytest.importorskip("zmq")
+
+CFG = dict(model_type="llama", hidden_size=128, num_hidden_layers=4, num_attention_heads=4, num_key_value_heads=2,
+           intermediate_size=256, vocab_size=300, max_position_embeddings=64, rms_norm_eps=1e-5, rope_theta=10000.0)
+
+
+def _model_dir(tmp_path, dtype):
+    d = str(tmp_path / "model")
+    os.makedirs(d, exist_ok=True)
+    sd = random_init.random_stage_parameters(CFG, range(4), True, True, 1234, dtype, init="full")
+    torch.save({("model." + k if k != "lm_head.weight" else k): v for k, v in sd.items()}, os.path.join(d, "pytorch_model.bin"))
+    with open(os.path.join(d, "config.json"), "w") as f:
+        json.dump(CFG, f)
+    return d, sd
+
+
+def _cluster(n_workers):
+    master = MasterNode(host="127.0.0.1", port=0)
+    master.start()
+    workers = []
+    for i in range(n_workers):
+        w = WorkerNode(host="127.0.0.1", port=0, master_address=f"127.0.0.1:{master.port}")
+        w.start()
+        workers.append(w)
+        deadline = time.time() + 10
+        while len(master.workers) < i + 1 and time.time() < deadline:  # register in a known order
+            time.sleep(0.02)
+    assert len(master.workers) == n_workers
+    return master, workers
+
+
+def _shutdown(master, workers):
+    for w in workers:
+        w.stop()
+    master.stop()
+
+
+def test_register_assign_distribute_and_errors(tmp_path):
+    d, _ = _model_dir(tmp_path, torch.float32)
+    master, workers = _cluster(2)
+    try:
+        assert all("has_gpu" in info for info in master.workers.values())  # REGISTER carried the capabilities
+        shard_dir = master.initialize_model(d, num_shards=2)
+        assert sorted(f for f in os.listdir(shard_dir) if f.endswith(".pt")) == ["shard_0.pt", "shard_1.pt"]
+        assign = master.assign_shards()
+        assert sorted(assign.values()) == [[0], [1]]
+        master.distribute_shards(timeout=60)          # LOAD_SHARD -> SHARD_LOADED round trips over ZeroMQ
+        assert all(len(w.shards) == 1 for w in workers)
+        assert workers[0].shards[0].config == CFG and "embed_tokens.weight" in workers[0].shards[0].parameters
+        assert "lm_head.weight" in workers[1].shards[1].parameters
+        if not torch.cuda.is_available():
+            # without CUDA the stage cannot run: the worker reports it and the master raises (no silent CPU path)
+            with pytest.raises(RuntimeError, match="no CPU"):
+                master.run_inference([1, 2, 3], timeout=20, max_new_tokens=2)
+    finally:
+        _shutdown(master, workers)
+
+
+def test_no_workers_and_heartbeat_eviction():
+    master = MasterNode(host="127.0.0.1", port=0)
+    master.start()
+    try:
+        master.shard_manager = type("M", (), {"num_shards": 2})()
+        with pytest.raises(ValueError):
+            master.assign_shards()
+        master.workers["w"] = {"identity": b"w", "last_heartbeat": time.time() - 100, "status": "connected"}
+        master.shard_assignments = {"w": [0]}
+        assert master.evict_stale_workers() == ["w"] and not master.workers and not master.shard_assignments
+    finally:
+        master.stop()
+
+
+def test_sampler():
+    logits = torch.tensor([[0.1, 2.0, 2.0, -1.0]])
+    assert GreedySampler()(logits).tolist() == [1]                       # first index of the maximum
+    s = GreedySampler(temperature=1.0, top_k=2, seed=1)
+    assert all(int(s(logits)) in (1, 2) for _ in range(20))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_master_two_workers_greedy_decode_matches_oracle(tmp_path, dtype):
+    from oracle.shard_oracle import ShardModelConfig, build_pipeline, greedy_generate
+    d, sd = _model_dir(tmp_path, dtype)
+    master, workers = _cluster(2)
+    try:
+        master.initialize_model(d, num_shards=2)
+        master.assign_shards()
+        master.distribute_shards(timeout=120)
+        prompt = torch.randint(0, CFG["vocab_size"], (1, 11), generator=torch.Generator().manual_seed(5))
+        got = master.run_inference(prompt, timeout=120, max_new_tokens=16)
+        cfg = ShardModelConfig.from_hf_dict(CFG)
+        want, _, margins = greedy_generate(build_pipeline(cfg, sd, 2, dtype), prompt, 16, record=True)
+        got_ids = torch.tensor(got["token_ids"])
+        if dtype == torch.float32:
+            assert torch.equal(got_ids, want)
+        else:
+            same = (got_ids == want).long().cumprod(1).bool()
+            assert same.all() or float(margins[0, int((~same[0]).float().argmax())]) < 2 ** -6
+    finally:
+        _shutdown(master, workers)
