@@ -268,8 +268,17 @@ def run_single(args) -> int:
     algo = stage_bytes_per_step(hf, L, True, batch, ctx_mid)
     step_s = dec_ms * 1e-3 / K
     achieved = algo / step_s / 1e9
+    traffic = None
+    try:  # DRAM bytes per step from the committed ncu --set full capture of this workload (profiles/)
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f).get(model)
+        if t and batch == WORKLOADS[model][1]:
+            traffic = t["dram_bytes_per_step"]
+    except Exception:
+        pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "peak_kind": peak_kind, "kernel": "decode step (CUDA graph of the stage's fused GEMV/attention kernels)",
+                "traffic": traffic, "peak_kind": peak_kind,
+                "kernel": "decode_megakernel: one persistent launch per decode loop; unit = one decode step of the stage",
                 "algorithmic_bytes_per_launch": algo}
 
     # ---- CPU baseline on the host cores (bounded sample) ----

@@ -466,7 +466,7 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     if (const char* e = getenv("DLLM_MK_SPLITS")) { long v = atol(e); if (v >= 1 && v <= s_cap && (long)n_rows * c.n_heads * v <= s->max_partials) S = v; }
     p.part_units = s->mk_part_units;
     p.attn_out = s->attn_out; p.attn_counters = s->attn_counters;
-    p.prefetch_kb = 32;
+    p.prefetch_kb = 0;  // off by default: measured slower than the rings alone (profiles/r1b_summary.md)
     if (const char* e = getenv("DLLM_MK_PREFETCH_KB")) { long v = atol(e); if (v >= 0 && v <= 1024) p.prefetch_kb = (int)v; }
     p.n_splits = (int)S; p.advance = advance ? 1 : 0; p.tok_base = 0; p.eps = c.norm_eps;
     p.h = s->h; p.q = s->qbuf; p.act = s->act; p.part_o = s->part_o; p.part_ml = s->part_ml;
