@@ -75,6 +75,31 @@ struct EmbedParams {
     int32_t n_rows, hidden, vocab;
 };
 
+// Prefill GEMM on tcgen05 (prefill_gemm.cu): C[M, N] = A[M, K] . W[N, K]^T, bf16 in, fp32 accumulate in TMEM.
+enum GemmEpi { GEMM_EPI_BIAS = 0, GEMM_EPI_RESIDUAL = 1, GEMM_EPI_SWIGLU = 2, GEMM_EPI_GELU = 3 };
+struct GemmTcParams {
+    const void* a;      // [M, K] activations, row-major (lda = K)
+    const void* w;      // [N, K] weights (nn.Linear layout)
+    const void* w2;     // SWIGLU: the up projection (w = gate)
+    const void* bias;   // [N] or null
+    void* c;            // [M, ldc] output; RESIDUAL adds into it in place
+    int32_t M, N, K, ldc, epi;
+};
+struct RopeAppendParams {
+    const void* qkv;    // [R, (H+2KV)*hd] projected rows (bias added)
+    void* q;            // [R, H*hd]
+    PagedKV kv;
+    const int32_t* positions;
+    const int32_t* seq_ids;
+    const float* rope_cos;
+    const float* rope_sin;
+    int32_t n_rows, n_heads, n_kv_heads, head_dim, rope;
+};
+cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st);
+cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
+                             cudaStream_t st);
+cudaError_t launch_rope_append(const RopeAppendParams& p, cudaStream_t st);
+
 // Each returns cudaGetLastError() of its launch.  dtype: 0 = bf16, 1 = fp32.
 cudaError_t gemv_init_device();  // once per device, outside stream capture
 cudaError_t launch_gemv(int dtype, const GemvParams& p, int num_sms, cudaStream_t s);

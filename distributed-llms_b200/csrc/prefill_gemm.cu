@@ -1,0 +1,391 @@
+// Prefill GEMM for sm_100a: C[M, N] = A[M, K] . W[N, K]^T on the 5th-generation tensor cores.
+//
+// Only prefill is a dense contraction: M = tokens of the prompt chunk, N = output features,
+// both operands K-major in HBM exactly as the activations / nn.Linear weights already lie there.
+//   * TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) stages 128x64 tiles of A and W into a 4-deep ring;
+//   * one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=128, K=16) from shared-memory
+//     descriptors; the fp32 accumulator lives in tensor memory (128 lanes x 128 or 256 columns);
+//   * tcgen05.commit releases ring slots and finally signals the epilogue warps, which read the accumulator with
+//     tcgen05.ld and apply the fused epilogue: bias | bias + residual (in place) | SwiGLU of a gate/up tile pair;
+//   * warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer, warps 2-5 = epilogue (one TMEM lane
+//     quarter each).  Rounding points are those of the decode kernels (bf16 after bias, after the residual add,
+//     after SiLU and after the product).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace dllm {
+
+namespace {
+
+constexpr int BM = 128, BN = 128, BK = 64;      // tile; BK * 2 bytes = one 128-byte swizzle row
+constexpr int kStages = 4;
+constexpr int kTileBytes = BM * BK * 2;         // 16 KB per operand tile
+constexpr int kGemmThreads = 192;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok = 0;
+    for (unsigned spins = 0; !ok; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (!ok && spins > (1u << 26)) __trap();  // never hang the GPU on a lost arrival
+    }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]; bf16 inputs, fp32 accumulate
+__device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// 32 lanes x 32 columns of fp32 -> 32 registers per thread (thread = lane, register = column)
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor of a K-major tile stored as rows of 128 bytes with the 128-byte swizzle
+// (what TMA SWIZZLE_128B writes): start address >> 4, leading byte offset 1 (unused for swizzled K-major),
+// stride byte offset = 8 rows * 128 B = 1024 B, descriptor version 1 (sm_100), layout type 2 (SWIZZLE_128B).
+__device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+// Instruction descriptor: D fp32, A and B bf16, both K-major, N = 128, M = 128.
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+
+__device__ __forceinline__ float silu_f(float g) { return g / (1.0f + expf(-g)); }
+__device__ __forceinline__ float gelu_new_f(float x) {
+    return 0.5f * x * (1.0f + tanhf(0.7978845608028654f * (x + 0.044715f * x * x * x)));
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+               const __grid_constant__ CUtensorMap tm_b2, const GemmTcParams p) {
+    constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
+    constexpr int kStageBytes = kTileBytes * (kDual ? 3 : 2);
+    constexpr uint32_t kTmemCols = kDual ? 256 : 128;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t bars[2 * kStages + 1];
+    __shared__ uint32_t s_tmem;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    const int num_kb = (p.K + BK - 1) / BK;
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages), tfull = smem_u32(bars + 2 * kStages);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(full0 + i * 8, 1);
+            mbar_init(empty0 + i * 8, 1);
+        }
+        mbar_init(tfull, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {  // one warp allocates tensor memory and later frees it
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % kStages;
+                mbar_wait(empty0 + s * 8, ((kb / kStages) & 1) ^ 1);
+                const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
+                mbar_expect_tx(full0 + s * 8, kStageBytes);
+                tma_load_2d(dst, &tm_a, kb * BK, m0, full0 + s * 8);
+                tma_load_2d(dst + kTileBytes, &tm_b, kb * BK, n0, full0 + s * 8);
+                if (kDual) tma_load_2d(dst + 2 * kTileBytes, &tm_b2, kb * BK, n0, full0 + s * 8);
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % kStages;
+                mbar_wait(full0 + s * 8, (kb / kStages) & 1);
+                tc_fence_after();
+                const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
+                const uint64_t da = make_sw128_desc(base), db = make_sw128_desc(base + kTileBytes);
+                const uint64_t db2 = make_sw128_desc(base + 2 * kTileBytes);
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                    // 16 k-elements = 32 bytes further along the swizzled row: +2 in the (address >> 4) field
+                    const uint32_t acc = (kb | k) ? 1u : 0u;
+                    tc_mma(tmem, da + 2 * k, db + 2 * k, kIdesc, acc);
+                    if (kDual) tc_mma(tmem + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
+                }
+                tc_commit(empty0 + s * 8);  // the slot is free once these MMAs have read it
+            }
+            tc_commit(tfull);               // accumulator complete
+        }
+    } else {
+        // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
+        mbar_wait(tfull, 0);
+        tc_fence_after();
+        const int quarter = warp & 3;
+        const int row = m0 + quarter * 32 + lane;
+        const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16);
+        bf16* out = static_cast<bf16*>(p.c);
+        const bf16* bias = static_cast<const bf16*>(p.bias);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+            uint32_t acc[32], acc2[32];
+            tc_ld32(tbase + c0, acc);
+            if (kDual) tc_ld32(tbase + BN + c0, acc2);
+            if (row < p.M) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 2) {
+                    const int n = n0 + c0 + j;
+                    if (n >= p.N) break;
+                    float v0 = __uint_as_float(acc[j]), v1 = __uint_as_float(acc[j + 1]);
+                    if (EPI == GEMM_EPI_SWIGLU) {
+                        const float g0 = bf16_round(v0), g1 = bf16_round(v1);
+                        const float u0 = bf16_round(__uint_as_float(acc2[j])), u1 = bf16_round(__uint_as_float(acc2[j + 1]));
+                        v0 = bf16_round(silu_f(g0)) * u0;
+                        v1 = bf16_round(silu_f(g1)) * u1;
+                    } else {
+                        v0 = bf16_round(v0 + (bias ? __bfloat162float(bias[n]) : 0.f));
+                        v1 = bf16_round(v1 + (bias && n + 1 < p.N ? __bfloat162float(bias[n + 1]) : 0.f));
+                        if (EPI == GEMM_EPI_RESIDUAL) {
+                            const uint32_t old = *reinterpret_cast<const uint32_t*>(out + (size_t)row * p.ldc + n);
+                            v0 += __uint_as_float(old << 16);
+                            v1 += __uint_as_float(old & 0xffff0000u);
+                        } else if (EPI == GEMM_EPI_GELU) {
+                            v0 = gelu_new_f(v0);
+                            v1 = gelu_new_f(v1);
+                        }
+                    }
+                    // N is even for every weight shape in use; a lone last column is written alone
+                    if (n + 1 < p.N) *reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * p.ldc + n) = __floats2bfloat162_rn(v0, v1);
+                    else out[(size_t)row * p.ldc + n] = __float2bfloat16_rn(v0);
+                }
+            }
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols));
+    }
+}
+
+// ---- small row-wise kernels around the GEMMs -------------------------------------------------------------------
+
+// xn[r] = norm(x[r]) for T rows (RMSNorm / LayerNorm with the rounding of the decode prologue); one warp per row
+__global__ void __launch_bounds__(256) norm_rows_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                        const bf16* __restrict__ b, bf16* __restrict__ y, int rows, int K,
+                                                        int norm, float eps) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const bf16* xr = x + (size_t)row * K;
+    bf16* yr = y + (size_t)row * K;
+    float s1 = 0.f, s2 = 0.f;
+    for (int k = lane * 8; k < K; k += 256) {
+        float f[8];
+        unpack<bf16>(ld_u4(xr + k), f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            s1 += f[j];
+            s2 = fmaf(f[j], f[j], s2);
+        }
+    }
+    float mean = 0.f, rstd;
+    if (norm == NORM_RMS) {
+        rstd = 1.0f / sqrtf(warp_sum(s2) / (float)K + eps);
+    } else {
+        mean = warp_sum(s1) / (float)K;
+        float sq = 0.f;
+        for (int k = lane * 8; k < K; k += 256) {
+            float f[8];
+            unpack<bf16>(ld_u4(xr + k), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq);
+        }
+        rstd = 1.0f / sqrtf(warp_sum(sq) / (float)K + eps);
+    }
+    for (int k = lane * 8; k < K; k += 256) {
+        float f[8], wf[8], bf[8];
+        unpack<bf16>(ld_u4(xr + k), f);
+        unpack<bf16>(ld_u4(w + k), wf);
+        if (norm == NORM_RMS) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = wf[j] * bf16_round(f[j] * rstd);
+        } else {
+            unpack<bf16>(ld_u4(b + k), bf);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaf((f[j] - mean) * rstd, wf[j], bf[j]);
+        }
+        uint4 o;
+        __nv_bfloat162 a0 = __floats2bfloat162_rn(f[0], f[1]), a1 = __floats2bfloat162_rn(f[2], f[3]);
+        __nv_bfloat162 a2 = __floats2bfloat162_rn(f[4], f[5]), a3 = __floats2bfloat162_rn(f[6], f[7]);
+        o.x = *reinterpret_cast<uint32_t*>(&a0);
+        o.y = *reinterpret_cast<uint32_t*>(&a1);
+        o.z = *reinterpret_cast<uint32_t*>(&a2);
+        o.w = *reinterpret_cast<uint32_t*>(&a3);
+        *reinterpret_cast<uint4*>(yr + k) = o;
+    }
+}
+
+// qkv [T, (H+2KV)*hd] (already bias-added and rounded) -> rotary on q and k, q to its buffer, k/v into the pages
+__global__ void __launch_bounds__(256) rope_append_kernel(const RopeAppendParams p) {
+    const int hd = p.head_dim, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
+    const int heads = H + 2 * KV;
+    const int per_row = heads * half;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < p.n_rows * per_row; i += gridDim.x * blockDim.x) {
+        const int r = i / per_row, u = i - r * per_row;
+        const int head = u / half, j = u - head * half;
+        const bf16* src = static_cast<const bf16*>(p.qkv) + (size_t)r * heads * hd + (size_t)head * hd + j;
+        float v0 = __bfloat162float(src[0]), v1 = __bfloat162float(src[half]);
+        const int m = head < H ? 0 : (head < H + KV ? 1 : 2);
+        const int hl = head - (m == 0 ? 0 : (m == 1 ? H : H + KV));
+        const int pos = p.positions[r];
+        if (p.rope && m != 2) {
+            const float c = bf16_round(p.rope_cos[(size_t)pos * half + j]), s = bf16_round(p.rope_sin[(size_t)pos * half + j]);
+            const float o0 = bf16_round(bf16_round(v0 * c) + bf16_round(-v1 * s));
+            const float o1 = bf16_round(bf16_round(v1 * c) + bf16_round(v0 * s));
+            v0 = o0;
+            v1 = o1;
+        }
+        if (m == 0) {
+            bf16* q = static_cast<bf16*>(p.q) + (size_t)r * H * hd + hl * hd + j;
+            q[0] = __float2bfloat16_rn(v0);
+            q[half] = __float2bfloat16_rn(v1);
+        } else {
+            const int seq = p.seq_ids[r];
+            const int page = p.kv.block_table[(size_t)seq * p.kv.pages_per_seq + (pos >> p.kv.page_shift)];
+            const int off = pos & ((1 << p.kv.page_shift) - 1);
+            bf16* pool = static_cast<bf16*>(m == 1 ? p.kv.kpool : p.kv.vpool);
+            bf16* dst = pool + ((((size_t)page * KV + hl) << p.kv.page_shift) + off) * hd + j;
+            dst[0] = __float2bfloat16_rn(v0);
+            dst[half] = __float2bfloat16_rn(v1);
+        }
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* ptr = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    }
+    return fn;
+}
+
+// [rows, K] row-major bf16, box = 128 rows x 64 k, 128-byte swizzle, out-of-bounds reads return zero
+bool make_map(CUtensorMap* map, const void* base, int rows, int K) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return false;
+    cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+    cuuint32_t box[2] = {BK, BM};
+    cuuint32_t estr[2] = {1, 1};
+    return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int EPI>
+cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const GemmTcParams& p, cudaStream_t st) {
+    constexpr int stage = kTileBytes * (EPI == GEMM_EPI_SWIGLU ? 3 : 2);
+    const size_t smem = (size_t)kStages * stage + 1024;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
+    gemm_tc_kernel<EPI><<<grid, kGemmThreads, smem, st>>>(a, b, b2, p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
+    if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || p.ldc % 2) return cudaErrorInvalidValue;
+    CUtensorMap a, b, b2;
+    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K)) return cudaErrorNotSupported;
+    if (p.epi == GEMM_EPI_SWIGLU) {
+        if (!make_map(&b2, p.w2, p.N, p.K)) return cudaErrorNotSupported;
+    } else {
+        b2 = b;
+    }
+    switch (p.epi) {
+        case GEMM_EPI_BIAS: return launch_epi<GEMM_EPI_BIAS>(a, b, b2, p, st);
+        case GEMM_EPI_RESIDUAL: return launch_epi<GEMM_EPI_RESIDUAL>(a, b, b2, p, st);
+        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU>(a, b, b2, p, st);
+        case GEMM_EPI_GELU: return launch_epi<GEMM_EPI_GELU>(a, b, b2, p, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
+                             cudaStream_t st) {
+    if (rows <= 0 || K % 8) return cudaErrorInvalidValue;
+    norm_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(w),
+                                                     static_cast<const bf16*>(b), static_cast<bf16*>(y), rows, K, norm, eps);
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rope_append(const RopeAppendParams& p, cudaStream_t st) {
+    const int total = p.n_rows * (p.n_heads + 2 * p.n_kv_heads) * (p.head_dim / 2);
+    if (total <= 0) return cudaErrorInvalidValue;
+    int blocks = (total + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    rope_append_kernel<<<blocks, 256, 0, st>>>(p);
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace dllm

@@ -79,6 +79,8 @@ struct dllm_shard {
     void* qbuf = nullptr;      // [max_rows, H*hd]
     void* attn_out = nullptr;  // [max_rows, H*hd]
     void* act = nullptr;       // [max_rows, ffn]
+    void* xn = nullptr;        // [max_rows, d]   normalised rows (prefill GEMM input)
+    void* qkv_tmp = nullptr;   // [max_rows, (H+2KV)*hd] projected rows before rotary (prefill)
     int32_t *ids = nullptr, *pos = nullptr, *seq = nullptr, *logit_rows = nullptr, *arange = nullptr;
     int32_t *next_tok = nullptr, *block_table = nullptr, *tok_ring = nullptr, *step_ctr = nullptr;
     float* logits = nullptr;   // [max_logit_rows, V]
@@ -171,6 +173,9 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->qbuf, (size_t)c.max_rows * Hd * s->esz);
     add(&s->attn_out, (size_t)c.max_rows * Hd * s->esz);
     add(&s->act, (size_t)c.max_rows * c.ffn * s->esz);
+    const bool prefill_bufs = c.dtype == DLLM_DTYPE_BF16 && c.max_rows > 16;
+    add(&s->xn, prefill_bufs ? (size_t)c.max_rows * c.hidden * s->esz : 0);
+    add(&s->qkv_tmp, prefill_bufs ? (size_t)c.max_rows * (c.n_heads + 2 * c.n_kv_heads) * c.head_dim * s->esz : 0);
     add(&s->ids, (size_t)c.max_rows * 4);
     add(&s->pos, (size_t)c.max_rows * 4);
     add(&s->seq, (size_t)c.max_rows * 4);
@@ -507,6 +512,90 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     return 0;
 }
 
+// Prefill (many rows, bf16): the dense contractions run as tcgen05 GEMMs, the rest as row-wise kernels.
+static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, cudaStream_t st) {
+    const dllm_shard_config& c = s->cfg;
+    const bool gpt2 = c.arch == DLLM_ARCH_GPT2;
+    const int norm = gpt2 ? NORM_LAYER : NORM_RMS;
+    const int Hd = c.n_heads * c.head_dim, KVd = c.n_kv_heads * c.head_dim, QKVd = Hd + 2 * KVd;
+    if (c.has_embed) {
+        EmbedParams e{};
+        e.ids = s->ids; e.positions = s->pos; e.wte = s->io.wte; e.wpe = gpt2 ? s->io.wpe : nullptr;
+        e.out = s->h; e.n_rows = n_rows; e.hidden = c.hidden; e.vocab = c.vocab;
+        CUDA_TRY(launch_embed(0, e, st));
+    }
+    const int splits = pick_splits(s, n_rows);
+    char* qkv = static_cast<char*>(s->qkv_tmp);
+    for (int l = 0; l < c.n_layers; ++l) {
+        const dllm_layer_weights& w = s->layers[l];
+        PagedKV kv{s->kpool[l], s->vpool[l], s->block_table, s->pages_per_seq, s->page_shift};
+        CUDA_TRY(launch_norm_rows(s->h, w.norm1_w, w.norm1_b, s->xn, n_rows, c.hidden, norm, c.norm_eps, st));
+        {   // q, k, v projections into column slices of one [R, QKVd] buffer
+            GemmTcParams g{};
+            g.a = s->xn; g.M = n_rows; g.K = c.hidden; g.ldc = QKVd; g.epi = GEMM_EPI_BIAS;
+            g.w = w.wq; g.bias = w.bq; g.c = qkv; g.N = Hd;
+            CUDA_TRY(launch_gemm_tc(g, st));
+            g.w = w.wk; g.bias = w.bk; g.c = qkv + (size_t)Hd * 2; g.N = KVd;
+            CUDA_TRY(launch_gemm_tc(g, st));
+            g.w = w.wv; g.bias = w.bv; g.c = qkv + (size_t)(Hd + KVd) * 2; g.N = KVd;
+            CUDA_TRY(launch_gemm_tc(g, st));
+        }
+        {
+            RopeAppendParams ra{};
+            ra.qkv = qkv; ra.q = s->qbuf; ra.kv = kv; ra.positions = s->pos; ra.seq_ids = s->seq;
+            ra.rope_cos = s->io.rope_cos; ra.rope_sin = s->io.rope_sin;
+            ra.n_rows = n_rows; ra.n_heads = c.n_heads; ra.n_kv_heads = c.n_kv_heads; ra.head_dim = c.head_dim; ra.rope = !gpt2;
+            CUDA_TRY(launch_rope_append(ra, st));
+        }
+        {
+            AttnParams a{};
+            a.q = s->qbuf; a.kv = kv; a.positions = s->pos; a.seq_ids = s->seq;
+            a.n_rows = n_rows; a.n_heads = c.n_heads; a.n_kv_heads = c.n_kv_heads; a.head_dim = c.head_dim;
+            a.n_splits = splits; a.part_o = s->part_o; a.part_ml = s->part_ml; a.counters = s->attn_counters;
+            a.out = s->attn_out;
+            CUDA_TRY(launch_attn_decode(0, a, st));
+        }
+        {   // o-proj + residual (in place on the residual stream)
+            GemmTcParams g{};
+            g.a = s->attn_out; g.w = w.wo; g.bias = w.bo; g.c = s->h; g.M = n_rows; g.N = c.hidden; g.K = Hd;
+            g.ldc = c.hidden; g.epi = GEMM_EPI_RESIDUAL;
+            CUDA_TRY(launch_gemm_tc(g, st));
+        }
+        CUDA_TRY(launch_norm_rows(s->h, w.norm2_w, w.norm2_b, s->xn, n_rows, c.hidden, norm, c.norm_eps, st));
+        {
+            GemmTcParams g{};
+            g.a = s->xn; g.c = s->act; g.M = n_rows; g.N = c.ffn; g.K = c.hidden; g.ldc = c.ffn;
+            if (gpt2) { g.w = w.w_up; g.bias = w.b_up; g.epi = GEMM_EPI_GELU; }
+            else { g.w = w.w_gate; g.w2 = w.w_up; g.epi = GEMM_EPI_SWIGLU; }
+            CUDA_TRY(launch_gemm_tc(g, st));
+        }
+        {
+            GemmTcParams g{};
+            g.a = s->act; g.w = w.w_down; g.bias = w.b_down; g.c = s->h; g.M = n_rows; g.N = c.hidden; g.K = c.ffn;
+            g.ldc = c.hidden; g.epi = GEMM_EPI_RESIDUAL;
+            CUDA_TRY(launch_gemm_tc(g, st));
+        }
+    }
+    if (c.has_head && n_logit_rows > 0) {
+        GemvParams p{};
+        p.x = s->h; p.row_map = s->logit_rows; p.n_rows = n_logit_rows; p.K = c.hidden;
+        p.norm = norm; p.norm_w = s->io.final_norm_w; p.norm_b = s->io.final_norm_b; p.eps = c.norm_eps;
+        p.w[0] = s->io.lm_head; p.n[0] = c.vocab; p.epi = EPI_LOGITS;
+        p.logits = s->logits; p.arg_val = s->arg_val; p.arg_idx = s->arg_idx; p.counter = s->arg_counter;
+        p.next_token = s->next_tok;
+        if (gemv_grid_size(0, p, s->num_sms) > s->arg_grid_cap) return fail("internal: argmax scratch too small");
+        CUDA_TRY(launch_gemv(0, p, s->num_sms, st));
+    }
+    return 0;
+}
+
+static bool prefill_eligible(const dllm_shard* s, int n_rows) {
+    static const bool off = [] { const char* e = getenv("DLLM_PREFILL_GEMM"); return e && e[0] == '0'; }();
+    const dllm_shard_config& c = s->cfg;
+    return !off && c.dtype == DLLM_DTYPE_BF16 && n_rows > 16 && s->xn && c.n_layers > 0 &&
+           c.hidden % 8 == 0 && c.ffn % 8 == 0 && (c.n_heads * c.head_dim) % 8 == 0;
+}
+
 // Replay (capturing on first use) the graph of one step; large row counts launch directly.
 static int run_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advance, cudaStream_t st) {
     constexpr int kGraphMaxRows = 64;
@@ -569,6 +658,8 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
     }
     if (mk_eligible(s, n_rows, nl, logit_rows == nullptr)) {
         if (run_megakernel(s, n_rows, 1, false, st)) return 1;
+    } else if (prefill_eligible(s, n_rows)) {
+        if (enqueue_prefill(s, n_rows, nl, st)) return 1;
     } else if (run_step(s, n_rows, nl, false, st)) {
         return 1;
     }
@@ -648,6 +739,18 @@ extern "C" int dllm_op_gemv(int32_t dtype, const void* d_x, const void* d_w, con
     p.x = d_x; p.n_rows = n_rows; p.K = k; p.norm = NORM_NONE;
     p.w[0] = d_w; p.b[0] = d_bias; p.n[0] = n_out; p.epi = EPI_RESIDUAL; p.y = d_y; p.accumulate = accumulate;
     CUDA_TRY(launch_gemv(dtype, p, sms, (cudaStream_t)stream));
+    return 0;
+}
+
+extern "C" int dllm_op_gemm(const void* d_x, const void* d_w, const void* d_bias, void* d_y, int32_t m, int32_t n_out,
+                            int32_t k, int32_t accumulate, void* stream) {
+    if (!d_x || !d_w || !d_y || m <= 0 || n_out <= 0 || k <= 0) return fail("dllm_op_gemm: bad argument");
+    if (k % 8 || n_out % 2) return fail("dllm_op_gemm: k must be a multiple of 8 and n_out even");
+    if (dllm_device_count() == 0) return fail("dllm_op_gemm: no CUDA device (this library has no CPU path)");
+    GemmTcParams g{};
+    g.a = d_x; g.w = d_w; g.bias = d_bias; g.c = d_y; g.M = m; g.N = n_out; g.K = k; g.ldc = n_out;
+    g.epi = accumulate ? GEMM_EPI_RESIDUAL : GEMM_EPI_BIAS;
+    CUDA_TRY(launch_gemm_tc(g, (cudaStream_t)stream));
     return 0;
 }
 

@@ -55,6 +55,7 @@ SIGNATURES = {
     "dllm_shard_decode_loop": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
     "dllm_handoff_peer_copy": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _sz, _vp]),
     "dllm_op_gemv": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
+    "dllm_op_gemm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "dllm_op_decode_attention_scratch_bytes": (_sz, [_i32, _i32, _i32, _i32]),
     "dllm_op_decode_attention": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _vp, _vp, _i32, _i32, _i32, _i32,
                                            _i32, _vp, _vp, _vp]),

@@ -177,6 +177,12 @@ DLLM_API int dllm_handoff_peer_copy(void* dst_ptr, int dst_device, const void* s
 DLLM_API int dllm_op_gemv(int32_t dtype, const void* d_x, const void* d_w, const void* d_bias, void* d_y,
                  int32_t n_rows, int32_t n_out, int32_t k, int32_t accumulate, void* stream);
 
+/* y[m, n] (+)= sum_k x[m, k] * w[n, k] (+ bias[n]) for many rows: the prefill GEMM (TMA-fed tcgen05 tiles, fp32
+ * accumulation in tensor memory).  bf16 only; x [m, k], w [n, k], y [m, n] device memory; k a multiple of 8,
+ * n even.  Same contract as dllm_op_gemv, which is the decode (few rows) form of the same product. */
+DLLM_API int dllm_op_gemm(const void* d_x, const void* d_w, const void* d_bias, void* d_y, int32_t m, int32_t n_out,
+                 int32_t k, int32_t accumulate, void* stream);
+
 /* Split-K flash-decoding attention over a paged KV cache (GQA).
  *   d_q [n_rows, H, hd] `dtype`; d_kpool/d_vpool [num_pages, KV, page_size, hd] `dtype`;
  *   d_block_table int32 [max_seqs, pages_per_seq]; d_positions / d_seq_ids int32 [n_rows]
