@@ -100,6 +100,18 @@ cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* 
                              cudaStream_t st);
 cudaError_t launch_rope_append(const RopeAppendParams& p, cudaStream_t st);
 
+// Causal prefill attention over the paged cache (prefill_attention.cu): rows are `n_seqs` runs of `rows_per_seq`
+// consecutive positions of one sequence each (row = b * rows_per_seq + i), K/V of the run already appended.
+struct PrefillAttnParams {
+    const void* q;           // [R, H, hd] bf16
+    PagedKV kv;
+    const int32_t* positions;
+    const int32_t* seq_ids;
+    void* out;               // [R, H*hd] bf16
+    int32_t n_seqs, rows_per_seq, n_heads, n_kv_heads, head_dim;
+};
+cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st);
+
 // Each returns cudaGetLastError() of its launch.  dtype: 0 = bf16, 1 = fp32.
 cudaError_t gemv_init_device();  // once per device, outside stream capture
 cudaError_t launch_gemv(int dtype, const GemvParams& p, int num_sms, cudaStream_t s);

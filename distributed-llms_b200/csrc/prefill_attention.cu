@@ -1,0 +1,224 @@
+// Causal prefill attention over the paged KV cache, flash-attention style.
+//
+// One CTA = 64 consecutive query rows of one sequence x one query head; its 4 warps own 16 rows each.  The
+// sequence's K/V (already appended, rotary applied) are walked in 64-token tiles gathered from the pages into
+// shared memory with cp.async; S = Q.K^T and O += P.V run on the tensor cores (mma.sync m16n8k16, bf16 in, fp32
+// accumulate), the softmax is the usual online one in fp32 registers.  Rounding follows HF eager attention: the
+// score is rounded to bf16 after the dot product and after scaling, P is bf16 for the second product.
+// (The dense projections around it are the tcgen05 GEMMs of prefill_gemm.cu; attention is ~2 % of the prefill
+// flops at these lengths, so it uses the simpler warp-level tensor-core path for now.)
+#include <float.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace dllm {
+
+namespace {
+
+constexpr int kQT = 64, kKT = 64, kThreads = 128;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <int HD>
+__global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAttnParams p) {
+    constexpr int LD = HD + 8;  // padded rows: ldmatrix reads 8 rows x 16 bytes without bank conflicts
+    extern __shared__ __align__(16) unsigned char smem_dyn[];
+    bf16* sQ = reinterpret_cast<bf16*>(smem_dyn);
+    bf16* sK = sQ + kQT * LD;
+    bf16* sV = sK + kKT * LD;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int b = blockIdx.z, h = blockIdx.y, qt = blockIdx.x;
+    const int H = p.n_heads, KV = p.n_kv_heads, kvh = h / (H / KV);
+    const int n = p.rows_per_seq;
+    const int row0 = b * n + qt * kQT;                 // first row of this tile in the call's row array
+    const int rows_here = min(kQT, n - qt * kQT);
+    const int seq = p.seq_ids[row0];
+    const int pos0 = p.positions[row0];                // positions in the run are consecutive
+    const int32_t* bt = p.kv.block_table + (size_t)seq * p.kv.pages_per_seq;
+    const int pmask = (1 << p.kv.page_shift) - 1;
+    const bf16* kpool = static_cast<const bf16*>(p.kv.kpool);
+    const bf16* vpool = static_cast<const bf16*>(p.kv.vpool);
+    const float scale = rsqrtf((float)HD);
+
+    // Q tile -> shared memory (rows past the end of the run are zero)
+    for (int i = threadIdx.x; i < kQT * (HD / 8); i += kThreads) {
+        const int r = i / (HD / 8), c = i % (HD / 8);
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (r < rows_here) v = ld_u4(static_cast<const bf16*>(p.q) + ((size_t)(row0 + r) * H + h) * HD + c * 8);
+        *reinterpret_cast<uint4*>(sQ + r * LD + c * 8) = v;
+    }
+
+    float m_lo = -FLT_MAX, m_hi = -FLT_MAX, l_lo = 0.f, l_hi = 0.f;  // rows g and g+8 of this warp's 16
+    float o[HD / 8][4];
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    const int q_lo = pos0 + warp * 16 + g, q_hi = q_lo + 8;   // absolute positions of the two rows
+    const int last_key = pos0 + rows_here - 1;                // keys beyond the tile's last row are never needed
+
+    for (int kt0 = 0; kt0 <= last_key; kt0 += kKT) {
+        __syncthreads();  // previous tile fully consumed (also orders the Q stores before the first reads)
+        for (int i = threadIdx.x; i < kKT * (HD / 8); i += kThreads) {
+            const int r = i / (HD / 8), c = i % (HD / 8);
+            const int tok = kt0 + r;
+            if (tok <= last_key) {
+                const int page = bt[tok >> p.kv.page_shift];
+                const size_t base = ((((size_t)page * KV + kvh) << p.kv.page_shift) + (tok & pmask)) * HD + c * 8;
+                cp_async16(sK + r * LD + c * 8, kpool + base);
+                cp_async16(sV + r * LD + c * 8, vpool + base);
+            } else {
+                *reinterpret_cast<uint4*>(sK + r * LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(sV + r * LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+        cp_async_wait_all();
+        __syncthreads();
+        if (kt0 > pos0 + warp * 16 + 15) continue;  // every key of this tile lies after this warp's rows (warp-uniform)
+
+        // ---- S = Q K^T : 16 rows x 64 keys per warp ----
+        float s[kKT / 8][4];
+#pragma unroll
+        for (int i = 0; i < kKT / 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < HD / 16; ++ks) {
+            uint32_t a[4];
+            ldsm_x4(a, smem_u32(sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LD + ks * 16 + (lane >> 4) * 8));
+#pragma unroll
+            for (int nt = 0; nt < kKT / 8; nt += 2) {
+                uint32_t bfr[4];  // two key tiles of 8: {b0, b1} each
+                ldsm_x4(bfr, smem_u32(sK + (nt * 8 + (lane & 7) + (lane >> 4) * 8) * LD + ks * 16 + ((lane >> 3) & 1) * 8));
+                mma_bf16(s[nt], a, bfr[0], bfr[1]);
+                mma_bf16(s[nt + 1], a, bfr[2], bfr[3]);
+            }
+        }
+        // ---- scale, causal mask, online softmax ----
+        float mx_lo = -FLT_MAX, mx_hi = -FLT_MAX;
+#pragma unroll
+        for (int nt = 0; nt < kKT / 8; ++nt) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int key = kt0 + nt * 8 + 2 * t + (e & 1);
+                const int qpos = (e < 2) ? q_lo : q_hi;
+                float v = bf16_round(bf16_round(s[nt][e]) * scale);
+                if (key > qpos) v = -FLT_MAX;
+                s[nt][e] = v;
+            }
+            mx_lo = fmaxf(mx_lo, fmaxf(s[nt][0], s[nt][1]));
+            mx_hi = fmaxf(mx_hi, fmaxf(s[nt][2], s[nt][3]));
+        }
+        mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 1));
+        mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 2));
+        mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 1));
+        mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 2));
+        const float mn_lo = fmaxf(m_lo, mx_lo), mn_hi = fmaxf(m_hi, mx_hi);
+        const float c_lo = expf(m_lo - mn_lo), c_hi = expf(m_hi - mn_hi);
+        float sum_lo = 0.f, sum_hi = 0.f;
+        // P as A fragments (16 rows x 16 keys each), split into a bf16 head and a bf16 remainder: two MMAs per V tile
+        // keep ~16 bits of P, like the fp32 probabilities of the decode kernels (HF itself rounds P to bf16 once)
+        uint32_t pfr[kKT / 16][4], pfl[kKT / 16][4];
+#pragma unroll
+        for (int nt = 0; nt < kKT / 8; ++nt) {
+            const float p0 = s[nt][0] == -FLT_MAX ? 0.f : expf(s[nt][0] - mn_lo);
+            const float p1 = s[nt][1] == -FLT_MAX ? 0.f : expf(s[nt][1] - mn_lo);
+            const float p2 = s[nt][2] == -FLT_MAX ? 0.f : expf(s[nt][2] - mn_hi);
+            const float p3 = s[nt][3] == -FLT_MAX ? 0.f : expf(s[nt][3] - mn_hi);
+            sum_lo += p0 + p1;
+            sum_hi += p2 + p3;
+            // C fragment of key tile nt -> A fragment: tiles 2j and 2j+1 are the two k-halves of A step j
+            pfr[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0, p1);
+            pfr[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2, p3);
+            pfl[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0 - bf16_round(p0), p1 - bf16_round(p1));
+            pfl[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2 - bf16_round(p2), p3 - bf16_round(p3));
+        }
+        sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 1);
+        sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 2);
+        sum_hi += __shfl_xor_sync(0xffffffffu, sum_hi, 1);
+        sum_hi += __shfl_xor_sync(0xffffffffu, sum_hi, 2);
+        l_lo = l_lo * c_lo + sum_lo;
+        l_hi = l_hi * c_hi + sum_hi;
+        m_lo = mn_lo;
+        m_hi = mn_hi;
+#pragma unroll
+        for (int i = 0; i < HD / 8; ++i) {
+            o[i][0] *= c_lo;
+            o[i][1] *= c_lo;
+            o[i][2] *= c_hi;
+            o[i][3] *= c_hi;
+        }
+        // ---- O += P V : V[token][col] is read transposed (ldmatrix.trans) ----
+#pragma unroll
+        for (int kk = 0; kk < kKT / 16; ++kk) {
+            // A fragment order is (row g, k lo), (row g+8, k lo), (row g, k hi), (row g+8, k hi)
+            const uint32_t a[4] = {pfr[kk][0], pfr[kk][1], pfr[kk][2], pfr[kk][3]};
+            const uint32_t al[4] = {pfl[kk][0], pfl[kk][1], pfl[kk][2], pfl[kk][3]};
+#pragma unroll
+            for (int nt = 0; nt < HD / 8; nt += 2) {
+                uint32_t bfr[4];
+                ldsm_x4_trans(bfr, smem_u32(sV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LD + nt * 8 + (lane >> 4) * 8));
+                mma_bf16(o[nt], a, bfr[0], bfr[1]);
+                mma_bf16(o[nt + 1], a, bfr[2], bfr[3]);
+                mma_bf16(o[nt], al, bfr[0], bfr[1]);
+                mma_bf16(o[nt + 1], al, bfr[2], bfr[3]);
+            }
+        }
+    }
+
+    // ---- normalise and store ----
+    const float inv_lo = l_lo > 0.f ? 1.0f / l_lo : 0.f, inv_hi = l_hi > 0.f ? 1.0f / l_hi : 0.f;
+    const int r_lo = warp * 16 + g, r_hi = r_lo + 8;
+    bf16* out = static_cast<bf16*>(p.out);
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) {
+        const int col = h * HD + i * 8 + 2 * t;
+        if (r_lo < rows_here)
+            *reinterpret_cast<uint32_t*>(out + (size_t)(row0 + r_lo) * H * HD + col) = pack_bf16(o[i][0] * inv_lo, o[i][1] * inv_lo);
+        if (r_hi < rows_here)
+            *reinterpret_cast<uint32_t*>(out + (size_t)(row0 + r_hi) * H * HD + col) = pack_bf16(o[i][2] * inv_hi, o[i][3] * inv_hi);
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {
+    if (p.n_seqs <= 0 || p.rows_per_seq <= 0 || p.n_heads % p.n_kv_heads) return cudaErrorInvalidValue;
+    dim3 grid((p.rows_per_seq + kQT - 1) / kQT, p.n_heads, p.n_seqs);
+    const size_t smem = (size_t)(kQT + 2 * kKT) * (p.head_dim + 8) * 2;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)((kQT + 2 * kKT) * (128 + 8) * 2));
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    switch (p.head_dim) {
+        case 32: prefill_attn_kernel<32><<<grid, kThreads, smem, st>>>(p); break;
+        case 64: prefill_attn_kernel<64><<<grid, kThreads, smem, st>>>(p); break;
+        case 128: prefill_attn_kernel<128><<<grid, kThreads, smem, st>>>(p); break;
+        default: return cudaErrorInvalidValue;
+    }
+    count_launch();
+    return cudaGetLastError();
+}
+
+}  // namespace dllm

@@ -513,7 +513,30 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
 }
 
 // Prefill (many rows, bf16): the dense contractions run as tcgen05 GEMMs, the rest as row-wise kernels.
-static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, cudaStream_t st) {
+// If the caller's positions / seq ids are host-readable and the rows are `n_seqs` runs of `len` consecutive positions of
+// one sequence each (what a [B, T] prompt chunk is), return true and the run shape: the flash-style prefill attention
+// kernel applies.  Otherwise the per-row split-K kernel is used.
+static bool detect_runs(const int32_t* positions, const int32_t* seq_ids, int n_rows, int* n_seqs, int* len) {
+    cudaPointerAttributes ap{}, as{};
+    if (cudaPointerGetAttributes(&ap, positions) != cudaSuccess || cudaPointerGetAttributes(&as, seq_ids) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    if ((ap.type != cudaMemoryTypeHost && ap.type != cudaMemoryTypeUnregistered) ||
+        (as.type != cudaMemoryTypeHost && as.type != cudaMemoryTypeUnregistered))
+        return false;
+    int run = 1;
+    while (run < n_rows && seq_ids[run] == seq_ids[0] && positions[run] == positions[0] + run) ++run;
+    if (n_rows % run) return false;
+    for (int b = 0; b < n_rows / run; ++b)
+        for (int i = 0; i < run; ++i)
+            if (seq_ids[b * run + i] != seq_ids[b * run] || positions[b * run + i] != positions[b * run] + i) return false;
+    *n_seqs = n_rows / run;
+    *len = run;
+    return true;
+}
+
+static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_seqs, int run_len, cudaStream_t st) {
     const dllm_shard_config& c = s->cfg;
     const bool gpt2 = c.arch == DLLM_ARCH_GPT2;
     const int norm = gpt2 ? NORM_LAYER : NORM_RMS;
@@ -547,7 +570,13 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, cudaStre
             ra.n_rows = n_rows; ra.n_heads = c.n_heads; ra.n_kv_heads = c.n_kv_heads; ra.head_dim = c.head_dim; ra.rope = !gpt2;
             CUDA_TRY(launch_rope_append(ra, st));
         }
-        {
+        if (run_len > 0) {   // causal flash-style attention over each run of consecutive positions
+            PrefillAttnParams a{};
+            a.q = s->qbuf; a.kv = kv; a.positions = s->pos; a.seq_ids = s->seq; a.out = s->attn_out;
+            a.n_seqs = run_seqs; a.rows_per_seq = run_len; a.n_heads = c.n_heads; a.n_kv_heads = c.n_kv_heads;
+            a.head_dim = c.head_dim;
+            CUDA_TRY(launch_prefill_attn(a, st));
+        } else {
             AttnParams a{};
             a.q = s->qbuf; a.kv = kv; a.positions = s->pos; a.seq_ids = s->seq;
             a.n_rows = n_rows; a.n_heads = c.n_heads; a.n_kv_heads = c.n_kv_heads; a.head_dim = c.head_dim;
@@ -659,7 +688,10 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
     if (mk_eligible(s, n_rows, nl, logit_rows == nullptr)) {
         if (run_megakernel(s, n_rows, 1, false, st)) return 1;
     } else if (prefill_eligible(s, n_rows)) {
-        if (enqueue_prefill(s, n_rows, nl, st)) return 1;
+        int run_seqs = 0, run_len = 0;
+        static const bool fa_off = [] { const char* e = getenv("DLLM_PREFILL_ATTN"); return e && e[0] == '0'; }();
+        if (fa_off || !detect_runs(positions, seq_ids, n_rows, &run_seqs, &run_len)) run_seqs = run_len = 0;
+        if (enqueue_prefill(s, n_rows, nl, run_seqs, run_len, st)) return 1;
     } else if (run_step(s, n_rows, nl, false, st)) {
         return 1;
     }
