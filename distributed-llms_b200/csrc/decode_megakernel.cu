@@ -158,7 +158,7 @@ struct WIter {
     int step, ph, j, st, st_end;
     // cached at seek time so that advancing by one stage needs no division and no phase-table lookup
     const unsigned char* wp;
-    int n_panels, K, panel;
+    int n_panels, K, panel, xg;
 };
 
 __device__ __forceinline__ int local_panels(const MkPhase& ph) {
@@ -168,6 +168,7 @@ __device__ __forceinline__ int local_panels(const MkPhase& ph) {
 
 struct Ctx {
     int n_steps, n_phases;
+    const unsigned char* act_x;  // activation rows in fragment layout (xg phases)
     const MkPhase* phases;  // shared-memory copy
     const int* units;       // shared: (panel slot, k-split) units this CTA owns in each phase (0 = not a weight phase)
     int warp, lane;
@@ -201,16 +202,21 @@ __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
     }
 }
 
-__device__ __forceinline__ const unsigned char* stage_src(const Ctx& c, const WIter& it, uint32_t* bytes) {
-    return it.wp + mk_stage_offset(it.n_panels, it.K, it.panel, it.st, bytes);
-}
-
 __device__ __forceinline__ void issue_stage(const Ctx& c, const WIter& it, int slot) {
     if (c.lane == 0) {
         uint32_t bytes;
-        const unsigned char* src = stage_src(c, it, &bytes);
-        mbar_expect_tx(c.full + slot * 8, bytes);
-        bulk_g2s(c.ring + slot * kStageBytes, src, bytes, c.full + slot * 8);
+        const uint32_t dst = c.ring + slot * kStageBytes, bar = c.full + slot * 8;
+        if (!it.xg) {
+            const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, kStageBytes, &bytes);
+            mbar_expect_tx(bar, bytes);
+            bulk_g2s(dst, src, bytes, bar);
+        } else {
+            // half-size stage: 128 k of the panel, then the same 128 k of the (up to 8) input rows
+            const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, kStageBytes / 2, &bytes);
+            mbar_expect_tx(bar, bytes + kStageBytes / 2);
+            bulk_g2s(dst, src, bytes, bar);
+            bulk_g2s(dst + kStageBytes / 2, c.act_x + (size_t)it.st * (kStageBytes / 2), kStageBytes / 2, bar);
+        }
     }
 }
 
@@ -227,14 +233,15 @@ __device__ __forceinline__ void witer_next(const Ctx& c, WIter& it) {
 // microseconds of traffic) cannot cover.
 __device__ __forceinline__ void prefetch_next_phase(const Ctx& c, int step, int phi, int budget) {
     if (c.lane != 0 || budget <= 0) return;
-    WIter it = {step, phi + 1, 0, 0, 0, nullptr, 0, 0, 0};
+    WIter it = {step, phi + 1, 0, 0, 0, nullptr, 0, 0, 0, 0};
     witer_seek(c, it);
     const int ph0 = it.ph, step0 = it.step;
     while (it.step < c.n_steps && it.ph == ph0 && it.step == step0 && budget > 0) {
         uint32_t b0;
-        const unsigned char* src = it.wp + mk_stage_offset(it.n_panels, it.K, it.panel, it.st, &b0);
-        size_t bytes = (size_t)(it.st_end - it.st) * kStageBytes;
-        const size_t panel_left = (size_t)it.K * 16 - (size_t)it.st * kStageBytes;
+        const uint32_t sbytes = it.xg ? kStageBytes / 2 : kStageBytes;
+        const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, sbytes, &b0);
+        size_t bytes = (size_t)(it.st_end - it.st) * sbytes;
+        const size_t panel_left = (size_t)it.K * 16 - (size_t)it.st * sbytes;
         if (bytes > panel_left) bytes = panel_left;
         if (bytes > (size_t)budget) bytes = (size_t)budget & ~(size_t)15;
         if (bytes >= 16)
@@ -698,6 +705,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     c.n_steps = p.n_steps;
     c.n_phases = p.n_phases;
     c.phases = phases;
+    c.act_x = static_cast<const unsigned char*>(p.act);
     c.units = s_units;
     c.warp = warp;
     c.lane = lane;
@@ -705,7 +713,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     c.full = full_all + warp * p.stages * 8;
 
     // prime this warp's ring: the first `stages` entries of its static sequence
-    WIter prod = {0, 0, 0, 0, 0, nullptr, 0, 0, 0};
+    WIter prod = {0, 0, 0, 0, 0, nullptr, 0, 0, 0, 0};
     witer_seek(c, prod);
     for (int i = 0; i < p.stages && prod.step < p.n_steps; ++i) {
         issue_stage(c, prod, i);
@@ -782,7 +790,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             if (ph.kind == MK_QKV) stage_rows(p, p.h, ph.K, p.norm, L->norm1_w, L->norm1_b, xs, ldx, red);
             else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) stage_rows(p, p.h, ph.K, p.norm, L->norm2_w, L->norm2_b, xs, ldx, red);
             else if (ph.kind == MK_HEAD) stage_rows(p, p.h, ph.K, p.norm, p.final_norm_w, p.final_norm_b, xs, ldx, red);
-            else if (ph.kind == MK_DOWN) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
+            else if (ph.kind == MK_DOWN) {
+                if (!ph.xg) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
+            }
             else stage_attn_combine(p, sc, xs, ldx, reinterpret_cast<float*>(at.k));
             __syncthreads();
             if (tr) tr[1] = clock64();
@@ -819,15 +829,20 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     mbar_wait(c.full + slot * 8, (consumed / (unsigned)p.stages) & 1u);
                     if (tr) tq1 = clock64();
                     const uint32_t sbase = c.ring + slot * kStageBytes + (uint32_t)(lane * 16);  // [32-k block][row g][chunk t4]
-                    const int k0 = st * kStageK;
-                    const int nkb = min(kStageK, K - k0) >> 5;  // 32-k blocks in this stage
-                    const uint32_t xlo = xrow_lo + (uint32_t)((k0 + t4 * 8) * 2);
+                    const int stage_k = ph.xg ? kStageK / 2 : kStageK;
+                    const int k0 = st * stage_k;
+                    const int nkb = min(stage_k, K - k0) >> 5;  // 32-k blocks in this stage
+                    // input rows: from the shared-memory copy (row-major), or from the second half of the stage
+                    // (fragment layout: [32-k block][row g][chunk t4], 512 bytes per block)
+                    const uint32_t xstep = ph.xg ? 512u : 64u;
+                    const uint32_t xlo = ph.xg ? c.ring + slot * kStageBytes + kStageBytes / 2 + (uint32_t)(lane * 16)
+                                               : xrow_lo + (uint32_t)((k0 + t4 * 8) * 2);
                     const uint32_t xhi = xrow_hi + (uint32_t)((k0 + t4 * 8) * 2);
                     // lane (g, t4) holds 8 consecutive k of weight row g and of batch row g: two mma k-steps per block
 #define DLLM_MK_BLOCK2(KB)                                                                          \
     {                                                                                               \
         const uint4 wa = lds_u4(sbase + (KB) * 512), wb = lds_u4(sbase + (KB) * 512 + 512);         \
-        const uint4 xa = lds_u4(xlo + (KB) * 64), xb = lds_u4(xlo + (KB) * 64 + 64);                \
+        const uint4 xa = lds_u4(xlo + (KB) * xstep), xb = lds_u4(xlo + (KB) * xstep + xstep);       \
         uint4 ha = make_uint4(0u, 0u, 0u, 0u), hb = ha;                                             \
         if (HI) {                                                                                   \
             ha = lds_u4(xhi + (KB) * 64);                                                           \
@@ -845,7 +860,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         for (; kb + 1 < nkb; kb += 2) DLLM_MK_BLOCK2(kb)
                         if (kb < nkb) {
                             const uint4 wa = lds_u4(sbase + kb * 512);
-                            const uint4 xa = lds_u4(xlo + kb * 64);
+                            const uint4 xa = lds_u4(xlo + kb * xstep);
                             uint4 ha = make_uint4(0u, 0u, 0u, 0u);
                             if (HI) ha = lds_u4(xhi + kb * 64);
                             mma_bf16(acc, xa.x, ha.x, xa.y, ha.y, wa.x, wa.y);
@@ -928,13 +943,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 } else if (ph.kind == MK_GATEUP) {
                     const int n = panel * 4 + i;
                     const float gg = bf16_round(v0), uu = bf16_round(v1);
-                    static_cast<bf16*>(p.act)[(size_t)r * ph.n0 + n] = __float2bfloat16_rn(bf16_round(silu_f(gg)) * uu);
+                    const size_t ai = p.act_xlayout ? ((size_t)(n >> 5) * 8 + r) * 32 + (n & 31) : (size_t)r * ph.n0 + n;
+                    static_cast<bf16*>(p.act)[ai] = __float2bfloat16_rn(bf16_round(silu_f(gg)) * uu);
                 } else {
                     const int n = panel * 8 + 2 * i;  // rows n, n+1
                     if (n >= ph.n0) continue;
                     const bool valid1 = n + 1 < ph.n0;
                     if (ph.kind == MK_FC_GELU) {
-                        bf16* y = static_cast<bf16*>(p.act) + (size_t)r * ph.n0 + n;
+                        bf16* y = static_cast<bf16*>(p.act) +
+                                  (p.act_xlayout ? ((size_t)(n >> 5) * 8 + r) * 32 + (n & 31) : (size_t)r * ph.n0 + n);
                         y[0] = __float2bfloat16_rn(gelu_new_f(bf16_round(v0 + (L->b_up ? ldf(L->b_up, n) : 0.f))));
                         if (valid1) y[1] = __float2bfloat16_rn(gelu_new_f(bf16_round(v1 + (L->b_up ? ldf(L->b_up, n + 1) : 0.f))));
                     } else if (ph.kind == MK_OPROJ || ph.kind == MK_DOWN) {
@@ -1059,9 +1076,8 @@ __global__ void pack_panels_kernel(const PackJob j) {
         }
         uint4 v = make_uint4(0u, 0u, 0u, 0u);
         if (src) v = *reinterpret_cast<const uint4*>(src + (size_t)kc * 8);
-        uint32_t sbytes;
-        // inside a stage: [32-k block][row][4 chunks of 8 k]: the 32 lanes of a warp read 512 contiguous bytes
-        const size_t off = mk_stage_offset(j.n_panels, j.K, panel, kc >> 5, &sbytes) + (size_t)((kc & 31) >> 2) * 512 + r * 64 + (kc & 3) * 16;
+        // [panel][32-k block][row][4 chunks of 8 k]: the 32 lanes of a warp read 512 contiguous bytes
+        const size_t off = (size_t)panel * j.K * 16 + (size_t)(kc >> 2) * 512 + r * 64 + (kc & 3) * 16;
         *reinterpret_cast<uint4*>(static_cast<unsigned char*>(j.dst) + off) = v;
     }
 }

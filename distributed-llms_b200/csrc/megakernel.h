@@ -29,7 +29,11 @@ struct MkPhase {
     int16_t kind;        // MkKind
     int16_t layer;
     int16_t ksplit;      // warps of one CTA that share a panel (split along K, summed in fixed order)
-    int16_t n_stages;    // ceil(K / 256)
+    int16_t n_stages;    // ceil(K / 256); K / 128 when xg
+    int16_t xg;          // 1: the input rows are streamed from global memory with the weights (half-size stages:
+                         //    2 KB of weights + 2 KB of rows in fragment layout) instead of being staged in shared
+                         //    memory by the prologue -- used for the down projection when R x ffn does not fit
+    int16_t pad_;
 };
 
 struct MkLayer {
@@ -46,7 +50,8 @@ struct MkParams {
     float eps;
     void* h;                 // [R, d] residual stream
     void* q;                 // [R, H*hd]
-    void* act;               // [R, ffn]
+    void* act;               // [R, ffn]; with act_xlayout: [ffn / 32][8 rows][32] (the fragment order the down phase streams)
+    int32_t act_xlayout;
     void* attn_out;          // [R, H*hd] merged attention output
     unsigned* attn_counters; // [R, KV] tickets, zero between phases
     float* part_o;           // [R, H, S, hd]
@@ -69,13 +74,12 @@ struct MkParams {
 };
 
 // Packed layout, panel-major: a panel's stages are consecutive, so any k-range of a panel (one warp unit) is
-// one contiguous run -- a single L2 prefetch instruction covers it.
-__host__ __device__ inline size_t mk_stage_offset(int n_panels, int K, int panel, int st, uint32_t* bytes) {
-    (void)n_panels;
+// one contiguous run -- a single L2 prefetch instruction covers it.  `stage_bytes` = 4096 (256 k) or 2048 (128 k).
+__host__ __device__ inline size_t mk_stage_offset(int K, int panel, int st, uint32_t stage_bytes, uint32_t* bytes) {
     const size_t panel_bytes = (size_t)K * 16;
-    const size_t off = (size_t)st * MK_STAGE_BYTES;
+    const size_t off = (size_t)st * stage_bytes;
     const size_t left = panel_bytes - off;
-    *bytes = (uint32_t)(left < (size_t)MK_STAGE_BYTES ? left : (size_t)MK_STAGE_BYTES);
+    *bytes = (uint32_t)(left < (size_t)stage_bytes ? left : (size_t)stage_bytes);
     return (size_t)panel * panel_bytes + off;
 }
 

@@ -89,6 +89,9 @@ struct dllm_shard {
     uint32_t *attn_counters = nullptr, *arg_counter = nullptr;
     // persistent decode kernel (bf16, <= 4 rows)
     MkPhase* mk_phases = nullptr;
+    MkPhase* mk_phases_xg = nullptr;  // same step with the down projection in xg mode (rows streamed from global)
+    int mk_part_units_xg = 1, mk_k_max_xg = 0;
+    bool mk_xg_ok = false;
     MkLayer* mk_layers = nullptr;
     unsigned* mk_sync = nullptr;  // [0] barrier, [1] done, [2] argmax ticket
     void* mk_packed = nullptr;    // streaming-layout copy of the weights (megakernel.h)
@@ -172,8 +175,8 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->h, (size_t)c.max_rows * c.hidden * s->esz);
     add(&s->qbuf, (size_t)c.max_rows * Hd * s->esz);
     add(&s->attn_out, (size_t)c.max_rows * Hd * s->esz);
-    add(&s->act, (size_t)c.max_rows * c.ffn * s->esz);
-    const bool prefill_bufs = c.dtype == DLLM_DTYPE_BF16 && c.max_rows > 16;
+    add(&s->act, (size_t)std::max(c.max_rows, 8) * c.ffn * s->esz);
+    const bool prefill_bufs = c.dtype == DLLM_DTYPE_BF16 && c.max_rows > 4;
     add(&s->xn, prefill_bufs ? (size_t)c.max_rows * c.hidden * s->esz : 0);
     add(&s->qkv_tmp, prefill_bufs ? (size_t)c.max_rows * (c.n_heads + 2 * c.n_kv_heads) * c.head_dim * s->esz : 0);
     add(&s->ids, (size_t)c.max_rows * 4);
@@ -194,6 +197,7 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->arg_counter, 4);
     const int mk_phase_cap = 5 * c.n_layers + 2;
     add(&s->mk_phases, (size_t)mk_phase_cap * sizeof(MkPhase));
+    add(&s->mk_phases_xg, (size_t)mk_phase_cap * sizeof(MkPhase));
     add(&s->mk_layers, (size_t)(c.n_layers > 0 ? c.n_layers : 1) * sizeof(MkLayer));
     add(&s->mk_sync, 16);
     {   // the persistent decode kernel streams a packed copy of the weights (bf16, every K a multiple of 32)
@@ -298,6 +302,23 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
         s->mk_k_max = std::max(std::max(c.hidden, Hd), c.ffn);
         if (me == cudaSuccess) me = cudaMemcpy(s->mk_phases, ph.data(), ph.size() * sizeof(MkPhase), cudaMemcpyHostToDevice);
         if (me == cudaSuccess) me = cudaMemcpy(s->mk_layers, ly.data(), ly.size() * sizeof(MkLayer), cudaMemcpyHostToDevice);
+        // variant: down projection with its input rows streamed from global memory (half-size stages)
+        s->mk_xg_ok = c.ffn % 128 == 0;
+        if (s->mk_xg_ok) {
+            std::vector<MkPhase> px = ph;
+            int pu = 1;
+            for (auto& q : px) {
+                if (q.kind == MK_DOWN) {
+                    q.xg = 1;
+                    q.n_stages = (int16_t)(q.K / (MK_STAGE_K / 2));
+                    q.ksplit = (int16_t)mk_ksplit(q.n_panels, q.n_stages, G);
+                }
+                if (q.wp) pu = std::max(pu, ((q.n_panels + G - 1) / G) * (int)q.ksplit);
+            }
+            s->mk_part_units_xg = std::min(pu, 24);
+            s->mk_k_max_xg = std::max(c.hidden, Hd);
+            if (me == cudaSuccess) me = cudaMemcpy(s->mk_phases_xg, px.data(), px.size() * sizeof(MkPhase), cudaMemcpyHostToDevice);
+        }
         if (me == cudaSuccess) me = cudaDeviceSynchronize();
         s->mk_enabled = me == cudaSuccess;
         cudaGetLastError();
@@ -442,34 +463,44 @@ static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advanc
     return 0;
 }
 
-// One launch of the persistent decode kernel for `n_steps` steps (bf16, <= 4 rows, logits for every row).
-static bool mk_eligible(const dllm_shard* s, int n_rows, int n_logit_rows, bool identity_rows) {
-    if (!s->mk_enabled || !mk_supported(n_rows, s->cfg.n_heads, s->cfg.n_kv_heads, s->cfg.head_dim)) return false;
-    if (mk_max_splits(n_rows, s->cfg.n_heads, s->cfg.head_dim) < 1) return false;
-    {   // the rows' inputs must fit in shared memory next to at least two ring stages per warp
-        MkParams q{};
-        q.n_phases = s->mk_n_phases; q.n_rows = n_rows; q.k_max = s->mk_k_max; q.part_units = s->mk_part_units;
-        q.head_dim = s->cfg.head_dim; q.pages_per_seq = s->pages_per_seq;
-        if (mk_smem_bytes(q, 2) > (size_t)(227 * 1024 - 1536)) return false;
+// One launch of the persistent decode kernel for `n_steps` steps (bf16, <= 16 rows, logits for every row).
+// Returns 0 = not eligible, 1 = plain variant, 2 = variant with the down projection's rows streamed from global.
+static int mk_variant(const dllm_shard* s, int n_rows, int n_logit_rows, bool identity_rows) {
+    if (!s->mk_enabled || !mk_supported(n_rows, s->cfg.n_heads, s->cfg.n_kv_heads, s->cfg.head_dim)) return 0;
+    if (mk_max_splits(n_rows, s->cfg.n_heads, s->cfg.head_dim) < 1) return 0;
+    if (s->cfg.has_head && !(identity_rows && n_logit_rows == n_rows)) return 0;
+    MkParams q{};
+    q.n_phases = s->mk_n_phases; q.n_rows = n_rows; q.head_dim = s->cfg.head_dim; q.pages_per_seq = s->pages_per_seq;
+    q.k_max = s->mk_k_max; q.part_units = s->mk_part_units;
+    if (mk_smem_bytes(q, 2) <= (size_t)(227 * 1024 - 1536)) return 1;
+    if (s->mk_xg_ok && n_rows <= 8) {
+        q.k_max = s->mk_k_max_xg; q.part_units = s->mk_part_units_xg;
+        if (mk_smem_bytes(q, 2) <= (size_t)(227 * 1024 - 1536)) return 2;
     }
-    if (s->cfg.has_head && !(identity_rows && n_logit_rows == n_rows)) return false;
-    return true;
+    return 0;
+}
+
+static bool mk_eligible(const dllm_shard* s, int n_rows, int n_logit_rows, bool identity_rows) {
+    return mk_variant(s, n_rows, n_logit_rows, identity_rows) != 0;
 }
 
 static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, cudaStream_t st) {
     const dllm_shard_config& c = s->cfg;
+    const int variant = mk_variant(s, n_rows, n_rows, true);
+    if (variant == 0) return fail("internal: persistent kernel not eligible");
     MkParams p{};
-    p.phases = s->mk_phases; p.layers = s->mk_layers; p.n_phases = s->mk_n_phases;
+    p.phases = variant == 2 ? s->mk_phases_xg : s->mk_phases; p.layers = s->mk_layers; p.n_phases = s->mk_n_phases;
+    p.act_xlayout = variant == 2 ? 1 : 0;
     p.n_steps = n_steps; p.n_rows = n_rows;
     p.hidden = c.hidden; p.n_heads = c.n_heads; p.n_kv_heads = c.n_kv_heads; p.head_dim = c.head_dim;
-    p.vocab = c.vocab; p.k_max = s->mk_k_max;
+    p.vocab = c.vocab; p.k_max = variant == 2 ? s->mk_k_max_xg : s->mk_k_max;
     p.norm = c.arch == DLLM_ARCH_GPT2 ? NORM_LAYER : NORM_RMS; p.rope = c.arch != DLLM_ARCH_GPT2;
     long S = (s->num_sms + (long)n_rows * c.n_kv_heads - 1) / ((long)n_rows * c.n_kv_heads);
     const long s_cap = mk_max_splits(n_rows, c.n_heads, c.head_dim);
     if (S > s_cap) S = s_cap;
     while (S > 1 && (long)n_rows * c.n_heads * S > s->max_partials) --S;
     if (const char* e = getenv("DLLM_MK_SPLITS")) { long v = atol(e); if (v >= 1 && v <= s_cap && (long)n_rows * c.n_heads * v <= s->max_partials) S = v; }
-    p.part_units = s->mk_part_units;
+    p.part_units = variant == 2 ? s->mk_part_units_xg : s->mk_part_units;
     p.attn_out = s->attn_out; p.attn_counters = s->attn_counters;
     p.prefetch_kb = 0;  // off by default: measured slower than the rings alone (profiles/r1b_summary.md)
     if (const char* e = getenv("DLLM_MK_PREFETCH_KB")) { long v = atol(e); if (v >= 0 && v <= 1024) p.prefetch_kb = (int)v; }
@@ -621,21 +652,29 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
 static bool prefill_eligible(const dllm_shard* s, int n_rows) {
     static const bool off = [] { const char* e = getenv("DLLM_PREFILL_GEMM"); return e && e[0] == '0'; }();
     const dllm_shard_config& c = s->cfg;
-    return !off && c.dtype == DLLM_DTYPE_BF16 && n_rows > 16 && s->xn && c.n_layers > 0 &&
+    // more than 4 rows: the GEMM streams every weight once (the GEMV kernels re-read them per 4 rows)
+    return !off && c.dtype == DLLM_DTYPE_BF16 && n_rows > 4 && s->xn && c.n_layers > 0 &&
            c.hidden % 8 == 0 && c.ffn % 8 == 0 && (c.n_heads * c.head_dim) % 8 == 0;
 }
 
-// Replay (capturing on first use) the graph of one step; large row counts launch directly.
-static int run_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advance, cudaStream_t st) {
+// Replay (capturing on first use) the CUDA graph of one step.  mode 0: per-op decode kernels (large row counts launch
+// directly); mode 1: the tcgen05 GEMM path (prefill chunks and decode batches the persistent kernel cannot take).
+static int run_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advance, cudaStream_t st, int mode = 0,
+                    int run_seqs = 0, int run_len = 0) {
     constexpr int kGraphMaxRows = 64;
-    if (n_rows > kGraphMaxRows) return enqueue_step(s, n_rows, n_logit_rows, advance, st);
-    const unsigned long long key = ((unsigned long long)n_rows << 32) | ((unsigned long long)n_logit_rows << 1) | (advance ? 1 : 0);
+    auto enqueue = [&](cudaStream_t q) {
+        return mode == 1 ? enqueue_prefill(s, n_rows, n_logit_rows, run_seqs, run_len, q)
+                         : enqueue_step(s, n_rows, n_logit_rows, advance, q);
+    };
+    if (mode == 0 && n_rows > kGraphMaxRows) return enqueue(st);
+    const unsigned long long key = ((unsigned long long)n_rows << 40) | ((unsigned long long)run_len << 20) |
+                                   ((unsigned long long)n_logit_rows << 2) | ((unsigned long long)mode << 1) | (advance ? 1 : 0);
     auto it = s->graphs.find(key);
     if (it == s->graphs.end()) {
         cudaGraph_t graph = nullptr;
         const unsigned long long before = launch_count();
         CUDA_TRY(cudaStreamBeginCapture(s->cap_stream, cudaStreamCaptureModeThreadLocal));
-        const int rc = enqueue_step(s, n_rows, n_logit_rows, advance, s->cap_stream);
+        const int rc = enqueue(s->cap_stream);
         const cudaError_t ce = cudaStreamEndCapture(s->cap_stream, &graph);
         if (rc) {
             if (graph) cudaGraphDestroy(graph);
@@ -691,7 +730,7 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
         int run_seqs = 0, run_len = 0;
         static const bool fa_off = [] { const char* e = getenv("DLLM_PREFILL_ATTN"); return e && e[0] == '0'; }();
         if (fa_off || !detect_runs(positions, seq_ids, n_rows, &run_seqs, &run_len)) run_seqs = run_len = 0;
-        if (enqueue_prefill(s, n_rows, nl, run_seqs, run_len, st)) return 1;
+        if (run_step(s, n_rows, nl, false, st, 1, run_seqs, run_len)) return 1;
     } else if (run_step(s, n_rows, nl, false, st)) {
         return 1;
     }
@@ -719,8 +758,15 @@ extern "C" int dllm_shard_decode_loop(dllm_shard* s, int32_t n_rows, int32_t n_s
     if (mk_eligible(s, n_rows, n_rows, true)) {
         if (run_megakernel(s, n_rows, n_steps, true, st)) return 1;
     } else {
-        for (int i = 0; i < n_steps; ++i)
-            if (run_step(s, n_rows, n_rows, true, st)) return 1;
+        const bool gemm = prefill_eligible(s, n_rows);
+        for (int i = 0; i < n_steps; ++i) {
+            if (gemm) {  // GEMM-path graph for the layers, then the device-side token feedback
+                if (run_step(s, n_rows, n_rows, false, st, 1, 0, 0)) return 1;
+                CUDA_TRY(launch_advance(s->ids, s->pos, s->next_tok, s->tok_ring, s->step_ctr, n_rows, st));
+            } else if (run_step(s, n_rows, n_rows, true, st)) {
+                return 1;
+            }
+        }
     }
     if (tokens_out)
         CUDA_TRY(cudaMemcpyAsync(tokens_out, s->tok_ring, (size_t)n_steps * n_rows * 4, cudaMemcpyDefault, st));
