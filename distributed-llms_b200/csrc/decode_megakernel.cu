@@ -169,6 +169,9 @@ __device__ __forceinline__ int local_panels(const MkPhase& ph) {
 struct Ctx {
     int n_steps, n_phases;
     const unsigned char* act_x;  // activation rows in fragment layout (xg phases)
+    int cur_key;            // step * n_phases + phase the CTA is consuming now
+    int* xkey;              // shared, per ring slot of this warp: key of the xg stage whose row half is still to be issued
+    int* xst;               //         and its stage index (lane 0 only)
     const MkPhase* phases;  // shared-memory copy
     const int* units;       // shared: (panel slot, k-split) units this CTA owns in each phase (0 = not a weight phase)
     int warp, lane;
@@ -191,6 +194,7 @@ __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
                 it.wp = static_cast<const unsigned char*>(ph.wp);
                 it.n_panels = ph.n_panels;
                 it.K = ph.K;
+                it.xg = ph.xg;
                 it.panel = blockIdx.x + gridDim.x * slot;
                 return;
             }
@@ -212,11 +216,32 @@ __device__ __forceinline__ void issue_stage(const Ctx& c, const WIter& it, int s
             bulk_g2s(dst, src, bytes, bar);
         } else {
             // half-size stage: 128 k of the panel, then the same 128 k of the (up to 8) input rows
+            // The weights may run ahead of the grid barrier, the rows may not: they are written by the phase before.
+            // A stage issued early arms the barrier for both halves and leaves the row half to issue_deferred_rows().
             const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, kStageBytes / 2, &bytes);
             mbar_expect_tx(bar, bytes + kStageBytes / 2);
             bulk_g2s(dst, src, bytes, bar);
-            bulk_g2s(dst + kStageBytes / 2, c.act_x + (size_t)it.st * (kStageBytes / 2), kStageBytes / 2, bar);
+            const int key = it.step * c.n_phases + it.ph;
+            if (key == c.cur_key) {
+                bulk_g2s(dst + kStageBytes / 2, c.act_x + (size_t)it.st * (kStageBytes / 2), kStageBytes / 2, bar);
+            } else {
+                c.xkey[slot] = key;
+                c.xst[slot] = it.st;
+            }
         }
+    }
+}
+
+// Start of an xg phase (after the grid barrier): issue the row halves of the stages that were armed early.
+__device__ __forceinline__ void issue_deferred_rows(const Ctx& c, int stages) {
+    if (c.lane == 0) {
+        asm volatile("fence.proxy.async.global;" ::: "memory");
+        for (int slot = 0; slot < stages; ++slot)
+            if (c.xkey[slot] == c.cur_key) {
+                c.xkey[slot] = -1;
+                bulk_g2s(c.ring + slot * kStageBytes + kStageBytes / 2, c.act_x + (size_t)c.xst[slot] * (kStageBytes / 2),
+                         kStageBytes / 2, c.full + slot * 8);
+            }
     }
 }
 
@@ -683,6 +708,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     __shared__ float s_val[kWarps][MK_MAX_ROWS];
     __shared__ int s_idx[kWarps][MK_MAX_ROWS];
     __shared__ int s_last;
+    __shared__ int s_xkey[kWarps][8], s_xst[kWarps][8];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t4 = lane & 3;  // mma fragment coordinates
@@ -706,6 +732,11 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     c.n_phases = p.n_phases;
     c.phases = phases;
     c.act_x = static_cast<const unsigned char*>(p.act);
+    c.cur_key = -1;
+    c.xkey = s_xkey[warp];
+    c.xst = s_xst[warp];
+    if (lane < 8) s_xkey[warp][lane] = -1;
+    __syncwarp();
     c.units = s_units;
     c.warp = warp;
     c.lane = lane;
@@ -732,6 +763,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             const MkLayer* L = p.layers + ph.layer;
             if (need_barrier) grid_barrier(p.barrier, bar_target);
             need_barrier = true;
+            c.cur_key = step * p.n_phases + phi;
+            if (ph.xg) issue_deferred_rows(c, p.stages);
             if (phi == 0) {
                 // positions / slots / KV page of every row, and the rotary rows of those positions
                 if ((int)threadIdx.x < R) {
@@ -945,6 +978,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     const float gg = bf16_round(v0), uu = bf16_round(v1);
                     const size_t ai = p.act_xlayout ? ((size_t)(n >> 5) * 8 + r) * 32 + (n & 31) : (size_t)r * ph.n0 + n;
                     static_cast<bf16*>(p.act)[ai] = __float2bfloat16_rn(bf16_round(silu_f(gg)) * uu);
+                    if (p.act_xlayout) asm volatile("fence.proxy.async.global;" ::: "memory");  // read back by bulk copies
                 } else {
                     const int n = panel * 8 + 2 * i;  // rows n, n+1
                     if (n >= ph.n0) continue;
@@ -954,6 +988,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                                   (p.act_xlayout ? ((size_t)(n >> 5) * 8 + r) * 32 + (n & 31) : (size_t)r * ph.n0 + n);
                         y[0] = __float2bfloat16_rn(gelu_new_f(bf16_round(v0 + (L->b_up ? ldf(L->b_up, n) : 0.f))));
                         if (valid1) y[1] = __float2bfloat16_rn(gelu_new_f(bf16_round(v1 + (L->b_up ? ldf(L->b_up, n + 1) : 0.f))));
+                        if (p.act_xlayout) asm volatile("fence.proxy.async.global;" ::: "memory");
                     } else if (ph.kind == MK_OPROJ || ph.kind == MK_DOWN) {
                         const void* bias = ph.kind == MK_OPROJ ? L->bo : L->b_down;
                         bf16* y = static_cast<bf16*>(p.h) + (size_t)r * ph.n0 + n;

@@ -367,3 +367,31 @@ def test_tinyllama_full_size_properties():
     chunk = one2.compute({"input_ids": prompt[:, :64]})
     # two bf16 evaluation orders (different split-K and row tiling), each within 1e-2 of exact arithmetic
     assert rel_err(step["logits"], chunk["logits"]) < 3e-2
+
+
+@pytest.mark.parametrize("batch", [1, 3, 8])
+def test_streamed_rows_variant_matches_oracle(batch, monkeypatch):
+    """The persistent kernel's second variant (down-projection rows streamed from global memory with the weights,
+    what Llama-3-8B at batch 2-8 uses) forced on a small model: bf16 logits against the live oracle."""
+    monkeypatch.setenv("DLLM_MK_XG", "1")
+    cfg = ShardModelConfig("llama", 512, 3, 4, 2, 128, 1024, 1000, 256, 1e-5, 500000.0)
+    sd = make_state_dict(cfg, 99, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, batch, 21, seed=5)
+    sdd = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+    o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16), prompts, 12, record=True)
+    stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=64, max_seqs=8, max_context=128, page_size=16)
+    ids, lg = gpu_generate(stages, prompts, 12)
+    same_prefix = (ids == o_ids).long().cumprod(1).bool()
+    for t in range(12):
+        rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
+        if rows.any():
+            assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
+    for b in range(ids.shape[0]):
+        if not same_prefix[b].all():
+            t = int((~same_prefix[b]).float().argmax())
+            assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
+    # and the device-resident loop through the same variant reproduces the stepwise tokens
+    stages[0].reset()
+    first = stages[0].compute({"input_ids": prompts})["next_token"].cpu()
+    rest = stages[0].decode_loop(batch, 11).cpu()
+    assert torch.equal(torch.cat([first[:, None], rest], 1), ids)
