@@ -5,8 +5,8 @@
 
 One "step" = one decode step of the whole pipeline over the batch (one new token per sequence).
 N=1 : BASELINE.json configs[1]  -- TinyLlama-1.1B bf16, batch 1, 512-token prompt, one stage on one B200.
-N>1 : BASELINE.json configs[2]  -- Llama-3-8B bf16 layer-sharded over N stages (one rank per GPU), batch 16 per
-      micro-batch, N micro-batches in flight, hidden-state hand-off over NCCL send/recv (NVLink).
+N>1 : BASELINE.json configs[2]  -- Llama-3-8B bf16 layer-sharded over N stages (one rank per GPU), batch 1 per
+      micro-batch (--batch B for 2..16), N micro-batches in flight, hidden-state hand-off over NCCL send/recv (NVLink).
 Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle pipeline (the reference itself emits no
 tokens) on the host cores for the same metric / config.
 """
@@ -110,10 +110,18 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def workload_name(model: str, batch: int, prompt_len: int, stages: int, n_layers: int) -> str:
+    """The same string in both arms' `config.workload`."""
+    if stages == 1:
+        return f"{model} decode, batch {batch}, {prompt_len}-token prompt, 1 stage"
+    return (f"{model} decode, {stages} stages x {n_layers // stages} layers, {stages} micro-batches of {batch} in flight, "
+            f"{prompt_len}-token prompts")
+
+
 WORKLOADS = {
     # name: (model, batch per micro-batch, prompt length)
     "tinyllama-1.1b": ("tinyllama-1.1b", 1, 512),
-    "llama3-8b": ("llama3-8b", 16, 512),
+    "llama3-8b": ("llama3-8b", 1, 512),
     "gpt2-small": ("gpt2-small", 1, 16),
 }
 
@@ -166,12 +174,19 @@ def run_reference(args) -> int:
     model, batch, prompt = WORKLOADS[args.workload or ("tinyllama-1.1b" if args.gpus == 1 else "llama3-8b")]
     steps = args.steps if args.steps > 0 else 16
     warm = args.warmup if args.warmup >= 0 else 3
-    tps, desc, cores, ms, done = cpu_pipeline_tokens_per_sec(model, batch, prompt, steps, warm, n_stages=max(1, args.gpus))
+    if args.batch:
+        batch = args.batch
+    from oracle.shard_oracle import NAMED_CONFIGS as ORACLE_CONFIGS
+    n_stages = max(1, args.gpus)
+    # N micro-batches of `batch` rows go through the N CPU stages one after another (the host cores are shared by
+    # every stage, so micro-batches cannot overlap): tokens/s = batch / time of one pass through all the layers
+    tps, desc, cores, ms, done = cpu_pipeline_tokens_per_sec(model, batch, prompt, steps, warm, n_stages=n_stages)
     line = {
         "impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus, "steps": done,
-        "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "warmup": warm, "ms_per_step": ms * n_stages, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{model} decode, batch {batch}, {prompt}-token prompt", "stages": max(1, args.gpus)},
+        "config": {"workload": workload_name(model, batch, prompt, n_stages, ORACLE_CONFIGS[model].n_layers),
+                   "model": model, "batch": batch, "micro_batches": n_stages, "prompt_len": prompt, "stages": n_stages},
         "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "the reference as shipped emits no tokens (BASELINE.md 1); this is its CPU restatement (oracle/)",

@@ -64,11 +64,26 @@ class StagePipeline:
         self.batch, self.n_micro = batch, n_micro
         self.hidden_in = [torch.empty(batch, hidden, dtype=act_dtype, device=device) for _ in range(n_micro)]
         self.tok_in = [torch.zeros(batch, dtype=torch.int32, device=device) for _ in range(n_micro)]
+        self.tok_host = None  # pinned staging of the host-driven loop (first stage, allocated on first use)
+        self.tok_dev = [torch.zeros(batch, dtype=torch.int32, device=device) for _ in range(n_micro)]
+
+    def _via_host(self, m: int, x: torch.Tensor) -> torch.Tensor:
+        """Token ids of micro-batch m: device -> pinned host (synchronous read, what a master does with every result)
+        -> device again as the next step's input.  Only micro-batch m waits; the other micro-batches keep the
+        stages busy meanwhile."""
+        if self.tok_host is None:
+            pin = torch.cuda.is_available()
+            self.tok_host = [torch.zeros(self.batch, dtype=torch.int32, pin_memory=pin) for _ in range(self.n_micro)]
+        self.tok_host[m].copy_(x)
+        self.tok_dev[m].copy_(self.tok_host[m], non_blocking=True)
+        return self.tok_dev[m]
 
     def decode(self, first_tokens: Optional[List[torch.Tensor]], n_steps: int,
-               record: bool = False) -> Optional[torch.Tensor]:
+               record: bool = False, via_host: bool = False) -> Optional[torch.Tensor]:
         """`first_tokens[m]`: int32 [B] for step 0 (first stage only).  With `record`, the first stage returns the
-        int32 tokens [n_micro, B, n_steps] that came back around the ring (one extra ring transfer per step)."""
+        int32 tokens [n_micro, B, n_steps] that came back around the ring (one extra ring transfer per step).
+        With `via_host`, every token id the first stage receives is read back to pinned host memory and fed to the
+        next step from there (the master-driven loop): same schedule, one host round trip per micro-batch step."""
         link = self.link
         log = [[] for _ in range(self.n_micro)] if (record and link.is_first) else None
         pending = [None] * self.n_micro  # the send of micro-batch m's previous output (its buffer is reused)
@@ -84,6 +99,8 @@ class StagePipeline:
                         x = link.recv_tokens(self.tok_in[m]) if link.world > 1 else self._loop_tok[m]
                         if log is not None:
                             log[m].append(x.clone())
+                    if via_host:
+                        x = self._via_host(m, x)
                 else:
                     x = link.recv_hidden(self.hidden_in[m])
                 out = self.compute(m, x)
@@ -102,6 +119,8 @@ class StagePipeline:
         if link.is_first:
             for m in range(self.n_micro):
                 x = link.recv_tokens(self.tok_in[m]) if link.world > 1 else self._loop_tok[m]
+                if via_host:
+                    x = self._via_host(m, x)
                 if log is not None:
                     log[m].append(x.clone())
         if log is not None:

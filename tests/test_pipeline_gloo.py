@@ -46,7 +46,7 @@ def _expected(world, hidden, first, n_micro, n_steps):
     return out
 
 
-def _worker(rank, world, port, hidden, n_micro, n_steps, q):
+def _worker(rank, world, port, hidden, n_micro, n_steps, q, via_host=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -54,20 +54,21 @@ def _worker(rank, world, port, hidden, n_micro, n_steps, q):
         first = [torch.tensor([3 + m, 11 + m], dtype=torch.int32) for m in range(n_micro)]
         pipe = StagePipeline(link, _stub(rank, world, hidden), batch=2, n_micro=n_micro, hidden=hidden,
                              act_dtype=torch.float32, device="cpu")
-        got = pipe.decode(first if rank == 0 else None, n_steps, record=True)
+        got = pipe.decode(first if rank == 0 else None, n_steps, record=True, via_host=via_host)
         if rank == 0:
             q.put(got)
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n_micro,n_steps", [(2, 5), (3, 4)])
-def test_two_stage_schedule_and_token_ring(n_micro, n_steps):
+@pytest.mark.parametrize("n_micro,n_steps,via_host", [(2, 5, False), (3, 4, False), (2, 4, True)])
+def test_two_stage_schedule_and_token_ring(n_micro, n_steps, via_host):
+    """`via_host`: the master-driven loop (every token id staged through host memory) follows the same schedule."""
     world, hidden = 2, 8
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, hidden, n_micro, n_steps, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, hidden, n_micro, n_steps, q, via_host)) for r in range(world)]
     for p in procs:
         p.start()
     got = q.get(timeout=120)
