@@ -151,14 +151,18 @@ struct StepCache {
 };
 
 // ---- a warp's static sequence of stages -------------------------------------------------------------------
-// Panel p belongs to CTA p % grid (local slot p / grid).  Inside the CTA the (slot, k-split) pairs are dealt
-// round-robin to the warps.  The issue side and the consume side walk the same sequence; the issue side is
-// `stages` entries ahead.
+// Panel p belongs to CTA p % grid (local index p / grid).  A CTA works through its panels in rounds of up to
+// MK_ROUND_PANELS; the stages of a round (panel-major) are cut into kWarps equal contiguous chunks, one per
+// warp, so the warps finish together whatever the panel count (a chunk may end one panel and begin the next:
+// the warp then writes two partial sums).  The issue side and the consume side walk the same sequence; the
+// issue side is `stages` entries ahead.
 struct WIter {
-    int step, ph, j, st, st_end;
+    int step, ph, j0;       // decode step, phase, first local panel of the round
+    int x, x_end;           // position / end of this warp's chunk in the round's stage sequence
+    int jr, st;             // local panel inside the round and stage inside the panel at x
     // cached at seek time so that advancing by one stage needs no division and no phase-table lookup
     const unsigned char* wp;
-    int n_panels, K, panel, xg;
+    int K, ns, xg;
 };
 
 __device__ __forceinline__ int local_panels(const MkPhase& ph) {
@@ -173,33 +177,37 @@ struct Ctx {
     int* xkey;              // shared, per ring slot of this warp: key of the xg stage whose row half is still to be issued
     int* xst;               //         and its stage index (lane 0 only)
     const MkPhase* phases;  // shared-memory copy
-    const int* units;       // shared: (panel slot, k-split) units this CTA owns in each phase (0 = not a weight phase)
+    const int* units;       // shared: panels this CTA owns in each phase (0 = not a weight phase)
     int warp, lane;
     uint32_t ring;          // shared address of this warp's stages
     uint32_t full;          // shared address of this warp's mbarriers
 };
 
-__device__ __forceinline__ int ks_shift_of(int ks) { return ks == 1 ? 0 : (ks == 2 ? 1 : (ks == 4 ? 2 : 3)); }
+// chunk of warp w in a round of T stages: [w * T / kWarps, (w + 1) * T / kWarps)
+__device__ __forceinline__ int chunk_begin(int w, int T) { return (w * T) / kWarps; }
 
 __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
     while (it.step < c.n_steps) {
         while (it.ph < c.n_phases) {
-            const int idx = c.warp + kWarps * it.j;
-            if (idx < c.units[it.ph]) {
+            const int n_local = c.units[it.ph];
+            while (it.j0 < n_local) {
                 const MkPhase& ph = c.phases[it.ph];
-                const int sh = ks_shift_of(ph.ksplit);
-                const int slot = idx >> sh, s = idx & (ph.ksplit - 1);
-                it.st = (s * ph.n_stages) >> sh;
-                it.st_end = ((s + 1) * ph.n_stages) >> sh;
-                it.wp = static_cast<const unsigned char*>(ph.wp);
-                it.n_panels = ph.n_panels;
-                it.K = ph.K;
-                it.xg = ph.xg;
-                it.panel = blockIdx.x + gridDim.x * slot;
-                return;
+                const int T = min(MK_ROUND_PANELS, n_local - it.j0) * ph.n_stages;
+                it.x = chunk_begin(c.warp, T);
+                it.x_end = chunk_begin(c.warp + 1, T);
+                if (it.x < it.x_end) {
+                    it.ns = ph.n_stages;
+                    it.jr = it.x / it.ns;
+                    it.st = it.x - it.jr * it.ns;
+                    it.wp = static_cast<const unsigned char*>(ph.wp);
+                    it.K = ph.K;
+                    it.xg = ph.xg;
+                    return;
+                }
+                it.j0 += MK_ROUND_PANELS;
             }
             ++it.ph;
-            it.j = 0;
+            it.j0 = 0;
         }
         it.ph = 0;
         ++it.step;
@@ -210,15 +218,16 @@ __device__ __forceinline__ void issue_stage(const Ctx& c, const WIter& it, int s
     if (c.lane == 0) {
         uint32_t bytes;
         const uint32_t dst = c.ring + slot * kStageBytes, bar = c.full + slot * 8;
+        const int panel = blockIdx.x + gridDim.x * (it.j0 + it.jr);
         if (!it.xg) {
-            const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, kStageBytes, &bytes);
+            const unsigned char* src = it.wp + mk_stage_offset(it.K, panel, it.st, kStageBytes, &bytes);
             mbar_expect_tx(bar, bytes);
             bulk_g2s(dst, src, bytes, bar);
         } else {
-            // half-size stage: 128 k of the panel, then the same 128 k of the (up to 8) input rows
+            // half-size stage: 128 k of the panel, then the same 128 k of the (up to 8) input rows.
             // The weights may run ahead of the grid barrier, the rows may not: they are written by the phase before.
             // A stage issued early arms the barrier for both halves and leaves the row half to issue_deferred_rows().
-            const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, kStageBytes / 2, &bytes);
+            const unsigned char* src = it.wp + mk_stage_offset(it.K, panel, it.st, kStageBytes / 2, &bytes);
             mbar_expect_tx(bar, bytes + kStageBytes / 2);
             bulk_g2s(dst, src, bytes, bar);
             const int key = it.step * c.n_phases + it.ph;
@@ -246,34 +255,12 @@ __device__ __forceinline__ void issue_deferred_rows(const Ctx& c, int stages) {
 }
 
 __device__ __forceinline__ void witer_next(const Ctx& c, WIter& it) {
-    if (++it.st == it.st_end) {
-        ++it.j;
+    if (++it.x == it.x_end) {
+        it.j0 += MK_ROUND_PANELS;
         witer_seek(c, it);
-    }
-}
-
-// At the start of a phase every warp asks L2 for (up to `budget` bytes of) its units of the NEXT weight phase,
-// one prefetch instruction per unit (a unit is contiguous in the packed layout).  HBM then has work to do
-// during this phase's barrier, prologue, epilogue and attention, which the shared-memory ring alone (a few
-// microseconds of traffic) cannot cover.
-__device__ __forceinline__ void prefetch_next_phase(const Ctx& c, int step, int phi, int budget) {
-    if (c.lane != 0 || budget <= 0) return;
-    WIter it = {step, phi + 1, 0, 0, 0, nullptr, 0, 0, 0, 0};
-    witer_seek(c, it);
-    const int ph0 = it.ph, step0 = it.step;
-    while (it.step < c.n_steps && it.ph == ph0 && it.step == step0 && budget > 0) {
-        uint32_t b0;
-        const uint32_t sbytes = it.xg ? kStageBytes / 2 : kStageBytes;
-        const unsigned char* src = it.wp + mk_stage_offset(it.K, it.panel, it.st, sbytes, &b0);
-        size_t bytes = (size_t)(it.st_end - it.st) * sbytes;
-        const size_t panel_left = (size_t)it.K * 16 - (size_t)it.st * sbytes;
-        if (bytes > panel_left) bytes = panel_left;
-        if (bytes > (size_t)budget) bytes = (size_t)budget & ~(size_t)15;
-        if (bytes >= 16)
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"((uint32_t)bytes) : "memory");
-        budget -= (int)bytes;
-        ++it.j;
-        witer_seek(c, it);
+    } else if (++it.st == it.ns) {
+        it.st = 0;
+        ++it.jr;
     }
 }
 
@@ -709,6 +696,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     __shared__ int s_idx[kWarps][MK_MAX_ROWS];
     __shared__ int s_last;
     __shared__ int s_xkey[kWarps][8], s_xst[kWarps][8];
+    __shared__ int s_wfirst[MK_ROUND_PANELS], s_wlast[MK_ROUND_PANELS];  // warps holding partial sums of a round's panels
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t4 = lane & 3;  // mma fragment coordinates
@@ -719,7 +707,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
         reinterpret_cast<uint32_t*>(phases)[i] = reinterpret_cast<const uint32_t*>(p.phases)[i];
     for (int i = threadIdx.x; i < p.n_phases; i += kThreads) {
         const MkPhase& q = p.phases[i];
-        s_units[i] = is_weight_phase(q.kind) ? local_panels(q) * q.ksplit : 0;
+        s_units[i] = is_weight_phase(q.kind) ? local_panels(q) : 0;
     }
     if (threadIdx.x == 0) {
         for (int i = 0; i < kWarps * p.stages; ++i) mbar_init(full_all + i * 8, 1);
@@ -744,7 +732,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     c.full = full_all + warp * p.stages * 8;
 
     // prime this warp's ring: the first `stages` entries of its static sequence
-    WIter prod = {0, 0, 0, 0, 0, nullptr, 0, 0, 0, 0};
+    WIter prod = {0, 0, 0, 0, 0, 0, 0, nullptr, 0, 0, 0};
     witer_seek(c, prod);
     for (int i = 0; i < p.stages && prod.step < p.n_steps; ++i) {
         issue_stage(c, prod, i);
@@ -788,7 +776,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 }
                 __syncthreads();
             }
-            if (p.prefetch_kb > 0 && ph.kind != MK_ATTN) prefetch_next_phase(c, step, phi, p.prefetch_kb * 1024);
             long long* tr = (p.trace && blockIdx.x == 0 && threadIdx.x == 0) ? p.trace + ((size_t)step * p.n_phases + phi) * 8 : nullptr;
             if (tr) tr[0] = clock64();
 
@@ -831,7 +818,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             if (tr) tr[1] = clock64();
 
             // ---- main: this warp's (panel slot, k-split) units on the tensor cores ----
-            const int K = ph.K, ks = ph.ksplit, ns = ph.n_stages;
+            const int K = ph.K, ns = ph.n_stages;
             const int n_local = local_panels(ph);
             // the epilogue of the residual phases needs the old residual: fetch this thread's first pair now,
             // so that the L2 round trip overlaps the main loop
@@ -842,20 +829,26 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 if (r < R && n < ph.n0)
                     old_pref = __ldcg(reinterpret_cast<const uint32_t*>(static_cast<const bf16*>(p.h) + (size_t)r * ph.n0 + n));
             }
-            const int ksh = ks_shift_of(ks);
-            const int n_units_cta = n_local * ks;
             ArgBest best = {-FLT_MAX, INT_MAX};
-            // units are processed in rounds of `part_units` (a multiple of the warp count and of ks) so that the
-            // partial buffer stays small however many panels a CTA owns (the lm_head: ~100 per CTA)
-            for (int base = 0; base < n_units_cta; base += p.part_units) {
-            const int round_end = min(n_units_cta, base + p.part_units);
-            for (int idx = base + warp; idx < round_end; idx += kWarps) {
-                const int s = idx & (ks - 1);
-                const int sb = (s * ns) >> ksh, se = ((s + 1) * ns) >> ksh;
+            // panels are processed in rounds of MK_ROUND_PANELS so that the partial buffer stays small however many
+            // panels a CTA owns (the lm_head: ~100 per CTA); inside a round every warp takes an equal chunk of stages
+            for (int base = 0; base < n_local; base += MK_ROUND_PANELS) {
+            const int n_round = min(MK_ROUND_PANELS, n_local - base);
+            const int T = n_round * ns;
+            if ((int)threadIdx.x < n_round) {  // which warps hold a piece of panel jr: chunk_begin(w) <= x < chunk_begin(w + 1)
+                s_wfirst[threadIdx.x] = (kWarps * ((int)threadIdx.x * ns + 1) - 1) / T;
+                s_wlast[threadIdx.x] = (kWarps * ((int)threadIdx.x * ns + ns) - 1) / T;
+            }
+            int x = chunk_begin(warp, T);
+            const int x_end = chunk_begin(warp + 1, T);
+            int jr = x < x_end ? x / ns : 0;
+            int st = x - jr * ns;
+            while (x < x_end) {
+                const int seg_end = min(x_end, (jr + 1) * ns);
                 // four independent accumulator sets: the mma dependency chain of a stage is 4 long, not 16
                 float acc[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
                 float acc2[4] = {0.f, 0.f, 0.f, 0.f}, acc3[4] = {0.f, 0.f, 0.f, 0.f};
-                for (int st = sb; st < se; ++st) {
+                for (; x < seg_end; ++x, ++st) {
                     const unsigned slot = consumed % (unsigned)p.stages;
                     long long tq0 = 0, tq1 = 0, tq2 = 0;
                     if (tr) tq0 = clock64();
@@ -917,8 +910,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 }
 #pragma unroll
                 for (int q = 0; q < 4; ++q) acc[q] = (acc[q] + acc1[q]) + (acc2[q] + acc3[q]);
-                // C[batch g][panel rows 2*t4, 2*t4+1] (and batch g+8) -> partial buffer [idx][panel row][batch]
-                float* dstp = spart + (size_t)(idx - base) * kPartStride;
+                // C[batch g][panel rows 2*t4, 2*t4+1] (and batch g+8) -> partial buffer [jr + warp][panel row][batch]
+                // (jr and warp both grow along the round's stage sequence, so jr + warp is unique per piece)
+                float* dstp = spart + (size_t)(jr + warp) * kPartStride;
                 if (g < R) {
                     dstp[(2 * t4) * MK_MAX_ROWS + g] = acc[0];
                     dstp[(2 * t4 + 1) * MK_MAX_ROWS + g] = acc[1];
@@ -927,23 +921,26 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     dstp[(2 * t4) * MK_MAX_ROWS + g + 8] = acc[2];
                     dstp[(2 * t4 + 1) * MK_MAX_ROWS + g + 8] = acc[3];
                 }
+                ++jr;
+                st = 0;
             }
             __syncthreads();
             if (tr) tr[2] = clock64();
 
-            // ---- epilogue: one thread per (local panel, row pair, batch row); k-splits summed in fixed order ----
-            const int slot0 = base >> ksh, n_slots = (round_end - base) >> ksh;
-            for (int o = threadIdx.x; o < n_slots * 4 * RP; o += kThreads) {
+            // ---- epilogue: one thread per (local panel, row pair, batch row); pieces summed in fixed order ----
+            for (int o = threadIdx.x; o < n_round * 4 * RP; o += kThreads) {
                 const int r = o & (RP - 1);
-                const int pi = o / RP, slot = slot0 + (pi >> 2), i = pi & 3;
+                const int pi = o / RP, pj = pi >> 2, i = pi & 3;
                 if (r >= R) continue;
                 float v0 = 0.f, v1 = 0.f;
-                for (int s = 0; s < ks; ++s) {
-                    const float* src = spart + (size_t)((slot - slot0) * ks + s) * kPartStride;
+                const int w1 = s_wlast[pj];
+                for (int w = s_wfirst[pj]; w <= w1; ++w) {
+                    if (T < kWarps && chunk_begin(w, T) == chunk_begin(w + 1, T)) continue;  // a warp without stages
+                    const float* src = spart + (size_t)(pj + w) * kPartStride;
                     v0 += src[(2 * i) * MK_MAX_ROWS + r];
                     v1 += src[(2 * i + 1) * MK_MAX_ROWS + r];
                 }
-                const int panel = blockIdx.x + gridDim.x * slot;
+                const int panel = blockIdx.x + gridDim.x * (base + pj);
                 if (ph.kind == MK_QKV) {
                     const int hd = p.head_dim, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
                     const int ppb = half >> 2;  // panels per head
@@ -1146,7 +1143,7 @@ size_t mk_smem_bytes(const MkParams& p, int stages) {
 
 static int mk_pick_stages(const MkParams& p) {
     for (int s = 6; s >= 2; --s)
-        if (mk_smem_bytes(p, s) <= (size_t)(227 * 1024 - 1536)) return s;
+        if (mk_smem_bytes(p, s) <= (size_t)MK_SMEM_BUDGET) return s;
     return 0;
 }
 

@@ -12,6 +12,9 @@ constexpr int MK_STAGE_BYTES = 8 * MK_STAGE_K * 2; // one stage = 8 weight rows 
 constexpr int MK_MAX_ROWS = 16;
 constexpr int MK_MAX_SPLITS = 8;   // one batch of eight 16-byte loads per thread in the merge
 constexpr int MK_MAX_PHASES = 512;  // 5 per layer + 2: up to 102 layers per stage
+constexpr int MK_SMEM_BUDGET = 227 * 1024 - 6 * 1024;  // dynamic shared memory: the opt-in maximum less the kernel's static arrays
+constexpr int MK_ROUND_PANELS = 13; // panels a CTA works on between two epilogues
+constexpr int MK_PART_UNITS = MK_ROUND_PANELS + MK_THREADS / 32 - 1;  // partial sums of a round: one per (panel, warp) piece
 
 enum MkKind { MK_EMBED = 0, MK_QKV, MK_ATTN, MK_OPROJ, MK_GATEUP, MK_FC_GELU, MK_DOWN, MK_HEAD };
 
@@ -28,7 +31,7 @@ struct MkPhase {
     int32_t n0;          // logical output rows (un-padded)
     int16_t kind;        // MkKind
     int16_t layer;
-    int16_t ksplit;      // warps of one CTA that share a panel (split along K, summed in fixed order)
+    int16_t ksplit;      // unused (the kernel cuts a round's stages into equal per-warp chunks)
     int16_t n_stages;    // ceil(K / 256); K / 128 when xg
     int16_t xg;          // 1: the input rows are streamed from global memory with the weights (half-size stages:
                          //    2 KB of weights + 2 KB of rows in fragment layout) instead of being staged in shared
@@ -69,7 +72,6 @@ struct MkParams {
     const void *wte, *wpe, *final_norm_w, *final_norm_b;
     const float *rope_cos, *rope_sin;
     unsigned *barrier, *done, *arg_counter;  // zero between launches
-    int32_t prefetch_kb;     // KB per warp of the NEXT phase pulled into L2 at each phase start (0 = off)
     long long* trace;        // optional [n_steps][n_phases][4] SM-clock stamps of CTA 0 (debug, DLLM_MK_TRACE)
 };
 
@@ -81,15 +83,6 @@ __host__ __device__ inline size_t mk_stage_offset(int K, int panel, int st, uint
     const size_t left = panel_bytes - off;
     *bytes = (uint32_t)(left < (size_t)stage_bytes ? left : (size_t)stage_bytes);
     return (size_t)panel * panel_bytes + off;
-}
-
-// geometry helpers shared by host and device
-__host__ __device__ inline int mk_ksplit(int n_panels, int n_stages, int grid) {
-    const int per_cta = (n_panels + grid - 1) / grid;
-    const int want = (MK_THREADS / 32 + per_cta - 1) / per_cta;  // enough units to keep every warp of the CTA busy
-    int ks = 1;
-    while (ks < want && ks < 8 && ks * 2 <= n_stages) ks *= 2;   // power of two: the kernel splits with shifts
-    return ks;
 }
 
 // packer: kind selects the row order (QKV pairs, gate/up pairs, plain)

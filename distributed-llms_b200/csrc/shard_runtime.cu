@@ -274,8 +274,7 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
             MkPhase q{};
             q.wp = pk; q.n_panels = n_panels; q.K = K; q.n0 = n0; q.kind = (int16_t)kind; q.layer = (int16_t)layer;
             q.n_stages = (int16_t)((K + MK_STAGE_K - 1) / MK_STAGE_K);
-            q.ksplit = (int16_t)mk_ksplit(n_panels, q.n_stages, G);
-            part_units = std::max(part_units, ((n_panels + G - 1) / G) * (int)q.ksplit);
+            q.ksplit = 1;
             ph.push_back(q);
             pk += align_up(mk_packed_bytes(n_panels, K), 256);
         };
@@ -298,7 +297,7 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
         }
         if (c.has_head) weight_phase(MK_HEAD, 0, (c.vocab + 7) / 8, c.hidden, c.vocab, s->io.lm_head, nullptr, nullptr);
         s->mk_n_phases = (int)ph.size();
-        s->mk_part_units = std::min(part_units, 24);  // rounds of 24 units (multiple of the warp count and of every k-split)
+        s->mk_part_units = MK_PART_UNITS;
         s->mk_k_max = std::max(std::max(c.hidden, Hd), c.ffn);
         if (me == cudaSuccess) me = cudaMemcpy(s->mk_phases, ph.data(), ph.size() * sizeof(MkPhase), cudaMemcpyHostToDevice);
         if (me == cudaSuccess) me = cudaMemcpy(s->mk_layers, ly.data(), ly.size() * sizeof(MkLayer), cudaMemcpyHostToDevice);
@@ -311,11 +310,9 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
                 if (q.kind == MK_DOWN) {
                     q.xg = 1;
                     q.n_stages = (int16_t)(q.K / (MK_STAGE_K / 2));
-                    q.ksplit = (int16_t)mk_ksplit(q.n_panels, q.n_stages, G);
                 }
-                if (q.wp) pu = std::max(pu, ((q.n_panels + G - 1) / G) * (int)q.ksplit);
             }
-            s->mk_part_units_xg = std::min(pu, 24);
+            s->mk_part_units_xg = MK_PART_UNITS;
             s->mk_k_max_xg = std::max(c.hidden, Hd);
             if (me == cudaSuccess) me = cudaMemcpy(s->mk_phases_xg, px.data(), px.size() * sizeof(MkPhase), cudaMemcpyHostToDevice);
         }
@@ -474,10 +471,10 @@ static int mk_variant(const dllm_shard* s, int n_rows, int n_logit_rows, bool id
     q.k_max = s->mk_k_max; q.part_units = s->mk_part_units;
     const char* force_xg = getenv("DLLM_MK_XG");  // tests: take the streamed-rows variant even when the plain one fits
     if (!(force_xg && atoi(force_xg) == 1 && s->mk_xg_ok && n_rows <= 8) &&
-        mk_smem_bytes(q, 2) <= (size_t)(227 * 1024 - 1536)) return 1;
+        mk_smem_bytes(q, 2) <= (size_t)MK_SMEM_BUDGET) return 1;
     if (s->mk_xg_ok && n_rows <= 8) {
         q.k_max = s->mk_k_max_xg; q.part_units = s->mk_part_units_xg;
-        if (mk_smem_bytes(q, 2) <= (size_t)(227 * 1024 - 1536)) return 2;
+        if (mk_smem_bytes(q, 2) <= (size_t)MK_SMEM_BUDGET) return 2;
     }
     return 0;
 }
@@ -504,8 +501,6 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     if (const char* e = getenv("DLLM_MK_SPLITS")) { long v = atol(e); if (v >= 1 && v <= s_cap && (long)n_rows * c.n_heads * v <= s->max_partials) S = v; }
     p.part_units = variant == 2 ? s->mk_part_units_xg : s->mk_part_units;
     p.attn_out = s->attn_out; p.attn_counters = s->attn_counters;
-    p.prefetch_kb = 0;  // off by default: measured slower than the rings alone (profiles/r1b_summary.md)
-    if (const char* e = getenv("DLLM_MK_PREFETCH_KB")) { long v = atol(e); if (v >= 0 && v <= 1024) p.prefetch_kb = (int)v; }
     p.n_splits = (int)S; p.advance = advance ? 1 : 0; p.tok_base = 0; p.eps = c.norm_eps;
     p.h = s->h; p.q = s->qbuf; p.act = s->act; p.part_o = s->part_o; p.part_ml = s->part_ml;
     p.logits = c.has_head ? s->logits : nullptr; p.arg_val = s->arg_val; p.arg_idx = s->arg_idx;
