@@ -659,6 +659,13 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 
 // ---- the kernel ----------------------------------------------------------------------------------------
 
+// shared region that holds the staged input rows (weight phases) or the attention tiles (attention phase)
+__host__ __device__ inline size_t mk_rows_region_bytes(const MkParams& p) {
+    const size_t rows = (size_t)p.n_rows * (p.k_max + 8) * 2;
+    const size_t attn = (size_t)2 * kTT * (p.head_dim + 8) * 2 + (size_t)kMaxGq * kTT * 4 + (size_t)kMaxGq * p.head_dim * 4;
+    return ((rows > attn ? rows : attn) + 127) / 128 * 128;
+}
+
 template <bool HI>  // HI: more than 8 batch rows (second half of the mma M dimension in use)
 __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -669,23 +676,27 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     sp += (size_t)((p.n_phases * sizeof(MkPhase) + 127) / 128) * 128;
     const uint32_t full_all = smem_u32(sp);
     sp += (size_t)((kWarps * p.stages * 8 + 127) / 128) * 128;
+    // the staged input rows of the weight phases and the K/V tiles of the attention phase are never live together:
+    // one region serves both
     bf16* xs = reinterpret_cast<bf16*>(sp);
-    sp += (size_t)((p.n_rows * ldx * 2 + 127) / 128) * 128;
+    AttnSmem at;
+    {
+        unsigned char* ap = sp;
+        at.k = reinterpret_cast<bf16*>(ap);
+        ap += (size_t)kTT * (p.head_dim + 8) * 2;
+        at.v = reinterpret_cast<bf16*>(ap);
+        ap += (size_t)kTT * (p.head_dim + 8) * 2;
+        at.s = reinterpret_cast<float*>(ap);
+        ap += kMaxGq * kTT * 4;
+        at.q = reinterpret_cast<float*>(ap);
+    }
+    sp += mk_rows_region_bytes(p);
     float* spart = reinterpret_cast<float*>(sp);
     sp += (size_t)p.part_units * kPartStride * 4;
     float* srope = reinterpret_cast<float*>(sp);  // [R][head_dim]: cos row then sin row of each batch row's position
     sp += (size_t)p.n_rows * p.head_dim * 4;
     int* sbt = reinterpret_cast<int*>(sp);        // [R][pages_per_seq]: block-table row of each batch row's sequence
     sp += (size_t)((p.n_rows * p.pages_per_seq * 4 + 15) / 16) * 16;
-    AttnSmem at;
-    at.k = reinterpret_cast<bf16*>(sp);
-    sp += (size_t)kTT * (p.head_dim + 8) * 2;
-    at.v = reinterpret_cast<bf16*>(sp);
-    sp += (size_t)kTT * (p.head_dim + 8) * 2;
-    at.s = reinterpret_cast<float*>(sp);
-    sp += kMaxGq * kTT * 4;
-    at.q = reinterpret_cast<float*>(sp);
-    sp += kMaxGq * p.head_dim * 4;
     sp = reinterpret_cast<unsigned char*>(((uintptr_t)sp + 127) & ~(uintptr_t)127);
     const uint32_t ring_all = smem_u32(sp);
 
@@ -813,7 +824,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             else if (ph.kind == MK_DOWN) {
                 if (!ph.xg) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
             }
-            else stage_attn_combine(p, sc, xs, ldx, reinterpret_cast<float*>(at.k));
+            else stage_attn_combine(p, sc, xs, ldx, spart);  // merge scratch: the partial buffer is idle in a prologue
             __syncthreads();
             if (tr) tr[1] = clock64();
 
@@ -1131,11 +1142,10 @@ size_t mk_smem_bytes(const MkParams& p, int stages) {
     auto up = [](size_t v) { return (v + 127) / 128 * 128; };
     size_t b = up((size_t)p.n_phases * sizeof(MkPhase));
     b += up((size_t)kWarps * stages * 8);
-    b += up((size_t)p.n_rows * (p.k_max + 8) * 2);
+    b += mk_rows_region_bytes(p);
     b += (size_t)p.part_units * kPartStride * 4;
     b += (size_t)p.n_rows * p.head_dim * 4;
     b += (size_t)((p.n_rows * p.pages_per_seq * 4 + 15) / 16) * 16;
-    b += (size_t)2 * kTT * (p.head_dim + 8) * 2 + kMaxGq * kTT * 4 + (size_t)kMaxGq * p.head_dim * 4;
     b = up(b) + 128;
     b += (size_t)kWarps * stages * kStageBytes;
     return b;
@@ -1170,7 +1180,7 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
     MkParams p = p_in;
     if (!mk_supported(p.n_rows, p.n_heads, p.n_kv_heads, p.head_dim)) return cudaErrorInvalidValue;
     if (p.n_splits < 1 || p.n_splits > kMaxSplits || p.n_phases > MK_MAX_PHASES) return cudaErrorInvalidValue;
-    if ((size_t)p.n_rows * p.n_heads * p.n_splits * 8 > (size_t)2 * kTT * (p.head_dim + 8) * 2) return cudaErrorInvalidValue;  // merge scratch
+    if ((size_t)p.n_rows * p.n_heads * p.n_splits * 8 > (size_t)MK_PART_UNITS * kPartStride * 4) return cudaErrorInvalidValue;  // merge scratch
     p.stages = mk_pick_stages(p);
     if (p.stages == 0) return cudaErrorInvalidValue;
     const size_t smem = mk_smem_bytes(p, p.stages);
@@ -1178,7 +1188,8 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
 }
 
 int mk_max_splits(int n_rows, int n_heads, int head_dim) {
-    const size_t scratch = (size_t)2 * kTT * (head_dim + 8) * 2;  // the K/V tile buffers double as merge scratch
+    (void)head_dim;
+    const size_t scratch = (size_t)MK_PART_UNITS * kPartStride * 4;  // the partial buffer doubles as merge scratch
     const long s = (long)(scratch / ((size_t)n_rows * n_heads * 8));
     return (int)(s > kMaxSplits ? kMaxSplits : s);
 }
