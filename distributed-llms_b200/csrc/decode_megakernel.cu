@@ -106,6 +106,31 @@ __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target) {
     __syncthreads();
 }
 
+// ---- tickets in (peer) mailboxes: system scope, the writer may be another GPU ------------------------------
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// One thread waits until the slot's ticket reaches `want`.  The producer is another kernel (on another GPU): give
+// it 20 s -- processes start seconds apart -- then trap rather than hang the device.
+__device__ __forceinline__ void wait_ticket(const unsigned* flag, unsigned want) {
+    if ((int)(ld_acquire_sys(flag) - want) >= 0) return;
+    const unsigned long long t0 = global_ns();
+    while ((int)(ld_acquire_sys(flag) - want) < 0) {
+        __nanosleep(64);
+        if (global_ns() - t0 > 20000000000ull) __trap();
+    }
+}
+
 __device__ __forceinline__ uint4 pack8(const float (&in)[8]) {
     uint4 r;
     __nv_bfloat162 a = __floats2bfloat162_rn(in[0], in[1]);
@@ -756,7 +781,16 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     const uint32_t xrow_lo = smem_u32(xs) + (uint32_t)(min(g, R - 1) * ldx * 2);
     const uint32_t xrow_hi = smem_u32(xs) + (uint32_t)(min(g + 8, R - 1) * ldx * 2);
 
+    const bool piped = p.in_flag != nullptr;  // fused hand-off: inputs arrive in / outputs leave through mailboxes
     for (int step = 0; step < p.n_steps; ++step) {
+        // micro-batch of this step and its decode step inside the launch (classic mode: m = 0, gstep = step)
+        const int m = piped ? step % p.n_micro : 0;
+        const int gstep = piped ? step / p.n_micro : step;
+        const int32_t* pos_m = p.pos + m * R;
+        const int32_t* seq_m = p.seq + m * R;
+        const int pos_add = piped ? gstep : 0;  // piped: the position arrays stay as the host wrote them
+        const int32_t* ids_m = piped ? p.in_tokens + m * R : p.ids;
+        bf16* h_m = static_cast<bf16*>(piped && p.in_hidden ? p.in_hidden : p.h) + (piped ? (size_t)m * R * p.hidden : 0);
         for (int phi = 0; phi < p.n_phases; ++phi) {
             const MkPhase& ph = phases[phi];
             const MkLayer* L = p.layers + ph.layer;
@@ -765,9 +799,18 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             c.cur_key = step * p.n_phases + phi;
             if (ph.xg) issue_deferred_rows(c, p.stages);
             if (phi == 0) {
+                if (piped && threadIdx.x == 0) {
+                    // every CTA is past the barrier: the previous step's rows are complete in the next stage's inbox
+                    if (blockIdx.x == 0 && step > 0 && p.out_hidden) {
+                        const int pm = (step - 1) % p.n_micro, pg = (step - 1) / p.n_micro;
+                        st_release_sys(p.out_flag + (size_t)pm * p.flag_stride, p.ticket_base + pg + 1);
+                    }
+                    wait_ticket(p.in_flag + (size_t)m * p.flag_stride, p.ticket_base + gstep + 1);
+                }
+                if (piped) __syncthreads();
                 // positions / slots / KV page of every row, and the rotary rows of those positions
                 if ((int)threadIdx.x < R) {
-                    const int ps = ldcg_i32(p.pos + threadIdx.x), sq = ldcg_i32(p.seq + threadIdx.x);
+                    const int ps = ldcg_i32(pos_m + threadIdx.x) + pos_add, sq = ldcg_i32(seq_m + threadIdx.x);
                     sc.pos[threadIdx.x] = ps;
                     sc.seq[threadIdx.x] = sq;
                     sc.page[threadIdx.x] = p.block_table[(size_t)sq * p.pages_per_seq + (ps >> p.page_shift)];
@@ -775,13 +818,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 }
                 for (int i = threadIdx.x; i < R * p.pages_per_seq; i += kThreads) {
                     const int r = i / p.pages_per_seq;
-                    sbt[i] = p.block_table[(size_t)ldcg_i32(p.seq + r) * p.pages_per_seq + (i - r * p.pages_per_seq)];
+                    sbt[i] = p.block_table[(size_t)ldcg_i32(seq_m + r) * p.pages_per_seq + (i - r * p.pages_per_seq)];
                 }
                 if (p.rope) {
                     const int half = p.head_dim >> 1;
                     for (int i = threadIdx.x; i < R * p.head_dim; i += kThreads) {
                         const int r = i / p.head_dim, e = i - r * p.head_dim;
-                        const int ps = ldcg_i32(p.pos + r);
+                        const int ps = ldcg_i32(pos_m + r) + pos_add;
                         srope[i] = e < half ? p.rope_cos[(size_t)ps * half + e] : p.rope_sin[(size_t)ps * half + e - half];
                     }
                 }
@@ -795,7 +838,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 const int vecs = p.hidden >> 3;
                 for (int i = blockIdx.x * kThreads + threadIdx.x; i < R * vecs; i += gridDim.x * kThreads) {
                     const int r = i / vecs, v = i - r * vecs;
-                    int id = ldcg_i32(p.ids + r);
+                    int id = ldcg_i32(ids_m + r);
+                    if (piped && v == 0) p.tok_ring[(size_t)step * R + r] = id;  // the ids this stage fed, step-major
                     id = min(max(id, 0), p.vocab - 1);
                     uint4 val = ld_u4(static_cast<const bf16*>(p.wte) + (size_t)id * p.hidden + v * 8);
                     if (p.wpe) {
@@ -806,7 +850,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         for (int j = 0; j < 8; ++j) a[j] += b[j];
                         val = pack8(a);
                     }
-                    *reinterpret_cast<uint4*>(static_cast<bf16*>(p.h) + (size_t)r * p.hidden + v * 8) = val;
+                    *reinterpret_cast<uint4*>(h_m + (size_t)r * p.hidden + v * 8) = val;
                 }
                 if (tr) tr[1] = tr[2] = tr[3] = clock64();
                 continue;
@@ -818,9 +862,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             }
 
             // ---- weight-streaming phase: prologue ----
-            if (ph.kind == MK_QKV) stage_rows(p, p.h, ph.K, p.norm, L->norm1_w, L->norm1_b, xs, ldx, red);
-            else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) stage_rows(p, p.h, ph.K, p.norm, L->norm2_w, L->norm2_b, xs, ldx, red);
-            else if (ph.kind == MK_HEAD) stage_rows(p, p.h, ph.K, p.norm, p.final_norm_w, p.final_norm_b, xs, ldx, red);
+            if (ph.kind == MK_QKV) stage_rows(p, h_m, ph.K, p.norm, L->norm1_w, L->norm1_b, xs, ldx, red);
+            else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) stage_rows(p, h_m, ph.K, p.norm, L->norm2_w, L->norm2_b, xs, ldx, red);
+            else if (ph.kind == MK_HEAD) stage_rows(p, h_m, ph.K, p.norm, p.final_norm_w, p.final_norm_b, xs, ldx, red);
             else if (ph.kind == MK_DOWN) {
                 if (!ph.xg) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
             }
@@ -838,8 +882,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 const int r = threadIdx.x & (RP - 1), pi = threadIdx.x / RP;
                 const int n = (blockIdx.x + gridDim.x * (pi >> 2)) * 8 + 2 * (pi & 3);
                 if (r < R && n < ph.n0)
-                    old_pref = __ldcg(reinterpret_cast<const uint32_t*>(static_cast<const bf16*>(p.h) + (size_t)r * ph.n0 + n));
+                    old_pref = __ldcg(reinterpret_cast<const uint32_t*>(h_m + (size_t)r * ph.n0 + n));
             }
+            const bool send_rows = piped && p.out_hidden && ph.kind == MK_DOWN && ph.layer == p.last_layer;
             ArgBest best = {-FLT_MAX, INT_MAX};
             // panels are processed in rounds of MK_ROUND_PANELS so that the partial buffer stays small however many
             // panels a CTA owns (the lm_head: ~100 per CTA); inside a round every warp takes an equal chunk of stages
@@ -999,11 +1044,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         if (p.act_xlayout) asm volatile("fence.proxy.async.global;" ::: "memory");
                     } else if (ph.kind == MK_OPROJ || ph.kind == MK_DOWN) {
                         const void* bias = ph.kind == MK_OPROJ ? L->bo : L->b_down;
-                        bf16* y = static_cast<bf16*>(p.h) + (size_t)r * ph.n0 + n;
+                        bf16* y = h_m + (size_t)r * ph.n0 + n;
                         const uint32_t old = (o == (int)threadIdx.x && base == 0) ? old_pref : __ldcg(reinterpret_cast<const uint32_t*>(y));  // two bf16 of the residual
                         v0 = bf16_round(v0 + (bias ? ldf(bias, n) : 0.f)) + __uint_as_float(old << 16);
                         v1 = bf16_round(v1 + (bias ? ldf(bias, n + 1) : 0.f)) + __uint_as_float(old & 0xffff0000u);
                         *reinterpret_cast<__nv_bfloat162*>(y) = __floats2bfloat162_rn(v0, v1);
+                        if (send_rows)  // the stage's output row goes straight into the next stage's inbox (peer store)
+                            *reinterpret_cast<__nv_bfloat162*>(static_cast<bf16*>(p.out_hidden) + ((size_t)m * R + r) * ph.n0 + n) =
+                                __floats2bfloat162_rn(v0, v1);
                     } else {  // MK_HEAD: logits in the model dtype, argmax = first index of the maximum
                         v0 = bf16_round(v0);
                         v1 = bf16_round(v1);
@@ -1020,6 +1068,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
 
             __syncthreads();  // the partial buffer is reused by the next round
             }  // rounds
+            if (send_rows) __threadfence_system();  // peer stores performed before this CTA arrives at the next barrier
 
             if (ph.kind == MK_QKV && phi + 1 < p.n_phases && phases[phi + 1].kind == MK_ATTN) {
                 // prefetch the old K/V rows of this CTA's first attention tile before the barrier
@@ -1069,6 +1118,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         }
                         if (lane == 0) {
                             p.next_token[r] = b.idx;
+                            if (piped) p.out_tokens[(size_t)m * R + r] = b.idx;  // into the first stage's inbox
                             if (p.advance) {
                                 p.ids[r] = b.idx;
                                 p.pos[r] = ldcg_i32(p.pos + r) + 1;
@@ -1078,11 +1128,23 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     }
                     if (threadIdx.x == 0) *p.arg_counter = 0u;
                     __threadfence();
+                    if (piped) {  // s_last is uniform in the CTA: the ids are out, publish the slot's next ticket
+                        __threadfence_system();
+                        __syncthreads();
+                        if (threadIdx.x == 0) st_release_sys(p.out_flag + (size_t)m * p.flag_stride, p.ticket_base + gstep + 2);
+                    }
                 }
             }
         }
     }
 
+    if (piped && p.out_hidden && p.n_steps > 0) {  // the last step's rows: complete once every CTA has arrived
+        grid_barrier(p.barrier, bar_target);
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            const int pm = (p.n_steps - 1) % p.n_micro, pg = (p.n_steps - 1) / p.n_micro;
+            st_release_sys(p.out_flag + (size_t)pm * p.flag_stride, p.ticket_base + pg + 1);
+        }
+    }
     // leave the barrier words at zero for the next launch: the last CTA out resets them
     __syncthreads();
     if (threadIdx.x == 0) {

@@ -73,6 +73,19 @@ struct MkParams {
     const float *rope_cos, *rope_sin;
     unsigned *barrier, *done, *arg_counter;  // zero between launches
     long long* trace;        // optional [n_steps][n_phases][4] SM-clock stamps of CTA 0 (debug, DLLM_MK_TRACE)
+    // ---- fused hand-off (null in_flag = off).  The kernel runs n_steps = decode steps x n_micro micro-batch steps;
+    // micro-batch m = step % n_micro uses rows [m*R, (m+1)*R) of pos / seq and slot m of the mailboxes.  A slot's
+    // ticket counts the inputs delivered to it: the consumer of decode step G waits for ticket >= G + 1.
+    int32_t n_micro;
+    uint32_t ticket_base;    // decode step number of this launch's first step
+    int32_t flag_stride;     // uint32 elements between two slots' tickets
+    int32_t last_layer;      // layer whose down projection produces the stage's output
+    unsigned* in_flag;       // local inbox: tickets,
+    const int32_t* in_tokens;//   token ids [n_micro][R] (first stage),
+    void* in_hidden;         //   hidden rows [n_micro][R][d] (other stages; used in place as the residual stream)
+    unsigned* out_flag;      // the next stage's inbox (peer memory; the first stage's inbox for the last stage)
+    int32_t* out_tokens;
+    void* out_hidden;
 };
 
 // Packed layout, panel-major: a panel's stages are consecutive, so any k-range of a panel (one warp unit) is

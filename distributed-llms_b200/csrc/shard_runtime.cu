@@ -186,7 +186,7 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->arange, (size_t)c.max_rows * 4);
     add(&s->next_tok, (size_t)c.max_rows * 4);
     add(&s->block_table, (size_t)c.max_seqs * s->pages_per_seq * 4);
-    add(&s->tok_ring, c.has_head && c.has_embed ? s->tok_ring_cap * 4 : 0);
+    add(&s->tok_ring, c.has_embed ? s->tok_ring_cap * 4 : 0);
     add(&s->step_ctr, 4);
     add(&s->logits, (size_t)s->max_logit_rows * c.vocab * 4);
     add(&s->part_o, (size_t)s->max_partials * c.head_dim * 4);
@@ -483,7 +483,28 @@ static bool mk_eligible(const dllm_shard* s, int n_rows, int n_logit_rows, bool 
     return mk_variant(s, n_rows, n_logit_rows, identity_rows) != 0;
 }
 
-static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, cudaStream_t st) {
+// mailboxes of the fused hand-off (see include/dllm_b200.h)
+struct dllm_mailbox {
+    int device = 0;           // device the pointers are valid on
+    int n_slots = 0, rows = 0, hidden = 0;
+    char* base = nullptr;
+    bool owner = false, ipc = false;
+    unsigned* flags() const { return reinterpret_cast<unsigned*>(base); }
+    int32_t* tokens() const { return reinterpret_cast<int32_t*>(base + align_up((size_t)n_slots * 128, 256)); }
+    void* hidden_rows() const { return base + align_up((size_t)n_slots * 128, 256) + align_up((size_t)n_slots * rows * 4, 256); }
+    size_t bytes() const {
+        return align_up((size_t)n_slots * 128, 256) + align_up((size_t)n_slots * rows * 4, 256) + (size_t)n_slots * rows * hidden * 2;
+    }
+};
+constexpr int kFlagStride = 32;  // one ticket per 128-byte line
+
+struct MkPipe {
+    const dllm_mailbox *in, *out;
+    int n_micro;
+    unsigned step_base;
+};
+
+static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, cudaStream_t st, const MkPipe* pipe = nullptr) {
     const dllm_shard_config& c = s->cfg;
     const int variant = mk_variant(s, n_rows, n_rows, true);
     if (variant == 0) return fail("internal: persistent kernel not eligible");
@@ -510,6 +531,16 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     p.final_norm_w = s->io.final_norm_w; p.final_norm_b = s->io.final_norm_b;
     p.rope_cos = s->io.rope_cos; p.rope_sin = s->io.rope_sin;
     p.barrier = s->mk_sync; p.done = s->mk_sync + 1; p.arg_counter = s->mk_sync + 2;
+    p.n_micro = 1;
+    if (pipe) {
+        p.n_micro = pipe->n_micro; p.ticket_base = pipe->step_base; p.flag_stride = kFlagStride;
+        p.last_layer = c.n_layers - 1;
+        p.in_flag = pipe->in->flags(); p.in_tokens = pipe->in->tokens();
+        p.in_hidden = c.has_embed ? nullptr : pipe->in->hidden_rows();
+        p.out_flag = pipe->out->flags(); p.out_tokens = pipe->out->tokens();
+        p.out_hidden = c.has_head ? nullptr : pipe->out->hidden_rows();
+        p.logits = nullptr;
+    }
     if (s->num_sms > s->arg_grid_cap) return fail("internal: argmax scratch too small for the persistent kernel");
     const char* trace_path = getenv("DLLM_MK_TRACE");
     long long* d_trace = nullptr;
@@ -771,6 +802,132 @@ extern "C" int dllm_shard_decode_loop(dllm_shard* s, int32_t n_rows, int32_t n_s
 }
 
 // ---- hand-off ---------------------------------------------------------------------------------------
+
+static int mailbox_shape_ok(int n_slots, int rows, int hidden) {
+    return n_slots >= 1 && n_slots <= 64 && rows >= 1 && rows <= MK_MAX_ROWS && hidden >= 8 && hidden % 8 == 0;
+}
+
+extern "C" int dllm_mailbox_create(int32_t device, int32_t n_slots, int32_t rows, int32_t hidden, dllm_mailbox** out) {
+    if (!out) return fail("dllm_mailbox_create: null out");
+    if (!mailbox_shape_ok(n_slots, rows, hidden)) return fail("dllm_mailbox_create: bad shape (1..64 slots, 1..16 rows, hidden % 8 == 0)");
+    if (dllm_device_count() == 0) return fail("dllm_mailbox_create: no CUDA device (this library has no CPU path)");
+    CUDA_TRY(cudaSetDevice(device));
+    dllm_mailbox* b = new dllm_mailbox();
+    b->device = device; b->n_slots = n_slots; b->rows = rows; b->hidden = hidden; b->owner = true;
+    cudaError_t e = cudaMalloc((void**)&b->base, b->bytes());
+    if (e == cudaSuccess) e = cudaMemset(b->base, 0, b->bytes());
+    if (e != cudaSuccess) {
+        if (b->base) cudaFree(b->base);
+        delete b;
+        CUDA_TRY(e);
+    }
+    *out = b;
+    return 0;
+}
+
+extern "C" int dllm_mailbox_export(dllm_mailbox* b, void* ipc_handle_out) {
+    if (!b || !b->owner || !ipc_handle_out) return fail("dllm_mailbox_export: needs the owner's mailbox and a 64-byte buffer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == DLLM_MAILBOX_IPC_BYTES, "IPC handle size");
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaSetDevice(b->device));
+    CUDA_TRY(cudaIpcGetMemHandle(&h, b->base));
+    memcpy(ipc_handle_out, &h, sizeof(h));
+    return 0;
+}
+
+extern "C" int dllm_mailbox_import(int32_t device, const void* ipc_handle, int32_t n_slots, int32_t rows, int32_t hidden,
+                                   dllm_mailbox** out) {
+    if (!out || !ipc_handle) return fail("dllm_mailbox_import: null argument");
+    if (!mailbox_shape_ok(n_slots, rows, hidden)) return fail("dllm_mailbox_import: bad shape");
+    CUDA_TRY(cudaSetDevice(device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, ipc_handle, sizeof(h));
+    void* ptr = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    dllm_mailbox* b = new dllm_mailbox();
+    b->device = device; b->n_slots = n_slots; b->rows = rows; b->hidden = hidden; b->base = (char*)ptr; b->ipc = true;
+    *out = b;
+    return 0;
+}
+
+extern "C" int dllm_mailbox_view(dllm_mailbox* box, int32_t device, dllm_mailbox** out) {
+    if (!box || !out) return fail("dllm_mailbox_view: null argument");
+    if (device != box->device) {
+        int can = 0;
+        CUDA_TRY(cudaDeviceCanAccessPeer(&can, device, box->device));
+        if (!can) return fail("dllm_mailbox_view: no peer access between the two devices");
+        CUDA_TRY(cudaSetDevice(device));
+        cudaError_t e = cudaDeviceEnablePeerAccess(box->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CUDA_TRY(e);
+        cudaGetLastError();
+    }
+    dllm_mailbox* b = new dllm_mailbox(*box);
+    b->device = device; b->owner = false; b->ipc = false;
+    *out = b;
+    return 0;
+}
+
+extern "C" int dllm_mailbox_post_tokens(dllm_mailbox* b, int32_t slot, const int32_t* tokens, uint32_t ticket, void* stream) {
+    if (!b || !b->owner || !tokens || slot < 0 || slot >= b->n_slots) return fail("dllm_mailbox_post_tokens: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(b->device));
+    CUDA_TRY(cudaMemcpyAsync(b->tokens() + (size_t)slot * b->rows, tokens, (size_t)b->rows * 4, cudaMemcpyDefault, st));
+    // after the ids, stream-ordered (a copy from a pageable host word is staged before the call returns)
+    CUDA_TRY(cudaMemcpyAsync(b->flags() + (size_t)slot * kFlagStride, &ticket, 4, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int dllm_mailbox_read_tokens(dllm_mailbox* b, int32_t slot, int32_t* tokens_out, uint32_t* ticket_out, void* stream) {
+    if (!b || !b->owner || !tokens_out || slot < 0 || slot >= b->n_slots) return fail("dllm_mailbox_read_tokens: bad argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(b->device));
+    CUDA_TRY(cudaMemcpyAsync(tokens_out, b->tokens() + (size_t)slot * b->rows, (size_t)b->rows * 4, cudaMemcpyDefault, st));
+    if (ticket_out) CUDA_TRY(cudaMemcpyAsync(ticket_out, b->flags() + (size_t)slot * kFlagStride, 4, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int dllm_mailbox_destroy(dllm_mailbox* b) {
+    if (!b) return 0;
+    cudaSetDevice(b->device);
+    if (b->owner && b->base) {
+        cudaDeviceSynchronize();
+        cudaFree(b->base);
+    } else if (b->ipc && b->base) {
+        cudaIpcCloseMemHandle(b->base);
+    }
+    delete b;
+    return 0;
+}
+
+extern "C" int dllm_shard_decode_pipelined(dllm_shard* s, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
+                                           int32_t rows, int32_t n_steps, uint32_t step_base, const int32_t* positions,
+                                           const int32_t* seq_ids, int32_t* fed_tokens_out, void* stream) {
+    if (!s || !inbox || !outbox || !positions || !seq_ids) return fail("dllm_shard_decode_pipelined: null argument");
+    const dllm_shard_config& c = s->cfg;
+    if (n_micro < 1 || rows < 1 || n_steps < 1) return fail("dllm_shard_decode_pipelined: n_micro, rows and n_steps must be positive");
+    if ((long)n_micro * rows > c.max_rows)
+        return fail("dllm_shard_decode_pipelined: n_micro * rows exceeds max_rows");
+    if (!inbox->owner || inbox->device != s->device || outbox->device != s->device)
+        return fail("dllm_shard_decode_pipelined: the inbox must be this stage's own mailbox and the outbox a view mapped on this stage's device");
+    for (const dllm_mailbox* b : {inbox, outbox})
+        if (b->n_slots < n_micro || b->rows != rows || b->hidden != c.hidden) return fail("dllm_shard_decode_pipelined: mailbox shape does not match");
+    if (c.has_embed && (size_t)n_steps * n_micro * rows > s->tok_ring_cap) return fail("dllm_shard_decode_pipelined: n_steps out of range");
+    if (c.n_layers < 1) return fail("dllm_shard_decode_pipelined: the stage has no layers");
+    if (!mk_eligible(s, rows, rows, true)) return fail("dllm_shard_decode_pipelined: shape not taken by the persistent kernel (bf16, <= 16 rows, fits shared memory)");
+    cudaStream_t st = (cudaStream_t)stream;
+    int dev = -1;
+    cudaGetDevice(&dev);
+    if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaMemcpyAsync(s->pos, positions, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
+    CUDA_TRY(cudaMemcpyAsync(s->seq, seq_ids, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
+    MkPipe pipe{inbox, outbox, n_micro, step_base};
+    if (run_megakernel(s, rows, n_steps * n_micro, false, st, &pipe)) return 1;
+    if (c.has_embed && fed_tokens_out)
+        CUDA_TRY(cudaMemcpyAsync(fed_tokens_out, s->tok_ring, (size_t)n_steps * n_micro * rows * 4, cudaMemcpyDefault, st));
+    return 0;
+}
 
 extern "C" int dllm_handoff_peer_copy(void* dst_ptr, int dst_device, const void* src_ptr, int src_device,
                                       size_t bytes, void* stream) {

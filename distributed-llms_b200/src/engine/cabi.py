@@ -54,6 +54,14 @@ SIGNATURES = {
     "dllm_shard_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp, _vp, _vp]),
     "dllm_shard_decode_loop": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
     "dllm_handoff_peer_copy": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _sz, _vp]),
+    "dllm_mailbox_create": (C.c_int, [_i32, _i32, _i32, _i32, C.POINTER(C.c_void_p)]),
+    "dllm_mailbox_export": (C.c_int, [_vp, _vp]),
+    "dllm_mailbox_import": (C.c_int, [_i32, _vp, _i32, _i32, _i32, C.POINTER(C.c_void_p)]),
+    "dllm_mailbox_view": (C.c_int, [_vp, _i32, C.POINTER(C.c_void_p)]),
+    "dllm_mailbox_post_tokens": (C.c_int, [_vp, _i32, _vp, C.c_uint32, _vp]),
+    "dllm_mailbox_read_tokens": (C.c_int, [_vp, _i32, _vp, _vp, _vp]),
+    "dllm_mailbox_destroy": (C.c_int, [_vp]),
+    "dllm_shard_decode_pipelined": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, C.c_uint32, _vp, _vp, _vp, _vp]),
     "dllm_op_gemv": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "dllm_op_gemm": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),
     "dllm_op_decode_attention_scratch_bytes": (_sz, [_i32, _i32, _i32, _i32]),

@@ -311,4 +311,25 @@ class ShardExecutor:
             cabi.check(cabi.lib().dllm_shard_decode_loop(self._handle, batch, n_steps, toks.data_ptr(), st))
         return toks.t().to(torch.int64)
 
+    def decode_pipelined(self, inbox, outbox, n_micro: int, rows: int, n_steps: int, step_base: int,
+                         positions: torch.Tensor, seq_ids: torch.Tensor) -> Optional[torch.Tensor]:
+        """`n_steps` decode steps of `n_micro` micro-batches in ONE persistent launch with the hand-off fused into
+        the kernel (`dllm_shard_decode_pipelined`; mailboxes from `src/network/handoff.py`).  `positions` /
+        `seq_ids`: int32 [n_micro, rows] -- position of the token fed at the first step, KV slot of each row.
+        Asynchronous on the current stream.  The first stage returns the int32 ids it fed, [n_steps, n_micro, rows]."""
+        pos = positions.to("cpu", torch.int32).reshape(n_micro * rows).contiguous()
+        seq = seq_ids.to("cpu", torch.int32).reshape(n_micro * rows).contiguous()
+        if int(pos.max()) + n_steps > self.max_context:
+            raise ValueError("decode_pipelined would run past max_context")
+        fed = torch.empty(n_steps, n_micro, rows, dtype=torch.int32, device=self.device) if self.has_embed else None
+        with self.lock, torch.cuda.device(self.device):
+            st = self._stream()
+            for s_, p_ in zip(seq.tolist(), pos.tolist()):
+                cabi.check(cabi.lib().dllm_shard_kv_reserve(self._handle, s_, p_ + n_steps, st))
+                self._seq_len[s_] = max(self._seq_len.get(s_, 0), p_ + n_steps)
+            cabi.check(cabi.lib().dllm_shard_decode_pipelined(
+                self._handle, inbox.handle, outbox.handle, n_micro, rows, n_steps, step_base, pos.data_ptr(),
+                seq.data_ptr(), fed.data_ptr() if fed is not None else None, st))
+        return fed
+
     _last_seqs: List[int] = []

@@ -67,3 +67,81 @@ class StageLink:
         if self.is_first and self.world > 1:
             dist.recv(buf, src=self.world - 1, group=self.ring_group)
         return buf
+
+
+# ---- fused hand-off: mailboxes in peer memory ----------------------------------------------------------------
+
+class Mailbox:
+    """A stage's inbox (owner side) or a producer's view of another stage's inbox (`dllm_mailbox_*`,
+    include/dllm_b200.h).  Per slot (micro-batch): a ticket, `rows` token ids, `rows x hidden` bf16 rows."""
+
+    def __init__(self, handle, device: int, n_slots: int, rows: int, hidden: int, owner: bool):
+        self.handle, self.device, self.n_slots, self.rows, self.hidden, self.owner = handle, device, n_slots, rows, hidden, owner
+
+    @classmethod
+    def create(cls, device: int, n_slots: int, rows: int, hidden: int) -> "Mailbox":
+        import ctypes as C
+        from ..engine import cabi
+        h = C.c_void_p()
+        cabi.check(cabi.lib().dllm_mailbox_create(device, n_slots, rows, hidden, C.byref(h)))
+        return cls(h, device, n_slots, rows, hidden, True)
+
+    def export_handle(self) -> bytes:
+        import ctypes as C
+        from ..engine import cabi
+        buf = C.create_string_buffer(64)
+        cabi.check(cabi.lib().dllm_mailbox_export(self.handle, buf))
+        return buf.raw
+
+    @classmethod
+    def open_peer(cls, device: int, ipc: bytes, n_slots: int, rows: int, hidden: int) -> "Mailbox":
+        """Another process's mailbox, mapped on `device` (cudaIpcOpenMemHandle)."""
+        import ctypes as C
+        from ..engine import cabi
+        h = C.c_void_p()
+        cabi.check(cabi.lib().dllm_mailbox_import(device, C.create_string_buffer(ipc, 64), n_slots, rows, hidden, C.byref(h)))
+        return cls(h, device, n_slots, rows, hidden, False)
+
+    def view_from(self, device: int) -> "Mailbox":
+        """Same process, other GPU."""
+        import ctypes as C
+        from ..engine import cabi
+        h = C.c_void_p()
+        cabi.check(cabi.lib().dllm_mailbox_view(self.handle, device, C.byref(h)))
+        return Mailbox(h, device, self.n_slots, self.rows, self.hidden, False)
+
+    def post_tokens(self, slot: int, tokens: torch.Tensor, ticket: int) -> None:
+        from ..engine import cabi
+        t = tokens.to(torch.int32).contiguous()
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        cabi.check(cabi.lib().dllm_mailbox_post_tokens(self.handle, slot, t.data_ptr(), ticket, st))
+
+    def read_tokens(self, slot: int) -> tuple[torch.Tensor, int]:
+        import ctypes as C
+        from ..engine import cabi
+        out = torch.empty(self.rows, dtype=torch.int32)
+        ticket = C.c_uint32(0)
+        st = torch.cuda.current_stream(self.device).cuda_stream
+        cabi.check(cabi.lib().dllm_mailbox_read_tokens(self.handle, slot, out.data_ptr(), C.byref(ticket), st))
+        return out, int(ticket.value)
+
+    def close(self) -> None:
+        if self.handle is not None:
+            from ..engine import cabi
+            cabi.lib().dllm_mailbox_destroy(self.handle)
+            self.handle = None
+
+
+def exchange_mailboxes(rank: int, world: int, device: int, n_slots: int, rows: int, hidden: int):
+    """Every stage creates its inbox and opens the next stage's (the first stage's for the last stage).  Collective:
+    the 64-byte IPC handles travel through `all_gather` of the existing process group.  Returns (inbox, outbox)."""
+    inbox = Mailbox.create(device, n_slots, rows, hidden)
+    if world == 1:
+        return inbox, inbox
+    dev = torch.device("cuda", device)
+    mine = torch.frombuffer(bytearray(inbox.export_handle()), dtype=torch.uint8).to(dev)
+    everyone = [torch.empty(64, dtype=torch.uint8, device=dev) for _ in range(world)]
+    dist.all_gather(everyone, mine)
+    nxt = (rank + 1) % world
+    outbox = Mailbox.open_peer(device, bytes(everyone[nxt].cpu().numpy().tobytes()), n_slots, rows, hidden)
+    return inbox, outbox

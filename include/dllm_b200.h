@@ -162,6 +162,48 @@ DLLM_API int dllm_shard_decode_loop(dllm_shard* shard, int32_t n_rows, int32_t n
 
 /* ---- stage-to-stage hand-off ------------------------------------------------------------------ */
 
+/* Fused hand-off for the steady-state decode loop.  Replaces, for the data plane inside one NVLink box,
+ * the request/response round trip `MessageProtocol.send_message` / `receive_message` (reference
+ * src/network/protocol.py:38-129) that `MasterNode._process_tasks` (reference src/master/node.py:227-277)
+ * would drive once per token: every stage runs ONE persistent kernel for the whole loop; a stage's last
+ * down-projection epilogue stores its output rows straight into the next stage's *mailbox* (peer memory over
+ * NVLink) and publishes a ticket; the last stage stores the sampled token ids into the first stage's mailbox.
+ * No launch, no collective library call and no host involvement per token.
+ *
+ * A mailbox is device memory of its owner: per slot (micro-batch) a ticket, `rows` int32 token ids and
+ * `rows x hidden` bf16 hidden rows.  Slot tickets count delivered inputs: the consumer of decode step G waits
+ * for ticket >= G + 1.  One process per GPU: the owner exports a 64-byte IPC handle, the producer imports it. */
+typedef struct dllm_mailbox dllm_mailbox;
+#define DLLM_MAILBOX_IPC_BYTES 64
+DLLM_API int dllm_mailbox_create(int32_t device, int32_t n_slots, int32_t rows, int32_t hidden, dllm_mailbox** out);
+/* `ipc_handle_out`: DLLM_MAILBOX_IPC_BYTES bytes (host) to hand to the producer's process. */
+DLLM_API int dllm_mailbox_export(dllm_mailbox* box, void* ipc_handle_out);
+/* The producer's view of another process's mailbox, mapped on `device` (the producer's GPU). */
+DLLM_API int dllm_mailbox_import(int32_t device, const void* ipc_handle, int32_t n_slots, int32_t rows, int32_t hidden,
+                        dllm_mailbox** out);
+/* Same process, different GPU (tests, single-process multi-GPU hosts): a view of `box` usable from `device`. */
+DLLM_API int dllm_mailbox_view(dllm_mailbox* box, int32_t device, dllm_mailbox** out);
+/* Owner side: put `rows` token ids (host or device) into `slot` and set its ticket (seeds decode step
+ * `ticket - 1`), stream-ordered.  */
+DLLM_API int dllm_mailbox_post_tokens(dllm_mailbox* box, int32_t slot, const int32_t* tokens, uint32_t ticket, void* stream);
+/* Owner side: copy out the token ids currently in `slot` (host or device destination) and, if `ticket_out`
+ * (host) is given, the slot's ticket; synchronises `stream`. */
+DLLM_API int dllm_mailbox_read_tokens(dllm_mailbox* box, int32_t slot, int32_t* tokens_out, uint32_t* ticket_out, void* stream);
+DLLM_API int dllm_mailbox_destroy(dllm_mailbox* box);
+
+/* `n_steps` decode steps of `n_micro` micro-batches of `rows` rows each in one persistent launch (bf16, rows
+ * <= 16, shapes the persistent kernel takes).  `inbox` is this stage's own mailbox, `outbox` the next stage's
+ * (the first stage's for the last stage; for a single stage pass its own inbox twice).  `positions`, `seq_ids`
+ * (host or device, int32 [n_micro * rows]): position of the token fed at this call's first step and the KV slot of
+ * every row; KV pages must be reserved up to position + n_steps.  `step_base`: decode steps done by earlier calls
+ * (tickets keep counting).  `fed_tokens_out` (first stage only, host or device, int32 [n_steps][n_micro][rows],
+ * may be null): the token ids this stage fed at every step -- the seed at step 0, afterwards what the last stage
+ * generated one step earlier; the ids generated by the final step are in the inbox (dllm_mailbox_read_tokens)
+ * once every stage has finished. */
+DLLM_API int dllm_shard_decode_pipelined(dllm_shard* shard, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
+                                int32_t rows, int32_t n_steps, uint32_t step_base, const int32_t* positions,
+                                const int32_t* seq_ids, int32_t* fed_tokens_out, void* stream);
+
 /* Replaces `MessageProtocol.send_message` / `receive_message` (reference
  * src/network/protocol.py:38-129) for the data plane inside one NVLink box: copy the hand-off tile
  * (`bytes` of hidden states) from this device to `dst_ptr` on device `dst_device` over NVLink

@@ -395,3 +395,42 @@ def test_streamed_rows_variant_matches_oracle(batch, monkeypatch):
     first = stages[0].compute({"input_ids": prompts})["next_token"].cpu()
     rest = stages[0].decode_loop(batch, 11).cpu()
     assert torch.equal(torch.cat([first[:, None], rest], 1), ids)
+
+
+@pytest.mark.parametrize("n_micro,rows", [(1, 1), (3, 2), (2, 8)])
+def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows):
+    """One stage, its own mailbox as in- and outbox: the persistent kernel feeds the token ids round through the
+    mailbox tickets.  Every micro-batch must reproduce, bit for bit, what the classic device loop generates."""
+    from src.network.handoff import Mailbox
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    n_steps, T = 7, 10
+    (st,) = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=64, max_seqs=n_micro * rows, max_context=64, page_size=16)
+    prompts = [make_prompts(cfg.vocab, rows, T, seed=20 + m) for m in range(n_micro)]
+    want, seeds = [], []
+    for m in range(n_micro):
+        seqs = torch.arange(m * rows, (m + 1) * rows, dtype=torch.int32)
+        first = st.compute({"input_ids": prompts[m], "seq_ids": seqs})["next_token"].cpu()
+        want.append(torch.cat([first[:, None], st.decode_loop(rows, n_steps).cpu()], 1))  # [rows, 1 + n_steps]
+    st.reset()
+    for m in range(n_micro):
+        seqs = torch.arange(m * rows, (m + 1) * rows, dtype=torch.int32)
+        seeds.append(st.compute({"input_ids": prompts[m], "seq_ids": seqs})["next_token"].to(torch.int32))
+    box = Mailbox.create(0, n_micro, rows, cfg.hidden)
+    try:
+        for m in range(n_micro):
+            box.post_tokens(m, seeds[m], ticket=1)
+        pos = torch.full((n_micro, rows), T, dtype=torch.int32)
+        seq = torch.arange(n_micro * rows, dtype=torch.int32).reshape(n_micro, rows)
+        # two launches: tickets and positions carry over
+        fed_a = st.executor.decode_pipelined(box, box, n_micro, rows, 4, 0, pos, seq)
+        fed_b = st.executor.decode_pipelined(box, box, n_micro, rows, n_steps - 4, 4, pos + 4, seq)
+        torch.cuda.synchronize()
+        fed = torch.cat([fed_a, fed_b]).cpu()  # [n_steps, n_micro, rows]: seed, then the ids generated one step earlier
+        for m in range(n_micro):
+            last, ticket = box.read_tokens(m)
+            assert ticket == n_steps + 1
+            got = torch.cat([fed[:, m, :].t(), last[:, None]], 1).to(torch.int64)
+            assert torch.equal(got, want[m]), m
+    finally:
+        box.close()
