@@ -114,7 +114,7 @@ def workload_name(model: str, batch: int, prompt_len: int, stages: int, n_layers
     """The same string in both arms' `config.workload`."""
     if stages == 1:
         return f"{model} decode, batch {batch}, {prompt_len}-token prompt, 1 stage"
-    return (f"{model} decode, {stages} stages x {n_layers // stages} layers, {stages} micro-batches of {batch} in flight, "
+    return (f"{model} decode, {n_layers} layers over {stages} stages, {stages} micro-batches of {batch} in flight, "
             f"{prompt_len}-token prompts")
 
 

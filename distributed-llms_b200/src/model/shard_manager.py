@@ -43,6 +43,23 @@ def contiguous_partition(n_layers: int, num_shards: int) -> List[range]:
     return [range(c(i), c(i + 1)) for i in range(num_shards)]
 
 
+def balanced_partition(n_layers: int, num_shards: int, head_cost_layers: float) -> List[range]:
+    """Contiguous layer ranges that even out the bytes a stage streams per decode step when the last stage also
+    owns the lm_head (`head_cost_layers` = head bytes / bytes of one layer): the last stage gets fewer layers.
+    Minimises the slowest stage; ties keep the split closest to `contiguous_partition`."""
+    if num_shards == 1 or head_cost_layers <= 0:
+        return contiguous_partition(n_layers, num_shards)
+    best = None
+    for last in range(1, n_layers - (num_shards - 1) + 1):
+        rest = n_layers - last
+        cost = max(-(-rest // (num_shards - 1)), last + head_cost_layers)
+        if best is None or cost < best[0] - 1e-9 or (abs(cost - best[0]) <= 1e-9 and last > best[1]):
+            best = (cost, last)
+    last = best[1]
+    head = contiguous_partition(n_layers - last, num_shards - 1)
+    return head + [range(n_layers - last, n_layers)]
+
+
 def partition_state_dict(state_dict: Dict[str, torch.Tensor], num_shards: int, tie_head: bool = False
                          ) -> List[Dict[str, torch.Tensor]]:
     sd = {strip_prefix(k): v for k, v in state_dict.items()}

@@ -220,3 +220,15 @@ class TestMessageProtocol:
         header, payload = client.receive_message(dealer, timeout=5)
         assert header["command"] == "LOAD_SHARD" and header["shard_id"] == 3 and payload == b"abc"
         router.close(); dealer.close()
+
+
+def test_balanced_partition_accounts_for_the_head():
+    from src.model.shard_manager import balanced_partition, contiguous_partition
+    # Llama-3-8B: the lm_head streams as many bytes as 2.4 layers
+    for stages, biggest, last in ((2, 17, 15), (4, 9, 6), (8, 5, 2)):
+        parts = balanced_partition(32, stages, 2.4)
+        assert max(len(r) for r in parts) == biggest and len(parts[-1]) == last and len(parts) == stages
+        assert [i for r in parts for i in r] == list(range(32))  # contiguous, complete, in order
+    assert balanced_partition(32, 1, 2.4) == contiguous_partition(32, 1)
+    assert balanced_partition(12, 4, 0.0) == contiguous_partition(12, 4)
+    assert [len(r) for r in balanced_partition(4, 4, 5.0)] == [1, 1, 1, 1]
