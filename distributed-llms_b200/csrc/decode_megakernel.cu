@@ -582,7 +582,8 @@ __device__ __forceinline__ int attn_safe_end(const StepCache& sc, const AttnUnit
     return sc.pos[a.r] - (MK_MAX_ROWS - 1);
 }
 
-__device__ __forceinline__ void attention_phase(const MkParams& p, const StepCache& sc, const int* sbt, const MkLayer& L, const AttnSmem& sm, bool prefetched) {
+__device__ __forceinline__ void attention_phase(const MkParams& p, const StepCache& sc, const int* sbt, const MkLayer& L, const AttnSmem& sm, bool prefetched,
+                                                long long* tr = nullptr) {
     const int hd = p.head_dim, H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int epl = hd >> 5;  // output columns per lane: 1, 2 or 4
@@ -592,17 +593,31 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
     for (int u = blockIdx.x; u < n_units; u += gridDim.x, first = false) {
         const AttnUnit a = attn_unit(p, sc, u);
         if (a.t0 >= a.t1) continue;  // split past the end of the context: the merge never reads it
-        // q of the Gq heads of this KV head -> shared, fp32
-        for (int i = threadIdx.x; i < Gq * hd; i += kThreads)
-            sm.q[i] = __bfloat162float(__ldcg(static_cast<const bf16*>(p.q) + ((size_t)a.r * H + a.kvh * Gq) * hd + i));
-        float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};  // warp g owns head g: (m, l) and hd/32 columns per lane
+        // Every warp works for head `hw`; the warps of one head split a tile's tokens between them (token t belongs to
+        // slice t % n_sl) and keep their own running output; (m, l) are computed redundantly and so agree bit for bit.
+        const int n_sl = kWarps / Gq > 0 ? min(kWarps / Gq, 4) : 1;  // token slices per head
+        const int hw = warp % Gq, sl = warp / Gq;                    // meaningful while warp < Gq * n_sl
+        const bool pv_warp = warp < Gq * n_sl;
+        float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};   // (m, l) of head hw; hd/32 output columns per lane
         for (int tile0 = a.t0; tile0 < a.t1; tile0 += kTT) {
             const int tend = min(a.t1, tile0 + kTT), nt = tend - tile0;
             int from = tile0;
             if (first && prefetched && tile0 == a.t0) from = max(tile0, min(tend, attn_safe_end(sc, a)));
             attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend);
+            if (tile0 == a.t0) {
+                // q of the Gq heads of this KV head -> shared, fp32: one 16-byte L2 load per thread, in flight together
+                // with the K/V copies above
+                for (int i = threadIdx.x; i < (Gq * hd) >> 3; i += kThreads) {
+                    float f[8];
+                    unpack<bf16>(__ldcg(reinterpret_cast<const uint4*>(static_cast<const bf16*>(p.q) + ((size_t)a.r * H + a.kvh * Gq) * hd) + i), f);
+                    *reinterpret_cast<float4*>(sm.q + i * 8) = make_float4(f[0], f[1], f[2], f[3]);
+                    *reinterpret_cast<float4*>(sm.q + i * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
+                }
+                if (tr) tr[4] = clock64();  // q staged
+            }
             cp_async_wait_all();
             __syncthreads();
+            if (tr) tr[5] = clock64();  // K/V tile in shared memory
             // scores: one (token, head) pair per thread-iteration; lanes walk tokens (padded rows: no conflicts)
             for (int i = threadIdx.x; i < kTT * Gq; i += kThreads) {
                 const int t = i & (kTT - 1), g = i / kTT;
@@ -622,8 +637,9 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 }
             }
             __syncthreads();
-            if (warp < Gq) {  // online softmax + P.V for head `warp`
-                float* sg = sm.s + warp * kTT;
+            if (tr) tr[6] = clock64();  // scores done
+            if (pv_warp) {  // online softmax (whole tile) + P.V over this warp's token slice
+                const float* sg = sm.s + hw * kTT;
                 const float s0 = lane < nt ? sg[lane] : -FLT_MAX;
                 const float s1 = lane + 32 < nt ? sg[lane + 32] : -FLT_MAX;
                 const float mn = fmaxf(m, warp_max(fmaxf(s0, s1)));
@@ -632,43 +648,64 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 const float corr = expf(m - mn);
                 l = l * corr + warp_sum(p0 + p1);
                 m = mn;
-                if (lane < nt) sg[lane] = p0;
-                if (lane + 32 < nt) sg[lane + 32] = p1;
-                __syncwarp();
 #pragma unroll
                 for (int e = 0; e < 4; ++e) o[e] *= corr;
-                if (epl == 2) {
-                    float oa0 = 0.f, oa1 = 0.f, ob0 = 0.f, ob1 = 0.f;  // two independent chains
-                    int t = 0;
-                    for (; t + 1 < nt; t += 2) {
-                        const uint32_t va = *reinterpret_cast<const uint32_t*>(sm.v + (size_t)t * ld + lane * 2);
-                        const uint32_t vb = *reinterpret_cast<const uint32_t*>(sm.v + (size_t)(t + 1) * ld + lane * 2);
-                        const float pa = sg[t], pb = sg[t + 1];
-                        oa0 = fmaf(pa, __uint_as_float(va << 16), oa0);
-                        oa1 = fmaf(pa, __uint_as_float(va & 0xffff0000u), oa1);
-                        ob0 = fmaf(pb, __uint_as_float(vb << 16), ob0);
-                        ob1 = fmaf(pb, __uint_as_float(vb & 0xffff0000u), ob1);
-                    }
-                    if (t < nt) {
-                        const uint32_t va = *reinterpret_cast<const uint32_t*>(sm.v + (size_t)t * ld + lane * 2);
-                        oa0 = fmaf(sg[t], __uint_as_float(va << 16), oa0);
-                        oa1 = fmaf(sg[t], __uint_as_float(va & 0xffff0000u), oa1);
-                    }
-                    o[0] += oa0 + ob0;
-                    o[1] += oa1 + ob1;
-                } else {
-                    for (int t = 0; t < nt; ++t) {
-                        const float pt = sg[t];
-                        const bf16* vr = sm.v + (size_t)t * ld + lane * epl;
-#pragma unroll
-                        for (int e = 0; e < 4; ++e)
-                            if (e < epl) o[e] = fmaf(pt, __bfloat162float(vr[e]), o[e]);
+                // probabilities stay in registers: token t's weight lives in lane t % 32 (p0 for t < 32, else p1)
+                float oa[4] = {0.f, 0.f, 0.f, 0.f}, ob[4] = {0.f, 0.f, 0.f, 0.f};  // two independent chains
+                int t = sl;
+                for (; t + n_sl < nt; t += 2 * n_sl) {
+                    const int tb = t + n_sl;
+                    const float pa = __shfl_sync(0xffffffffu, t < 32 ? p0 : p1, t & 31);
+                    const float pb = __shfl_sync(0xffffffffu, tb < 32 ? p0 : p1, tb & 31);
+                    const bf16* va = sm.v + (size_t)t * ld + lane * epl;
+                    const bf16* vb = sm.v + (size_t)tb * ld + lane * epl;
+                    if (epl == 4) {
+                        const uint2 ra = *reinterpret_cast<const uint2*>(va), rb = *reinterpret_cast<const uint2*>(vb);
+                        oa[0] = fmaf(pa, __uint_as_float(ra.x << 16), oa[0]); oa[1] = fmaf(pa, __uint_as_float(ra.x & 0xffff0000u), oa[1]);
+                        oa[2] = fmaf(pa, __uint_as_float(ra.y << 16), oa[2]); oa[3] = fmaf(pa, __uint_as_float(ra.y & 0xffff0000u), oa[3]);
+                        ob[0] = fmaf(pb, __uint_as_float(rb.x << 16), ob[0]); ob[1] = fmaf(pb, __uint_as_float(rb.x & 0xffff0000u), ob[1]);
+                        ob[2] = fmaf(pb, __uint_as_float(rb.y << 16), ob[2]); ob[3] = fmaf(pb, __uint_as_float(rb.y & 0xffff0000u), ob[3]);
+                    } else if (epl == 2) {
+                        const uint32_t ra = *reinterpret_cast<const uint32_t*>(va), rb = *reinterpret_cast<const uint32_t*>(vb);
+                        oa[0] = fmaf(pa, __uint_as_float(ra << 16), oa[0]); oa[1] = fmaf(pa, __uint_as_float(ra & 0xffff0000u), oa[1]);
+                        ob[0] = fmaf(pb, __uint_as_float(rb << 16), ob[0]); ob[1] = fmaf(pb, __uint_as_float(rb & 0xffff0000u), ob[1]);
+                    } else {
+                        oa[0] = fmaf(pa, __bfloat162float(va[0]), oa[0]);
+                        ob[0] = fmaf(pb, __bfloat162float(vb[0]), ob[0]);
                     }
                 }
+                if (t < nt) {
+                    const float pa = __shfl_sync(0xffffffffu, t < 32 ? p0 : p1, t & 31);
+                    const bf16* va = sm.v + (size_t)t * ld + lane * epl;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (e < epl) oa[e] = fmaf(pa, __bfloat162float(va[e]), oa[e]);
+                }
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] += oa[e] + ob[e];
             }
             __syncthreads();  // tile buffers are reused
+            if (tr) tr[7] = clock64();  // softmax + P.V done
         }
-        if (warp < Gq) {
+        // sum the token slices of a head in fixed order (through the score buffer, free now), slice 0 stores
+        if (n_sl > 1) {
+            float* red = sm.q;  // [Gq][hd] fp32, free after the last tile's scores; slices 1.. add in turn
+            for (int k2 = 1; k2 < n_sl; ++k2) {
+                if (pv_warp && sl == k2) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (e < epl) red[hw * hd + lane * epl + e] = o[e];
+                }
+                __syncthreads();
+                if (pv_warp && sl == 0) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (e < epl) o[e] += red[hw * hd + lane * epl + e];
+                }
+                __syncthreads();
+            }
+        }
+        if (warp < Gq) {  // slice 0 of head `warp` (hw == warp, sl == 0)
             const size_t pidx = ((size_t)a.r * H + a.kvh * Gq + warp) * S + a.split;
 #pragma unroll
             for (int e = 0; e < 4; ++e)
@@ -856,7 +893,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 continue;
             }
             if (ph.kind == MK_ATTN) {
-                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true);
+                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true, tr);
                 if (tr) tr[1] = tr[2] = tr[3] = clock64();
                 continue;
             }
