@@ -205,6 +205,8 @@ def run_single(args) -> int:
     from src.worker.node import ModelShard
 
     model, batch, prompt_len = WORKLOADS[args.workload or "tinyllama-1.1b"]
+    if args.prompt_len:
+        prompt_len = args.prompt_len
     if args.batch:
         batch = args.batch
     K = args.steps if args.steps > 0 else 256
@@ -216,7 +218,7 @@ def run_single(args) -> int:
     dev = "cuda:0"
     params = random_init.random_stage_parameters(hf, range(L), True, True, 1234, torch.bfloat16, device=dev)
     max_ctx = prompt_len + 2 * (W + K) + 16
-    shard = ModelShard(0, params, config=hf, max_rows=max(prompt_len * batch, 128), max_seqs=batch, max_context=max_ctx, page_size=64)
+    shard = ModelShard(0, params, config=hf, max_rows=max(min(prompt_len, 2048) * batch, 128), max_seqs=batch, max_context=max_ctx, page_size=64)
     shard.to_device()
     ex = shard.executor
     g = torch.Generator().manual_seed(7)
@@ -330,6 +332,7 @@ def main() -> int:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=[None, *WORKLOADS])
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--prompt-len", type=int, default=0, help="override the workload's prompt length (single GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

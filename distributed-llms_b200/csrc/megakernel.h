@@ -10,7 +10,7 @@ constexpr int MK_THREADS = 384;
 constexpr int MK_STAGE_K = 256;                    // k-elements of one stage
 constexpr int MK_STAGE_BYTES = 8 * MK_STAGE_K * 2; // one stage = 8 weight rows x 256 k, bf16 = 4 KB
 constexpr int MK_MAX_ROWS = 16;
-constexpr int MK_MAX_SPLITS = 8;   // one batch of eight 16-byte loads per thread in the merge
+constexpr int MK_MAX_SPLITS = 16;  // the merge loads the partials in batches of eight 16-byte vectors per thread
 constexpr int MK_MAX_PHASES = 512;  // 5 per layer + 2: up to 102 layers per stage
 constexpr int MK_SMEM_BUDGET = 227 * 1024 - 6 * 1024;  // dynamic shared memory: the opt-in maximum less the kernel's static arrays
 constexpr int MK_ROUND_PANELS = 13; // panels a CTA works on between two epilogues

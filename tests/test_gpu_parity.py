@@ -434,3 +434,26 @@ def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows):
             assert torch.equal(got, want[m]), m
     finally:
         box.close()
+
+
+@pytest.mark.parametrize("batch,prompt_len", [(1, 1300), (2, 2100)])
+def test_long_context_decode_matches_oracle(batch, prompt_len):
+    """Contexts beyond 64 tokens x 16 splits: every attention unit of the persistent kernel walks several K/V tiles
+    (online softmax across tiles, merge across splits); chunked flash-style prefill before it.  bf16 vs the oracle."""
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 2304, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 11, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, batch, prompt_len, seed=9)
+    sdd = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+    n_new = 6
+    o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16, max_context=prompt_len + 16), prompts, n_new, record=True)
+    stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=1024, max_seqs=batch, max_context=prompt_len + 16, page_size=64)
+    ids, lg = gpu_generate(stages, prompts, n_new)
+    same_prefix = (ids == o_ids).long().cumprod(1).bool()
+    for t in range(n_new):
+        rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
+        if rows.any():
+            assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
+    for b in range(ids.shape[0]):
+        if not same_prefix[b].all():
+            t = int((~same_prefix[b]).float().argmax())
+            assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
