@@ -14,6 +14,7 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -22,9 +23,11 @@ namespace dllm {
 
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 64;      // tile; BK * 2 bytes = one 128-byte swizzle row
+constexpr int BM = 128, BK = 64;                // tile rows / k-slice; BK * 2 bytes = one 128-byte swizzle row
 constexpr int kStages = 4;
-constexpr int kTileBytes = BM * BK * 2;         // 16 KB per operand tile
+constexpr int kTileBytes = BM * BK * 2;         // 16 KB per 128-row operand tile
+// Output tile width BN: 128, or 256 when the grid still fills the machine -- the A tile is then read once per
+// 256 columns (87 instead of 64 flop per shared-memory byte staged).
 constexpr int kGemmThreads = 192;
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -83,21 +86,26 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 
-// Instruction descriptor: D fp32, A and B bf16, both K-major, N = 128, M = 128.
-constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// Instruction descriptor: D fp32, A and B bf16, both K-major, N = bn, M = 128.
+constexpr uint32_t make_idesc(int bn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+}
 
 __device__ __forceinline__ float silu_f(float g) { return g / (1.0f + expf(-g)); }
 __device__ __forceinline__ float gelu_new_f(float x) {
     return 0.5f * x * (1.0f + tanhf(0.7978845608028654f * (x + 0.044715f * x * x * x)));
 }
 
-template <int EPI>
+template <int EPI, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                const __grid_constant__ CUtensorMap tm_b2, const GemmTcParams p) {
     constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
-    constexpr int kStageBytes = kTileBytes * (kDual ? 3 : 2);
-    constexpr uint32_t kTmemCols = kDual ? 256 : 128;
+    static_assert(!(kDual && BN != 128), "the dual-B tile is 128 wide");
+    constexpr int kBTileBytes = BN * BK * 2;
+    constexpr int kStageBytes = kTileBytes + kBTileBytes * (kDual ? 2 : 1);
+    constexpr uint32_t kTmemCols = kDual ? 256 : BN;
+    constexpr uint32_t kIdesc = make_idesc(BN);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bars[2 * kStages + 1];
@@ -135,7 +143,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 mbar_expect_tx(full0 + s * 8, kStageBytes);
                 tma_load_2d(dst, &tm_a, kb * BK, m0, full0 + s * 8);
                 tma_load_2d(dst + kTileBytes, &tm_b, kb * BK, n0, full0 + s * 8);
-                if (kDual) tma_load_2d(dst + 2 * kTileBytes, &tm_b2, kb * BK, n0, full0 + s * 8);
+                if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, kb * BK, n0, full0 + s * 8);
             }
         }
     } else if (warp == 1) {
@@ -147,7 +155,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 tc_fence_after();
                 const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
                 const uint64_t da = make_sw128_desc(base), db = make_sw128_desc(base + kTileBytes);
-                const uint64_t db2 = make_sw128_desc(base + 2 * kTileBytes);
+                const uint64_t db2 = make_sw128_desc(base + kTileBytes + kBTileBytes);
 #pragma unroll
                 for (int k = 0; k < BK / 16; ++k) {
                     // 16 k-elements = 32 bytes further along the swizzled row: +2 in the (address >> 4) field
@@ -320,33 +328,40 @@ EncodeTiledFn get_encode() {
     return fn;
 }
 
-// [rows, K] row-major bf16, box = 128 rows x 64 k, 128-byte swizzle, out-of-bounds reads return zero
-bool make_map(CUtensorMap* map, const void* base, int rows, int K) {
+// [rows, K] row-major bf16, box = box_rows (128 or 256) rows x 64 k, 128-byte swizzle, out-of-bounds reads return zero
+bool make_map(CUtensorMap* map, const void* base, int rows, int K, int box_rows = BM) {
     EncodeTiledFn enc = get_encode();
     if (!enc) return false;
     cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
     cuuint64_t strides[1] = {(cuuint64_t)K * 2};
-    cuuint32_t box[2] = {BK, BM};
+    cuuint32_t box[2] = {BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
     return enc(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int EPI>
+template <int EPI, int BN>
 cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const GemmTcParams& p, cudaStream_t st) {
-    constexpr int stage = kTileBytes * (EPI == GEMM_EPI_SWIGLU ? 3 : 2);
+    constexpr int stage = kTileBytes + BN * BK * 2 * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
     const size_t smem = (size_t)kStages * stage + 1024;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
     dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
-    gemm_tc_kernel<EPI><<<grid, kGemmThreads, smem, st>>>(a, b, b2, p);
+    gemm_tc_kernel<EPI, BN><<<grid, kGemmThreads, smem, st>>>(a, b, b2, p);
     count_launch();
     return cudaGetLastError();
+}
+
+// 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give)
+bool wide_tiles(const GemmTcParams& p) {
+    static const bool off = [] { const char* e = getenv("DLLM_GEMM_BN256"); return e && e[0] == '0'; }();
+    if (off || p.epi == GEMM_EPI_SWIGLU || p.N % 256) return false;
+    return (long)((p.M + BM - 1) / BM) * (p.N / 256) >= 148;
 }
 
 }  // namespace
@@ -354,17 +369,18 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
     if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || p.ldc % 2) return cudaErrorInvalidValue;
     CUtensorMap a, b, b2;
-    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K)) return cudaErrorNotSupported;
+    const bool wide = wide_tiles(p);
+    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, wide ? 256 : 128)) return cudaErrorNotSupported;
     if (p.epi == GEMM_EPI_SWIGLU) {
         if (!make_map(&b2, p.w2, p.N, p.K)) return cudaErrorNotSupported;
     } else {
         b2 = b;
     }
     switch (p.epi) {
-        case GEMM_EPI_BIAS: return launch_epi<GEMM_EPI_BIAS>(a, b, b2, p, st);
-        case GEMM_EPI_RESIDUAL: return launch_epi<GEMM_EPI_RESIDUAL>(a, b, b2, p, st);
-        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU>(a, b, b2, p, st);
-        case GEMM_EPI_GELU: return launch_epi<GEMM_EPI_GELU>(a, b, b2, p, st);
+        case GEMM_EPI_BIAS: return wide ? launch_epi<GEMM_EPI_BIAS, 256>(a, b, b2, p, st) : launch_epi<GEMM_EPI_BIAS, 128>(a, b, b2, p, st);
+        case GEMM_EPI_RESIDUAL: return wide ? launch_epi<GEMM_EPI_RESIDUAL, 256>(a, b, b2, p, st) : launch_epi<GEMM_EPI_RESIDUAL, 128>(a, b, b2, p, st);
+        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU, 128>(a, b, b2, p, st);
+        case GEMM_EPI_GELU: return wide ? launch_epi<GEMM_EPI_GELU, 256>(a, b, b2, p, st) : launch_epi<GEMM_EPI_GELU, 128>(a, b, b2, p, st);
     }
     return cudaErrorInvalidValue;
 }
