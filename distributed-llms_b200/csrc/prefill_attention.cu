@@ -22,7 +22,9 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
@@ -46,8 +48,7 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
     constexpr int LD = HD + 8;  // padded rows: ldmatrix reads 8 rows x 16 bytes without bank conflicts
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     bf16* sQ = reinterpret_cast<bf16*>(smem_dyn);
-    bf16* sK = sQ + kQT * LD;
-    bf16* sV = sK + kKT * LD;
+    bf16* sKV = sQ + kQT * LD;  // two buffers of {K tile, V tile}: tile i+1 is gathered while tile i is multiplied
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     const int b = blockIdx.z, h = blockIdx.y, qt = blockIdx.x;
     const int H = p.n_heads, KV = p.n_kv_heads, kvh = h / (H / KV);
@@ -77,24 +78,40 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
     const int q_lo = pos0 + warp * 16 + g, q_hi = q_lo + 8;   // absolute positions of the two rows
     const int last_key = pos0 + rows_here - 1;                // keys beyond the tile's last row are never needed
 
-    for (int kt0 = 0; kt0 <= last_key; kt0 += kKT) {
-        __syncthreads();  // previous tile fully consumed (also orders the Q stores before the first reads)
+    auto gather_tile = [&](int kt0, int buf) {  // one commit group per tile
+        bf16* dK = sKV + (size_t)buf * 2 * kKT * LD;
+        bf16* dV = dK + kKT * LD;
         for (int i = threadIdx.x; i < kKT * (HD / 8); i += kThreads) {
             const int r = i / (HD / 8), c = i % (HD / 8);
             const int tok = kt0 + r;
             if (tok <= last_key) {
                 const int page = bt[tok >> p.kv.page_shift];
                 const size_t base = ((((size_t)page * KV + kvh) << p.kv.page_shift) + (tok & pmask)) * HD + c * 8;
-                cp_async16(sK + r * LD + c * 8, kpool + base);
-                cp_async16(sV + r * LD + c * 8, vpool + base);
+                cp_async16(dK + r * LD + c * 8, kpool + base);
+                cp_async16(dV + r * LD + c * 8, vpool + base);
             } else {
-                *reinterpret_cast<uint4*>(sK + r * LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
-                *reinterpret_cast<uint4*>(sV + r * LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(dK + r * LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
+                *reinterpret_cast<uint4*>(dV + r * LD + c * 8) = make_uint4(0u, 0u, 0u, 0u);
             }
         }
-        cp_async_wait_all();
-        __syncthreads();
-        if (kt0 > pos0 + warp * 16 + 15) continue;  // every key of this tile lies after this warp's rows (warp-uniform)
+        cp_async_commit();
+    };
+    gather_tile(0, 0);
+    int it = 0;
+    for (int kt0 = 0; kt0 <= last_key; kt0 += kKT, ++it) {
+        const bf16* sK = sKV + (size_t)(it & 1) * 2 * kKT * LD;
+        const bf16* sV = sK + kKT * LD;
+        if (kt0 + kKT <= last_key) {
+            gather_tile(kt0 + kKT, (it + 1) & 1);  // that buffer was released by the barrier that ended tile it - 1
+            cp_async_wait_group<1>();              // tile it has landed, tile it + 1 may still be in flight
+        } else {
+            cp_async_wait_group<0>();
+        }
+        __syncthreads();  // tile it visible to every warp (also orders the Q stores before the first reads)
+        if (kt0 > pos0 + warp * 16 + 15) {  // every key of this tile lies after this warp's rows (warp-uniform)
+            __syncthreads();
+            continue;
+        }
 
         // ---- S = Q K^T : 16 rows x 64 keys per warp ----
         float s[kKT / 8][4];
@@ -182,6 +199,7 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
                 mma_bf16(o[nt + 1], al, bfr[2], bfr[3]);
             }
         }
+        __syncthreads();  // tile it fully consumed: its buffer is the target of the gather two tiles on
     }
 
     // ---- normalise and store ----
@@ -203,11 +221,11 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
 cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {
     if (p.n_seqs <= 0 || p.rows_per_seq <= 0 || p.n_heads % p.n_kv_heads) return cudaErrorInvalidValue;
     dim3 grid((p.rows_per_seq + kQT - 1) / kQT, p.n_heads, p.n_seqs);
-    const size_t smem = (size_t)(kQT + 2 * kKT) * (p.head_dim + 8) * 2;
+    const size_t smem = (size_t)(kQT + 4 * kKT) * (p.head_dim + 8) * 2;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)((kQT + 2 * kKT) * (128 + 8) * 2));
+                                             (int)((kQT + 4 * kKT) * (128 + 8) * 2));
         if (e != cudaSuccess) return e;
         attr_done = true;
     }

@@ -747,10 +747,10 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
             if (n_logit_rows <= 0 || n_logit_rows > n_rows) return fail("dllm_shard_forward: n_logit_rows out of range");
             nl = n_logit_rows;
             CUDA_TRY(cudaMemcpyAsync(s->logit_rows, logit_rows, (size_t)nl * 4, cudaMemcpyDefault, st));
-        } else {
+        } else if (n_logit_rows >= 0) {
             nl = n_rows;
             CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
-        }
+        }  // n_logit_rows < 0 with no row list: no logits this call (an inner chunk of a chunked prefill)
     }
     if (mk_eligible(s, n_rows, nl, logit_rows == nullptr)) {
         if (run_megakernel(s, n_rows, 1, false, st)) return 1;

@@ -266,7 +266,7 @@ class ShardExecutor:
                     lr = (torch.arange(B, dtype=torch.int32) * n + (n - 1)).contiguous()
                 cabi.check(L.dllm_shard_forward(
                     self._handle, xc.data_ptr(), pc.data_ptr(), sc.data_ptr(), B * n, _ptr(hc),
-                    _ptr(lr), B if lr is not None else 0,
+                    _ptr(lr), B if lr is not None else (0 if emit or not self.has_head else -1),
                     _ptr(logits) if emit else None, _ptr(next_tok) if emit else None, st))
                 if hc is not None and hc is not hidden_out:
                     hidden_out[:, t0:t1] = hc

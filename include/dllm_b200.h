@@ -141,7 +141,8 @@ DLLM_API int dllm_shard_kv_free_pages(const dllm_shard* shard);
  *   input        has_embed: int32 token ids [n_rows]; else hidden states [n_rows, d] in `dtype`
  *   positions    int32 [n_rows]          seq_ids   int32 [n_rows]
  *   hidden_out   [n_rows, d] in `dtype`: the hand-off tile for the next stage (NULL if has_head)
- *   logit_rows   int32 [n_logit_rows]: rows whose logits are wanted (has_head; NULL = all rows)
+ *   logit_rows   int32 [n_logit_rows]: rows whose logits are wanted (has_head; NULL = all rows, or -- with
+ *                n_logit_rows < 0 -- none: the inner chunks of a chunked prefill skip the head)
  *   logits_out   fp32 [n_logit_rows, V] or NULL;  next_token_out int32 [n_logit_rows] or NULL
  *                (greedy: lowest index of the maximum, like torch.argmax)
  * All seven data pointers may be host or device memory. */
