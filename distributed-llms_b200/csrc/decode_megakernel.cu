@@ -67,6 +67,8 @@ __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_but_one() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 __device__ __forceinline__ uint4 lds_u4(uint32_t addr) {
     uint4 r;
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr));
@@ -545,16 +547,17 @@ struct AttnSmem {
 
 // cp.async the K and V rows of tokens [a, b) of (seq, kvh) into tile rows (token - tile0)
 __device__ __forceinline__ void attn_load_rows(const MkParams& p, const MkLayer& L, const AttnSmem& sm, const int* bt,
-                                               int kvh, int tile0, int a, int b) {
+                                               int kvh, int tile0, int a, int b, bool load_k, bool load_v) {
     const int hd = p.head_dim, vecs = hd >> 3, ld = hd + 8;
     const int mask = (1 << p.page_shift) - 1;
     for (int i = threadIdx.x; i < (b - a) * vecs; i += kThreads) {
         const int t = a + i / vecs, v = i % vecs;
         const int page = bt[t >> p.page_shift];
         const size_t base = ((((size_t)page * p.n_kv_heads + kvh) << p.page_shift) + (t & mask)) * hd + v * 8;
-        cp_async16(sm.k + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.kpool) + base);
-        cp_async16(sm.v + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.vpool) + base);
+        if (load_k) cp_async16(sm.k + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.kpool) + base);
+        if (load_v) cp_async16(sm.v + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.vpool) + base);
     }
+    cp_async_commit();  // one group per call: the K rows and the V rows of a tile are waited for separately
 }
 
 struct AttnUnit {
@@ -601,9 +604,15 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
         float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};   // (m, l) of head hw; hd/32 output columns per lane
         for (int tile0 = a.t0; tile0 < a.t1; tile0 += kTT) {
             const int tend = min(a.t1, tile0 + kTT), nt = tend - tile0;
-            int from = tile0;
-            if (first && prefetched && tile0 == a.t0) from = max(tile0, min(tend, attn_safe_end(sc, a)));
-            attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend);
+            const bool has_next = tile0 + kTT < a.t1;
+            if (tile0 == a.t0) {
+                // first tile of the unit: its K rows, then its V rows (later tiles were requested while the tile
+                // before them was being multiplied)
+                int from = tile0;
+                if (first && prefetched) from = max(tile0, min(tend, attn_safe_end(sc, a)));
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, true, false);
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, false, true);
+            }
             if (tile0 == a.t0) {
                 // q of the Gq heads of this KV head -> shared, fp32: one 16-byte L2 load per thread, in flight together
                 // with the K/V copies above
@@ -615,9 +624,9 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 }
                 if (tr) tr[4] = clock64();  // q staged
             }
-            cp_async_wait_all();
+            cp_async_wait_but_one();  // everything but the newest group (this tile's V rows): the K rows are in
             __syncthreads();
-            if (tr) tr[5] = clock64();  // K/V tile in shared memory
+            if (tr) tr[5] = clock64();  // K tile in shared memory
             // scores: one (token, head) pair per thread-iteration; lanes walk tokens (padded rows: no conflicts)
             for (int i = threadIdx.x; i < kTT * Gq; i += kThreads) {
                 const int t = i & (kTT - 1), g = i / kTT;
@@ -638,6 +647,13 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
             }
             __syncthreads();
             if (tr) tr[6] = clock64();  // scores done
+            if (has_next) {  // the K buffer is free: request the next tile's K rows, then wait for this tile's V rows
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), true, false);
+                cp_async_wait_but_one();
+            } else {
+                cp_async_wait_all();
+            }
+            __syncthreads();
             if (pv_warp) {  // online softmax (whole tile) + P.V over this warp's token slice
                 const float* sg = sm.s + hw * kTT;
                 const float s0 = lane < nt ? sg[lane] : -FLT_MAX;
@@ -684,7 +700,9 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 #pragma unroll
                 for (int e = 0; e < 4; ++e) o[e] += oa[e] + ob[e];
             }
-            __syncthreads();  // tile buffers are reused
+            __syncthreads();  // the V buffer is free
+            if (has_next)
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), false, true);
             if (tr) tr[7] = clock64();  // softmax + P.V done
         }
         // sum the token slices of a head in fixed order (through the score buffer, free now), slice 0 stores
@@ -1114,7 +1132,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     const AttnUnit a = attn_unit(p, sc, blockIdx.x);
                     const int tend = min(a.t1, a.t0 + kTT);
                     const int upto = max(a.t0, min(tend, attn_safe_end(sc, a)));
-                    if (upto > a.t0) attn_load_rows(p, *L, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto);
+                    if (upto > a.t0) {
+                        attn_load_rows(p, *L, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, true, false);
+                        attn_load_rows(p, *L, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, false, true);
+                    }
                 }
             }
 

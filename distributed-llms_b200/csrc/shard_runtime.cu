@@ -515,7 +515,8 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     p.hidden = c.hidden; p.n_heads = c.n_heads; p.n_kv_heads = c.n_kv_heads; p.head_dim = c.head_dim;
     p.vocab = c.vocab; p.k_max = variant == 2 ? s->mk_k_max_xg : s->mk_k_max;
     p.norm = c.arch == DLLM_ARCH_GPT2 ? NORM_LAYER : NORM_RMS; p.rope = c.arch != DLLM_ARCH_GPT2;
-    long S = (s->num_sms + (long)n_rows * c.n_kv_heads - 1) / ((long)n_rows * c.n_kv_heads);
+    long S = s->num_sms / ((long)n_rows * c.n_kv_heads);  // rows x KV heads x S units: at most one per CTA
+    if (S < 1) S = 1;
     const long s_cap = mk_max_splits(n_rows, c.n_heads, c.head_dim);
     if (S > s_cap) S = s_cap;
     while (S > 1 && (long)n_rows * c.n_heads * S > s->max_partials) --S;
