@@ -457,3 +457,30 @@ def test_long_context_decode_matches_oracle(batch, prompt_len):
         if not same_prefix[b].all():
             t = int((~same_prefix[b]).float().argmax())
             assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
+
+
+@pytest.mark.parametrize("model", ["llama3-8b", "qwen2.5-14b", "llama3-70b"])
+def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
+    """Two layers at the real widths of the BASELINE configs (hidden 4096 / 5120 / 8192, GQA 4 / 5 / 8, head_dim 128,
+    full vocabulary): no CPU oracle in seconds at these sizes, so the persistent kernel (several rounds of panels per
+    CTA, the streamed-rows variant at batch 4-8) is checked against the independent per-op CUDA path, which the small
+    cases pin to the oracle.  Prefill (tcgen05 GEMMs) feeds both."""
+    hf = dict(random_init.NAMED_CONFIGS[model])
+    hf["num_hidden_layers"] = 2
+    params = random_init.random_stage_parameters(hf, range(2), True, True, 77, torch.bfloat16, device="cuda")
+    limits = dict(max_rows=256, max_seqs=8, max_context=128, page_size=64)
+    shards = {}
+    for mk in ("1", "0"):
+        monkeypatch.setenv("DLLM_MEGAKERNEL", mk)
+        shards[mk] = ModelShard(0, dict(params), config=hf, **limits)
+        shards[mk].to_device()
+    for batch in (1, 4, 8):
+        prompts = make_prompts(hf["vocab_size"], batch, 24, seed=batch)
+        outs = {}
+        for mk, sh in shards.items():
+            sh.reset()
+            first = sh.compute({"input_ids": prompts})
+            step = sh.compute({"input_ids": first["next_token"][:, None]})
+            outs[mk] = (first["logits"].cpu(), step["logits"].cpu())
+        assert torch.equal(outs["1"][0], outs["0"][0])               # same prefill kernels on both sides
+        assert bf16_logits_close(outs["1"][1], outs["0"][1]), batch  # decode step: persistent kernel vs per-op kernels
