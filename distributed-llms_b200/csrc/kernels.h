@@ -76,7 +76,8 @@ struct EmbedParams {
 };
 
 // Prefill GEMM on tcgen05 (prefill_gemm.cu): C[M, N] = A[M, K] . W[N, K]^T, bf16 in, fp32 accumulate in TMEM.
-enum GemmEpi { GEMM_EPI_BIAS = 0, GEMM_EPI_RESIDUAL = 1, GEMM_EPI_SWIGLU = 2, GEMM_EPI_GELU = 3 };
+enum GemmEpi { GEMM_EPI_BIAS = 0, GEMM_EPI_RESIDUAL = 1, GEMM_EPI_SWIGLU = 2, GEMM_EPI_GELU = 3,
+               GEMM_EPI_LOGITS = 4 };  // LOGITS: c is fp32 [M, ldc], values rounded to bf16 (M <= 64 only)
 struct GemmTcParams {
     const void* a;      // [M, K] activations, row-major (lda = K)
     const void* w;      // [N, K] weights (nn.Linear layout)
@@ -97,7 +98,9 @@ struct RopeAppendParams {
 };
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st);
 cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
-                             cudaStream_t st);
+                             cudaStream_t st, const int32_t* row_map = nullptr);  // y[r] = norm(x[row_map ? row_map[r] : r])
+// next_token[r] = lowest index of the maximum of logits[r, 0..n) (fp32 rows of stride n)
+cudaError_t launch_argmax_rows(const float* logits, int rows, int n, int32_t* next_token, cudaStream_t st);
 cudaError_t launch_rope_append(const RopeAppendParams& p, cudaStream_t st);
 
 // Causal prefill attention over the paged cache (prefill_attention.cu): rows are `n_seqs` runs of `rows_per_seq`

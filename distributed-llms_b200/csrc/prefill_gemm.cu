@@ -13,6 +13,7 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
+#include <float.h>
 #include <stdint.h>
 #include <stdlib.h>
 
@@ -219,6 +220,170 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     }
 }
 
+// ---- decode batches of 5..64 rows: swap-AB, split-K across a cluster ----------------------------------------------
+// With a handful of rows the contraction is weight-streaming work again: what matters is that every SM keeps many
+// 16 KB weight tiles in flight.  The weights take the M side of the UMMA (128 weight rows per CTA), the batch rows
+// the N side (16 / 32 / 64), so a stage is one weight tile (two for gate/up) plus a 2-8 KB row tile and the ring is
+// 5-10 stages deep.  Narrow matrices are split along K over the CTAs of a cluster (<= 8): every CTA reads its
+// accumulator from tensor memory and stores it into the leader's shared memory (DSMEM), the leader adds the
+// pieces in rank order -- the same sum on every run -- and applies the epilogue.
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void st_dsmem_f32(uint32_t local_addr, uint32_t rank, float v) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
+}
+
+template <int EPI, int MP>
+struct SwapAbCfg {
+    static constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
+    static constexpr int kCols = (kDual ? 2 : 1) * MP;                 // accumulator columns (fp32)
+    static constexpr int kXBytes = MP * BK * 2;
+    static constexpr int kStageBytes = kTileBytes * (kDual ? 2 : 1) + kXBytes;
+    static constexpr int kStagesS = (200 * 1024 / kStageBytes) > 10 ? 10 : (200 * 1024 / kStageBytes);
+    static constexpr uint32_t kTmemCols = kCols <= 32 ? 32 : (kCols <= 64 ? 64 : 128);
+    static constexpr int kMaxSplit = 256 / kCols > 8 ? 8 : 256 / kCols;  // partial buffer (split x cols x 512 B) fits the ring
+};
+
+template <int EPI, int MP>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_w2,
+                   const __grid_constant__ CUtensorMap tm_x, const GemmTcParams p, const int kb_per_cta) {
+    using Cfg = SwapAbCfg<EPI, MP>;
+    constexpr bool kDual = Cfg::kDual;
+    constexpr int kCols = Cfg::kCols, kStageBytes = Cfg::kStageBytes, kSt = Cfg::kStagesS;
+    constexpr uint32_t kIdesc = make_idesc(MP);  // M = 128 weight rows, N = MP batch rows
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    __shared__ __align__(8) uint64_t bars[2 * kSt + 1];
+    __shared__ uint32_t s_tmem;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n0 = blockIdx.x * BM;
+    const int ksplit = gridDim.y, krank = (int)cluster_rank();   // the cluster spans the whole y dimension
+    const int total_kb = (p.K + BK - 1) / BK;
+    const int kb0 = krank * kb_per_cta;
+    const int num_kb = max(0, min(kb_per_cta, total_kb - kb0));
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kSt), tfull = smem_u32(bars + 2 * kSt);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kSt; ++i) {
+            mbar_init(full0 + i * 8, 1);
+            mbar_init(empty0 + i * 8, 1);
+        }
+        mbar_init(tfull, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(Cfg::kTmemCols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = s_tmem;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % kSt;
+                mbar_wait(empty0 + s * 8, ((kb / kSt) & 1) ^ 1);
+                const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
+                mbar_expect_tx(full0 + s * 8, kStageBytes);
+                tma_load_2d(dst, &tm_w, (kb0 + kb) * BK, n0, full0 + s * 8);
+                if (kDual) tma_load_2d(dst + kTileBytes, &tm_w2, (kb0 + kb) * BK, n0, full0 + s * 8);
+                tma_load_2d(dst + kTileBytes * (kDual ? 2 : 1), &tm_x, (kb0 + kb) * BK, 0, full0 + s * 8);
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && num_kb > 0) {
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const int s = kb % kSt;
+                mbar_wait(full0 + s * 8, (kb / kSt) & 1);
+                tc_fence_after();
+                const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
+                const uint64_t dw = make_sw128_desc(base), dw2 = make_sw128_desc(base + kTileBytes);
+                const uint64_t dx = make_sw128_desc(base + kTileBytes * (kDual ? 2 : 1));
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                    const uint32_t acc = (kb | k) ? 1u : 0u;
+                    tc_mma(tmem, dw + 2 * k, dx + 2 * k, kIdesc, acc);
+                    if (kDual) tc_mma(tmem + MP, dw2 + 2 * k, dx + 2 * k, kIdesc, acc);
+                }
+                tc_commit(empty0 + s * 8);
+            }
+            tc_commit(tfull);
+        }
+    } else if (num_kb > 0) {
+        mbar_wait(tfull, 0);  // every MMA of this CTA has read its operands: the ring is free
+        tc_fence_after();
+    }
+    // 1st cluster barrier: every CTA's ring is idle, so the leader's can take the partial sums
+    cluster_sync_all();
+    float* part = reinterpret_cast<float*>(smem);  // leader: [krank][column][128 weight rows]
+    if (warp >= 2) {
+        const int quarter = warp & 3, nl = quarter * 32 + lane;
+        const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < kCols; c0 += 32) {
+            uint32_t acc[32];
+            if (num_kb > 0) {
+                tc_ld32(tbase + c0, acc);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) acc[j] = 0u;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (c0 + j < kCols)
+                    st_dsmem_f32(smem_u32(part + ((size_t)krank * kCols + c0 + j) * BM + nl), 0u, __uint_as_float(acc[j]));
+        }
+        tc_fence_before();
+    }
+    // 2nd cluster barrier: all pieces are in the leader's shared memory
+    cluster_sync_all();
+    if (krank == 0 && warp >= 2) {
+        const int quarter = warp & 3, nl = quarter * 32 + lane, n = n0 + nl;
+        bf16* out = static_cast<bf16*>(p.c);
+        const bf16* bias = static_cast<const bf16*>(p.bias);
+        if (n < p.N) {
+            const float bn = (bias && EPI != GEMM_EPI_SWIGLU) ? __bfloat162float(bias[n]) : 0.f;
+            for (int j = 0; j < MP && j < p.M; ++j) {
+                float v = 0.f, u = 0.f;
+                for (int k = 0; k < ksplit; ++k) {
+                    v += part[((size_t)k * kCols + j) * BM + nl];
+                    if (kDual) u += part[((size_t)k * kCols + MP + j) * BM + nl];
+                }
+                if (EPI == GEMM_EPI_LOGITS) {  // fp32 row of logits, in the model dtype's precision
+                    static_cast<float*>(p.c)[(size_t)j * p.ldc + n] = bf16_round(v);
+                    continue;
+                }
+                bf16* y = out + (size_t)j * p.ldc + n;
+                if (EPI == GEMM_EPI_SWIGLU) {
+                    v = bf16_round(silu_f(bf16_round(v))) * bf16_round(u);
+                } else {
+                    v = bf16_round(v + bn);
+                    if (EPI == GEMM_EPI_RESIDUAL) v += __bfloat162float(*y);
+                    else if (EPI == GEMM_EPI_GELU) v = gelu_new_f(v);
+                }
+                *y = __float2bfloat16_rn(v);
+            }
+        }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(Cfg::kTmemCols));
+    }
+}
+
 // ---- small row-wise kernels around the GEMMs -------------------------------------------------------------------
 
 // xn[r] = norm(x[r]) for T rows (RMSNorm / LayerNorm with the rounding of the decode prologue); one warp per row
@@ -273,6 +438,108 @@ __global__ void __launch_bounds__(256) norm_rows_kernel(const bf16* __restrict__
         o.z = *reinterpret_cast<uint32_t*>(&a2);
         o.w = *reinterpret_cast<uint32_t*>(&a3);
         *reinterpret_cast<uint4*>(yr + k) = o;
+    }
+}
+
+// The same for a handful of rows (decode batches): one CTA per row, the row stays in registers (K <= 16384), and the
+// rows may be gathered (row_map) -- the final norm in front of the lm_head GEMM reads the rows whose logits are wanted.
+__global__ void __launch_bounds__(256) norm_rows_cta_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
+                                                            const bf16* __restrict__ b, bf16* __restrict__ y,
+                                                            const int32_t* __restrict__ row_map, int K, int norm, float eps) {
+    __shared__ float red[32];
+    const int row = blockIdx.x, src = row_map ? row_map[row] : row;
+    const bf16* xr = x + (size_t)src * K;
+    bf16* yr = y + (size_t)row * K;
+    constexpr int kMaxV = 8;  // 8 vectors of 8 per thread: K <= 16384
+    float f[kMaxV][8];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < kMaxV; ++i) {
+        const int k = (i * 256 + threadIdx.x) * 8;
+        if (k < K) {
+            unpack<bf16>(ld_u4(xr + k), f[i]);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                s1 += f[i][j];
+                s2 = fmaf(f[i][j], f[i][j], s2);
+            }
+        }
+    }
+    float mean = 0.f, rstd;
+    if (norm == NORM_RMS) {
+        rstd = 1.0f / sqrtf(block_sum(s2, red) / (float)K + eps);
+    } else {
+        mean = block_sum(s1, red) / (float)K;
+        float sq = 0.f;
+#pragma unroll
+        for (int i = 0; i < kMaxV; ++i)
+            if ((i * 256 + (int)threadIdx.x) * 8 < K) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sq = fmaf(f[i][j] - mean, f[i][j] - mean, sq);
+            }
+        rstd = 1.0f / sqrtf(block_sum(sq, red) / (float)K + eps);
+    }
+#pragma unroll
+    for (int i = 0; i < kMaxV; ++i) {
+        const int k = (i * 256 + threadIdx.x) * 8;
+        if (k < K) {
+            float wf[8], bf[8], o8[8];
+            unpack<bf16>(ld_u4(w + k), wf);
+            if (norm == NORM_RMS) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o8[j] = wf[j] * bf16_round(f[i][j] * rstd);
+            } else {
+                unpack<bf16>(ld_u4(b + k), bf);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) o8[j] = fmaf((f[i][j] - mean) * rstd, wf[j], bf[j]);
+            }
+            uint4 o;
+            __nv_bfloat162 a0 = __floats2bfloat162_rn(o8[0], o8[1]), a1 = __floats2bfloat162_rn(o8[2], o8[3]);
+            __nv_bfloat162 a2 = __floats2bfloat162_rn(o8[4], o8[5]), a3 = __floats2bfloat162_rn(o8[6], o8[7]);
+            o.x = *reinterpret_cast<uint32_t*>(&a0);
+            o.y = *reinterpret_cast<uint32_t*>(&a1);
+            o.z = *reinterpret_cast<uint32_t*>(&a2);
+            o.w = *reinterpret_cast<uint32_t*>(&a3);
+            *reinterpret_cast<uint4*>(yr + k) = o;
+        }
+    }
+}
+
+// next_token[r] = lowest index of the maximum of a row of fp32 logits (torch.argmax semantics); one CTA per row
+__global__ void __launch_bounds__(256) argmax_rows_kernel(const float* __restrict__ logits, int n, int32_t* __restrict__ next_token) {
+    __shared__ float s_val[8];
+    __shared__ int s_idx[8];
+    const float* row = logits + (size_t)blockIdx.x * n;
+    float best = -FLT_MAX;
+    int bi = 0x7fffffff;
+    for (int i = threadIdx.x; i < n; i += 256) {
+        const float v = row[i];
+        if (v > best || (v == best && i < bi)) {
+            best = v;
+            bi = i;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+        if (ov > best || (ov == best && oi < bi)) {
+            best = ov;
+            bi = oi;
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+        s_val[threadIdx.x >> 5] = best;
+        s_idx[threadIdx.x >> 5] = bi;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int wv = 1; wv < 8; ++wv)
+            if (s_val[wv] > best || (s_val[wv] == best && s_idx[wv] < bi)) {
+                best = s_val[wv];
+                bi = s_idx[wv];
+            }
+        next_token[blockIdx.x] = bi;
     }
 }
 
@@ -364,10 +631,73 @@ bool wide_tiles(const GemmTcParams& p) {
     return (long)((p.M + BM - 1) / BM) * (p.N / 256) >= 148;
 }
 
+template <int EPI, int MP>
+cudaError_t launch_swapab(const GemmTcParams& p, cudaStream_t st) {
+    using Cfg = SwapAbCfg<EPI, MP>;
+    CUtensorMap w, w2, x;
+    if (!make_map(&w, p.w, p.N, p.K, BM) || !make_map(&x, p.a, p.M, p.K, MP)) return cudaErrorNotSupported;
+    if (Cfg::kDual) {
+        if (!make_map(&w2, p.w2, p.N, p.K, BM)) return cudaErrorNotSupported;
+    } else {
+        w2 = w;
+    }
+    const int tiles = (p.N + BM - 1) / BM, total_kb = (p.K + BK - 1) / BK;
+    int ksplit = 1;
+    // one wave of CTAs: every CTA pays a fixed set-up (tensor memory, barriers, two cluster barriers, the DSMEM pass),
+    // so 128 CTAs streaming twice as much each beat 256 CTAs in two waves
+    while (ksplit < Cfg::kMaxSplit && tiles * ksplit * 2 <= 160 && ksplit * 2 <= total_kb) ksplit *= 2;
+    const int kb_per_cta = (total_kb + ksplit - 1) / ksplit;
+    const size_t smem = (size_t)Cfg::kStagesS * Cfg::kStageBytes + 1024;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(gemm_swapab_kernel<EPI, MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(tiles, ksplit);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = ksplit;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_swapab_kernel<EPI, MP>, w, w2, x, p, kb_per_cta);
+    count_launch();
+    return e;
+}
+
+template <int EPI>
+cudaError_t launch_swapab_rows(const GemmTcParams& p, cudaStream_t st) {
+    if (p.M <= 16) return launch_swapab<EPI, 16>(p, st);
+    if (p.M <= 32) return launch_swapab<EPI, 32>(p, st);
+    return launch_swapab<EPI, 64>(p, st);
+}
+
+bool small_m(const GemmTcParams& p) {
+    static const bool off = [] { const char* e = getenv("DLLM_GEMM_SWAPAB"); return e && e[0] == '0'; }();
+    return !off && p.M <= 64;
+}
+
 }  // namespace
 
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
-    if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || p.ldc % 2) return cudaErrorInvalidValue;
+    if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || (p.ldc % 2 && p.epi != GEMM_EPI_LOGITS)) return cudaErrorInvalidValue;
+    if (small_m(p)) {
+        switch (p.epi) {
+            case GEMM_EPI_BIAS: return launch_swapab_rows<GEMM_EPI_BIAS>(p, st);
+            case GEMM_EPI_RESIDUAL: return launch_swapab_rows<GEMM_EPI_RESIDUAL>(p, st);
+            case GEMM_EPI_SWIGLU: return launch_swapab_rows<GEMM_EPI_SWIGLU>(p, st);
+            case GEMM_EPI_GELU: return launch_swapab_rows<GEMM_EPI_GELU>(p, st);
+            case GEMM_EPI_LOGITS: return launch_swapab_rows<GEMM_EPI_LOGITS>(p, st);
+        }
+        return cudaErrorInvalidValue;
+    }
+    if (p.epi == GEMM_EPI_LOGITS) return cudaErrorInvalidValue;
     CUtensorMap a, b, b2;
     const bool wide = wide_tiles(p);
     if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, wide ? 256 : 128)) return cudaErrorNotSupported;
@@ -386,10 +716,23 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
 }
 
 cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
-                             cudaStream_t st) {
+                             cudaStream_t st, const int32_t* row_map) {
     if (rows <= 0 || K % 8) return cudaErrorInvalidValue;
-    norm_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(w),
-                                                     static_cast<const bf16*>(b), static_cast<bf16*>(y), rows, K, norm, eps);
+    if ((rows <= 64 || row_map) && K <= 16384) {
+        norm_rows_cta_kernel<<<rows, 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(w),
+                                                   static_cast<const bf16*>(b), static_cast<bf16*>(y), row_map, K, norm, eps);
+    } else {
+        if (row_map) return cudaErrorInvalidValue;
+        norm_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(w),
+                                                         static_cast<const bf16*>(b), static_cast<bf16*>(y), rows, K, norm, eps);
+    }
+    count_launch();
+    return cudaGetLastError();
+}
+
+cudaError_t launch_argmax_rows(const float* logits, int rows, int n, int32_t* next_token, cudaStream_t st) {
+    if (rows <= 0 || n <= 0) return cudaErrorInvalidValue;
+    argmax_rows_kernel<<<rows, 256, 0, st>>>(logits, n, next_token);
     count_launch();
     return cudaGetLastError();
 }

@@ -665,7 +665,16 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
             CUDA_TRY(launch_gemm_tc(g, st));
         }
     }
-    if (c.has_head && n_logit_rows > 0) {
+    if (c.has_head && n_logit_rows > 4 && n_logit_rows <= 64 && c.hidden <= 16384) {
+        // lm_head for 5..64 rows: final norm of the wanted rows -> swap-AB GEMM (one pass over the head) -> argmax
+        CUDA_TRY(launch_norm_rows(s->h, s->io.final_norm_w, s->io.final_norm_b, s->xn, n_logit_rows, c.hidden, norm,
+                                  c.norm_eps, st, s->logit_rows));
+        GemmTcParams g{};
+        g.a = s->xn; g.w = s->io.lm_head; g.c = s->logits; g.M = n_logit_rows; g.N = c.vocab; g.K = c.hidden;
+        g.ldc = c.vocab; g.epi = GEMM_EPI_LOGITS;
+        CUDA_TRY(launch_gemm_tc(g, st));
+        CUDA_TRY(launch_argmax_rows(s->logits, n_logit_rows, c.vocab, s->next_tok, st));
+    } else if (c.has_head && n_logit_rows > 0) {
         GemvParams p{};
         p.x = s->h; p.row_map = s->logit_rows; p.n_rows = n_logit_rows; p.K = c.hidden;
         p.norm = norm; p.norm_w = s->io.final_norm_w; p.norm_b = s->io.final_norm_b; p.eps = c.norm_eps;
@@ -759,6 +768,7 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
         int run_seqs = 0, run_len = 0;
         static const bool fa_off = [] { const char* e = getenv("DLLM_PREFILL_ATTN"); return e && e[0] == '0'; }();
         if (fa_off || !detect_runs(positions, seq_ids, n_rows, &run_seqs, &run_len)) run_seqs = run_len = 0;
+        if (run_len < 8) run_seqs = run_len = 0;  // decode-like rows: the split-K kernel spreads one row's keys over CTAs
         if (run_step(s, n_rows, nl, false, st, 1, run_seqs, run_len)) return 1;
     } else if (run_step(s, n_rows, nl, false, st)) {
         return 1;

@@ -63,10 +63,12 @@ def test_gemv_matches_fp32_reference(dtype, rows, n_out, k):
 
 
 @pytest.mark.parametrize("m,n_out,k", [(128, 128, 64), (512, 256, 2048), (37, 130, 704), (200, 2560, 256), (1, 64, 128),
-                                       (300, 5632, 2048), (1300, 4096, 320), (2500, 2048, 192)])
+                                       (300, 5632, 2048), (1300, 4096, 320), (2500, 2048, 192), (16, 4096, 4096), (33, 1024, 2048),
+                                       (64, 640, 1088), (7, 50, 72)])
 def test_prefill_gemm_matches_fp32_reference(m, n_out, k):
     """The tcgen05 / TMA GEMM (bf16 in, fp32 accumulate in tensor memory) against a plain fp32 matmul, with ragged
-    tiles in every dimension, bias, and the in-place residual form.  The last two shapes take the 256-wide tiles."""
+    tiles in every dimension, bias, and the in-place residual form.  Shapes with more than 148 tiles of 128 x 256 take
+    the 256-wide tiles; m <= 64 takes the swap-AB kernel that splits K over a cluster (16 x 4096 x 4096: 8 ways)."""
     g = torch.Generator().manual_seed(m * 7 + n_out)
     x = torch.randn(m, k, generator=g).to(torch.bfloat16)
     w = (torch.randn(n_out, k, generator=g) * 0.05).to(torch.bfloat16)
