@@ -11,6 +11,7 @@
 // (HF rounds them to bf16 before P@V -- documented difference, below bf16 output resolution).
 #include <float.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/dllm_b200.h"
 #include "common.cuh"
@@ -157,6 +158,8 @@ static cudaError_t launch_t(const AttnParams& p, cudaStream_t s) {
 
 cudaError_t launch_attn_decode(int dtype, const AttnParams& p, cudaStream_t s) {
     if (p.n_rows <= 0 || p.n_splits <= 0 || p.n_heads % p.n_kv_heads != 0) return cudaErrorInvalidValue;
+    static const bool gqa_off = [] { const char* e = getenv("DLLM_ATTN_GQA"); return e && e[0] == '0'; }();
+    if (dtype == 0 && !gqa_off && attn_decode_gqa_supported(p)) return launch_attn_decode_gqa(p, s);
     return dtype == 0 ? launch_t<bf16>(p, s) : launch_t<float>(p, s);
 }
 

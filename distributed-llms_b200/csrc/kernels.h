@@ -120,6 +120,9 @@ cudaError_t gemv_init_device();  // once per device, outside stream capture
 cudaError_t launch_gemv(int dtype, const GemvParams& p, int num_sms, cudaStream_t s);
 int gemv_grid_size(int dtype, const GemvParams& p, int num_sms);  // grid launch_gemv will use (sizes arg scratch)
 cudaError_t launch_attn_decode(int dtype, const AttnParams& p, cudaStream_t s);
+// bf16, grouped heads on the tensor cores (attention_gqa.cu); launch_attn_decode dispatches to it
+bool attn_decode_gqa_supported(const AttnParams& p);
+cudaError_t launch_attn_decode_gqa(const AttnParams& p, cudaStream_t s);
 cudaError_t launch_embed(int dtype, const EmbedParams& p, cudaStream_t s);
 cudaError_t launch_decode_begin(int32_t* ids, int32_t* positions, int32_t* seq_ids, const int32_t* next_token,
                                 const int32_t* logit_rows, int32_t n, int32_t* step_ctr, cudaStream_t s);
