@@ -85,6 +85,11 @@ struct GemmTcParams {
     const void* bias;   // [N] or null
     void* c;            // [M, ldc] output; RESIDUAL adds into it in place
     int32_t M, N, K, ldc, epi;
+    // BIAS epilogue with M <= 64 only: up to two more weight matrices whose rows continue the logical [N, K] matrix
+    // (q | k | v in one launch); their outputs continue in the columns of c after N
+    const void* w_more[2];
+    const void* bias_more[2];
+    int32_t n_more[2];
 };
 struct RopeAppendParams {
     const void* qkv;    // [R, (H+2KV)*hd] projected rows (bias added)

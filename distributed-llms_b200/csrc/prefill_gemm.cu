@@ -255,7 +255,8 @@ struct SwapAbCfg {
 template <int EPI, int MP>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_constant__ CUtensorMap tm_w2,
-                   const __grid_constant__ CUtensorMap tm_x, const GemmTcParams p, const int kb_per_cta) {
+                   const __grid_constant__ CUtensorMap tm_w3, const __grid_constant__ CUtensorMap tm_x,
+                   const GemmTcParams p, const int kb_per_cta) {
     using Cfg = SwapAbCfg<EPI, MP>;
     constexpr bool kDual = Cfg::kDual;
     constexpr int kCols = Cfg::kCols, kStageBytes = Cfg::kStageBytes, kSt = Cfg::kStagesS;
@@ -266,7 +267,15 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
     __shared__ uint32_t s_tmem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n0 = blockIdx.x * BM;
+    // row segment of the logical weight matrix this tile belongs to (q | k | v): its tensor map, bias, columns
+    int seg = 0, tile = blockIdx.x, col0 = 0, seg_n = p.N;
+    if (!kDual) {
+        const int t0 = (p.N + BM - 1) / BM, t1 = (p.n_more[0] + BM - 1) / BM;
+        if (tile >= t0 + t1) { seg = 2; tile -= t0 + t1; col0 = p.N + p.n_more[0]; seg_n = p.n_more[1]; }
+        else if (tile >= t0) { seg = 1; tile -= t0; col0 = p.N; seg_n = p.n_more[0]; }
+    }
+    const CUtensorMap* map_w = seg == 0 ? &tm_w : (seg == 1 ? &tm_w2 : &tm_w3);
+    const int n0 = tile * BM;
     const int ksplit = gridDim.y, krank = (int)cluster_rank();   // the cluster spans the whole y dimension
     const int total_kb = (p.K + BK - 1) / BK;
     const int kb0 = krank * kb_per_cta;
@@ -297,7 +306,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
                 mbar_wait(empty0 + s * 8, ((kb / kSt) & 1) ^ 1);
                 const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
                 mbar_expect_tx(full0 + s * 8, kStageBytes);
-                tma_load_2d(dst, &tm_w, (kb0 + kb) * BK, n0, full0 + s * 8);
+                tma_load_2d(dst, map_w, (kb0 + kb) * BK, n0, full0 + s * 8);
                 if (kDual) tma_load_2d(dst + kTileBytes, &tm_w2, (kb0 + kb) * BK, n0, full0 + s * 8);
                 tma_load_2d(dst + kTileBytes * (kDual ? 2 : 1), &tm_x, (kb0 + kb) * BK, 0, full0 + s * 8);
             }
@@ -351,9 +360,9 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
     cluster_sync_all();
     if (krank == 0 && warp >= 2) {
         const int quarter = warp & 3, nl = quarter * 32 + lane, n = n0 + nl;
-        bf16* out = static_cast<bf16*>(p.c);
-        const bf16* bias = static_cast<const bf16*>(p.bias);
-        if (n < p.N) {
+        bf16* out = static_cast<bf16*>(p.c) + col0;
+        const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
+        if (n < seg_n) {
             const float bn = (bias && EPI != GEMM_EPI_SWIGLU) ? __bfloat162float(bias[n]) : 0.f;
             for (int j = 0; j < MP && j < p.M; ++j) {
                 float v = 0.f, u = 0.f;
@@ -362,7 +371,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
                     if (kDual) u += part[((size_t)k * kCols + MP + j) * BM + nl];
                 }
                 if (EPI == GEMM_EPI_LOGITS) {  // fp32 row of logits, in the model dtype's precision
-                    static_cast<float*>(p.c)[(size_t)j * p.ldc + n] = bf16_round(v);
+                    static_cast<float*>(p.c)[(size_t)j * p.ldc + col0 + n] = bf16_round(v);
                     continue;
                 }
                 bf16* y = out + (size_t)j * p.ldc + n;
@@ -634,14 +643,18 @@ bool wide_tiles(const GemmTcParams& p) {
 template <int EPI, int MP>
 cudaError_t launch_swapab(const GemmTcParams& p, cudaStream_t st) {
     using Cfg = SwapAbCfg<EPI, MP>;
-    CUtensorMap w, w2, x;
+    CUtensorMap w, w2, w3, x;
     if (!make_map(&w, p.w, p.N, p.K, BM) || !make_map(&x, p.a, p.M, p.K, MP)) return cudaErrorNotSupported;
+    w2 = w3 = w;
+    int tiles = (p.N + BM - 1) / BM;
     if (Cfg::kDual) {
         if (!make_map(&w2, p.w2, p.N, p.K, BM)) return cudaErrorNotSupported;
     } else {
-        w2 = w;
+        if (p.n_more[0] > 0 && !make_map(&w2, p.w_more[0], p.n_more[0], p.K, BM)) return cudaErrorNotSupported;
+        if (p.n_more[1] > 0 && !make_map(&w3, p.w_more[1], p.n_more[1], p.K, BM)) return cudaErrorNotSupported;
+        tiles += (p.n_more[0] + BM - 1) / BM + (p.n_more[1] + BM - 1) / BM;
     }
-    const int tiles = (p.N + BM - 1) / BM, total_kb = (p.K + BK - 1) / BK;
+    const int total_kb = (p.K + BK - 1) / BK;
     int ksplit = 1;
     // one wave of CTAs: every CTA pays a fixed set-up (tensor memory, barriers, two cluster barriers, the DSMEM pass),
     // so 128 CTAs streaming twice as much each beat 256 CTAs in two waves
@@ -666,7 +679,7 @@ cudaError_t launch_swapab(const GemmTcParams& p, cudaStream_t st) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_swapab_kernel<EPI, MP>, w, w2, x, p, kb_per_cta);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_swapab_kernel<EPI, MP>, w, w2, w3, x, p, kb_per_cta);
     count_launch();
     return e;
 }
@@ -687,6 +700,22 @@ bool small_m(const GemmTcParams& p) {
 
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
     if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || (p.ldc % 2 && p.epi != GEMM_EPI_LOGITS)) return cudaErrorInvalidValue;
+    const bool more = p.n_more[0] > 0 || p.n_more[1] > 0;
+    if (more && (p.epi != GEMM_EPI_BIAS || (p.n_more[1] > 0 && p.n_more[0] <= 0) || p.ldc < p.N + p.n_more[0] + p.n_more[1]))
+        return cudaErrorInvalidValue;
+    if (more && !small_m(p)) {  // the wide kernels take one matrix per launch
+        GemmTcParams q = p;
+        q.n_more[0] = q.n_more[1] = 0;
+        cudaError_t e = launch_gemm_tc(q, st);
+        int col = p.N;
+        for (int i = 0; i < 2 && e == cudaSuccess && p.n_more[i] > 0; ++i) {
+            q.w = p.w_more[i]; q.bias = p.bias_more[i]; q.N = p.n_more[i];
+            q.c = static_cast<bf16*>(p.c) + col;
+            col += p.n_more[i];
+            e = launch_gemm_tc(q, st);
+        }
+        return e;
+    }
     if (small_m(p)) {
         switch (p.epi) {
             case GEMM_EPI_BIAS: return launch_swapab_rows<GEMM_EPI_BIAS>(p, st);
