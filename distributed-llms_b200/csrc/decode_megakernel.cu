@@ -587,6 +587,7 @@ __device__ __forceinline__ int attn_safe_end(const StepCache& sc, const AttnUnit
 
 __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCache& sc, const int* sbt, const MkLayer& L, const AttnSmem& sm, bool prefetched,
                                                 long long* tr = nullptr) {
+    __shared__ int s_attn_last;
     const int hd = p.head_dim, H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int epl = hd >> 5;  // output columns per lane: 1, 2 or 4
@@ -731,6 +732,69 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
             if (lane == 0) {
                 p.part_ml[pidx * 2 + 0] = m;
                 p.part_ml[pidx * 2 + 1] = l;
+            }
+        }
+        // The last unit of this (row, KV head) to finish -- atomic ticket -- merges the splits and writes the bf16
+        // attention rows the o-projection stages: one CTA loads Gq x S partial rows once, instead of every CTA
+        // loading all of them in the next prologue.
+        const int n_act = attn_active_splits(p, sc, a.r);
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned* ctr = p.attn_counters + (size_t)a.r * KV + a.kvh;
+            const bool last = atomicAdd(ctr, 1u) == (unsigned)n_act - 1;
+            if (last) *ctr = 0u;  // every unit of the group has arrived: leave the ticket at zero for the next phase
+            s_attn_last = last;
+        }
+        __syncthreads();
+        if (s_attn_last) {
+            __threadfence();
+            float* wgt = sm.s;  // [Gq][S] merge weights (the score buffer is free)
+            const size_t pb = ((size_t)a.r * H + a.kvh * Gq) * S;
+            for (int i = threadIdx.x; i < Gq * S; i += kThreads) {
+                const int s2 = i % S;
+                float2 ml = make_float2(-FLT_MAX, 0.f);
+                if (s2 < n_act) ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml) + pb + i);
+                wgt[i] = ml.x;
+                sm.q[i] = ml.y;  // [Gq][S] split sums (q is free as well)
+            }
+            __syncthreads();
+            for (int hq = threadIdx.x; hq < Gq; hq += kThreads) {
+                float Mg = -FLT_MAX, Lg = 0.f;
+                for (int s2 = 0; s2 < n_act; ++s2) Mg = fmaxf(Mg, wgt[hq * S + s2]);
+                for (int s2 = 0; s2 < n_act; ++s2) {
+                    const float w = expf(wgt[hq * S + s2] - Mg);
+                    Lg = fmaf(sm.q[hq * S + s2], w, Lg);
+                    wgt[hq * S + s2] = w;
+                }
+                const float inv = 1.0f / Lg;
+                for (int s2 = 0; s2 < n_act; ++s2) wgt[hq * S + s2] *= inv;
+            }
+            __syncthreads();
+            for (int i = threadIdx.x; i < (Gq * hd) >> 2; i += kThreads) {
+                const int hq = (i * 4) / hd, c = i * 4 - hq * hd;
+                const float* po = p.part_o + (pb + (size_t)hq * S) * hd + c;
+                float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int s0 = 0; s0 < n_act; s0 += 8) {  // eight 16-byte loads in flight
+                    float4 v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        v[j] = s0 + j < n_act ? ldcg_f4(po + (size_t)(s0 + j) * hd) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        if (s0 + j < n_act) {
+                            const float w = wgt[hq * S + s0 + j];
+                            acc.x = fmaf(v[j].x, w, acc.x);
+                            acc.y = fmaf(v[j].y, w, acc.y);
+                            acc.z = fmaf(v[j].z, w, acc.z);
+                            acc.w = fmaf(v[j].w, w, acc.w);
+                        }
+                }
+                __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y), hi = __floats2bfloat162_rn(acc.z, acc.w);
+                uint2 out;
+                out.x = *reinterpret_cast<uint32_t*>(&lo);
+                out.y = *reinterpret_cast<uint32_t*>(&hi);
+                *reinterpret_cast<uint2*>(static_cast<bf16*>(p.attn_out) + ((size_t)a.r * H + a.kvh * Gq + hq) * hd + c) = out;
             }
         }
         __syncthreads();  // shared buffers are reused by the next unit
@@ -923,7 +987,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             else if (ph.kind == MK_DOWN) {
                 if (!ph.xg) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
             }
-            else stage_attn_combine(p, sc, xs, ldx, spart);  // merge scratch: the partial buffer is idle in a prologue
+            else stage_rows(p, p.attn_out, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);  // o-proj: merged attention rows
             __syncthreads();
             if (tr) tr[1] = clock64();
 
