@@ -602,7 +602,10 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
         const int n_sl = kWarps / Gq > 0 ? min(kWarps / Gq, 4) : 1;  // token slices per head
         const int hw = warp % Gq, sl = warp / Gq;                    // meaningful while warp < Gq * n_sl
         const bool pv_warp = warp < Gq * n_sl;
-        float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};   // (m, l) of head hw; hd/32 output columns per lane
+        const int pv_lpg = hd >> 2;                                   // lanes that cover one row of V, four columns each
+        const int pv_gi = lane / pv_lpg, pv_c4 = (lane - pv_gi * pv_lpg) * 4;
+        const int pv_stride = n_sl * (32 / pv_lpg);                   // tokens between two iterations of one lane group
+        float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};   // (m, l) of head hw; this lane group's share of 4 columns
         for (int tile0 = a.t0; tile0 < a.t1; tile0 += kTT) {
             const int tend = min(a.t1, tile0 + kTT), nt = tend - tile0;
             const bool has_next = tile0 + kTT < a.t1;
@@ -667,36 +670,23 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 m = mn;
 #pragma unroll
                 for (int e = 0; e < 4; ++e) o[e] *= corr;
-                // probabilities stay in registers: token t's weight lives in lane t % 32 (p0 for t < 32, else p1)
+                // Every lane owns four output columns; with head_dim < 128 the warp's lanes form 32 / (hd / 4) groups that
+                // take different tokens of the slice.  Probabilities stay in registers: token t's weight lives in lane
+                // t % 32 (p0 for t < 32, else p1).  The loop bounds are warp-uniform (shuffles inside).
                 float oa[4] = {0.f, 0.f, 0.f, 0.f}, ob[4] = {0.f, 0.f, 0.f, 0.f};  // two independent chains
-                int t = sl;
-                for (; t + n_sl < nt; t += 2 * n_sl) {
-                    const int tb = t + n_sl;
-                    const float pa = __shfl_sync(0xffffffffu, t < 32 ? p0 : p1, t & 31);
-                    const float pb = __shfl_sync(0xffffffffu, tb < 32 ? p0 : p1, tb & 31);
-                    const bf16* va = sm.v + (size_t)t * ld + lane * epl;
-                    const bf16* vb = sm.v + (size_t)tb * ld + lane * epl;
-                    if (epl == 4) {
-                        const uint2 ra = *reinterpret_cast<const uint2*>(va), rb = *reinterpret_cast<const uint2*>(vb);
-                        oa[0] = fmaf(pa, __uint_as_float(ra.x << 16), oa[0]); oa[1] = fmaf(pa, __uint_as_float(ra.x & 0xffff0000u), oa[1]);
-                        oa[2] = fmaf(pa, __uint_as_float(ra.y << 16), oa[2]); oa[3] = fmaf(pa, __uint_as_float(ra.y & 0xffff0000u), oa[3]);
-                        ob[0] = fmaf(pb, __uint_as_float(rb.x << 16), ob[0]); ob[1] = fmaf(pb, __uint_as_float(rb.x & 0xffff0000u), ob[1]);
-                        ob[2] = fmaf(pb, __uint_as_float(rb.y << 16), ob[2]); ob[3] = fmaf(pb, __uint_as_float(rb.y & 0xffff0000u), ob[3]);
-                    } else if (epl == 2) {
-                        const uint32_t ra = *reinterpret_cast<const uint32_t*>(va), rb = *reinterpret_cast<const uint32_t*>(vb);
-                        oa[0] = fmaf(pa, __uint_as_float(ra << 16), oa[0]); oa[1] = fmaf(pa, __uint_as_float(ra & 0xffff0000u), oa[1]);
-                        ob[0] = fmaf(pb, __uint_as_float(rb << 16), ob[0]); ob[1] = fmaf(pb, __uint_as_float(rb & 0xffff0000u), ob[1]);
-                    } else {
-                        oa[0] = fmaf(pa, __bfloat162float(va[0]), oa[0]);
-                        ob[0] = fmaf(pb, __bfloat162float(vb[0]), ob[0]);
-                    }
-                }
-                if (t < nt) {
-                    const float pa = __shfl_sync(0xffffffffu, t < 32 ? p0 : p1, t & 31);
-                    const bf16* va = sm.v + (size_t)t * ld + lane * epl;
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        if (e < epl) oa[e] = fmaf(pa, __bfloat162float(va[e]), oa[e]);
+                for (int b0 = sl; b0 < nt; b0 += 2 * pv_stride) {
+                    const int ta = b0 + pv_gi * n_sl, tb = ta + pv_stride;
+                    const int ca = min(ta, nt - 1), cb = min(tb, nt - 1);
+                    const float a0 = __shfl_sync(0xffffffffu, p0, ca & 31), a1 = __shfl_sync(0xffffffffu, p1, ca & 31);
+                    const float b0v = __shfl_sync(0xffffffffu, p0, cb & 31), b1v = __shfl_sync(0xffffffffu, p1, cb & 31);
+                    const float pa = ta < nt ? (ca < 32 ? a0 : a1) : 0.f;
+                    const float pb = tb < nt ? (cb < 32 ? b0v : b1v) : 0.f;
+                    const uint2 ra = *reinterpret_cast<const uint2*>(sm.v + (size_t)ca * ld + pv_c4);
+                    const uint2 rb = *reinterpret_cast<const uint2*>(sm.v + (size_t)cb * ld + pv_c4);
+                    oa[0] = fmaf(pa, __uint_as_float(ra.x << 16), oa[0]); oa[1] = fmaf(pa, __uint_as_float(ra.x & 0xffff0000u), oa[1]);
+                    oa[2] = fmaf(pa, __uint_as_float(ra.y << 16), oa[2]); oa[3] = fmaf(pa, __uint_as_float(ra.y & 0xffff0000u), oa[3]);
+                    ob[0] = fmaf(pb, __uint_as_float(rb.x << 16), ob[0]); ob[1] = fmaf(pb, __uint_as_float(rb.x & 0xffff0000u), ob[1]);
+                    ob[2] = fmaf(pb, __uint_as_float(rb.y << 16), ob[2]); ob[3] = fmaf(pb, __uint_as_float(rb.y & 0xffff0000u), ob[3]);
                 }
 #pragma unroll
                 for (int e = 0; e < 4; ++e) o[e] += oa[e] + ob[e];
@@ -706,29 +696,28 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), false, true);
             if (tr) tr[7] = clock64();  // softmax + P.V done
         }
+        // lane groups of a warp hold different tokens of the same four columns: add them (fixed order)
+        for (int off = pv_lpg; off < 32; off <<= 1) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o[e] += __shfl_xor_sync(0xffffffffu, o[e], off);
+        }
         // sum the token slices of a head in fixed order (through the score buffer, free now), slice 0 stores
         if (n_sl > 1) {
             float* red = sm.q;  // [Gq][hd] fp32, free after the last tile's scores; slices 1.. add in turn
             for (int k2 = 1; k2 < n_sl; ++k2) {
-                if (pv_warp && sl == k2) {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        if (e < epl) red[hw * hd + lane * epl + e] = o[e];
-                }
+                if (pv_warp && sl == k2 && pv_gi == 0)
+                    *reinterpret_cast<float4*>(red + hw * hd + pv_c4) = make_float4(o[0], o[1], o[2], o[3]);
                 __syncthreads();
-                if (pv_warp && sl == 0) {
-#pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        if (e < epl) o[e] += red[hw * hd + lane * epl + e];
+                if (pv_warp && sl == 0 && pv_gi == 0) {
+                    const float4 v = *reinterpret_cast<const float4*>(red + hw * hd + pv_c4);
+                    o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
                 }
                 __syncthreads();
             }
         }
         if (warp < Gq) {  // slice 0 of head `warp` (hw == warp, sl == 0)
             const size_t pidx = ((size_t)a.r * H + a.kvh * Gq + warp) * S + a.split;
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-                if (e < epl) p.part_o[pidx * hd + lane * epl + e] = o[e];
+            if (pv_gi == 0) *reinterpret_cast<float4*>(p.part_o + pidx * hd + pv_c4) = make_float4(o[0], o[1], o[2], o[3]);
             if (lane == 0) {
                 p.part_ml[pidx * 2 + 0] = m;
                 p.part_ml[pidx * 2 + 1] = l;
