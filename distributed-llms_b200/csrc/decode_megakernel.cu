@@ -740,12 +740,22 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
             __threadfence();
             float* wgt = sm.s;  // [Gq][S] merge weights (the score buffer is free)
             const size_t pb = ((size_t)a.r * H + a.kvh * Gq) * S;
-            for (int i = threadIdx.x; i < Gq * S; i += kThreads) {
-                const int s2 = i % S;
-                float2 ml = make_float2(-FLT_MAX, 0.f);
-                if (s2 < n_act) ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml) + pb + i);
-                wgt[i] = ml.x;
-                sm.q[i] = ml.y;  // [Gq][S] split sums (q is free as well)
+            // one L2 round trip: every thread asks for its (m, l) pair and for the first eight partial rows of its
+            // four output columns before anything is used
+            const int mi = threadIdx.x;  // (head, split) pair of this thread, Gq * S <= 128 < kThreads
+            float2 ml = make_float2(-FLT_MAX, 0.f);
+            if (mi < Gq * S && mi % S < n_act) ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml) + pb + mi);
+            const int oi = threadIdx.x;  // four output columns of this thread, Gq * hd / 4 <= 256 < kThreads
+            const bool has_o = oi < ((Gq * hd) >> 2);
+            const int ohq = has_o ? (oi * 4) / hd : 0, oc = oi * 4 - ohq * hd;
+            const float* po = p.part_o + (pb + (size_t)ohq * S) * hd + oc;
+            float4 v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                v[j] = has_o && j < n_act ? ldcg_f4(po + (size_t)j * hd) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (mi < Gq * S) {
+                wgt[mi] = ml.x;
+                sm.q[mi] = ml.y;  // [Gq][S] split sums (q is free as well)
             }
             __syncthreads();
             for (int hq = threadIdx.x; hq < Gq; hq += kThreads) {
@@ -760,19 +770,18 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 for (int s2 = 0; s2 < n_act; ++s2) wgt[hq * S + s2] *= inv;
             }
             __syncthreads();
-            for (int i = threadIdx.x; i < (Gq * hd) >> 2; i += kThreads) {
-                const int hq = (i * 4) / hd, c = i * 4 - hq * hd;
-                const float* po = p.part_o + (pb + (size_t)hq * S) * hd + c;
+            if (has_o) {
                 float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int s0 = 0; s0 < n_act; s0 += 8) {  // eight 16-byte loads in flight
-                    float4 v[8];
+                for (int s0 = 0; s0 < n_act; s0 += 8) {
+                    if (s0 > 0) {  // more than eight splits: the next batch of rows
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        v[j] = s0 + j < n_act ? ldcg_f4(po + (size_t)(s0 + j) * hd) : make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int j = 0; j < 8; ++j)
+                            v[j] = s0 + j < n_act ? ldcg_f4(po + (size_t)(s0 + j) * hd) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         if (s0 + j < n_act) {
-                            const float w = wgt[hq * S + s0 + j];
+                            const float w = wgt[ohq * S + s0 + j];
                             acc.x = fmaf(v[j].x, w, acc.x);
                             acc.y = fmaf(v[j].y, w, acc.y);
                             acc.z = fmaf(v[j].z, w, acc.z);
@@ -783,7 +792,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 uint2 out;
                 out.x = *reinterpret_cast<uint32_t*>(&lo);
                 out.y = *reinterpret_cast<uint32_t*>(&hi);
-                *reinterpret_cast<uint2*>(static_cast<bf16*>(p.attn_out) + ((size_t)a.r * H + a.kvh * Gq + hq) * hd + c) = out;
+                *reinterpret_cast<uint2*>(static_cast<bf16*>(p.attn_out) + ((size_t)a.r * H + a.kvh * Gq + ohq) * hd + oc) = out;
             }
         }
         __syncthreads();  // shared buffers are reused by the next unit
