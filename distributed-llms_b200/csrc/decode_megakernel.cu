@@ -460,9 +460,7 @@ __device__ __forceinline__ void stage_rows(const MkParams& p, const void* src, i
     }
 }
 
-// OPROJ prologue: merge the split-K attention partials of every (row, head) into bf16 rows in shared memory.
-// Batched L2 round trips: the (m, l) pairs, then the partial outputs as 16-byte vectors, eight in flight per
-// thread; splits past the end of a row's context are skipped.  `sw` = 2*R*H*S floats of scratch.
+// number of splits of row r that own at least one token (the others never run and are never read)
 __device__ __forceinline__ int attn_active_splits(const MkParams& p, const StepCache& sc, int r) {
     const int S = p.n_splits, len = sc.pos[r] + 1;
     int chunk = (len + S - 1) / S;
@@ -471,70 +469,6 @@ __device__ __forceinline__ int attn_active_splits(const MkParams& p, const StepC
 }
 
 __device__ __forceinline__ float4 ldcg_f4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
-
-__device__ __forceinline__ void stage_attn_combine(const MkParams& p, const StepCache& sc, bf16* xs, int ldx, float* sw) {
-    const int hd = p.head_dim, H = p.n_heads, S = p.n_splits, Hd = H * hd;
-    const int n_pairs = p.n_rows * H;
-    float* sm_w = sw;                 // [pair][S]  split maxima, then normalised weights
-    float* sm_l = sw + n_pairs * S;   // [pair][S]  split sums
-    for (int i = threadIdx.x; i < n_pairs * S; i += kThreads) {
-        const int pair = i / S, s2 = i - pair * S;
-        float2 ml = make_float2(-FLT_MAX, 0.f);
-        if (s2 < attn_active_splits(p, sc, pair / H)) ml = __ldcg(reinterpret_cast<const float2*>(p.part_ml) + i);
-        sm_w[i] = ml.x;
-        sm_l[i] = ml.y;
-    }
-    __syncthreads();
-    for (int pair = threadIdx.x; pair < n_pairs; pair += kThreads) {
-        float Mg = -FLT_MAX, Lg = 0.f;
-        for (int s2 = 0; s2 < S; ++s2) Mg = fmaxf(Mg, sm_w[pair * S + s2]);
-        for (int s2 = 0; s2 < S; ++s2) {
-            const float w = expf(sm_w[pair * S + s2] - Mg);
-            Lg = fmaf(sm_l[pair * S + s2], w, Lg);
-            sm_w[pair * S + s2] = w;
-        }
-        const float inv = 1.0f / Lg;
-        for (int s2 = 0; s2 < S; ++s2) sm_w[pair * S + s2] *= inv;
-    }
-    __syncthreads();
-    const int vec_per_row = Hd >> 2;  // groups of four output elements
-    for (int idx = threadIdx.x; idx < p.n_rows * vec_per_row; idx += kThreads) {
-        const int r = idx / vec_per_row, c = (idx - r * vec_per_row) * 4, h = c / hd, e = c - h * hd;
-        const int pair = r * H + h;
-        const int ns = attn_active_splits(p, sc, r);
-        const float* po = p.part_o + (size_t)pair * S * hd + e;
-        const float* wg = sm_w + pair * S;
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int s0 = 0; s0 < ns; s0 += 8) {
-            float4 v0, v1, v2, v3, v4, v5, v6, v7;
-            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-            v0 = ldcg_f4(po + (size_t)s0 * hd);
-            v1 = s0 + 1 < ns ? ldcg_f4(po + (size_t)(s0 + 1) * hd) : z4;
-            v2 = s0 + 2 < ns ? ldcg_f4(po + (size_t)(s0 + 2) * hd) : z4;
-            v3 = s0 + 3 < ns ? ldcg_f4(po + (size_t)(s0 + 3) * hd) : z4;
-            v4 = s0 + 4 < ns ? ldcg_f4(po + (size_t)(s0 + 4) * hd) : z4;
-            v5 = s0 + 5 < ns ? ldcg_f4(po + (size_t)(s0 + 5) * hd) : z4;
-            v6 = s0 + 6 < ns ? ldcg_f4(po + (size_t)(s0 + 6) * hd) : z4;
-            v7 = s0 + 7 < ns ? ldcg_f4(po + (size_t)(s0 + 7) * hd) : z4;
-#define DLLM_ACC4(V, I)                                    \
-    if (s0 + (I) < ns) {                                   \
-        const float w = wg[s0 + (I)];                      \
-        acc.x = fmaf((V).x, w, acc.x);                     \
-        acc.y = fmaf((V).y, w, acc.y);                     \
-        acc.z = fmaf((V).z, w, acc.z);                     \
-        acc.w = fmaf((V).w, w, acc.w);                     \
-    }
-            DLLM_ACC4(v0, 0) DLLM_ACC4(v1, 1) DLLM_ACC4(v2, 2) DLLM_ACC4(v3, 3)
-            DLLM_ACC4(v4, 4) DLLM_ACC4(v5, 5) DLLM_ACC4(v6, 6) DLLM_ACC4(v7, 7)
-#undef DLLM_ACC4
-        }
-        __nv_bfloat162 lo = __floats2bfloat162_rn(acc.x, acc.y), hi = __floats2bfloat162_rn(acc.z, acc.w);
-        uint2 out;
-        out.x = *reinterpret_cast<uint32_t*>(&lo);
-        out.y = *reinterpret_cast<uint32_t*>(&hi);
-        *reinterpret_cast<uint2*>(xs + (size_t)r * ldx + c) = out;
-    }
-}
 
 // ---- attention phase ------------------------------------------------------------------------------------
 
@@ -590,7 +524,6 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
     __shared__ int s_attn_last;
     const int hd = p.head_dim, H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int epl = hd >> 5;  // output columns per lane: 1, 2 or 4
     const float scale = rsqrtf((float)hd);
     const int n_units = p.n_rows * KV * S;
     bool first = true;

@@ -470,13 +470,13 @@ def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
     hf = dict(random_init.NAMED_CONFIGS[model])
     hf["num_hidden_layers"] = 2
     params = random_init.random_stage_parameters(hf, range(2), True, True, 77, torch.bfloat16, device="cuda")
-    limits = dict(max_rows=256, max_seqs=8, max_context=128, page_size=64)
+    limits = dict(max_rows=512, max_seqs=16, max_context=128, page_size=64)
     shards = {}
     for mk in ("1", "0"):
         monkeypatch.setenv("DLLM_MEGAKERNEL", mk)
         shards[mk] = ModelShard(0, dict(params), config=hf, **limits)
         shards[mk].to_device()
-    for batch in (1, 4, 8):
+    for batch in (1, 4, 8, 16):  # 16: the swap-AB GEMMs + grouped-head attention on one side, per-op kernels on the other
         prompts = make_prompts(hf["vocab_size"], batch, 24, seed=batch)
         outs = {}
         for mk, sh in shards.items():
