@@ -123,6 +123,8 @@ WORKLOADS = {
     "tinyllama-1.1b": ("tinyllama-1.1b", 1, 512),
     "llama3-8b": ("llama3-8b", 1, 512),
     "gpt2-small": ("gpt2-small", 1, 16),
+    "qwen2.5-14b": ("qwen2.5-14b", 1, 2048),   # BASELINE configs[3]: 4 stages, micro-batched prefill of 4 x 2048 tokens
+    "llama3-70b": ("llama3-70b", 32, 4096),    # BASELINE configs[4]: 8 stages, batch 32, 4k context
 }
 
 

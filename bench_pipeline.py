@@ -27,8 +27,11 @@ def run_pipeline(args) -> int:
     torch.cuda.set_device(local)
     rank, world = init_stage_group("nccl")
     dev = torch.device("cuda", local)
-    model, _, prompt_len = WORKLOADS[args.workload or "llama3-8b"]
-    batch = args.batch or 1
+    model, wl_batch, prompt_len = WORKLOADS[args.workload or "llama3-8b"]
+    if args.prompt_len:
+        prompt_len = args.prompt_len
+    batch = args.batch or (wl_batch if model == "llama3-70b" else 1)
+    fused = batch <= 8  # the persistent kernel (and with it the fused hand-off) takes up to 8 rows at these widths
     n_micro = world
     K = args.steps if args.steps > 0 else 64
     W = max(args.warmup if args.warmup >= 0 else 4, 3)
@@ -42,8 +45,8 @@ def run_pipeline(args) -> int:
     first, last = rank == 0, rank == world - 1
     params = random_init.random_stage_parameters(hf, layers, first, last, 1234, torch.bfloat16, device=str(dev))
     max_ctx = prompt_len + 3 * (W + K) + 16
-    shard = ModelShard(rank, params, config=hf, max_rows=max(128, batch * prompt_len), max_seqs=n_micro * batch, max_context=max_ctx,
-                       page_size=64)
+    shard = ModelShard(rank, params, config=hf, max_rows=max(128, min(batch * prompt_len, 4096)), max_seqs=n_micro * batch,
+                       max_context=max_ctx, page_size=64)
     shard.to_device()
     ex = shard.executor
     link = StageLink(rank, world)
@@ -78,7 +81,13 @@ def run_pipeline(args) -> int:
                     dist.recv(toks[m], src=world - 1)
         return toks
 
-    prefill_all(3)  # untimed: NCCL point-to-point communicators, tensor maps and module loading happen here
+    big = n_micro * batch * prompt_len > 65536
+    if big:  # a second full prefill would cost minutes: warm the links and the kernels with a short prompt instead
+        full_len, prompt_len = prompt_len, 64
+        prefill_all(3)
+        prompt_len = full_len
+    else:
+        prefill_all(3)  # untimed: NCCL point-to-point communicators, tensor maps and module loading happen here
     torch.cuda.synchronize()
     shard.reset()
     t_pre0, t_pre1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -93,35 +102,39 @@ def run_pipeline(args) -> int:
     prefill_ms = float(pre)
 
     # ---- fused hand-off: one launch per stage for W warm-up steps, one for the K timed steps ----
-    inbox, outbox = exchange_mailboxes(rank, world, local, n_micro, batch, d)
-    if first:
-        for m in range(n_micro):
-            inbox.post_tokens(m, first_tokens[m], ticket=1)
-    seq_all = torch.arange(n_micro * batch, dtype=torch.int32).reshape(n_micro, batch)
-    pos0 = torch.full((n_micro, batch), prompt_len, dtype=torch.int32)
-    ex.decode_pipelined(inbox, outbox, n_micro, batch, W, 0, pos0, seq_all)
-    torch.cuda.synchronize()
-    dist.barrier()
+    inbox = outbox = None
     launches0 = cabi.kernel_launch_count()
     sampler = ClockSampler(local)
-    if first:
-        sampler.start()
-    torch.cuda.synchronize()
-    dist.barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    ex.decode_pipelined(inbox, outbox, n_micro, batch, K, W, pos0 + W, seq_all)
-    f1.record()
-    torch.cuda.synchronize()
-    dist.barrier()
-    fms = torch.tensor([f0.elapsed_time(f1)], device=dev)
-    dist.all_reduce(fms, op=dist.ReduceOp.MAX)  # the slowest rank defines the step time
-    dec_ms = float(fms)
+    done = 0  # decode steps so far
+    fused_last = first_tokens if first else None
+    dec_ms = None
+    if fused:
+        inbox, outbox = exchange_mailboxes(rank, world, local, n_micro, batch, d)
+        if first:
+            for m in range(n_micro):
+                inbox.post_tokens(m, first_tokens[m], ticket=1)
+        seq_all = torch.arange(n_micro * batch, dtype=torch.int32).reshape(n_micro, batch)
+        pos0 = torch.full((n_micro, batch), prompt_len, dtype=torch.int32)
+        ex.decode_pipelined(inbox, outbox, n_micro, batch, W, 0, pos0, seq_all)
+        torch.cuda.synchronize()
+        dist.barrier()
+        launches0 = cabi.kernel_launch_count()
+        if first:
+            sampler.start()
+        torch.cuda.synchronize()
+        dist.barrier()
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record()
+        ex.decode_pipelined(inbox, outbox, n_micro, batch, K, W, pos0 + W, seq_all)
+        f1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        fms = torch.tensor([f0.elapsed_time(f1)], device=dev)
+        dist.all_reduce(fms, op=dist.ReduceOp.MAX)  # the slowest rank defines the step time
+        dec_ms = float(fms)
+        fused_last = [inbox.read_tokens(m)[0].to(dev) for m in range(n_micro)] if first else None
+        done = W + K
     launches = torch.tensor([cabi.kernel_launch_count() - launches0], device=dev, dtype=torch.int64)
-    dist.all_reduce(launches)
-    value = n_micro * batch * K / (dec_ms * 1e-3)
-    fused_last = [inbox.read_tokens(m)[0].to(dev) for m in range(n_micro)] if first else None
-    done = W + K  # decode steps so far
 
     stepper = ShardStepper(shard, batch, n_micro)
     for m in range(n_micro):
@@ -145,7 +158,16 @@ def run_pipeline(args) -> int:
     # without touching the host) -- reported beside the fused number
     _, got = timed(W, fused_last, record=True)
     nxt = [got[m, :, -1].contiguous() for m in range(n_micro)] if first else None
+    if not fused:  # more rows than the persistent kernel takes: this schedule is the measured one
+        launches0 = cabi.kernel_launch_count()
+        if first:
+            sampler.start()
     nccl_ms, got = timed(K, nxt, record=True)
+    if not fused:
+        launches = torch.tensor([cabi.kernel_launch_count() - launches0], device=dev, dtype=torch.int64)
+        dec_ms = nccl_ms
+    dist.all_reduce(launches)
+    value = n_micro * batch * K / (dec_ms * 1e-3)
 
     # end to end: the first stage takes every step's token ids from pinned host memory and the returned tokens
     # are read back to the host before the next step (what a master-driven loop does)
@@ -181,7 +203,8 @@ def run_pipeline(args) -> int:
                        "micro_batches": n_micro, "prompt_len": prompt_len, "stages": world,
                        "layers_per_stage": [len(r) for r in partition],
                        "weights": "random-init (HF default init, seed 1234)",
-                       "handoff": "fused: peer stores from the down-projection epilogue into the next stage's mailbox + tickets",
+                       "handoff": ("fused: peer stores from the down-projection epilogue into the next stage's mailbox + tickets"
+                                   if fused else "NCCL send/recv per micro-batch step (batch above the persistent kernel's 8 rows)"),
                        "l2": "inputs larger than L2: every stage streams >= 1.7 GB of weights per micro-batch step"},
             "e2e": {"value": n_micro * batch * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 4 * batch * n_micro,
                     "d2h_bytes_per_step": 4 * batch * n_micro, "ms_per_step": e2e_ms / K},
@@ -189,10 +212,15 @@ def run_pipeline(args) -> int:
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": float(fr[worst]) * hbm_peak, "peak": hbm_peak, "unit": "GB/s",
                          "frac": float(fr[worst]), "traffic": None, "peak_kind": peak_kind,
-                         "kernel": f"decode_megakernel of stage {worst} (slowest stage): one persistent launch for the timed loop, "
-                                   "unit = one micro-batch step of the stage",
+                         "kernel": (f"decode_megakernel of stage {worst} (slowest stage): one persistent launch for the timed loop, "
+                                    "unit = one micro-batch step of the stage") if fused else
+                                   (f"micro-batch step of stage {worst} (slowest stage): CUDA graph of swap-AB tcgen05 GEMMs + "
+                                    "grouped-head decode attention"),
                          "per_stage_frac": [round(float(x), 4) for x in fr]},
             "cpu_baseline": None,
+            "note": "N=1 of this bench is BASELINE configs[1] (TinyLlama-1.1B); N >= 2 is configs[2] (this model). "
+                    "For the same model on one B200 run `bench.py --workload " + (args.workload or "llama3-8b") + "` "
+                    "(Llama-3-8B: 296 tok/s, profiles/r1d_summary.md)",
             "nccl_handoff": {"value": n_micro * batch * K / (nccl_ms * 1e-3), "unit": UNIT, "ms_per_step": nccl_ms / K,
                              "note": "same schedule, one launch per micro-batch step, NCCL send/recv + token ring"},
             "prefill": {"tokens_per_sec": n_micro * batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
@@ -200,9 +228,10 @@ def run_pipeline(args) -> int:
         }
         print(json.dumps(line))
     dist.barrier()
-    if outbox is not inbox:
+    if outbox is not None and outbox is not inbox:
         outbox.close()
     dist.barrier()
-    inbox.close()
+    if inbox is not None:
+        inbox.close()
     dist.destroy_process_group()
     return 0
