@@ -17,6 +17,7 @@
 //     cp.async before the barrier that precedes attention.
 // Rounding points are those of the per-op kernels in decode_gemv.cu / attention.cu.
 #include <float.h>
+#include <stdlib.h>
 #include <limits.h>
 
 #include "common.cuh"
@@ -1267,7 +1268,9 @@ size_t mk_smem_bytes(const MkParams& p, int stages) {
 }
 
 static int mk_pick_stages(const MkParams& p) {
-    for (int s = 6; s >= 2; --s)
+    int cap = 6;
+    if (const char* e = getenv("DLLM_MK_STAGES")) { const int v = atoi(e); if (v >= 2 && v <= 6) cap = v; }  // experiments
+    for (int s = cap; s >= 2; --s)
         if (mk_smem_bytes(p, s) <= (size_t)MK_SMEM_BUDGET) return s;
     return 0;
 }
