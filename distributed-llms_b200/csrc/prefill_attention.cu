@@ -151,9 +151,8 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
         const float mn_lo = fmaxf(m_lo, mx_lo), mn_hi = fmaxf(m_hi, mx_hi);
         const float c_lo = expf(m_lo - mn_lo), c_hi = expf(m_hi - mn_hi);
         float sum_lo = 0.f, sum_hi = 0.f;
-        // P as A fragments (16 rows x 16 keys each), split into a bf16 head and a bf16 remainder: two MMAs per V tile
-        // keep ~16 bits of P, like the fp32 probabilities of the decode kernels (HF itself rounds P to bf16 once)
-        uint32_t pfr[kKT / 16][4], pfl[kKT / 16][4];
+        // P as A fragments (16 rows x 16 keys each), rounded to bf16 -- where HF eager attention rounds it
+        uint32_t pfr[kKT / 16][4];
 #pragma unroll
         for (int nt = 0; nt < kKT / 8; ++nt) {
             const float p0 = s[nt][0] == -FLT_MAX ? 0.f : expf(s[nt][0] - mn_lo);
@@ -165,8 +164,6 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
             // C fragment of key tile nt -> A fragment: tiles 2j and 2j+1 are the two k-halves of A step j
             pfr[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0, p1);
             pfr[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2, p3);
-            pfl[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0 - bf16_round(p0), p1 - bf16_round(p1));
-            pfl[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2 - bf16_round(p2), p3 - bf16_round(p3));
         }
         sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 1);
         sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 2);
@@ -188,15 +185,12 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
         for (int kk = 0; kk < kKT / 16; ++kk) {
             // A fragment order is (row g, k lo), (row g+8, k lo), (row g, k hi), (row g+8, k hi)
             const uint32_t a[4] = {pfr[kk][0], pfr[kk][1], pfr[kk][2], pfr[kk][3]};
-            const uint32_t al[4] = {pfl[kk][0], pfl[kk][1], pfl[kk][2], pfl[kk][3]};
 #pragma unroll
             for (int nt = 0; nt < HD / 8; nt += 2) {
                 uint32_t bfr[4];
                 ldsm_x4_trans(bfr, smem_u32(sV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * LD + nt * 8 + (lane >> 4) * 8));
                 mma_bf16(o[nt], a, bfr[0], bfr[1]);
                 mma_bf16(o[nt + 1], a, bfr[2], bfr[3]);
-                mma_bf16(o[nt], al, bfr[0], bfr[1]);
-                mma_bf16(o[nt + 1], al, bfr[2], bfr[3]);
             }
         }
         __syncthreads();  // tile it fully consumed: its buffer is the target of the gather two tiles on
