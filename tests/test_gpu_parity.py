@@ -399,12 +399,16 @@ def test_streamed_rows_variant_matches_oracle(batch, monkeypatch):
     assert torch.equal(torch.cat([first[:, None], rest], 1), ids)
 
 
+@pytest.mark.parametrize("arch", ["llama", "gpt2"])
 @pytest.mark.parametrize("n_micro,rows", [(1, 1), (3, 2), (2, 8)])
-def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows):
+def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, arch):
     """One stage, its own mailbox as in- and outbox: the persistent kernel feeds the token ids round through the
     mailbox tickets.  Every micro-batch must reproduce, bit for bit, what the classic device loop generates."""
     from src.network.handoff import Mailbox
-    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    if arch == "llama":
+        cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    else:
+        cfg = ShardModelConfig("gpt2", 128, 3, 4, 4, 32, 512, 211, 96, 1e-5, 10000.0, tie_head=True)
     sd = make_state_dict(cfg, 3, torch.float32, init="full")
     n_steps, T = 7, 10
     (st,) = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=64, max_seqs=n_micro * rows, max_context=64, page_size=16)
