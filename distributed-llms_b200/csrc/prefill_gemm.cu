@@ -100,7 +100,7 @@ __device__ __forceinline__ float gelu_new_f(float x) {
 template <int EPI, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-               const __grid_constant__ CUtensorMap tm_b2, const GemmTcParams p) {
+               const __grid_constant__ CUtensorMap tm_b2, const __grid_constant__ CUtensorMap tm_b3, const GemmTcParams p) {
     constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
     static_assert(!(kDual && BN != 128), "the dual-B tile is 128 wide");
     constexpr int kBTileBytes = BN * BK * 2;
@@ -113,7 +113,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     __shared__ uint32_t s_tmem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+    // row segment of the logical weight matrix this tile belongs to (q | k | v in one launch; BIAS epilogue only)
+    int seg = 0, tile = blockIdx.x, col0 = 0, seg_n = p.N;
+    if (!kDual) {
+        const int t0 = (p.N + BN - 1) / BN, t1 = (p.n_more[0] + BN - 1) / BN;
+        if (tile >= t0 + t1) { seg = 2; tile -= t0 + t1; col0 = p.N + p.n_more[0]; seg_n = p.n_more[1]; }
+        else if (tile >= t0) { seg = 1; tile -= t0; col0 = p.N; seg_n = p.n_more[0]; }
+    }
+    const CUtensorMap* map_b = seg == 0 ? &tm_b : (seg == 1 ? &tm_b2 : &tm_b3);
+    const int m0 = blockIdx.y * BM, n0 = tile * BN;
     const int num_kb = (p.K + BK - 1) / BK;
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages), tfull = smem_u32(bars + 2 * kStages);
 
@@ -143,7 +151,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
                 mbar_expect_tx(full0 + s * 8, kStageBytes);
                 tma_load_2d(dst, &tm_a, kb * BK, m0, full0 + s * 8);
-                tma_load_2d(dst + kTileBytes, &tm_b, kb * BK, n0, full0 + s * 8);
+                tma_load_2d(dst + kTileBytes, map_b, kb * BK, n0, full0 + s * 8);
                 if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, kb * BK, n0, full0 + s * 8);
             }
         }
@@ -175,8 +183,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         const int quarter = warp & 3;
         const int row = m0 + quarter * 32 + lane;
         const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16);
-        bf16* out = static_cast<bf16*>(p.c);
-        const bf16* bias = static_cast<const bf16*>(p.bias);
+        bf16* out = static_cast<bf16*>(p.c) + col0;
+        const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 32) {
             uint32_t acc[32], acc2[32];
@@ -186,7 +194,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 #pragma unroll
                 for (int j = 0; j < 32; j += 2) {
                     const int n = n0 + c0 + j;
-                    if (n >= p.N) break;
+                    if (n >= seg_n) break;
                     float v0 = __uint_as_float(acc[j]), v1 = __uint_as_float(acc[j + 1]);
                     if (EPI == GEMM_EPI_SWIGLU) {
                         const float g0 = bf16_round(v0), g1 = bf16_round(v1);
@@ -195,7 +203,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                         v1 = bf16_round(silu_f(g1)) * u1;
                     } else {
                         v0 = bf16_round(v0 + (bias ? __bfloat162float(bias[n]) : 0.f));
-                        v1 = bf16_round(v1 + (bias && n + 1 < p.N ? __bfloat162float(bias[n + 1]) : 0.f));
+                        v1 = bf16_round(v1 + (bias && n + 1 < seg_n ? __bfloat162float(bias[n + 1]) : 0.f));
                         if (EPI == GEMM_EPI_RESIDUAL) {
                             const uint32_t old = *reinterpret_cast<const uint32_t*>(out + (size_t)row * p.ldc + n);
                             v0 += __uint_as_float(old << 16);
@@ -206,7 +214,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                         }
                     }
                     // N is even for every weight shape in use; a lone last column is written alone
-                    if (n + 1 < p.N) *reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * p.ldc + n) = __floats2bfloat162_rn(v0, v1);
+                    if (n + 1 < seg_n) *reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * p.ldc + n) = __floats2bfloat162_rn(v0, v1);
                     else out[(size_t)row * p.ldc + n] = __float2bfloat16_rn(v0);
                 }
             }
@@ -618,7 +626,8 @@ bool make_map(CUtensorMap* map, const void* base, int rows, int K, int box_rows 
 }
 
 template <int EPI, int BN>
-cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const GemmTcParams& p, cudaStream_t st) {
+cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const CUtensorMap& b3, const GemmTcParams& p,
+                       cudaStream_t st) {
     constexpr int stage = kTileBytes + BN * BK * 2 * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
     const size_t smem = (size_t)kStages * stage + 1024;
     static bool attr_done = false;
@@ -627,8 +636,10 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    dim3 grid((p.N + BN - 1) / BN, (p.M + BM - 1) / BM);
-    gemm_tc_kernel<EPI, BN><<<grid, kGemmThreads, smem, st>>>(a, b, b2, p);
+    int tiles = (p.N + BN - 1) / BN;
+    if (EPI != GEMM_EPI_SWIGLU) tiles += (p.n_more[0] + BN - 1) / BN + (p.n_more[1] + BN - 1) / BN;
+    dim3 grid(tiles, (p.M + BM - 1) / BM);
+    gemm_tc_kernel<EPI, BN><<<grid, kGemmThreads, smem, st>>>(a, b, b2, b3, p);
     count_launch();
     return cudaGetLastError();
 }
@@ -636,8 +647,16 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
 // 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give)
 bool wide_tiles(const GemmTcParams& p) {
     static const bool off = [] { const char* e = getenv("DLLM_GEMM_BN256"); return e && e[0] == '0'; }();
-    if (off || p.epi == GEMM_EPI_SWIGLU || p.N % 256) return false;
-    return (long)((p.M + BM - 1) / BM) * (p.N / 256) >= 148;
+    if (off || p.epi == GEMM_EPI_SWIGLU || p.N % 256 || p.n_more[0] % 256 || p.n_more[1] % 256) return false;
+    return (long)((p.M + BM - 1) / BM) * ((p.N + p.n_more[0] + p.n_more[1]) / 256) >= 148;
+}
+
+// 64-wide tiles when 128-wide ones would leave SMs without a tile (mid-size prompts: M = 256 .. 1024)
+bool narrow_tiles(const GemmTcParams& p) {
+    static const bool off = [] { const char* e = getenv("DLLM_GEMM_BN64"); return e && e[0] == '0'; }();
+    if (off || p.epi == GEMM_EPI_SWIGLU) return false;
+    const long n_all = (long)p.N + p.n_more[0] + p.n_more[1];
+    return (long)((p.M + BM - 1) / BM) * ((n_all + 127) / 128) < 148;
 }
 
 template <int EPI, int MP>
@@ -703,19 +722,6 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
     const bool more = p.n_more[0] > 0 || p.n_more[1] > 0;
     if (more && (p.epi != GEMM_EPI_BIAS || (p.n_more[1] > 0 && p.n_more[0] <= 0) || p.ldc < p.N + p.n_more[0] + p.n_more[1]))
         return cudaErrorInvalidValue;
-    if (more && !small_m(p)) {  // the wide kernels take one matrix per launch
-        GemmTcParams q = p;
-        q.n_more[0] = q.n_more[1] = 0;
-        cudaError_t e = launch_gemm_tc(q, st);
-        int col = p.N;
-        for (int i = 0; i < 2 && e == cudaSuccess && p.n_more[i] > 0; ++i) {
-            q.w = p.w_more[i]; q.bias = p.bias_more[i]; q.N = p.n_more[i];
-            q.c = static_cast<bf16*>(p.c) + col;
-            col += p.n_more[i];
-            e = launch_gemm_tc(q, st);
-        }
-        return e;
-    }
     if (small_m(p)) {
         switch (p.epi) {
             case GEMM_EPI_BIAS: return launch_swapab_rows<GEMM_EPI_BIAS>(p, st);
@@ -727,20 +733,26 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
         return cudaErrorInvalidValue;
     }
     if (p.epi == GEMM_EPI_LOGITS) return cudaErrorInvalidValue;
-    CUtensorMap a, b, b2;
-    const bool wide = wide_tiles(p);
-    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, wide ? 256 : 128)) return cudaErrorNotSupported;
+    CUtensorMap a, b, b2, b3;
+    const int bn = wide_tiles(p) ? 256 : (narrow_tiles(p) ? 64 : 128);
+    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, bn)) return cudaErrorNotSupported;
+    b2 = b3 = b;
     if (p.epi == GEMM_EPI_SWIGLU) {
         if (!make_map(&b2, p.w2, p.N, p.K)) return cudaErrorNotSupported;
     } else {
-        b2 = b;
+        if (p.n_more[0] > 0 && !make_map(&b2, p.w_more[0], p.n_more[0], p.K, bn)) return cudaErrorNotSupported;
+        if (p.n_more[1] > 0 && !make_map(&b3, p.w_more[1], p.n_more[1], p.K, bn)) return cudaErrorNotSupported;
     }
+#define DLLM_GEMM_BY_BN(E)                                                                        \
+    (bn == 256 ? launch_epi<E, 256>(a, b, b2, b3, p, st)                                          \
+               : (bn == 64 ? launch_epi<E, 64>(a, b, b2, b3, p, st) : launch_epi<E, 128>(a, b, b2, b3, p, st)))
     switch (p.epi) {
-        case GEMM_EPI_BIAS: return wide ? launch_epi<GEMM_EPI_BIAS, 256>(a, b, b2, p, st) : launch_epi<GEMM_EPI_BIAS, 128>(a, b, b2, p, st);
-        case GEMM_EPI_RESIDUAL: return wide ? launch_epi<GEMM_EPI_RESIDUAL, 256>(a, b, b2, p, st) : launch_epi<GEMM_EPI_RESIDUAL, 128>(a, b, b2, p, st);
-        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU, 128>(a, b, b2, p, st);
-        case GEMM_EPI_GELU: return wide ? launch_epi<GEMM_EPI_GELU, 256>(a, b, b2, p, st) : launch_epi<GEMM_EPI_GELU, 128>(a, b, b2, p, st);
+        case GEMM_EPI_BIAS: return DLLM_GEMM_BY_BN(GEMM_EPI_BIAS);
+        case GEMM_EPI_RESIDUAL: return DLLM_GEMM_BY_BN(GEMM_EPI_RESIDUAL);
+        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU, 128>(a, b, b2, b3, p, st);
+        case GEMM_EPI_GELU: return DLLM_GEMM_BY_BN(GEMM_EPI_GELU);
     }
+#undef DLLM_GEMM_BY_BN
     return cudaErrorInvalidValue;
 }
 

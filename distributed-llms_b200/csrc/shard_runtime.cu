@@ -617,17 +617,10 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
             GemmTcParams g{};
             g.a = s->xn; g.M = n_rows; g.K = c.hidden; g.ldc = QKVd; g.epi = GEMM_EPI_BIAS;
             g.w = w.wq; g.bias = w.bq; g.c = qkv; g.N = Hd;
-            if (n_rows <= 64) {  // small batch: q | k | v as row segments of one launch
-                g.w_more[0] = w.wk; g.bias_more[0] = w.bk; g.n_more[0] = KVd;
-                g.w_more[1] = w.wv; g.bias_more[1] = w.bv; g.n_more[1] = KVd;
-                CUDA_TRY(launch_gemm_tc(g, st));
-            } else {
-                CUDA_TRY(launch_gemm_tc(g, st));
-                g.w = w.wk; g.bias = w.bk; g.c = qkv + (size_t)Hd * 2; g.N = KVd;
-                CUDA_TRY(launch_gemm_tc(g, st));
-                g.w = w.wv; g.bias = w.bv; g.c = qkv + (size_t)(Hd + KVd) * 2; g.N = KVd;
-                CUDA_TRY(launch_gemm_tc(g, st));
-            }
+            // q | k | v as row segments of one launch
+            g.w_more[0] = w.wk; g.bias_more[0] = w.bk; g.n_more[0] = KVd;
+            g.w_more[1] = w.wv; g.bias_more[1] = w.bv; g.n_more[1] = KVd;
+            CUDA_TRY(launch_gemm_tc(g, st));
         }
         {
             RopeAppendParams ra{};
