@@ -758,10 +758,12 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
             CUDA_TRY(cudaMemcpyAsync(s->logit_rows, logit_rows, (size_t)nl * 4, cudaMemcpyDefault, st));
         } else if (n_logit_rows >= 0) {
             nl = n_rows;
-            CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
         }  // n_logit_rows < 0 with no row list: no logits this call (an inner chunk of a chunked prefill)
     }
-    if (mk_eligible(s, n_rows, nl, logit_rows == nullptr)) {
+    const bool use_mk = mk_eligible(s, n_rows, nl, logit_rows == nullptr);
+    if (c.has_head && !logit_rows && nl > 0 && !use_mk)  // the persistent kernel takes every row's logits in place
+        CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
+    if (use_mk) {
         if (run_megakernel(s, n_rows, 1, false, st)) return 1;
     } else if (prefill_eligible(s, n_rows)) {
         int run_seqs = 0, run_len = 0;
