@@ -110,11 +110,11 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def workload_name(model: str, batch: int, prompt_len: int, stages: int, n_layers: int) -> str:
+def workload_name(model: str, batch: int, prompt_len: int, stages: int, n_layers: int, n_micro: int = 0) -> str:
     """The same string in both arms' `config.workload`."""
     if stages == 1:
         return f"{model} decode, batch {batch}, {prompt_len}-token prompt, 1 stage"
-    return (f"{model} decode, {n_layers} layers over {stages} stages, {stages} micro-batches of {batch} in flight, "
+    return (f"{model} decode, {n_layers} layers over {stages} stages, {n_micro or stages} micro-batches of {batch} in flight, "
             f"{prompt_len}-token prompts")
 
 
@@ -334,6 +334,7 @@ def main() -> int:
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=[None, *WORKLOADS])
     ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--micro", type=int, default=0, help="micro-batches in flight (N > 1; default: one per stage)")
     ap.add_argument("--prompt-len", type=int, default=0, help="override the workload's prompt length (single GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -32,7 +32,7 @@ def run_pipeline(args) -> int:
         prompt_len = args.prompt_len
     batch = args.batch or (wl_batch if model == "llama3-70b" else 1)
     fused = batch <= 8  # the persistent kernel (and with it the fused hand-off) takes up to 8 rows at these widths
-    n_micro = world
+    n_micro = args.micro if args.micro >= world else world
     K = args.steps if args.steps > 0 else 64
     W = max(args.warmup if args.warmup >= 0 else 4, 3)
     hf = random_init.NAMED_CONFIGS[model]
@@ -199,7 +199,7 @@ def run_pipeline(args) -> int:
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dec_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(model, batch, prompt_len, world, L), "model": model, "batch": batch,
+            "config": {"workload": workload_name(model, batch, prompt_len, world, L, n_micro), "model": model, "batch": batch,
                        "micro_batches": n_micro, "prompt_len": prompt_len, "stages": world,
                        "layers_per_stage": [len(r) for r in partition],
                        "weights": "random-init (HF default init, seed 1234)",
