@@ -25,7 +25,8 @@ namespace dllm {
 namespace {
 
 constexpr int BM = 128, BK = 64;                // tile rows / k-slice; BK * 2 bytes = one 128-byte swizzle row
-constexpr int kStages = 4;
+// ring depth: as many stages as 200 KB of shared memory hold (4 for the 48 KB stages, 6 for 32 KB, 8 for 24 KB)
+constexpr int gemm_stages(int stage_bytes) { return 200 * 1024 / stage_bytes > 8 ? 8 : 200 * 1024 / stage_bytes; }
 constexpr int kTileBytes = BM * BK * 2;         // 16 KB per 128-row operand tile
 // Output tile width BN: 128, or 256 when the grid still fills the machine -- the A tile is then read once per
 // 256 columns (87 instead of 64 flop per shared-memory byte staged).
@@ -107,6 +108,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     constexpr int kStageBytes = kTileBytes + kBTileBytes * (kDual ? 2 : 1);
     constexpr uint32_t kTmemCols = kDual ? 256 : BN;
     constexpr uint32_t kIdesc = make_idesc(BN);
+    constexpr int kStages = gemm_stages(kStageBytes);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     __shared__ __align__(8) uint64_t bars[2 * kStages + 1];
@@ -629,7 +631,7 @@ template <int EPI, int BN>
 cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const CUtensorMap& b3, const GemmTcParams& p,
                        cudaStream_t st) {
     constexpr int stage = kTileBytes + BN * BK * 2 * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
-    const size_t smem = (size_t)kStages * stage + 1024;
+    const size_t smem = (size_t)gemm_stages(stage) * stage + 1024;
     static bool attr_done = false;
     if (!attr_done) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -656,7 +658,7 @@ bool narrow_tiles(const GemmTcParams& p) {
     static const bool off = [] { const char* e = getenv("DLLM_GEMM_BN64"); return e && e[0] == '0'; }();
     if (off || p.epi == GEMM_EPI_SWIGLU) return false;
     const long n_all = (long)p.N + p.n_more[0] + p.n_more[1];
-    return (long)((p.M + BM - 1) / BM) * ((n_all + 127) / 128) < 148;
+    return (long)((p.M + BM - 1) / BM) * ((n_all + 127) / 128) <= 74;  // at most half the SMs would get a 128-wide tile
 }
 
 template <int EPI, int MP>
