@@ -252,11 +252,10 @@ cudaError_t launch_hd(const AttnParams& p, cudaStream_t st) {
     const size_t tiles = (size_t)(kRows + 4 * kKT) * LD * 2;
     const size_t merge = (size_t)kRows * LD * 2 + (size_t)kWarps * kRows * HD * 4;
     const size_t smem = tiles > merge ? tiles : merge;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.need()) {
         cudaError_t e = cudaFuncSetAttribute(attn_decode_gqa_kernel<HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     dim3 grid(p.n_splits, p.n_kv_heads, p.n_rows);
     attn_decode_gqa_kernel<HD><<<grid, kThreads, smem, st>>>(p);

@@ -136,6 +136,19 @@ cudaError_t launch_advance(int32_t* ids, int32_t* positions, const int32_t* next
 cudaError_t launch_legacy_matmul(const float* in, const float* param, float* out, int m, int k, int n,
                                  cudaStream_t s);
 
+// Function attributes (opt-in shared memory) are per device: remember, per kernel, on which devices they are set.
+struct PerDeviceOnce {
+    bool done[64] = {false};
+    bool need() {  // true the first time on the current device
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64) return true;
+        if (done[dev]) return false;
+        done[dev] = true;
+        return true;
+    }
+};
+
 int set_last_error(const char* msg);  // stores the message dllm_last_error() returns; always returns 1
 void count_launch(unsigned long long n = 1);
 unsigned long long launch_count();

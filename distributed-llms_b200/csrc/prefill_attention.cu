@@ -216,12 +216,11 @@ cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {
     if (p.n_seqs <= 0 || p.rows_per_seq <= 0 || p.n_heads % p.n_kv_heads) return cudaErrorInvalidValue;
     dim3 grid((p.rows_per_seq + kQT - 1) / kQT, p.n_heads, p.n_seqs);
     const size_t smem = (size_t)(kQT + 4 * kKT) * (p.head_dim + 8) * 2;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.need()) {
         cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)((kQT + 4 * kKT) * (128 + 8) * 2));
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     switch (p.head_dim) {
         case 32: prefill_attn_kernel<32><<<grid, kThreads, smem, st>>>(p); break;

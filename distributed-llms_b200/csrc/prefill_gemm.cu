@@ -632,11 +632,10 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
                        cudaStream_t st) {
     constexpr int stage = kTileBytes + BN * BK * 2 * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
     const size_t smem = (size_t)gemm_stages(stage) * stage + 1024;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.need()) {
         cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     int tiles = (p.N + BN - 1) / BN;
     if (EPI != GEMM_EPI_SWIGLU) tiles += (p.n_more[0] + BN - 1) / BN + (p.n_more[1] + BN - 1) / BN;
@@ -682,11 +681,10 @@ cudaError_t launch_swapab(const GemmTcParams& p, cudaStream_t st) {
     while (ksplit < Cfg::kMaxSplit && tiles * ksplit * 2 <= 160 && ksplit * 2 <= total_kb) ksplit *= 2;
     const int kb_per_cta = (total_kb + ksplit - 1) / ksplit;
     const size_t smem = (size_t)Cfg::kStagesS * Cfg::kStageBytes + 1024;
-    static bool attr_done = false;
-    if (!attr_done) {
+    static PerDeviceOnce attr_once;
+    if (attr_once.need()) {
         cudaError_t e = cudaFuncSetAttribute(gemm_swapab_kernel<EPI, MP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        attr_done = true;
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(tiles, ksplit);
