@@ -8,7 +8,7 @@ out=gpurun_out
 mkdir -p $out
 python bench.py --steps 8 --warmup 3 --no-cpu-baseline > $out/${tag}_bench_8step.json 2> $out/${tag}_bench_8step.err || exit 1
 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err || exit 1
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $out/${tag}_ncu_launches.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $out/${tag}_ncu_launches.csv \
     python bench.py --steps 8 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_launches.log 2>&1
 # the timed launch (8 steps) is the second decode_megakernel launch of that command with more than one step:
 # launches in order: prefill-side single-step launches (none for a 512-row chunk), warm-up loop (3 steps), timed loop (8)
