@@ -74,6 +74,8 @@ class MasterNode:
         self._loaded = threading.Condition()
         self._loaded_shards: set = set()
         self.heartbeat_timeout = 30.0
+        self.use_fused_handoff = True                 # decode through peer mailboxes when every stage has its own GPU
+        self.last_decode_path = None                  # "fused" | "per-step": how the last request was decoded
 
     # ---- life cycle (reference :29-52) -------------------------------------------------------------------
     def start(self):
@@ -215,6 +217,71 @@ class MasterNode:
             x = pickle.loads(payload)
         return x
 
+    # ---- fused hand-off: one persistent decode loop per stage, no message per token ---------------------------------
+    def _request(self, worker, task_id: str, command: str, payload=None, metadata=None, timeout: float = 60.0):
+        """Send a command and wait for its RESULT.  Returns the unpickled payload."""
+        md = dict(metadata or {})
+        md["task_id"] = task_id
+        self._send(worker, command, pickle.dumps(payload) if payload is not None else None, md)
+        try:
+            header, body = self._replies[task_id].get(timeout=timeout)
+        except Empty:
+            raise TimeoutError(f"no answer to {command}")
+        if header.get("error"):
+            raise RuntimeError(header["error"])
+        return pickle.loads(body) if body else {}
+
+    def _fused_decode(self, task_id: str, first_tokens: torch.Tensor, n_steps: int, timeout: float = 300.0) -> Optional[torch.Tensor]:
+        """Greedy decode of `n_steps` further tokens for the batch whose prefill just ran, with the hand-off fused into
+        the stages' kernels (workers: MAILBOX_* / RUN_DECODE_LOOP).  Needs one shard per worker and every worker on its
+        own GPU (two persistent kernels that wait for each other cannot share a device).  Returns int64 [B, n_steps]
+        -- the tokens after `first_tokens` -- or None when this cluster / batch cannot take the fused path."""
+        order = self._stage_order()
+        rows = int(first_tokens.numel())
+        if n_steps < 1 or rows > 8 or any(len(s) != 1 for _, s in order):
+            return None
+        places = [(self.workers[w].get("pid"), self.workers[w].get("device_index")) for w, _ in order]
+        if any(p[0] is None or p[1] is None or p[1] < 0 for p in places) or len(set(places)) != len(places):
+            return None
+        workers = [self.workers[w] for w, _ in order]
+        shard_ids = [s[0] for _, s in order]
+        opened = []
+        try:
+            infos = []
+            for st, (wk, sid) in enumerate(zip(workers, shard_ids)):
+                infos.append(self._request(wk, task_id, "MAILBOX_OPEN", None, {"shard_id": sid, "n_slots": 1, "rows": rows, "stage": st}))
+                opened.append(wk)
+            for st, wk in enumerate(workers):
+                self._request(wk, task_id, "MAILBOX_CONNECT", infos[(st + 1) % len(workers)], {"stage": st})
+            self._request(workers[0], task_id, "MAILBOX_POST", {"tokens": first_tokens.reshape(1, rows).to(torch.int32), "ticket": 1},
+                          {"stage": 0})
+            seq = torch.arange(rows, dtype=torch.int32)
+            for st, (wk, sid) in enumerate(zip(workers, shard_ids)):  # every stage starts its loop; they finish together
+                self._send(wk, "RUN_DECODE_LOOP", pickle.dumps({"seq_ids": seq, "positions": None}),
+                           {"task_id": task_id, "shard_id": sid, "n_micro": 1, "rows": rows, "n_steps": n_steps, "step_base": 0, "stage": st})
+            fed, errors = None, []
+            for _ in workers:  # wait for every stage, also when one of them failed: no reply may be left in the queue
+                try:
+                    header, body = self._replies[task_id].get(timeout=timeout)
+                except Empty:
+                    raise TimeoutError("a stage did not finish its decode loop")
+                if header.get("error"):
+                    errors.append(header["error"])
+                elif header.get("stage") == 0:
+                    fed = pickle.loads(body)["fed"]
+            if errors:
+                raise RuntimeError("; ".join(errors))
+            last = self._request(workers[0], task_id, "MAILBOX_READ", None, {"stage": 0})["tokens"]
+            # fed[i] = ids fed at step i (fed[0] = first_tokens); the ids generated by the last step are in the mailbox
+            gen = torch.cat([fed[1:, 0, :], last.reshape(1, rows)], dim=0)  # [n_steps, rows]
+            return gen.t().to(torch.int64)
+        finally:
+            for wk in opened:
+                try:
+                    self._request(wk, task_id, "MAILBOX_CLOSE", None, {}, timeout=10.0)
+                except Exception:
+                    pass
+
     def _process_tasks(self):
         while self.running:
             try:
@@ -236,7 +303,18 @@ class MasterNode:
                     raise RuntimeError("no shard assignments: call assign_shards() / distribute_shards() first")
                 out = self._pipeline_step(task_id, {"input_ids": ids}, reset=True, timeout=60.0)   # prefill
                 tokens = [self.sampler(out["logits"]) if "logits" in out else out["next_token"]]
-                for _ in range(max_new - 1):                                                         # decode
+                fused = None
+                if self.use_fused_handoff and max_new > 1 and self.sampler.temperature <= 0.0:
+                    try:
+                        fused = self._fused_decode(task_id, tokens[0].reshape(-1), max_new - 1)
+                    except RuntimeError as e:  # e.g. a shape the persistent kernel does not take: fall back below
+                        print(f"fused decode unavailable ({e}); falling back to the per-step loop")
+                        while not self._replies[task_id].empty():
+                            self._replies[task_id].get_nowait()
+                self.last_decode_path = "fused" if fused is not None else "per-step"
+                if fused is not None:
+                    tokens.extend(fused[:, i] for i in range(fused.shape[1]))
+                for _ in range(0 if fused is not None else max_new - 1):                             # decode
                     out = self._pipeline_step(task_id, {"input_ids": tokens[-1].reshape(-1, 1).to(torch.int64)},
                                               reset=False, timeout=60.0)
                     tokens.append(self.sampler(out["logits"]) if "logits" in out else out["next_token"])

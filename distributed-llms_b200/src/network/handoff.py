@@ -84,7 +84,9 @@ class Mailbox:
         from ..engine import cabi
         h = C.c_void_p()
         cabi.check(cabi.lib().dllm_mailbox_create(device, n_slots, rows, hidden, C.byref(h)))
-        return cls(h, device, n_slots, rows, hidden, True)
+        box = cls(h, device, n_slots, rows, hidden, True)
+        _LOCAL_MAILBOXES[box.export_handle()] = box
+        return box
 
     def export_handle(self) -> bytes:
         import ctypes as C
@@ -128,8 +130,24 @@ class Mailbox:
     def close(self) -> None:
         if self.handle is not None:
             from ..engine import cabi
+            if self.owner:
+                for k in [k for k, v in _LOCAL_MAILBOXES.items() if v is self]:
+                    del _LOCAL_MAILBOXES[k]
             cabi.lib().dllm_mailbox_destroy(self.handle)
             self.handle = None
+
+
+# Mailboxes created in this process, by IPC handle: a worker in the same process (threads, tests) cannot open its
+# neighbour's handle through CUDA IPC and takes a peer view of the object instead.
+_LOCAL_MAILBOXES: dict = {}
+
+
+def connect_mailbox(device: int, info: dict) -> Mailbox:
+    """The producer's side of `info` = {"ipc", "pid", "n_slots", "rows", "hidden"} (what a MAILBOX_OPEN reply carries)."""
+    local = _LOCAL_MAILBOXES.get(info["ipc"]) if info.get("pid") == os.getpid() else None
+    if local is not None:
+        return local if local.device == device else local.view_from(device)
+    return Mailbox.open_peer(device, info["ipc"], info["n_slots"], info["rows"], info["hidden"])
 
 
 def exchange_mailboxes(rank: int, world: int, device: int, n_slots: int, rows: int, hidden: int):

@@ -14,6 +14,7 @@ Fixed behind the names (each noted where it happens):
 from __future__ import annotations
 
 import io
+import os
 import pickle
 import socket
 import threading
@@ -158,10 +159,14 @@ def _load_parameters(shard_data: bytes) -> Dict[str, torch.Tensor]:
 class WorkerNode:
     """Reference src/worker/node.py:34-302."""
 
-    def __init__(self, host: str = "0.0.0.0", port: int = 65433, master_address: Optional[str] = None):
+    def __init__(self, host: str = "0.0.0.0", port: int = 65433, master_address: Optional[str] = None,
+                 device: Optional[int] = None):
         self.host = host
         self.port = port
         self.master_address = master_address
+        self.device = device  # CUDA device index of this worker (None: the process's current device)
+        self._inbox = None    # fused hand-off: this stage's mailbox and the view of the next stage's
+        self._outbox = None
         self.shards: Dict[int, ModelShard] = {}
         self.running = False
         self.server_socket = None
@@ -222,7 +227,9 @@ class WorkerNode:
                 capabilities = {
                     "has_gpu": torch.cuda.is_available(),
                     "device": "cuda" if torch.cuda.is_available() else "cpu",
-                    "memory": torch.cuda.get_device_properties(0).total_memory if torch.cuda.is_available() else 0,
+                    "memory": torch.cuda.get_device_properties(self.device or 0).total_memory if torch.cuda.is_available() else 0,
+                    "pid": os.getpid(),
+                    "device_index": self._device_index() if torch.cuda.is_available() else -1,
                 }
                 self._protocol.send_message(self.master_socket, "REGISTER", metadata={"capabilities": capabilities})
                 threading.Thread(target=self._handle_master, daemon=True).start()
@@ -271,9 +278,78 @@ class WorkerNode:
                 print(f"Error handling master connection: {e}")
 
     # -- shard-execution entry point (reference :189-261) ---------------------------------------------------
+    def _device_index(self) -> int:
+        return self.device if self.device is not None else torch.cuda.current_device()
+
     def _handle_command(self, sock, command, header, payload, protocol: Optional[MessageProtocol] = None):
+        if self.device is not None and torch.cuda.is_available():
+            with torch.cuda.device(self.device):  # the current device is per thread
+                return self._dispatch_command(sock, command, header, payload, protocol)
+        return self._dispatch_command(sock, command, header, payload, protocol)
+
+    # fused hand-off (include/dllm_b200.h "mailboxes"): the master opens a mailbox on every stage, tells every stage
+    # where the next one's is, seeds stage 0 and then starts ONE persistent decode loop per stage
+    def _mailbox_command(self, command: str, header: dict, payload: bytes) -> dict:
+        from ..network.handoff import Mailbox, connect_mailbox
+        args = pickle.loads(payload) if payload else {}
+        dev = self._device_index()
+        if command == "MAILBOX_OPEN":
+            shard = self.shards[header["shard_id"]]
+            hidden = shard.executor.geom.hidden
+            self._close_mailboxes()
+            self._inbox = Mailbox.create(dev, int(header["n_slots"]), int(header["rows"]), hidden)
+            return {"ipc": self._inbox.export_handle(), "pid": os.getpid(), "device_index": dev,
+                    "n_slots": self._inbox.n_slots, "rows": self._inbox.rows, "hidden": hidden}
+        if self._inbox is None:
+            raise RuntimeError("no mailbox is open on this worker")
+        if command == "MAILBOX_CONNECT":
+            mine = args["ipc"] == self._inbox.export_handle() and args.get("pid") == os.getpid()
+            self._outbox = self._inbox if mine else connect_mailbox(dev, args)
+            return {}
+        if command == "MAILBOX_POST":
+            for slot, toks in enumerate(args["tokens"]):
+                self._inbox.post_tokens(slot, torch.as_tensor(toks, dtype=torch.int32), int(args["ticket"]))
+            return {}
+        if command == "RUN_DECODE_LOOP":
+            if self._outbox is None:
+                raise RuntimeError("the mailbox of the next stage is not connected")
+            ex = self.shards[header["shard_id"]].executor
+            n_micro, rows, n_steps = int(header["n_micro"]), int(header["rows"]), int(header["n_steps"])
+            seq = torch.as_tensor(args["seq_ids"], dtype=torch.int32).reshape(n_micro, rows)
+            pos = args.get("positions")
+            if pos is None:  # continue every sequence where its cache ends
+                pos = torch.tensor([ex.seq_len(int(s)) for s in seq.reshape(-1)], dtype=torch.int32)
+            pos = torch.as_tensor(pos, dtype=torch.int32).reshape(n_micro, rows)
+            fed = ex.decode_pipelined(self._inbox, self._outbox, n_micro, rows, n_steps, int(header.get("step_base", 0)), pos, seq)
+            torch.cuda.synchronize()
+            return {"fed": fed.cpu() if fed is not None else None}
+        if command == "MAILBOX_READ":
+            got = [self._inbox.read_tokens(slot) for slot in range(self._inbox.n_slots)]
+            return {"tokens": torch.stack([g[0] for g in got]), "tickets": [g[1] for g in got]}
+        if command == "MAILBOX_CLOSE":
+            self._close_mailboxes()
+            return {}
+        raise ValueError(f"unknown mailbox command {command}")
+
+    def _close_mailboxes(self) -> None:
+        if self._outbox is not None and self._outbox is not self._inbox:
+            self._outbox.close()
+        if self._inbox is not None:
+            self._inbox.close()
+        self._inbox = self._outbox = None
+
+    def _dispatch_command(self, sock, command, header, payload, protocol: Optional[MessageProtocol] = None):
         protocol = protocol or MessageProtocol()
-        if command == "LOAD_SHARD":
+        if command.startswith("MAILBOX_") or command == "RUN_DECODE_LOOP":
+            task_id = header.get("task_id")
+            md = {"task_id": task_id, "stage": header.get("stage")}
+            try:
+                out = self._mailbox_command(command, header, payload)
+                protocol.send_message(sock, "RESULT", payload=pickle.dumps(out), metadata=md)
+            except Exception as e:
+                md["error"] = f"{type(e).__name__}: {e}"
+                protocol.send_message(sock, "RESULT", payload=pickle.dumps({}), metadata=md)
+        elif command == "LOAD_SHARD":
             shard_id = header.get("shard_id")
             ok = self.load_shard(shard_id, payload)
             protocol.send_message(sock, "SHARD_LOADED", metadata={"shard_id": shard_id, "ok": ok})

@@ -113,3 +113,40 @@ def test_master_two_workers_greedy_decode_matches_oracle(tmp_path, dtype):
             assert same.all() or float(margins[0, int((~same[0]).float().argmax())]) < 2 ** -6
     finally:
         _shutdown(master, workers)
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_master_uses_the_fused_handoff_when_every_stage_has_its_own_gpu(tmp_path):
+    """Two workers on two GPUs: after the prefill the master opens a mailbox on each stage, connects them into a ring
+    and starts one persistent decode loop per stage (no message per token).  Same tokens as the per-step loop."""
+    from oracle.shard_oracle import ShardModelConfig, build_pipeline, greedy_generate
+    d, sd = _model_dir(tmp_path, torch.bfloat16)
+    master = MasterNode(host="127.0.0.1", port=0)
+    master.start()
+    workers = []
+    try:
+        for dev in range(2):
+            w = WorkerNode(host="127.0.0.1", port=0, master_address=f"127.0.0.1:{master.port}", device=dev)
+            w.start()
+            workers.append(w)
+            deadline = time.time() + 10
+            while len(master.workers) < dev + 1 and time.time() < deadline:
+                time.sleep(0.02)
+        master.initialize_model(d, num_shards=2)
+        master.assign_shards()
+        master.distribute_shards(timeout=120)
+        prompt = torch.randint(0, CFG["vocab_size"], (2, 11), generator=torch.Generator().manual_seed(5))
+        got = torch.tensor(master.run_inference(prompt, timeout=180, max_new_tokens=16)["token_ids"])
+        assert master.last_decode_path == "fused"
+        master.use_fused_handoff = False
+        again = torch.tensor(master.run_inference(prompt, timeout=180, max_new_tokens=16)["token_ids"])
+        assert master.last_decode_path == "per-step"
+        assert torch.equal(got, again)  # same kernels, the hand-off copies bits
+        cfg = ShardModelConfig.from_hf_dict(CFG)
+        want, _, margins = greedy_generate(build_pipeline(cfg, sd, 2, torch.bfloat16), prompt, 16, record=True)
+        same = (got == want).long().cumprod(1).bool()
+        for b in range(2):
+            assert same[b].all() or float(margins[b, int((~same[b]).float().argmax())]) < 2 ** -6
+    finally:
+        _shutdown(master, workers)
