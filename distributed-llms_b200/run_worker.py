@@ -16,10 +16,8 @@ def main():
     ap.add_argument("--port", type=int, default=65433)
     ap.add_argument("--gpu", type=int, default=None, help="CUDA device of this worker (one worker per GPU)")
     a = ap.parse_args()
-    if a.gpu is not None:
-        import torch
-        torch.cuda.set_device(a.gpu)
-    worker = WorkerNode(host=a.host, port=a.port, master_address=a.master)
+    # the device is a property of the worker, not of the main thread: commands are handled on other threads
+    worker = WorkerNode(host=a.host, port=a.port, master_address=a.master, device=a.gpu)
     print(f"Worker node initialized and connecting to master at {a.master}")
     try:
         worker.start(block=True)
