@@ -232,12 +232,15 @@ class MasterNode:
         return pickle.loads(body) if body else {}
 
     def _fused_decode(self, task_id: str, first_tokens: torch.Tensor, n_steps: int, timeout: float = 300.0) -> Optional[torch.Tensor]:
-        """Greedy decode of `n_steps` further tokens for the batch whose prefill just ran, with the hand-off fused into
-        the stages' kernels (workers: MAILBOX_* / RUN_DECODE_LOOP).  Needs one shard per worker and every worker on its
-        own GPU (two persistent kernels that wait for each other cannot share a device).  Returns int64 [B, n_steps]
-        -- the tokens after `first_tokens` -- or None when this cluster / batch cannot take the fused path."""
+        """Greedy decode of `n_steps` further tokens for the micro-batches whose prefill just ran (`first_tokens`:
+        [n_micro, rows], sequence slots m * rows + r), with the hand-off fused into the stages' kernels (workers:
+        MAILBOX_* / RUN_DECODE_LOOP).  Needs one shard per worker and every worker on its own GPU (two persistent
+        kernels that wait for each other cannot share a device).  Returns int64 [n_micro, rows, n_steps] -- the tokens
+        after `first_tokens` -- or None when this cluster / batch cannot take the fused path."""
         order = self._stage_order()
-        rows = int(first_tokens.numel())
+        if first_tokens.dim() == 1:
+            first_tokens = first_tokens[None, :]
+        n_micro, rows = int(first_tokens.shape[0]), int(first_tokens.shape[1])
         if n_steps < 1 or rows > 8 or any(len(s) != 1 for _, s in order):
             return None
         places = [(self.workers[w].get("pid"), self.workers[w].get("device_index")) for w, _ in order]
@@ -249,16 +252,15 @@ class MasterNode:
         try:
             infos = []
             for st, (wk, sid) in enumerate(zip(workers, shard_ids)):
-                infos.append(self._request(wk, task_id, "MAILBOX_OPEN", None, {"shard_id": sid, "n_slots": 1, "rows": rows, "stage": st}))
+                infos.append(self._request(wk, task_id, "MAILBOX_OPEN", None, {"shard_id": sid, "n_slots": n_micro, "rows": rows, "stage": st}))
                 opened.append(wk)
             for st, wk in enumerate(workers):
                 self._request(wk, task_id, "MAILBOX_CONNECT", infos[(st + 1) % len(workers)], {"stage": st})
-            self._request(workers[0], task_id, "MAILBOX_POST", {"tokens": first_tokens.reshape(1, rows).to(torch.int32), "ticket": 1},
-                          {"stage": 0})
-            seq = torch.arange(rows, dtype=torch.int32)
+            self._request(workers[0], task_id, "MAILBOX_POST", {"tokens": first_tokens.to(torch.int32), "ticket": 1}, {"stage": 0})
+            seq = torch.arange(n_micro * rows, dtype=torch.int32)
             for st, (wk, sid) in enumerate(zip(workers, shard_ids)):  # every stage starts its loop; they finish together
                 self._send(wk, "RUN_DECODE_LOOP", pickle.dumps({"seq_ids": seq, "positions": None}),
-                           {"task_id": task_id, "shard_id": sid, "n_micro": 1, "rows": rows, "n_steps": n_steps, "step_base": 0, "stage": st})
+                           {"task_id": task_id, "shard_id": sid, "n_micro": n_micro, "rows": rows, "n_steps": n_steps, "step_base": 0, "stage": st})
             fed, errors = None, []
             for _ in workers:  # wait for every stage, also when one of them failed: no reply may be left in the queue
                 try:
@@ -273,14 +275,52 @@ class MasterNode:
                 raise RuntimeError("; ".join(errors))
             last = self._request(workers[0], task_id, "MAILBOX_READ", None, {"stage": 0})["tokens"]
             # fed[i] = ids fed at step i (fed[0] = first_tokens); the ids generated by the last step are in the mailbox
-            gen = torch.cat([fed[1:, 0, :], last.reshape(1, rows)], dim=0)  # [n_steps, rows]
-            return gen.t().to(torch.int64)
+            gen = torch.cat([fed[1:], last.reshape(1, n_micro, rows)], dim=0)  # [n_steps, n_micro, rows]
+            return gen.permute(1, 2, 0).to(torch.int64)
         finally:
             for wk in opened:
                 try:
                     self._request(wk, task_id, "MAILBOX_CLOSE", None, {}, timeout=10.0)
                 except Exception:
                     pass
+
+    def _decode_micro_batches(self, task_id: str, prompts: List[torch.Tensor], max_new: int) -> Dict[str, Any]:
+        """Several requests at once: prompt m ([rows, T_m] token ids, the same `rows` for all) becomes micro-batch m, its
+        rows use the sequence slots m * rows ... -- the stages work on different micro-batches at the same time."""
+        prompts = [p[None, :] if p.dim() == 1 else p for p in (torch.as_tensor(p, dtype=torch.int64) for p in prompts)]
+        rows = int(prompts[0].shape[0])
+        if any(int(p.shape[0]) != rows for p in prompts):
+            raise ValueError("every micro-batch needs the same number of rows")
+        M = len(prompts)
+        seqs = [torch.arange(m * rows, (m + 1) * rows, dtype=torch.int32) for m in range(M)]
+        first = []
+        for m, ids in enumerate(prompts):  # prefill, one micro-batch after the other through the stages
+            out = self._pipeline_step(task_id, {"input_ids": ids, "seq_ids": seqs[m]}, reset=(m == 0), timeout=60.0)
+            first.append(out["next_token"].reshape(-1).to(torch.int64))
+        tokens = torch.stack(first)[:, :, None]  # [M, rows, 1]
+        fused = None
+        if self.use_fused_handoff and max_new > 1:
+            try:
+                fused = self._fused_decode(task_id, torch.stack(first), max_new - 1)
+            except RuntimeError as e:
+                print(f"fused decode unavailable ({e}); falling back to the per-step loop")
+        self.last_decode_path = "fused" if fused is not None else "per-step"
+        if fused is not None:
+            tokens = torch.cat([tokens, fused], dim=2)
+        else:
+            cur = first
+            for _ in range(max_new - 1):
+                nxt = []
+                for m in range(M):
+                    out = self._pipeline_step(task_id, {"input_ids": cur[m].reshape(-1, 1), "seq_ids": seqs[m]}, reset=False, timeout=60.0)
+                    nxt.append(out["next_token"].reshape(-1).to(torch.int64))
+                cur = nxt
+                tokens = torch.cat([tokens, torch.stack(cur)[:, :, None]], dim=2)
+        return {"token_ids": tokens.tolist(), "text": None}
+
+    def run_many(self, prompts: Sequence[torch.Tensor], timeout: int = 120, max_new_tokens: int = 32):
+        """Decode several prompts as micro-batches of one pipeline pass.  Returns {"token_ids": [n_prompts][rows][new]}."""
+        return self.run_inference([torch.as_tensor(p) for p in prompts], timeout=timeout, max_new_tokens=max_new_tokens)
 
     def _process_tasks(self):
         while self.running:
@@ -291,38 +331,42 @@ class MasterNode:
             done = self._finished.get(task_id)
             self._replies[task_id] = Queue()
             try:
-                if isinstance(request, str):
-                    if self.tokenizer is None:
-                        raise ValueError("no tokenizer is available: pass the prompt as token ids")
-                    ids = self.tokenizer(request, return_tensors="pt")["input_ids"].to(torch.int64)
-                else:
-                    ids = torch.as_tensor(request, dtype=torch.int64)
-                    if ids.dim() == 1:
-                        ids = ids[None, :]
                 if not self.shard_assignments:
                     raise RuntimeError("no shard assignments: call assign_shards() / distribute_shards() first")
-                out = self._pipeline_step(task_id, {"input_ids": ids}, reset=True, timeout=60.0)   # prefill
-                tokens = [self.sampler(out["logits"]) if "logits" in out else out["next_token"]]
-                fused = None
-                if self.use_fused_handoff and max_new > 1 and self.sampler.temperature <= 0.0:
-                    try:
-                        fused = self._fused_decode(task_id, tokens[0].reshape(-1), max_new - 1)
-                    except RuntimeError as e:  # e.g. a shape the persistent kernel does not take: fall back below
-                        print(f"fused decode unavailable ({e}); falling back to the per-step loop")
-                        while not self._replies[task_id].empty():
-                            self._replies[task_id].get_nowait()
-                self.last_decode_path = "fused" if fused is not None else "per-step"
-                if fused is not None:
-                    tokens.extend(fused[:, i] for i in range(fused.shape[1]))
-                for _ in range(0 if fused is not None else max_new - 1):                             # decode
-                    out = self._pipeline_step(task_id, {"input_ids": tokens[-1].reshape(-1, 1).to(torch.int64)},
-                                              reset=False, timeout=60.0)
-                    tokens.append(self.sampler(out["logits"]) if "logits" in out else out["next_token"])
-                token_ids = torch.stack([t.reshape(-1).cpu() for t in tokens], dim=1)
-                text = None
-                if self.tokenizer is not None:
-                    text = self.tokenizer.batch_decode(token_ids.tolist())
-                result = {"token_ids": token_ids.tolist(), "text": text}
+                if isinstance(request, (list, tuple)) and request and isinstance(request[0], torch.Tensor):
+                    result = self._decode_micro_batches(task_id, list(request), max_new)  # prompts = micro-batches
+                else:
+                    if isinstance(request, str):
+                        if self.tokenizer is None:
+                            raise ValueError("no tokenizer is available: pass the prompt as token ids")
+                        ids = self.tokenizer(request, return_tensors="pt")["input_ids"].to(torch.int64)
+                    else:
+                        ids = torch.as_tensor(request, dtype=torch.int64)
+                        if ids.dim() == 1:
+                            ids = ids[None, :]
+                    out = self._pipeline_step(task_id, {"input_ids": ids}, reset=True, timeout=60.0)   # prefill
+                    tokens = [self.sampler(out["logits"]) if "logits" in out else out["next_token"]]
+                    fused = None
+                    if self.use_fused_handoff and max_new > 1 and self.sampler.temperature <= 0.0:
+                        try:
+                            fused = self._fused_decode(task_id, tokens[0].reshape(1, -1), max_new - 1)
+                            fused = fused[0] if fused is not None else None
+                        except RuntimeError as e:  # e.g. a shape the persistent kernel does not take: fall back below
+                            print(f"fused decode unavailable ({e}); falling back to the per-step loop")
+                            while not self._replies[task_id].empty():
+                                self._replies[task_id].get_nowait()
+                    self.last_decode_path = "fused" if fused is not None else "per-step"
+                    if fused is not None:
+                        tokens.extend(fused[:, i] for i in range(fused.shape[1]))
+                    for _ in range(0 if fused is not None else max_new - 1):                             # decode
+                        out = self._pipeline_step(task_id, {"input_ids": tokens[-1].reshape(-1, 1).to(torch.int64)},
+                                                  reset=False, timeout=60.0)
+                        tokens.append(self.sampler(out["logits"]) if "logits" in out else out["next_token"])
+                    token_ids = torch.stack([t.reshape(-1).cpu() for t in tokens], dim=1)
+                    text = None
+                    if self.tokenizer is not None:
+                        text = self.tokenizer.batch_decode(token_ids.tolist())
+                    result = {"token_ids": token_ids.tolist(), "text": text}
             except Exception as e:  # delivered to the caller instead of being printed and dropped (reference :240-242)
                 result = e
             finally:

@@ -148,5 +148,17 @@ def test_master_uses_the_fused_handoff_when_every_stage_has_its_own_gpu(tmp_path
         same = (got == want).long().cumprod(1).bool()
         for b in range(2):
             assert same[b].all() or float(margins[b, int((~same[b]).float().argmax())]) < 2 ** -6
+        # several requests at once = micro-batches of one pipelined loop (prompts of different lengths)
+        g = torch.Generator().manual_seed(9)
+        prompts = [torch.randint(0, CFG["vocab_size"], (1, n), generator=g) for n in (7, 13, 10)]
+        master.use_fused_handoff = True
+        many = torch.tensor(master.run_many(prompts, timeout=180, max_new_tokens=12)["token_ids"])  # [3, 1, 12]
+        assert master.last_decode_path == "fused"
+        master.use_fused_handoff = False
+        relay = torch.tensor(master.run_many(prompts, timeout=180, max_new_tokens=12)["token_ids"])
+        assert master.last_decode_path == "per-step" and torch.equal(many, relay)
+        for m, pr in enumerate(prompts):
+            alone = torch.tensor(master.run_inference(pr, timeout=180, max_new_tokens=12)["token_ids"])
+            assert torch.equal(alone, many[m])
     finally:
         _shutdown(master, workers)
