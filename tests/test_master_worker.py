@@ -84,6 +84,26 @@ def test_no_workers_and_heartbeat_eviction():
         master.stop()
 
 
+def test_fused_decode_is_only_tried_when_every_stage_has_its_own_gpu():
+    """Eligibility of the master's fused loop is decided from what the workers registered -- before any command goes out."""
+    m = MasterNode(host="127.0.0.1", port=0)
+    tok = torch.zeros(1, 2, dtype=torch.int64)
+
+    def cluster(places, shards=None):
+        m.workers = {f"w{i}": {"identity": b"x", "pid": p, "device_index": d} for i, (p, d) in enumerate(places)}
+        m.shard_assignments = shards or {f"w{i}": [i] for i in range(len(places))}
+
+    cluster([(10, 0), (10, 0)])                       # two stages of one process on one GPU: their kernels would wait for each other
+    assert m._fused_decode("t", tok, 4) is None
+    cluster([(10, 0), (None, None)])                  # a worker that did not say where it runs
+    assert m._fused_decode("t", tok, 4) is None
+    cluster([(10, 0), (11, 0)], {"w0": [0, 1], "w1": [2]})   # a worker with two stages
+    assert m._fused_decode("t", tok, 4) is None
+    cluster([(10, 0), (10, 1)])
+    assert m._fused_decode("t", torch.zeros(1, 9, dtype=torch.int64), 4) is None   # more rows than the persistent kernel takes
+    assert m._fused_decode("t", tok, 0) is None
+
+
 def test_sampler():
     logits = torch.tensor([[0.1, 2.0, 2.0, -1.0]])
     assert GreedySampler()(logits).tolist() == [1]                       # first index of the maximum
