@@ -64,6 +64,18 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
@@ -477,7 +489,7 @@ struct AttnSmem {
     bf16* k;      // [kTT][hd + 8]
     bf16* v;      // [kTT][hd + 8]
     float* s;     // [kMaxGq][kTT]
-    float* q;     // [kMaxGq][hd]
+    float* q;     // 16 bf16 rows [16][hd + 8] while a unit walks its tiles, then fp32 scratch of the split merge
 };
 
 // cp.async the K and V rows of tokens [a, b) of (seq, kvh) into tile rows (token - tile0)
@@ -491,6 +503,13 @@ __device__ __forceinline__ void attn_load_rows(const MkParams& p, const MkLayer&
         const size_t base = ((((size_t)page * p.n_kv_heads + kvh) << p.page_shift) + (t & mask)) * hd + v * 8;
         if (load_k) cp_async16(sm.k + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.kpool) + base);
         if (load_v) cp_async16(sm.v + (size_t)(t - tile0) * ld + v * 8, static_cast<const bf16*>(L.vpool) + base);
+    }
+    if (load_v) {
+        // V rows between the last token and the end of its 16-token MMA step: their probabilities are zero, but
+        // 0 x (stale NaN / Inf bits) is not -- clear them
+        const int r0 = b - tile0, r1 = min(kTT, (r0 + 15) & ~15);
+        for (int i = threadIdx.x; i < (r1 - r0) * vecs; i += kThreads)
+            *reinterpret_cast<uint4*>(sm.v + (size_t)(r0 + i / vecs) * ld + (i % vecs) * 8) = make_uint4(0u, 0u, 0u, 0u);
     }
     cp_async_commit();  // one group per call: the K rows and the V rows of a tile are waited for separately
 }
@@ -531,15 +550,15 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
     for (int u = blockIdx.x; u < n_units; u += gridDim.x, first = false) {
         const AttnUnit a = attn_unit(p, sc, u);
         if (a.t0 >= a.t1) continue;  // split past the end of the context: the merge never reads it
-        // Every warp works for head `hw`; the warps of one head split a tile's tokens between them (token t belongs to
-        // slice t % n_sl) and keep their own running output; (m, l) are computed redundantly and so agree bit for bit.
-        const int n_sl = kWarps / Gq > 0 ? min(kWarps / Gq, 4) : 1;  // token slices per head
-        const int hw = warp % Gq, sl = warp / Gq;                    // meaningful while warp < Gq * n_sl
-        const bool pv_warp = warp < Gq * n_sl;
-        const int pv_lpg = hd >> 2;                                   // lanes that cover one row of V, four columns each
-        const int pv_gi = lane / pv_lpg, pv_c4 = (lane - pv_gi * pv_lpg) * 4;
-        const int pv_stride = n_sl * (32 / pv_lpg);                   // tokens between two iterations of one lane group
-        float m = -FLT_MAX, l = 0.f, o[4] = {0.f, 0.f, 0.f, 0.f};   // (m, l) of head hw; this lane group's share of 4 columns
+        // Tensor-core unit: the Gq query heads of the KV head are the (zero-padded) 16 rows of mma.sync.m16n8k16; of a
+        // 64-token tile, warp w < 4 takes tokens 16 w .. 16 w + 15 and keeps its own online-softmax state (m, l) and
+        // output fragment; the four warps are merged once, after the last tile.  P is rounded to bf16 where HF rounds it.
+        const int g = lane >> 2, t4 = lane & 3;
+        bf16* sQ = reinterpret_cast<bf16*>(sm.q);  // [16][ld]
+        float m_lo = -FLT_MAX, m_hi = -FLT_MAX, l_lo = 0.f, l_hi = 0.f;  // heads g and g + 8, this warp's tokens only
+        float o[16][4];  // [hd / 8 column tiles][C fragment]; head_dim 32 / 64 use the first 4 / 8
+#pragma unroll
+        for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
         for (int tile0 = a.t0; tile0 < a.t1; tile0 += kTT) {
             const int tend = min(a.t1, tile0 + kTT), nt = tend - tile0;
             const bool has_next = tile0 + kTT < a.t1;
@@ -550,40 +569,35 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 if (first && prefetched) from = max(tile0, min(tend, attn_safe_end(sc, a)));
                 attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, true, false);
                 attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, false, true);
-            }
-            if (tile0 == a.t0) {
-                // q of the Gq heads of this KV head -> shared, fp32: one 16-byte L2 load per thread, in flight together
-                // with the K/V copies above
-                for (int i = threadIdx.x; i < (Gq * hd) >> 3; i += kThreads) {
-                    float f[8];
-                    unpack<bf16>(__ldcg(reinterpret_cast<const uint4*>(static_cast<const bf16*>(p.q) + ((size_t)a.r * H + a.kvh * Gq) * hd) + i), f);
-                    *reinterpret_cast<float4*>(sm.q + i * 8) = make_float4(f[0], f[1], f[2], f[3]);
-                    *reinterpret_cast<float4*>(sm.q + i * 8 + 4) = make_float4(f[4], f[5], f[6], f[7]);
+                // q of the Gq heads -> 16 bf16 rows in shared memory (rows past Gq zero): one 16-byte L2 load per
+                // thread, in flight together with the K/V copies above
+                const int vpr = hd >> 3;  // 16-byte vectors per row
+                for (int i = threadIdx.x; i < 16 * vpr; i += kThreads) {
+                    const int row = i / vpr, c = i - row * vpr;
+                    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                    if (row < Gq) v = __ldcg(reinterpret_cast<const uint4*>(static_cast<const bf16*>(p.q) + ((size_t)a.r * H + a.kvh * Gq + row) * hd) + c);
+                    *reinterpret_cast<uint4*>(sQ + row * ld + c * 8) = v;
                 }
-                if (tr) tr[4] = clock64();  // q staged
+                if (tr) {
+                    __threadfence_block();
+                    tr[4] = clock64();  // q staged
+                }
             }
             cp_async_wait_but_one();  // everything but the newest group (this tile's V rows): the K rows are in
             __syncthreads();
             if (tr) tr[5] = clock64();  // K tile in shared memory
-            // scores: one (token, head) pair per thread-iteration; lanes walk tokens (padded rows: no conflicts)
-            for (int i = threadIdx.x; i < kTT * Gq; i += kThreads) {
-                const int t = i & (kTT - 1), g = i / kTT;
-                if (t < nt) {
-                    const bf16* kr = sm.k + (size_t)t * ld;
-                    const float* qg = sm.q + g * hd;
-                    float d0 = 0.f, d1 = 0.f;
-                    for (int e = 0; e < hd; e += 8) {
-                        float kf[8];
-                        unpack<bf16>(*reinterpret_cast<const uint4*>(kr + e), kf);
-                        const float4 q0 = *reinterpret_cast<const float4*>(qg + e);
-                        const float4 q1 = *reinterpret_cast<const float4*>(qg + e + 4);
-                        d0 = fmaf(kf[0], q0.x, d0); d1 = fmaf(kf[1], q0.y, d1); d0 = fmaf(kf[2], q0.z, d0); d1 = fmaf(kf[3], q0.w, d1);
-                        d0 = fmaf(kf[4], q1.x, d0); d1 = fmaf(kf[5], q1.y, d1); d0 = fmaf(kf[6], q1.z, d0); d1 = fmaf(kf[7], q1.w, d1);
-                    }
-                    sm.s[g * kTT + t] = bf16_round(bf16_round(d0 + d1) * scale);
+            const bool my_tokens = warp < 4 && warp * 16 < nt;
+            float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+            if (my_tokens) {  // S = Q K^T : 16 heads x 16 tokens
+                for (int ks = 0; ks < (hd >> 4); ++ks) {
+                    uint32_t qa[4], kb[4];
+                    ldsm_x4(qa, smem_u32(sQ + ((lane & 7) + ((lane >> 3) & 1) * 8) * ld + ks * 16 + (lane >> 4) * 8));
+                    ldsm_x4(kb, smem_u32(sm.k + (warp * 16 + (lane & 7) + (lane >> 4) * 8) * ld + ks * 16 + ((lane >> 3) & 1) * 8));
+                    mma_bf16(s[0], qa[0], qa[1], qa[2], qa[3], kb[0], kb[1]);
+                    mma_bf16(s[1], qa[0], qa[1], qa[2], qa[3], kb[2], kb[3]);
                 }
             }
-            __syncthreads();
+            __syncthreads();  // every warp is done with the K tile
             if (tr) tr[6] = clock64();  // scores done
             if (has_next) {  // the K buffer is free: request the next tile's K rows, then wait for this tile's V rows
                 attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), true, false);
@@ -592,69 +606,104 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 cp_async_wait_all();
             }
             __syncthreads();
-            if (pv_warp) {  // online softmax (whole tile) + P.V over this warp's token slice
-                const float* sg = sm.s + hw * kTT;
-                const float s0 = lane < nt ? sg[lane] : -FLT_MAX;
-                const float s1 = lane + 32 < nt ? sg[lane + 32] : -FLT_MAX;
-                const float mn = fmaxf(m, warp_max(fmaxf(s0, s1)));
-                const float p0 = lane < nt ? expf(s0 - mn) : 0.f;
-                const float p1 = lane + 32 < nt ? expf(s1 - mn) : 0.f;
-                const float corr = expf(m - mn);
-                l = l * corr + warp_sum(p0 + p1);
-                m = mn;
+            if (my_tokens) {
+                // scale, mask the tokens past the end of the tile, online softmax over this warp's 16 tokens
+                float mx_lo = -FLT_MAX, mx_hi = -FLT_MAX;
 #pragma unroll
-                for (int e = 0; e < 4; ++e) o[e] *= corr;
-                // Every lane owns four output columns; with head_dim < 128 the warp's lanes form 32 / (hd / 4) groups that
-                // take different tokens of the slice.  Probabilities stay in registers: token t's weight lives in lane
-                // t % 32 (p0 for t < 32, else p1).  The loop bounds are warp-uniform (shuffles inside).
-                float oa[4] = {0.f, 0.f, 0.f, 0.f}, ob[4] = {0.f, 0.f, 0.f, 0.f};  // two independent chains
-                for (int b0 = sl; b0 < nt; b0 += 2 * pv_stride) {
-                    const int ta = b0 + pv_gi * n_sl, tb = ta + pv_stride;
-                    const int ca = min(ta, nt - 1), cb = min(tb, nt - 1);
-                    const float a0 = __shfl_sync(0xffffffffu, p0, ca & 31), a1 = __shfl_sync(0xffffffffu, p1, ca & 31);
-                    const float b0v = __shfl_sync(0xffffffffu, p0, cb & 31), b1v = __shfl_sync(0xffffffffu, p1, cb & 31);
-                    const float pa = ta < nt ? (ca < 32 ? a0 : a1) : 0.f;
-                    const float pb = tb < nt ? (cb < 32 ? b0v : b1v) : 0.f;
-                    const uint2 ra = *reinterpret_cast<const uint2*>(sm.v + (size_t)ca * ld + pv_c4);
-                    const uint2 rb = *reinterpret_cast<const uint2*>(sm.v + (size_t)cb * ld + pv_c4);
-                    oa[0] = fmaf(pa, __uint_as_float(ra.x << 16), oa[0]); oa[1] = fmaf(pa, __uint_as_float(ra.x & 0xffff0000u), oa[1]);
-                    oa[2] = fmaf(pa, __uint_as_float(ra.y << 16), oa[2]); oa[3] = fmaf(pa, __uint_as_float(ra.y & 0xffff0000u), oa[3]);
-                    ob[0] = fmaf(pb, __uint_as_float(rb.x << 16), ob[0]); ob[1] = fmaf(pb, __uint_as_float(rb.x & 0xffff0000u), ob[1]);
-                    ob[2] = fmaf(pb, __uint_as_float(rb.y << 16), ob[2]); ob[3] = fmaf(pb, __uint_as_float(rb.y & 0xffff0000u), ob[3]);
+                for (int n2 = 0; n2 < 2; ++n2) {
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const int key = warp * 16 + n2 * 8 + 2 * t4 + (e & 1);
+                        float v = bf16_round(bf16_round(s[n2][e]) * scale);
+                        if (key >= nt) v = -FLT_MAX;
+                        s[n2][e] = v;
+                    }
+                    mx_lo = fmaxf(mx_lo, fmaxf(s[n2][0], s[n2][1]));
+                    mx_hi = fmaxf(mx_hi, fmaxf(s[n2][2], s[n2][3]));
                 }
+                mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 1));
+                mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 2));
+                mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 1));
+                mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 2));
+                const float mn_lo = fmaxf(m_lo, mx_lo), mn_hi = fmaxf(m_hi, mx_hi);
+                const float c_lo = expf(m_lo - mn_lo), c_hi = expf(m_hi - mn_hi);
+                float sum_lo = 0.f, sum_hi = 0.f;
+                uint32_t pf[4];  // P as the A fragment of one 16-token k-step
 #pragma unroll
-                for (int e = 0; e < 4; ++e) o[e] += oa[e] + ob[e];
+                for (int n2 = 0; n2 < 2; ++n2) {
+                    const float p0 = s[n2][0] == -FLT_MAX ? 0.f : expf(s[n2][0] - mn_lo);
+                    const float p1 = s[n2][1] == -FLT_MAX ? 0.f : expf(s[n2][1] - mn_lo);
+                    const float p2 = s[n2][2] == -FLT_MAX ? 0.f : expf(s[n2][2] - mn_hi);
+                    const float p3 = s[n2][3] == -FLT_MAX ? 0.f : expf(s[n2][3] - mn_hi);
+                    sum_lo += p0 + p1;
+                    sum_hi += p2 + p3;
+                    pf[n2 * 2 + 0] = pack_bf16(p0, p1);
+                    pf[n2 * 2 + 1] = pack_bf16(p2, p3);
+                }
+                sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 1);
+                sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 2);
+                sum_hi += __shfl_xor_sync(0xffffffffu, sum_hi, 1);
+                sum_hi += __shfl_xor_sync(0xffffffffu, sum_hi, 2);
+                l_lo = l_lo * c_lo + sum_lo;
+                l_hi = l_hi * c_hi + sum_hi;
+                m_lo = mn_lo;
+                m_hi = mn_hi;
+                // O = O * corr + P V : V[token][col] is read transposed
+#pragma unroll
+                for (int ct = 0; ct < 16; ct += 2) {
+                    if (ct * 8 < hd) {
+                        uint32_t vb[4];
+                        ldsm_x4_trans(vb, smem_u32(sm.v + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ld + ct * 8 + (lane >> 4) * 8));
+                        o[ct][0] *= c_lo; o[ct][1] *= c_lo; o[ct][2] *= c_hi; o[ct][3] *= c_hi;
+                        o[ct + 1][0] *= c_lo; o[ct + 1][1] *= c_lo; o[ct + 1][2] *= c_hi; o[ct + 1][3] *= c_hi;
+                        mma_bf16(o[ct], pf[0], pf[1], pf[2], pf[3], vb[0], vb[1]);
+                        mma_bf16(o[ct + 1], pf[0], pf[1], pf[2], pf[3], vb[2], vb[3]);
+                    }
+                }
             }
             __syncthreads();  // the V buffer is free
             if (has_next)
                 attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), false, true);
             if (tr) tr[7] = clock64();  // softmax + P.V done
         }
-        // lane groups of a warp hold different tokens of the same four columns: add them (fixed order)
-        for (int off = pv_lpg; off < 32; off <<= 1) {
+        // merge the four token slices (fixed order) through shared memory: the K/V tile buffers are free now
+        float* mo = reinterpret_cast<float*>(sm.k);  // [4 warps][16 heads][hd] fp32  (<= the two tile buffers)
+        float* mm = sm.s;                            // [4][16] maxima, then [4][16] sums
+        if (warp < 4) {
+            if (t4 == 0) {
+                mm[warp * 16 + g] = m_lo; mm[warp * 16 + g + 8] = m_hi;
+                mm[64 + warp * 16 + g] = l_lo; mm[64 + warp * 16 + g + 8] = l_hi;
+            }
 #pragma unroll
-            for (int e = 0; e < 4; ++e) o[e] += __shfl_xor_sync(0xffffffffu, o[e], off);
-        }
-        // sum the token slices of a head in fixed order (through the score buffer, free now), slice 0 stores
-        if (n_sl > 1) {
-            float* red = sm.q;  // [Gq][hd] fp32, free after the last tile's scores; slices 1.. add in turn
-            for (int k2 = 1; k2 < n_sl; ++k2) {
-                if (pv_warp && sl == k2 && pv_gi == 0)
-                    *reinterpret_cast<float4*>(red + hw * hd + pv_c4) = make_float4(o[0], o[1], o[2], o[3]);
-                __syncthreads();
-                if (pv_warp && sl == 0 && pv_gi == 0) {
-                    const float4 v = *reinterpret_cast<const float4*>(red + hw * hd + pv_c4);
-                    o[0] += v.x; o[1] += v.y; o[2] += v.z; o[3] += v.w;
+            for (int ct = 0; ct < 16; ++ct) {
+                if (ct * 8 < hd) {
+                    float* d = mo + ((size_t)warp * 16 + g) * hd + ct * 8 + 2 * t4;
+                    d[0] = o[ct][0]; d[1] = o[ct][1];
+                    d[8 * hd] = o[ct][2]; d[8 * hd + 1] = o[ct][3];
                 }
-                __syncthreads();
             }
         }
-        if (warp < Gq) {  // slice 0 of head `warp` (hw == warp, sl == 0)
-            const size_t pidx = ((size_t)a.r * H + a.kvh * Gq + warp) * S + a.split;
-            if (pv_gi == 0) *reinterpret_cast<float4*>(p.part_o + pidx * hd + pv_c4) = make_float4(o[0], o[1], o[2], o[3]);
-            if (lane == 0) {
-                p.part_ml[pidx * 2 + 0] = m;
-                p.part_ml[pidx * 2 + 1] = l;
+        __syncthreads();
+        for (int i = threadIdx.x; i < (Gq * hd) >> 2; i += kThreads) {  // four columns of one head per thread
+            const int hq = (i * 4) / hd, c = i * 4 - hq * hd;
+            float M = -FLT_MAX;
+#pragma unroll
+            for (int w = 0; w < 4; ++w) M = fmaxf(M, mm[w * 16 + hq]);
+            float Lsum = 0.f;
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int w = 0; w < 4; ++w) {
+                const float mw = mm[w * 16 + hq];
+                const float e = mw == -FLT_MAX ? 0.f : expf(mw - M);
+                Lsum = fmaf(mm[64 + w * 16 + hq], e, Lsum);
+                const float4 v = *reinterpret_cast<const float4*>(mo + ((size_t)w * 16 + hq) * hd + c);
+                acc.x = fmaf(v.x, e, acc.x); acc.y = fmaf(v.y, e, acc.y); acc.z = fmaf(v.z, e, acc.z); acc.w = fmaf(v.w, e, acc.w);
+            }
+            const size_t pidx = ((size_t)a.r * H + a.kvh * Gq + hq) * S + a.split;
+            *reinterpret_cast<float4*>(p.part_o + pidx * hd + c) = acc;
+            if (c == 0) {
+                p.part_ml[pidx * 2 + 0] = M;
+                p.part_ml[pidx * 2 + 1] = Lsum;
             }
         }
         // The last unit of this (row, KV head) to finish -- atomic ticket -- merges the splits and writes the bf16
@@ -735,10 +784,16 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 
 // ---- the kernel ----------------------------------------------------------------------------------------
 
+// the query buffer of the attention phase: 16 bf16 rows (the MMA's M side) during the tiles, fp32 scratch afterwards
+__host__ __device__ inline size_t mk_attn_q_bytes(int head_dim) {
+    const size_t rows16 = (size_t)16 * (head_dim + 8) * 2, f32 = (size_t)kMaxGq * head_dim * 4;
+    return rows16 > f32 ? rows16 : f32;
+}
+
 // shared region that holds the staged input rows (weight phases) or the attention tiles (attention phase)
 __host__ __device__ inline size_t mk_rows_region_bytes(const MkParams& p) {
     const size_t rows = (size_t)p.n_rows * (p.k_max + 8) * 2;
-    const size_t attn = (size_t)2 * kTT * (p.head_dim + 8) * 2 + (size_t)kMaxGq * kTT * 4 + (size_t)kMaxGq * p.head_dim * 4;
+    const size_t attn = (size_t)2 * kTT * (p.head_dim + 8) * 2 + (size_t)kMaxGq * kTT * 4 + mk_attn_q_bytes(p.head_dim);
     return ((rows > attn ? rows : attn) + 127) / 128 * 128;
 }
 
