@@ -677,9 +677,9 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 #pragma unroll
             for (int ct = 0; ct < 16; ++ct) {
                 if (ct * 8 < hd) {
-                    float* d = mo + ((size_t)warp * 16 + g) * hd + ct * 8 + 2 * t4;
-                    d[0] = o[ct][0]; d[1] = o[ct][1];
-                    d[8 * hd] = o[ct][2]; d[8 * hd + 1] = o[ct][3];
+                    float* d = mo + ((size_t)warp * 16 + g) * hd + ct * 8 + 2 * t4;  // rows past Gq are padding
+                    if (g < Gq) *reinterpret_cast<float2*>(d) = make_float2(o[ct][0], o[ct][1]);
+                    if (g + 8 < Gq) *reinterpret_cast<float2*>(d + 8 * hd) = make_float2(o[ct][2], o[ct][3]);
                 }
             }
         }
