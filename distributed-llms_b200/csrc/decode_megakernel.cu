@@ -11,11 +11,16 @@
 //   * the dot products run on the tensor cores as a swap-AB skinny GEMM (mma.sync m16n8k16: M = batch rows,
 //     N = the 8 weight rows of a panel), which removes the bf16->fp32 unpack / FMA instruction stream that
 //     made the first version issue-bound; accumulation is fp32;
-//   * warps of a CTA that share a panel split K; partials are summed in a fixed order in shared memory
-//     (deterministic), then one thread per (row pair, batch row) runs the fused epilogue;
-//   * activations (a few KB) move between phases through L2 (ld.global.cg); old K/V tiles are prefetched with
-//     cp.async before the barrier that precedes attention.
-// Rounding points are those of the per-op kernels in decode_gemv.cu / attention.cu.
+//   * a CTA's panels are processed in rounds; the stages of a round are cut into equal per-warp chunks, the pieces
+//     of a panel are summed in a fixed order in shared memory (deterministic), then one thread per (row pair,
+//     batch row) runs the fused epilogue;
+//   * attention: one unit per (row, KV head, split); the group's query heads are the 16 rows of mma.sync, K/V
+//     tiles arrive through cp.async one tile ahead (the first one before the barrier that precedes the phase),
+//     the last unit of a (row, KV head) merges the splits;
+//   * activations (a few KB) move between phases through L2 (ld.global.cg);
+//   * optional fused hand-off: the last down projection also stores its rows into the next stage's mailbox
+//     (peer memory) and tickets replace kernel boundaries between pipeline stages (megakernel.h).
+// Rounding points are those of the per-op kernels in decode_gemv.cu / attention_gqa.cu.
 #include <float.h>
 #include <stdlib.h>
 #include <limits.h>
@@ -33,7 +38,7 @@ constexpr int kWarps = MK_THREADS / 32;
 constexpr int kStageBytes = MK_STAGE_BYTES;
 constexpr int kStageK = MK_STAGE_K;
 constexpr int kTT = 64;     // tokens per attention tile
-constexpr int kMaxGq = 8;   // query heads per KV head handled by one CTA (one warp each)
+constexpr int kMaxGq = 8;   // query heads per KV head handled by one attention unit
 constexpr int kMaxSplits = MK_MAX_SPLITS;
 constexpr int kPartStride = 8 * MK_MAX_ROWS;  // floats per unit in the partial buffer: [8 panel rows][16 batch]
 
