@@ -63,6 +63,30 @@ def stage_bytes_per_step(hf: dict, n_layers: int, has_head: bool, batch: int, ct
     return float(total)
 
 
+def stage_prefill_flops(hf: dict, n_layers: int, has_head: bool, batch: int, T: int) -> float:
+    """Algorithmic flops of one prefill of `batch` prompts of T tokens through one stage: the dense
+    projections, causal attention (half of T^2), and the lm_head for the last position of every prompt."""
+    d = hf.get("hidden_size", hf.get("n_embd"))
+    H = hf.get("num_attention_heads", hf.get("n_head"))
+    KV = hf.get("num_key_value_heads", H)
+    hd = hf.get("head_dim") or d // H
+    ffn = hf.get("intermediate_size", hf.get("n_inner") or 4 * d)
+    g = 2 if hf["model_type"] == "gpt2" else 3
+    w = d * H * hd + 2 * d * KV * hd + H * hd * d + g * d * ffn
+    per_layer = 2.0 * T * w + 4.0 * T * T * H * hd / 2.0
+    total = batch * n_layers * per_layer
+    if has_head:
+        total += batch * 2.0 * hf["vocab_size"] * d
+    return total
+
+
+def prefill_roofline(flops: float, ms: float) -> dict:
+    """Prefill is bound by the bf16 tensor cores: achieved TFLOP/s against the measured sustained cuBLAS figure."""
+    _, tf_peak, kind = load_peaks()
+    ach = flops / (ms * 1e-3) / 1e12
+    return {"bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s", "frac": ach / tf_peak, "peak_kind": kind}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
@@ -320,7 +344,8 @@ def run_single(args) -> int:
         "roofline": roofline,
         "cpu_baseline": cpu,
         "prefill": {"tokens_per_sec": batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
-                    "note": "one chunk: tcgen05/TMA GEMMs for the projections, flash-style causal attention (mma.sync) over the paged cache"},
+                    "roofline": prefill_roofline(stage_prefill_flops(hf, L, True, batch, prompt_len), prefill_ms),
+                    "note": "tcgen05/TMA GEMMs for the projections, flash-style causal attention (mma.sync) over the paged cache"},
     }
     print(json.dumps(line))
     return 0

@@ -12,7 +12,8 @@ import os
 import torch
 import torch.distributed as dist
 
-from bench import METRIC, UNIT, WORKLOADS, ClockSampler, load_peaks, stage_bytes_per_step, workload_name
+from bench import (METRIC, UNIT, WORKLOADS, ClockSampler, load_peaks, prefill_roofline, stage_bytes_per_step,
+                   stage_prefill_flops, workload_name)
 
 
 def run_pipeline(args) -> int:
@@ -224,6 +225,10 @@ def run_pipeline(args) -> int:
             "nccl_handoff": {"value": n_micro * batch * K / (nccl_ms * 1e-3), "unit": UNIT, "ms_per_step": nccl_ms / K,
                              "note": "same schedule, one launch per micro-batch step, NCCL send/recv + token ring"},
             "prefill": {"tokens_per_sec": n_micro * batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
+                        # the busiest stage's flops for all micro-batches over the whole (pipelined) prefill time:
+                        # includes the fill and drain bubbles of the (stages + micro-batches - 1)-slot schedule
+                        "roofline": prefill_roofline(n_micro * stage_prefill_flops(hf, max(len(r) for r in partition), False,
+                                                                                  batch, prompt_len), prefill_ms),
                         "note": "micro-batches follow each other through the stages; tcgen05 GEMMs + flash-style attention per stage"},
         }
         print(json.dumps(line))
