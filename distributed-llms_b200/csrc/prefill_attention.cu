@@ -8,6 +8,7 @@
 // (The dense projections around it are the tcgen05 GEMMs of prefill_gemm.cu; attention is ~2 % of the prefill
 // flops at these lengths, so it uses the simpler warp-level tensor-core path for now.)
 #include <float.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -16,7 +17,7 @@ namespace dllm {
 
 namespace {
 
-constexpr int kQT = 64, kKT = 64, kThreads = 128;
+constexpr int kKT = 64;  // keys per tile; the query tile QT is 64 rows (4 warps) or, for long prompts, 128 rows (8 warps)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
@@ -43,8 +44,9 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
-template <int HD>
-__global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAttnParams p) {
+template <int HD, int kQT>
+__global__ void __launch_bounds__(kQT * 2) prefill_attn_kernel(const PrefillAttnParams p) {
+    constexpr int kThreads = kQT * 2;  // one warp per 16 query rows
     constexpr int LD = HD + 8;  // padded rows: ldmatrix reads 8 rows x 16 bytes without bank conflicts
     extern __shared__ __align__(16) unsigned char smem_dyn[];
     bf16* sQ = reinterpret_cast<bf16*>(smem_dyn);
@@ -212,24 +214,31 @@ __global__ void __launch_bounds__(kThreads) prefill_attn_kernel(const PrefillAtt
 
 }  // namespace
 
-cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {
-    if (p.n_seqs <= 0 || p.rows_per_seq <= 0 || p.n_heads % p.n_kv_heads) return cudaErrorInvalidValue;
-    dim3 grid((p.rows_per_seq + kQT - 1) / kQT, p.n_heads, p.n_seqs);
-    const size_t smem = (size_t)(kQT + 4 * kKT) * (p.head_dim + 8) * 2;
+template <int HD, int QT>
+static cudaError_t launch_attn_t(const PrefillAttnParams& p, cudaStream_t st) {
+    const size_t smem = (size_t)(QT + 4 * kKT) * (HD + 8) * 2;
     static PerDeviceOnce attr_once;
     if (attr_once.need()) {
-        cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)((kQT + 4 * kKT) * (128 + 8) * 2));
+        cudaError_t e = cudaFuncSetAttribute(prefill_attn_kernel<HD, QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
-    switch (p.head_dim) {
-        case 32: prefill_attn_kernel<32><<<grid, kThreads, smem, st>>>(p); break;
-        case 64: prefill_attn_kernel<64><<<grid, kThreads, smem, st>>>(p); break;
-        case 128: prefill_attn_kernel<128><<<grid, kThreads, smem, st>>>(p); break;
-        default: return cudaErrorInvalidValue;
-    }
+    dim3 grid((p.rows_per_seq + QT - 1) / QT, p.n_heads, p.n_seqs);
+    prefill_attn_kernel<HD, QT><<<grid, QT * 2, smem, st>>>(p);
     count_launch();
     return cudaGetLastError();
+}
+
+cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {
+    if (p.n_seqs <= 0 || p.rows_per_seq <= 0 || p.n_heads % p.n_kv_heads) return cudaErrorInvalidValue;
+    // 128-row query tiles (8 warps share each K/V tile) once there are enough of them to fill the GPU
+    const char* env = getenv("DLLM_PREFILL_QT128");  // "0": never, "1": always (tests), unset: by grid size
+    const bool big = env ? env[0] == '1' : (long)((p.rows_per_seq + 127) / 128) * p.n_heads * p.n_seqs >= 296;
+    switch (p.head_dim) {
+        case 32: return launch_attn_t<32, 64>(p, st);
+        case 64: return big ? launch_attn_t<64, 128>(p, st) : launch_attn_t<64, 64>(p, st);
+        case 128: return big ? launch_attn_t<128, 128>(p, st) : launch_attn_t<128, 64>(p, st);
+    }
+    return cudaErrorInvalidValue;
 }
 
 }  // namespace dllm

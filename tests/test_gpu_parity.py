@@ -442,10 +442,12 @@ def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, arch):
         box.close()
 
 
+@pytest.mark.parametrize("qt128", ["0", "1"])
 @pytest.mark.parametrize("batch,prompt_len", [(1, 1300), (2, 2100)])
-def test_long_context_decode_matches_oracle(batch, prompt_len):
+def test_long_context_decode_matches_oracle(batch, prompt_len, qt128, monkeypatch):
     """Contexts beyond 64 tokens x 16 splits: every attention unit of the persistent kernel walks several K/V tiles
     (online softmax across tiles, merge across splits); chunked flash-style prefill before it.  bf16 vs the oracle."""
+    monkeypatch.setenv("DLLM_PREFILL_QT128", qt128)  # both query-tile sizes of the prefill attention kernel
     cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 2304, 1e-5, 10000.0)
     sd = make_state_dict(cfg, 11, torch.float32, init="full")
     prompts = make_prompts(cfg.vocab, batch, prompt_len, seed=9)
