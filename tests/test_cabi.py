@@ -72,6 +72,23 @@ def test_compute_fails_loudly_without_gpu():
     assert rc != 0 and b"no CUDA device" in lib.dllm_last_error() and not h.value
 
 
+def test_mailboxes_fail_loudly_without_gpu_and_reject_bad_shapes():
+    """The fused hand-off has no host stand-in either: no device -> error; shapes are checked before any CUDA call."""
+    import pytest
+    from src.network.handoff import Mailbox
+    lib = cabi.lib()
+    h = ctypes.c_void_p()
+    assert lib.dllm_mailbox_create(0, 0, 1, 64, ctypes.byref(h)) != 0 and b"bad shape" in lib.dllm_last_error()
+    assert lib.dllm_mailbox_create(0, 1, 17, 64, ctypes.byref(h)) != 0      # more rows than the persistent kernel takes
+    assert lib.dllm_mailbox_create(0, 1, 1, 60, ctypes.byref(h)) != 0       # hidden must be a multiple of 8
+    assert lib.dllm_mailbox_create(0, 2, 1, 64, ctypes.byref(h)) != 0 and b"no CUDA device" in lib.dllm_last_error()
+    assert not h.value
+    with pytest.raises(cabi.DllmError):
+        Mailbox.create(0, 2, 1, 64)
+    assert lib.dllm_shard_decode_pipelined(None, None, None, 1, 1, 1, 0, None, None, None, None) != 0
+    assert lib.dllm_mailbox_destroy(None) == 0
+
+
 def test_create_rejects_bad_geometry():
     lib = cabi.lib()
     cfg = cabi.ShardConfig(arch=1, dtype=0, hidden=64, n_heads=3, n_kv_heads=2, head_dim=48, ffn=64, vocab=16,
