@@ -148,12 +148,20 @@ class MasterNode:
             self.shard_assignments.setdefault(workers[i % len(workers)], []).append(i)
         return self.shard_assignments
 
-    def distribute_shards(self, wait: bool = True, timeout: float = 600.0):
+    def distribute_shards(self, wait: bool = True, timeout: float = 600.0, by_path: bool = False):
+        """Give every worker its shards.  `by_path`: the workers can read the model directory themselves (same box or a
+        shared file system) -- they are told where it is and load only their stage; otherwise the shard files travel
+        as messages like in the reference (:106-115)."""
         shard_paths = self.shard_manager.get_shard_paths()
         wanted = set()
         for worker_id, shard_ids in self.shard_assignments.items():
             for shard_id in shard_ids:
-                self._send_shard(self.workers[worker_id], shard_id, shard_paths[shard_id])
+                if by_path:
+                    self._send(self.workers[worker_id], "LOAD_SHARD_FROM_PATH", None,
+                               {"shard_id": shard_id, "model_path": os.path.abspath(self.model_path),
+                                "num_shards": self.shard_manager.num_shards, "shard_file": os.path.abspath(shard_paths[shard_id])})
+                else:
+                    self._send_shard(self.workers[worker_id], shard_id, shard_paths[shard_id])
                 wanted.add(shard_id)
         if wait:
             deadline = time.time() + timeout

@@ -92,6 +92,69 @@ def partition_state_dict(state_dict: Dict[str, torch.Tensor], num_shards: int, t
     return shards
 
 
+def _stage_of_key(key: str, owner: Dict[int, int], num_shards: int) -> int:
+    """Stage that owns a (prefix-stripped) checkpoint key; -1 for HF buffers that are not parameters."""
+    m = _LAYER_RE.match(key)
+    if m:
+        return owner[int(m.group(2))]
+    if key in ("wte.weight", "wpe.weight", "embed_tokens.weight"):
+        return 0
+    if key.endswith(("attn.bias", "attn.masked_bias", "rotary_emb.inv_freq")):
+        return -1
+    return num_shards - 1
+
+
+def load_stage_from_safetensors(model_path: str, shard_id: int, num_shards: int, dtype: torch.dtype = None
+                                ) -> Dict[str, torch.Tensor]:
+    """Read ONLY the tensors of stage `shard_id` from `model.safetensors` (or the files listed in
+    `model.safetensors.index.json`) -- a worker that can see the checkpoint loads its stage from disk instead of
+    receiving it as one message (reference src/master/node.py:213-225 ships whole `shard_i.pt` files of 7-17 GB).
+    Same partition and key names as `partition_state_dict`; the model config rides along under ``"__config__"``."""
+    from safetensors import safe_open
+    index = os.path.join(model_path, "model.safetensors.index.json")
+    if os.path.exists(index):
+        with open(index, "r") as f:
+            weight_map = json.load(f)["weight_map"]           # checkpoint key -> file
+    else:
+        single = os.path.join(model_path, "model.safetensors")
+        if not os.path.exists(single):
+            raise FileNotFoundError(f"no model.safetensors(.index.json) under {model_path}")
+        with safe_open(single, framework="pt", device="cpu") as f:
+            weight_map = {k: "model.safetensors" for k in f.keys()}
+    with open(os.path.join(model_path, "config.json"), "r") as f:
+        config = json.load(f)
+    stripped = {k: strip_prefix(k) for k in weight_map}
+    layer_ids = sorted({int(m.group(2)) for m in map(_LAYER_RE.match, stripped.values()) if m})
+    if not layer_ids:
+        raise ValueError("the checkpoint has no decoder layers (h.N.* / layers.N.*)")
+    owner = {}
+    for s, rng in enumerate(contiguous_partition(len(layer_ids), num_shards)):
+        for j in rng:
+            owner[layer_ids[j]] = s
+    wanted = {k: sk for k, sk in stripped.items() if _stage_of_key(sk, owner, num_shards) == shard_id}
+    tied = bool(config.get("tie_word_embeddings", config.get("model_type") == "gpt2"))
+    emb_key = next((k for k, sk in stripped.items() if sk in ("wte.weight", "embed_tokens.weight")), None)
+    need_tied_head = (shard_id == num_shards - 1 and "lm_head.weight" not in stripped.values() and emb_key is not None
+                      and (tied or stripped[emb_key] == "wte.weight"))
+    by_file: Dict[str, list] = {}
+    for k in wanted:
+        by_file.setdefault(weight_map[k], []).append(k)
+    if need_tied_head:
+        by_file.setdefault(weight_map[emb_key], [])
+    out: Dict[str, torch.Tensor] = {}
+    for fname, keys in by_file.items():
+        with safe_open(os.path.join(model_path, fname), framework="pt", device="cpu") as f:
+            for k in keys:
+                t = f.get_tensor(k)
+                out[wanted[k]] = t.to(dtype) if dtype is not None and t.is_floating_point() else t
+            if need_tied_head and fname == weight_map[emb_key]:
+                t = f.get_tensor(emb_key)  # tied head: the last stage needs its own copy of the embedding matrix
+                out["lm_head.weight"] = t.to(dtype) if dtype is not None else t
+    if config.get("model_type") in ("gpt2", "llama", "qwen2"):
+        out[CONFIG_KEY] = encode_config(config)
+    return out
+
+
 class ModelShardManager:
     def __init__(self, model_path: str, num_shards: int):
         self.model_path = model_path

@@ -353,6 +353,11 @@ class WorkerNode:
             shard_id = header.get("shard_id")
             ok = self.load_shard(shard_id, payload)
             protocol.send_message(sock, "SHARD_LOADED", metadata={"shard_id": shard_id, "ok": ok})
+        elif command == "LOAD_SHARD_FROM_PATH":  # same box / shared file system: read the stage, do not receive it
+            shard_id = header.get("shard_id")
+            ok = self.load_shard_from_path(shard_id, header.get("model_path"), int(header.get("num_shards", 1)),
+                                           header.get("shard_file"))
+            protocol.send_message(sock, "SHARD_LOADED", metadata={"shard_id": shard_id, "ok": ok})
         elif command == "UNLOAD_SHARD":
             shard_id = header.get("shard_id")
             self.unload_shard(shard_id)
@@ -395,6 +400,28 @@ class WorkerNode:
             return True
         except Exception as e:
             print(f"Error loading shard {shard_id}: {e}")
+            return False
+
+    def load_shard_from_path(self, shard_id: int, model_path: str, num_shards: int, shard_file: Optional[str] = None) -> bool:
+        """Load stage `shard_id` of `num_shards` from disk: only its tensors out of `model.safetensors` (or the files of
+        the index), else the shard file the master wrote.  The reference ships every shard as one message
+        (src/master/node.py:213-225), 7-17 GB per stage at the BASELINE sizes."""
+        from ..model.shard_manager import load_stage_from_safetensors
+        try:
+            dtype = torch.bfloat16 if torch.cuda.is_available() else None
+            try:
+                parameters = load_stage_from_safetensors(model_path, shard_id, num_shards, dtype)
+            except FileNotFoundError:
+                if not shard_file or not os.path.exists(shard_file):
+                    raise
+                parameters = torch.load(shard_file, map_location="cpu", weights_only=True, mmap=True)
+            shard = ModelShard(shard_id, parameters)
+            shard.to_device()
+            with self._shards_lock:
+                self.shards[shard_id] = shard
+            return True
+        except Exception as e:
+            print(f"Error loading shard {shard_id} from {model_path}: {e}")
             return False
 
     def unload_shard(self, shard_id: int) -> bool:

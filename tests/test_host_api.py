@@ -232,3 +232,57 @@ def test_balanced_partition_accounts_for_the_head():
     assert balanced_partition(32, 1, 2.4) == contiguous_partition(32, 1)
     assert balanced_partition(12, 4, 0.0) == contiguous_partition(12, 4)
     assert [len(r) for r in balanced_partition(4, 4, 5.0)] == [1, 1, 1, 1]
+
+
+def _tiny_checkpoint(tmp_path, model_type, sharded):
+    """A small safetensors checkpoint with HF key prefixes (one file, or two files + index)."""
+    import json as _json
+    from safetensors.torch import save_file
+    from src.model import random_init
+    if model_type == "llama":
+        cfg = dict(model_type="llama", hidden_size=64, num_hidden_layers=5, num_attention_heads=4, num_key_value_heads=2,
+                   intermediate_size=128, vocab_size=50, max_position_embeddings=32, rms_norm_eps=1e-5, rope_theta=10000.0)
+        sd = random_init.random_stage_parameters(cfg, range(5), True, True, 1, torch.float32, init="full")
+        full = {("model." + k if k != "lm_head.weight" else k): v.contiguous() for k, v in sd.items()}
+    else:
+        cfg = dict(model_type="gpt2", n_embd=64, n_layer=4, n_head=4, n_inner=256, vocab_size=50, n_positions=32,
+                   layer_norm_epsilon=1e-5, tie_word_embeddings=True)
+        sd = random_init.random_stage_parameters(cfg, range(4), True, True, 1, torch.float32, init="full")
+        sd.pop("lm_head.weight", None)  # tied: the checkpoint holds the embedding only
+        full = {"transformer." + k: v.contiguous() for k, v in sd.items()}
+    d = str(tmp_path / f"ckpt_{model_type}_{int(sharded)}")
+    os.makedirs(d, exist_ok=True)
+    if sharded:
+        keys = sorted(full)
+        half = len(keys) // 2
+        files = {"model-00001-of-00002.safetensors": keys[:half], "model-00002-of-00002.safetensors": keys[half:]}
+        for fname, ks in files.items():
+            save_file({k: full[k] for k in ks}, os.path.join(d, fname))
+        with open(os.path.join(d, "model.safetensors.index.json"), "w") as f:
+            _json.dump({"weight_map": {k: fname for fname, ks in files.items() for k in ks}}, f)
+    else:
+        save_file(full, os.path.join(d, "model.safetensors"))
+    with open(os.path.join(d, "config.json"), "w") as f:
+        _json.dump(cfg, f)
+    return d, cfg, full
+
+
+@pytest.mark.parametrize("model_type", ["llama", "gpt2"])
+@pytest.mark.parametrize("sharded", [False, True])
+def test_stage_loader_reads_exactly_the_partition(tmp_path, model_type, sharded):
+    """`load_stage_from_safetensors` gives each stage the tensors `partition_state_dict` gives it (one file or an
+    index of files; a tied head is materialised on the last stage), without reading the other stages' tensors."""
+    from src.engine.shard_exec import CONFIG_KEY, decode_config
+    from src.model.shard_manager import load_stage_from_safetensors, partition_state_dict
+    d, cfg, full = _tiny_checkpoint(tmp_path, model_type, sharded)
+    for n in (1, 2, 3):
+        want = partition_state_dict(full, n, tie_head=bool(cfg.get("tie_word_embeddings", False)))
+        for i in range(n):
+            got = load_stage_from_safetensors(d, i, n)
+            assert decode_config(got.pop(CONFIG_KEY)) == cfg
+            assert set(got) == set(want[i])
+            assert all(torch.equal(got[k], want[i][k]) for k in got)
+    bf = load_stage_from_safetensors(d, 0, 2, torch.bfloat16)
+    assert all(v.dtype == torch.bfloat16 for k, v in bf.items() if k != CONFIG_KEY)
+    with pytest.raises(FileNotFoundError):
+        load_stage_from_safetensors(str(tmp_path), 0, 2)

@@ -70,6 +70,33 @@ def test_register_assign_distribute_and_errors(tmp_path):
         _shutdown(master, workers)
 
 
+def test_workers_load_their_stage_from_the_model_directory(tmp_path):
+    """`distribute_shards(by_path=True)`: the master sends a path, every worker reads only its own stage -- from
+    `model.safetensors` when there is one, else from the shard file the master wrote."""
+    from safetensors.torch import save_file
+    d, sd = _model_dir(tmp_path, torch.float32)
+    master, workers = _cluster(2)
+    try:
+        master.initialize_model(d, num_shards=2)      # pytorch_model.bin only: workers fall back to shards/shard_i.pt
+        master.assign_shards()
+        master.distribute_shards(timeout=60, by_path=True)
+        assert all(len(w.shards) == 1 for w in workers)
+        assert "embed_tokens.weight" in workers[0].shards[0].parameters and "lm_head.weight" in workers[1].shards[1].parameters
+        for w in workers:
+            for sid in list(w.shards):
+                w.unload_shard(sid)
+        master._loaded_shards.clear()
+        full = torch.load(os.path.join(d, "pytorch_model.bin"), weights_only=True)
+        save_file({k: v.contiguous() for k, v in full.items()}, os.path.join(d, "model.safetensors"))
+        os.remove(os.path.join(d, "pytorch_model.bin"))
+        master.distribute_shards(timeout=60, by_path=True)   # now straight from model.safetensors, stage by stage
+        got = workers[1].shards[1].parameters
+        assert torch.equal(got["lm_head.weight"].float().cpu(), sd["lm_head.weight"].float())
+        assert not any(k.startswith("layers.0.") for k in got) and any(k.startswith("layers.3.") for k in got)
+    finally:
+        _shutdown(master, workers)
+
+
 def test_no_workers_and_heartbeat_eviction():
     master = MasterNode(host="127.0.0.1", port=0)
     master.start()
