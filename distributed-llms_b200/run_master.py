@@ -17,6 +17,8 @@ def main():
     ap.add_argument("--model", default="random:gpt2-small", help="local dir, random:<name> or a Hub id")
     ap.add_argument("--shards", type=int, default=2)
     ap.add_argument("--cache-dir", default="./models")
+    ap.add_argument("--by-path", action="store_true",
+                    help="workers read their stage from the model directory (same box / shared file system) instead of receiving it")
     a = ap.parse_args()
     master = MasterNode(host=a.host, port=a.port)
     master.start()
@@ -29,7 +31,7 @@ def main():
             if cmd == "assign":
                 print(f"Shard assignments: {master.assign_shards()}")
             elif cmd == "distribute":
-                master.distribute_shards()
+                master.distribute_shards(by_path=a.by_path)
                 print("Shards distributed to workers")
             elif cmd == "inference":
                 text = input("Enter text (or space-separated token ids) for inference: ")
