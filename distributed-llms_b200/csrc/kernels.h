@@ -102,6 +102,7 @@ struct RopeAppendParams {
     int32_t n_rows, n_heads, n_kv_heads, head_dim, rope;
 };
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st);
+bool gemm_swapab_enabled();  // false under DLLM_GEMM_SWAPAB=0: M <= 64 then takes the 128-row tiles, LOGITS is unavailable
 cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
                              cudaStream_t st, const int32_t* row_map = nullptr);  // y[r] = norm(x[row_map ? row_map[r] : r])
 // next_token[r] = lowest index of the maximum of logits[r, 0..n) (fp32 rows of stride n)

@@ -710,12 +710,14 @@ cudaError_t launch_swapab_rows(const GemmTcParams& p, cudaStream_t st) {
     return launch_swapab<EPI, 64>(p, st);
 }
 
-bool small_m(const GemmTcParams& p) {
-    static const bool off = [] { const char* e = getenv("DLLM_GEMM_SWAPAB"); return e && e[0] == '0'; }();
-    return !off && p.M <= 64;
-}
+bool small_m(const GemmTcParams& p) { return gemm_swapab_enabled() && p.M <= 64; }
 
 }  // namespace
+
+bool gemm_swapab_enabled() {
+    static const bool off = [] { const char* e = getenv("DLLM_GEMM_SWAPAB"); return e && e[0] == '0'; }();
+    return !off;
+}
 
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
     if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || (p.ldc % 2 && p.epi != GEMM_EPI_LOGITS)) return cudaErrorInvalidValue;

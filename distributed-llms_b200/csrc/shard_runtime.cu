@@ -664,7 +664,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
             CUDA_TRY(launch_gemm_tc(g, st));
         }
     }
-    if (c.has_head && n_logit_rows > 4 && n_logit_rows <= 64 && c.hidden <= 16384) {
+    if (c.has_head && n_logit_rows > 4 && n_logit_rows <= 64 && c.hidden <= 16384 && gemm_swapab_enabled()) {
         // lm_head for 5..64 rows: final norm of the wanted rows -> swap-AB GEMM (one pass over the head) -> argmax
         CUDA_TRY(launch_norm_rows(s->h, s->io.final_norm_w, s->io.final_norm_b, s->xn, n_logit_rows, c.hidden, norm,
                                   c.norm_eps, st, s->logit_rows));

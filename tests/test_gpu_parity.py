@@ -405,6 +405,8 @@ def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, arch):
     """One stage, its own mailbox as in- and outbox: the persistent kernel feeds the token ids round through the
     mailbox tickets.  Every micro-batch must reproduce, bit for bit, what the classic device loop generates."""
     from src.network.handoff import Mailbox
+    if os.environ.get("DLLM_MEGAKERNEL") == "0":
+        pytest.skip("the fused hand-off lives in the persistent kernel")
     if arch == "llama":
         cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
     else:
