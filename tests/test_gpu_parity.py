@@ -121,7 +121,9 @@ def _paged_kv(lens, KV, hd, page, dtype, gen):
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("H,KV,hd,splits,lens", [(4, 2, 64, 3, [5, 70]), (8, 1, 128, 8, [200, 1, 33]), (4, 4, 32, 1, [17]),
-                                                 (32, 4, 64, 16, [512]), (5, 1, 64, 64, [40, 41])])
+                                                 (32, 4, 64, 16, [512]), (5, 1, 64, 64, [40, 41]),
+                                                 (10, 2, 128, 2, [65, 129, 64]), (16, 1, 64, 4, [300, 63]),
+                                                 (7, 1, 32, 1, [1, 64, 127]), (40, 8, 128, 3, [257])])
 def test_decode_attention_matches_reference(dtype, H, KV, hd, splits, lens):
     gen = torch.Generator().manual_seed(H * 100 + hd)
     page = 16
