@@ -647,14 +647,16 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
 
 // 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give)
 bool wide_tiles(const GemmTcParams& p) {
-    static const bool off = [] { const char* e = getenv("DLLM_GEMM_BN256"); return e && e[0] == '0'; }();
+    const char* env = getenv("DLLM_GEMM_BN256");  // read per call: the tests compare both tile widths in one process
+    const bool off = env && env[0] == '0';
     if (off || p.epi == GEMM_EPI_SWIGLU || p.N % 256 || p.n_more[0] % 256 || p.n_more[1] % 256) return false;
     return (long)((p.M + BM - 1) / BM) * ((p.N + p.n_more[0] + p.n_more[1]) / 256) >= 148;
 }
 
 // 64-wide tiles when 128-wide ones would leave SMs without a tile (mid-size prompts: M = 256 .. 1024)
 bool narrow_tiles(const GemmTcParams& p) {
-    static const bool off = [] { const char* e = getenv("DLLM_GEMM_BN64"); return e && e[0] == '0'; }();
+    const char* env = getenv("DLLM_GEMM_BN64");
+    const bool off = env && env[0] == '0';
     if (off || p.epi == GEMM_EPI_SWIGLU) return false;
     const long n_all = (long)p.N + p.n_more[0] + p.n_more[1];
     return (long)((p.M + BM - 1) / BM) * ((n_all + 127) / 128) <= 74;  // at most half the SMs would get a 128-wide tile

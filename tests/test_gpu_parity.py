@@ -496,3 +496,21 @@ def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
             outs[mk] = (first["logits"].cpu(), step["logits"].cpu())
         assert torch.equal(outs["1"][0], outs["0"][0])               # same prefill kernels on both sides
         assert bf16_logits_close(outs["1"][1], outs["0"][1]), batch  # decode step: persistent kernel vs per-op kernels
+
+
+def test_prefill_tile_widths_agree_bit_for_bit(monkeypatch):
+    """A 4096-token prefill at Llama-3-8B width takes the 256-wide GEMM tiles (q | k | v as row segments of one
+    launch); with them switched off it takes 128-wide tiles.  Both walk K in the same order, so the logits must be
+    identical -- the tile width is a scheduling choice, not a numerical one.  (No CPU oracle at this size.)"""
+    hf = dict(random_init.NAMED_CONFIGS["llama3-8b"])
+    hf["num_hidden_layers"] = 2
+    params = random_init.random_stage_parameters(hf, range(2), True, True, 5, torch.bfloat16, device="cuda")
+    prompt = make_prompts(hf["vocab_size"], 1, 4096, seed=3)
+    outs = []
+    for bn256 in ("1", "0"):
+        monkeypatch.setenv("DLLM_GEMM_BN256", bn256)
+        sh = ModelShard(0, dict(params), config=hf, max_rows=4096, max_seqs=1, max_context=4160, page_size=64)
+        sh.to_device()
+        outs.append(sh.compute({"input_ids": prompt})["logits"].cpu())
+        del sh
+    assert torch.isfinite(outs[0]).all() and torch.equal(outs[0], outs[1])
