@@ -507,10 +507,12 @@ def test_prefill_tile_widths_agree_bit_for_bit(monkeypatch):
     params = random_init.random_stage_parameters(hf, range(2), True, True, 5, torch.bfloat16, device="cuda")
     prompt = make_prompts(hf["vocab_size"], 1, 4096, seed=3)
     outs = []
-    for bn256 in ("1", "0"):
+    for bn256, qt128 in (("1", None), ("0", None), ("1", "0")):
         monkeypatch.setenv("DLLM_GEMM_BN256", bn256)
+        if qt128 is not None:  # the same for the attention's query tile: 128 rows by default at this size, 64 forced
+            monkeypatch.setenv("DLLM_PREFILL_QT128", qt128)
         sh = ModelShard(0, dict(params), config=hf, max_rows=4096, max_seqs=1, max_context=4160, page_size=64)
         sh.to_device()
         outs.append(sh.compute({"input_ids": prompt})["logits"].cpu())
         del sh
-    assert torch.isfinite(outs[0]).all() and torch.equal(outs[0], outs[1])
+    assert torch.isfinite(outs[0]).all() and torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
