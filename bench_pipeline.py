@@ -12,8 +12,8 @@ import os
 import torch
 import torch.distributed as dist
 
-from bench import (METRIC, UNIT, WORKLOADS, ClockSampler, load_peaks, prefill_roofline, stage_bytes_per_step,
-                   stage_prefill_flops, workload_name)
+from bench import (METRIC, UNIT, WORKLOADS, ClockSampler, load_peaks, make_config, prefill_roofline, stage_bytes_per_step,
+                   stage_prefill_flops)
 
 
 def run_pipeline(args) -> int:
@@ -188,6 +188,80 @@ def run_pipeline(args) -> int:
     e2e_ms = float(ms)
     clocks = sampler.stop() if first else None
 
+    # ---- token check (multi-GPU parity inside the bench): from a fresh prefill, V decode steps through the fused
+    # hand-off and through the NCCL schedule must give the same ids for every micro-batch, and micro-batch 0 must
+    # equal the SAME model run as one stage on rank 0 alone.  A mismatch makes the bench exit non-zero. ----
+    V = 8
+    checked = {"fused_vs_nccl": None, "vs_single_stage": None, "steps": V}
+
+    def fresh_state():
+        shard.reset()
+        toks = prefill_all(7)
+        torch.cuda.synchronize()
+        dist.barrier()
+        return toks
+
+    seq_all = torch.arange(n_micro * batch, dtype=torch.int32).reshape(n_micro, batch)
+    fused_ids = None
+    if fused:
+        toks0 = fresh_state()
+        vin, vout = exchange_mailboxes(rank, world, local, n_micro, batch, d)
+        if first:
+            for m in range(n_micro):
+                vin.post_tokens(m, toks0[m], ticket=1)
+        dist.barrier()
+        fed = ex.decode_pipelined(vin, vout, n_micro, batch, V, 0, torch.full((n_micro, batch), prompt_len, dtype=torch.int32), seq_all)
+        torch.cuda.synchronize()
+        dist.barrier()
+        if first:  # [n_micro, batch, V + 1]: the seed, then the ids generated by steps 0 .. V-1
+            tail = torch.stack([vin.read_tokens(m)[0] for m in range(n_micro)])  # generated by the last step
+            fused_ids = torch.cat([fed.cpu().permute(1, 2, 0), tail[:, :, None]], dim=2)
+        dist.barrier()
+        if vout is not vin:
+            vout.close()
+        dist.barrier()
+        vin.close()
+    toks0 = fresh_state()
+    for m in range(n_micro):
+        stepper.set_positions(m, torch.full((batch,), prompt_len, dtype=torch.int32), reserve_to=max_ctx)
+    got = pipe.decode(toks0 if first else None, V, record=True)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ok = True
+    single_tps = None
+    if first:
+        nccl_ids = torch.cat([torch.stack(toks0).cpu()[:, :, None], got.cpu()], dim=2)  # [n_micro, batch, V + 1]
+        if fused_ids is not None:
+            checked["fused_vs_nccl"] = bool(torch.equal(fused_ids.to(torch.int64), nccl_ids.to(torch.int64)))
+            ok &= checked["fused_vs_nccl"]
+        # the same model as ONE stage on this GPU: the ids of micro-batch 0, and the single-GPU tokens/s of this very
+        # model (the driver's scaling table divides by the N=1 bench, which times a different, smaller model)
+        whole_bytes = stage_bytes_per_step(hf, L, True, 1, 0.0)
+        if 2.2 * whole_bytes < 100e9:
+            whole = ModelShard(100, random_init.random_stage_parameters(hf, range(L), True, True, 1234, torch.bfloat16, device=str(dev)),
+                               config=hf, max_rows=max(128, min(batch * prompt_len, 4096)), max_seqs=batch,
+                               max_context=max_ctx, page_size=64)
+            whole.to_device()
+            g = torch.Generator().manual_seed(7)
+            prompts0 = torch.randint(0, hf["vocab_size"], (batch, prompt_len), generator=g)  # micro-batch 0 of prefill_all(7)
+            t0 = whole.compute({"input_ids": prompts0})["next_token"].cpu()
+            loop = whole.decode_loop(batch, V).cpu()
+            single_ids = torch.cat([t0[:, None], loop], dim=1)
+            checked["vs_single_stage"] = bool(torch.equal(single_ids, nccl_ids[0].to(torch.int64)))
+            ok &= checked["vs_single_stage"]
+            whole.decode_loop(batch, W)
+            torch.cuda.synchronize()
+            s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s0.record()
+            whole.decode_loop(batch, K)
+            s1.record()
+            torch.cuda.synchronize()
+            single_tps = batch * K / (s0.elapsed_time(s1) * 1e-3)
+            del whole
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.broadcast(flag, src=0)
+    ok = bool(int(flag))
+
     # per-stage roofline: every stage runs n_micro * K micro-batch steps in the timed region
     ctx_mid = prompt_len + W + K / 2.0
     my_bytes = stage_bytes_per_step(hf, len(layers), last, batch, ctx_mid)
@@ -200,28 +274,29 @@ def run_pipeline(args) -> int:
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": dec_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": workload_name(model, batch, prompt_len, world, L, n_micro), "model": model, "batch": batch,
-                       "micro_batches": n_micro, "prompt_len": prompt_len, "stages": world,
-                       "layers_per_stage": [len(r) for r in partition],
-                       "weights": "random-init (HF default init, seed 1234)",
+            "config": make_config(model, batch, prompt_len, world, L, n_micro),
+            "detail": {"layers_per_stage": [len(r) for r in partition],
                        "handoff": ("fused: peer stores from the down-projection epilogue into the next stage's mailbox + tickets"
-                                   if fused else "NCCL send/recv per micro-batch step (batch above the persistent kernel's 8 rows)"),
-                       "l2": "inputs larger than L2: every stage streams >= 1.7 GB of weights per micro-batch step"},
+                                   if fused else "NCCL send/recv per micro-batch step (batch above the persistent kernel's rows)")},
+            "tokens_checked": ok, "token_check": checked,
+            "same_model_n1": ({"value": single_tps, "unit": UNIT, "scaling_efficiency": value / (world * single_tps),
+                               "note": "the same model as one stage on one B200, same batch; efficiency = value / (N x this)"}
+                              if single_tps else None),
             "e2e": {"value": n_micro * batch * K / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": 4 * batch * n_micro,
                     "d2h_bytes_per_step": 4 * batch * n_micro, "ms_per_step": e2e_ms / K},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": float(fr[worst]) * hbm_peak, "peak": hbm_peak, "unit": "GB/s",
                          "frac": float(fr[worst]), "traffic": None, "peak_kind": peak_kind,
-                         "kernel": (f"decode_megakernel of stage {worst} (slowest stage): one persistent launch for the timed loop, "
+                         "kernel": (f"decode_megakernel of stage {worst} (the stage with the lowest fraction: every stage takes the same step "
+                                    "time in the steady state, this one moves the fewest bytes): one persistent launch for the timed loop, "
                                     "unit = one micro-batch step of the stage") if fused else
-                                   (f"micro-batch step of stage {worst} (slowest stage): CUDA graph of swap-AB tcgen05 GEMMs + "
+                                   (f"micro-batch step of stage {worst} (the stage with the lowest fraction): CUDA graph of swap-AB tcgen05 GEMMs + "
                                     "grouped-head decode attention"),
                          "per_stage_frac": [round(float(x), 4) for x in fr]},
             "cpu_baseline": None,
-            "note": "N=1 of this bench is BASELINE configs[1] (TinyLlama-1.1B); N >= 2 is configs[2] (this model). "
-                    "For the same model on one B200 run `bench.py --workload " + (args.workload or "llama3-8b") + "` "
-                    "(Llama-3-8B: 296 tok/s, profiles/r1d_summary.md)",
+            "note": "N=1 of this bench is BASELINE configs[1] (TinyLlama-1.1B); N >= 2 is configs[2] (this model): "
+                    "`same_model_n1` is this model on one B200, measured in this run on rank 0",
             "nccl_handoff": {"value": n_micro * batch * K / (nccl_ms * 1e-3), "unit": UNIT, "ms_per_step": nccl_ms / K,
                              "note": "same schedule, one launch per micro-batch step, NCCL send/recv + token ring"},
             "prefill": {"tokens_per_sec": n_micro * batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
@@ -239,4 +314,4 @@ def run_pipeline(args) -> int:
     if inbox is not None:
         inbox.close()
     dist.destroy_process_group()
-    return 0
+    return 0 if ok else 3

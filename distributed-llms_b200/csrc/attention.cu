@@ -180,6 +180,8 @@ static __device__ __align__(256) unsigned char g_static_attn_scratch[DLLM_STATIC
 
 namespace {
 constexpr int kMaxDevices = 64;
+// Not locked: two threads making the first call on a device at the same moment both look the address up and both
+// store the same value (the symbol's address on a device never changes), so whichever store lands last is right.
 void* g_static_scratch_ptr[kMaxDevices] = {nullptr};
 
 size_t round_up_256(size_t v) { return (v + 255) / 256 * 256; }

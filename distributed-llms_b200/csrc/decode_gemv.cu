@@ -481,16 +481,17 @@ cudaError_t launch_embed(int dtype, const EmbedParams& p, cudaStream_t s) {
 }
 
 // Decode-loop bookkeeping, on the device so that no step needs the host.
-//   begin  : gather the state the previous forward left at its logit rows into a dense batch
+//   begin  : gather the state the previous call left at its logit rows into a dense batch; pos_add = 1 after a
+//            forward (the pending token sits one past the processed row), 0 after a loop (already advanced)
 //   advance: feed the sampled token back, move every position on by one, log the token
 __global__ void decode_begin_kernel(int32_t* ids, int32_t* positions, int32_t* seq_ids, const int32_t* next_token,
-                                    const int32_t* logit_rows, int n, int32_t* step_ctr) {
+                                    const int32_t* logit_rows, int n, int32_t* step_ctr, int pos_add) {
     const int i = threadIdx.x;
     int t = 0, ps = 0, sq = 0;
     if (i < n) {
         const int src = logit_rows[i];
         t = next_token[i];
-        ps = positions[src] + 1;
+        ps = positions[src] + pos_add;
         sq = seq_ids[src];
     }
     __syncthreads();
@@ -503,9 +504,10 @@ __global__ void decode_begin_kernel(int32_t* ids, int32_t* positions, int32_t* s
 }
 
 cudaError_t launch_decode_begin(int32_t* ids, int32_t* positions, int32_t* seq_ids, const int32_t* next_token,
-                                const int32_t* logit_rows, int32_t n, int32_t* step_ctr, cudaStream_t s) {
+                                const int32_t* logit_rows, int32_t n, int32_t* step_ctr, int32_t pos_add,
+                                cudaStream_t s) {
     if (n <= 0 || n > 1024) return cudaErrorInvalidValue;
-    decode_begin_kernel<<<1, 1024, 0, s>>>(ids, positions, seq_ids, next_token, logit_rows, n, step_ctr);
+    decode_begin_kernel<<<1, 1024, 0, s>>>(ids, positions, seq_ids, next_token, logit_rows, n, step_ctr, pos_add);
     count_launch();
     return cudaGetLastError();
 }

@@ -131,7 +131,8 @@ bool attn_decode_gqa_supported(const AttnParams& p);
 cudaError_t launch_attn_decode_gqa(const AttnParams& p, cudaStream_t s);
 cudaError_t launch_embed(int dtype, const EmbedParams& p, cudaStream_t s);
 cudaError_t launch_decode_begin(int32_t* ids, int32_t* positions, int32_t* seq_ids, const int32_t* next_token,
-                                const int32_t* logit_rows, int32_t n, int32_t* step_ctr, cudaStream_t s);
+                                const int32_t* logit_rows, int32_t n, int32_t* step_ctr, int32_t pos_add,
+                                cudaStream_t s);
 cudaError_t launch_advance(int32_t* ids, int32_t* positions, const int32_t* next_token, int32_t* tok_ring,
                            int32_t* step_ctr, int32_t n_rows, cudaStream_t s);
 cudaError_t launch_legacy_matmul(const float* in, const float* param, float* out, int m, int k, int n,

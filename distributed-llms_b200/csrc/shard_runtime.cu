@@ -109,6 +109,9 @@ struct dllm_shard {
     // graphs
     std::map<unsigned long long, GraphEntry> graphs;
     cudaStream_t cap_stream = nullptr;
+    // true after a decode loop: `pos` already holds the position of the pending token (the loops advance after
+    // every step, the last one included); false after a forward: `pos` is the position of the rows just processed
+    bool pos_at_pending = false;
 };
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -761,8 +764,11 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
         }  // n_logit_rows < 0 with no row list: no logits this call (an inner chunk of a chunked prefill)
     }
     const bool use_mk = mk_eligible(s, n_rows, nl, logit_rows == nullptr);
-    if (c.has_head && !logit_rows && nl > 0 && !use_mk)  // the persistent kernel takes every row's logits in place
+    // every path leaves logit_rows describing this call's logit rows: a decode loop that follows gathers its
+    // positions / slots through them (the persistent kernel itself takes every row's logits in place)
+    if (c.has_head && !logit_rows && nl > 0)
         CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
+    s->pos_at_pending = false;
     if (use_mk) {
         if (run_megakernel(s, n_rows, 1, false, st)) return 1;
     } else if (prefill_eligible(s, n_rows)) {
@@ -793,7 +799,10 @@ extern "C" int dllm_shard_decode_loop(dllm_shard* s, int32_t n_rows, int32_t n_s
     int dev = -1;
     cudaGetDevice(&dev);
     if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
-    CUDA_TRY(launch_decode_begin(s->ids, s->pos, s->seq, s->next_tok, s->logit_rows, n_rows, s->step_ctr, st));
+    // after a forward the pending token sits one past the processed rows; after a loop `pos` is already there
+    CUDA_TRY(launch_decode_begin(s->ids, s->pos, s->seq, s->next_tok, s->logit_rows, n_rows, s->step_ctr,
+                                 s->pos_at_pending ? 0 : 1, st));
+    s->pos_at_pending = true;
     CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)n_rows * 4, cudaMemcpyDeviceToDevice, st));
     if (mk_eligible(s, n_rows, n_rows, true)) {
         if (run_megakernel(s, n_rows, n_steps, true, st)) return 1;

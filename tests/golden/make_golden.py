@@ -9,6 +9,8 @@ Writes
                              on seeded inputs -- pins the placeholder path against the reference itself.
   hf_<model>.pt            : HF transformers 5.5.0 (eager attention, fp32) on the oracle's seeded
                              random-init weights: prompts, greedy tokens, last-position logits per step.
+  hf_<model>_bf16.pt       : the same HF classes in bf16 (weights cast to bf16, HF's own CPU bf16 kernels): greedy
+                             tokens and last-position logits per step -- pins the bf16 oracle's rounding points.
   oracle_<model>_<dtype>.pt: the oracle's own outputs (stage-boundary hidden states of the prefill, logits,
                              tokens, top-2 margins) for 2 shards, fp32 and bf16 -- regression pins.
 """
@@ -60,6 +62,10 @@ def main():
         hf_t, hf_l = hf_greedy(m, prompts, N_NEW)
         torch.save({"config": cfg.to_hf_dict(), "prompts": prompts, "tokens": hf_t, "logits": hf_l},
                    os.path.join(HERE, f"hf_{name}.pt"))
+        m16 = hf_model(cfg, {k: v.to(torch.bfloat16) for k, v in sd.items()}, torch.bfloat16)
+        hf_t16, hf_l16 = hf_greedy(m16, prompts, N_NEW)
+        torch.save({"config": cfg.to_hf_dict(), "prompts": prompts, "tokens": hf_t16, "logits": hf_l16},
+                   os.path.join(HERE, f"hf_{name}_bf16.pt"))
         for dt, tag in ((torch.float32, "fp32"), (torch.bfloat16, "bf16")):
             sdd = {k: v.to(dt) for k, v in sd.items()}
             stages = build_pipeline(cfg, sdd, 2, dt)
@@ -76,8 +82,12 @@ def main():
                 print(f"{name}: oracle fp32 == HF (tokens identical, logits rel err {err:.1e}); "
                       f"min margin {float(mg.min()):.2e}")
             else:
+                same = (ids == hf_t16).long().cumprod(1).bool()
+                err16 = max(float((lg[:, t][same[:, max(t - 1, 0)] | (t == 0)] - hf_l16[:, t][same[:, max(t - 1, 0)] | (t == 0)]).abs().max()
+                                  / hf_l16[:, t].abs().max()) for t in range(N_NEW) if bool((same[:, max(t - 1, 0)] | (t == 0)).any()))
                 print(f"{name}: bf16 min margin {float(mg.min()):.2e}; tokens equal to fp32 run: "
-                      f"{int((ids == hf_t).sum())}/{ids.numel()}")
+                      f"{int((ids == hf_t).sum())}/{ids.numel()}; vs HF bf16: tokens equal {int((ids == hf_t16).sum())}/{ids.numel()}, "
+                      f"logits rel err {err16:.2e} while the histories agree")
 
 
 if __name__ == "__main__":

@@ -1,0 +1,175 @@
+"""GPU: the CUDA path against the CPU oracle at the sizes BASELINE.json names.
+
+* TinyLlama-1.1B at full size (the config bench.py times): 512-token prompt, 32 greedy tokens.
+    fp32 -- token ids identical to the oracle's, logits within 1e-4 relative.
+    bf16 -- every one of the 32 steps is compared under the oracle's own token history (teacher forcing), so that
+            a near-tie in one step cannot hide the steps after it: logits within 1e-2 relative to the largest
+            |logit| of the step, no floor.  The free-running device loop (`decode_loop`, the persistent kernel)
+            must reproduce the oracle's ids up to the first step whose top-2 margin is inside the measured logit
+            error; the number of such steps is counted and bounded, and printed.
+* Llama-3-8B / Qwen2.5-14B / Llama-3-70B: two layers at the real width with the full vocabulary, bf16 -- the
+  persistent kernel at batch 1, its streamed-rows variant at batch 4 and 8, the swap-AB GEMMs + grouped-head attention at
+  batch 16 and 32, and 2048- / 4096-token prefills through the tcgen05 GEMMs and the prefill attention (head_dim 128).
+
+Why teacher forcing: random-init logits are nearly flat; the oracle's top-2 margin falls below bf16
+resolution in a few of 32 steps whatever the seed, and two correct bf16 evaluations may then pick different ids.
+Weights are generated once (seeded, bf16-rounded); the oracle gets the very same values as fp32 tensors.
+"""
+import os
+
+import pytest
+import torch
+
+from oracle.shard_oracle import NAMED_CONFIGS as ORACLE_CONFIGS
+from oracle.shard_oracle import OracleShard, ShardModelConfig, make_prompts
+from src.model import random_init
+from src.worker.node import ModelShard
+
+pytestmark = pytest.mark.gpu
+torch.set_num_threads(os.cpu_count() or 1)
+
+
+def rel_err(a, b):
+    a, b = a.float().cpu(), b.float().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def oracle_stage(params, cfg: ShardModelConfig, dtype, max_context):
+    """The oracle on the same values: bf16-rounded weights held as fp32 (the oracle's `.float()` is then free)."""
+    return OracleShard(0, {k: v.detach().to("cpu").float() for k, v in params.items()}, cfg, dtype, max_context)
+
+
+def teacher_forced(shard: ModelShard, oracle: OracleShard, prompts, n_new):
+    """Oracle greedy run; the GPU stage is fed the ORACLE's ids at every step.  Returns per-step
+    (relative logit error, GPU id == oracle id, oracle top-2 margin / largest |logit|)."""
+    oracle.reset()
+    shard.reset()
+    with torch.no_grad():
+        o = oracle.compute({"input_ids": prompts})
+        g = shard.compute({"input_ids": prompts})
+        stats, o_ids = [], []
+        for t in range(n_new):
+            scale = float(o["logits"].abs().max())
+            stats.append((rel_err(g["logits"], o["logits"]),
+                          (g["next_token"].cpu() == o["next_token"]),
+                          o["top2_margin"] / scale))
+            o_ids.append(o["next_token"])
+            if t + 1 < n_new:
+                o = oracle.compute({"input_ids": o["next_token"][:, None]})
+                g = shard.compute({"input_ids": o_ids[-1][:, None]})
+    return stats, torch.stack(o_ids, 1)
+
+
+# ---- BASELINE configs[1]: TinyLlama-1.1B, batch 1, 512-token prompt ------------------------------------------------
+@pytest.fixture(scope="module")
+def tinyllama_weights():
+    hf = random_init.NAMED_CONFIGS["tinyllama-1.1b"]
+    L = hf["num_hidden_layers"]
+    # per-key seeded CPU draw: bit-reproducible, the same tensors oracle.make_state_dict(seed 1234) yields
+    return hf, random_init.random_stage_parameters(hf, range(L), True, True, 1234, torch.bfloat16, device=None)
+
+
+def test_tinyllama_full_size_fp32_tokens_identical(tinyllama_weights):
+    """fp32 on both sides: 32 greedy ids identical (free-running on the GPU), logits within 1e-4."""
+    hf, params = tinyllama_weights
+    cfg = ORACLE_CONFIGS["tinyllama-1.1b"]
+    p32 = {k: v.float() for k, v in params.items()}
+    oracle = OracleShard(0, p32, cfg, torch.float32, 576)
+    prompts = make_prompts(cfg.vocab, 1, 512, seed=7)
+    with torch.no_grad():
+        o = oracle.compute({"input_ids": prompts})
+        o_ids, o_lg = [o["next_token"]], [o["logits"]]
+        for _ in range(31):
+            o = oracle.compute({"input_ids": o_ids[-1][:, None]})
+            o_ids.append(o["next_token"]); o_lg.append(o["logits"])
+    shard = ModelShard(0, dict(p32), config=hf, max_rows=512, max_seqs=1, max_context=576, page_size=64)
+    shard.to_device()
+    g = shard.compute({"input_ids": prompts})
+    ids, errs = [g["next_token"].cpu()], [rel_err(g["logits"], o_lg[0])]
+    for t in range(1, 32):
+        g = shard.compute({"input_ids": ids[-1][:, None]})
+        ids.append(g["next_token"].cpu())
+        errs.append(rel_err(g["logits"], o_lg[t]))
+    assert torch.equal(torch.stack(ids, 1), torch.stack(o_ids, 1))
+    assert max(errs) < 1e-4, errs
+    print(f"\n[parity] tinyllama-1.1b fp32: 32/32 greedy ids identical, worst logit rel err {max(errs):.2e}")
+
+
+def test_tinyllama_full_size_bf16_against_oracle(tinyllama_weights):
+    """The bench configuration itself, bf16: persistent kernel (single steps and the device loop) and the tcgen05
+    prefill against the bf16 oracle."""
+    hf, params = tinyllama_weights
+    cfg = ORACLE_CONFIGS["tinyllama-1.1b"]
+    oracle = oracle_stage(params, cfg, torch.bfloat16, 576)
+    shard = ModelShard(0, dict(params), config=hf, max_rows=512, max_seqs=1, max_context=576, page_size=64)
+    shard.to_device()
+    prompts = make_prompts(cfg.vocab, 1, 512, seed=7)
+    stats, o_ids = teacher_forced(shard, oracle, prompts, 32)
+    errs = [e for e, _, _ in stats]
+    flips = [t for t, (_, same, _) in enumerate(stats) if not bool(same.all())]
+    assert max(errs) <= 1e-2, errs                      # the north star's bf16 tolerance, no floor
+    for t in flips:                                     # a different id needs a margin inside twice the logit error
+        assert float(stats[t][2].min()) <= 2 * errs[t], (t, float(stats[t][2].min()), errs[t])
+    assert len(flips) <= 3, flips
+    # free-running device loop (one persistent launch for 31 steps): identical up to the first such step
+    shard.reset()
+    first = shard.compute({"input_ids": prompts})["next_token"].cpu()
+    loop = torch.cat([first[:, None], shard.decode_loop(1, 31).cpu()], 1)
+    agree = int((loop == o_ids).long().cumprod(1).sum())
+    first_flip = flips[0] if flips else 32
+    assert agree >= first_flip, (agree, flips)
+    print(f"\n[parity] tinyllama-1.1b bf16, 512-token prompt, 32 steps under the oracle's history: worst logit rel err "
+          f"{max(errs):.2e}, mean {sum(errs) / len(errs):.2e}; ids differ at steps {flips} (oracle top-2 margin / scale there: "
+          f"{[round(float(stats[t][2].min()), 5) for t in flips]}); free-running device loop identical for {agree}/32 ids")
+
+
+# ---- BASELINE configs[2..4]: real widths, two layers, full vocabulary ------------------------------------------------
+def _two_layer_stage(model: str, seed: int):
+    hf = dict(random_init.NAMED_CONFIGS[model])
+    hf["num_hidden_layers"] = 2
+    # drawn on the GPU (seeded; a 70B-wide pair of layers + head is 3.8 G values), then copied to the oracle
+    params = random_init.random_stage_parameters(hf, range(2), True, True, seed, torch.bfloat16, device="cuda")
+    c = ORACLE_CONFIGS[model]
+    cfg = ShardModelConfig(**{**c.__dict__, "n_layers": 2})
+    return hf, cfg, params
+
+
+@pytest.mark.parametrize("model", ["llama3-8b", "qwen2.5-14b", "llama3-70b"])
+def test_full_width_decode_against_oracle(model):
+    """Decode at batch 1 (persistent kernel), 4 and 8 (streamed-rows variant at these widths), 16 and 32 (swap-AB
+    tcgen05 GEMMs + grouped-head attention): a 24-token prefill and 3 decode steps each, logits within 1e-2."""
+    hf, cfg, params = _two_layer_stage(model, 77)
+    oracle = oracle_stage(params, cfg, torch.bfloat16, 64)
+    shard = ModelShard(0, dict(params), config=hf, max_rows=1024, max_seqs=32, max_context=64, page_size=16)
+    shard.to_device()
+    report = []
+    for batch in (1, 4, 8, 16, 32):
+        prompts = make_prompts(cfg.vocab, batch, 24, seed=batch)
+        stats, _ = teacher_forced(shard, oracle, prompts, 4)
+        errs = [e for e, _, _ in stats]
+        assert max(errs) <= 1e-2, (batch, errs)
+        n_flip = 0
+        for t, (e, same, mg) in enumerate(stats):
+            for b in (~same).nonzero().flatten().tolist():
+                n_flip += 1
+                assert float(mg[b]) <= 2 * e, (batch, t, b, float(mg[b]), e)
+        report.append(f"b{batch}: {max(errs):.1e} ({n_flip} of {4 * batch} ids differ)")
+    print(f"\n[parity] {model} width, 2 layers, full vocab, bf16 vs oracle, worst logit rel err per batch: " + "; ".join(report))
+
+
+@pytest.mark.parametrize("model,T", [("qwen2.5-14b", 2048), ("llama3-8b", 4096)])
+def test_long_prefill_against_oracle(model, T):
+    """One long prompt through the tcgen05 GEMMs and the prefill attention at head_dim 128 (BASELINE configs[3]
+    prefills 2048-token micro-batches), then 2 decode steps over the long context: logits within 1e-2."""
+    hf, cfg, params = _two_layer_stage(model, 5)
+    oracle = oracle_stage(params, cfg, torch.bfloat16, T + 16)
+    shard = ModelShard(0, dict(params), config=hf, max_rows=T, max_seqs=1, max_context=T + 16, page_size=64)
+    shard.to_device()
+    prompts = make_prompts(cfg.vocab, 1, T, seed=3)
+    stats, _ = teacher_forced(shard, oracle, prompts, 3)
+    errs = [e for e, _, _ in stats]
+    assert max(errs) <= 1e-2, errs
+    for t, (e, same, mg) in enumerate(stats):
+        if not bool(same.all()):
+            assert float(mg.min()) <= 2 * e, (t, float(mg.min()), e)
+    print(f"\n[parity] {model} width, 2 layers, {T}-token prefill + 2 decode steps, bf16 vs oracle: logit rel err {errs}")

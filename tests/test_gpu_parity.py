@@ -24,15 +24,41 @@ def rel_err(a, b):
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
 
 
+# Every bf16 comparison of this file lands here, so that the suite can print (and bound) how often the strict 1e-2
+# is exceeded and how many greedy ids differ, instead of passing silently: (relative error, error in bf16 quanta).
+BF16_LOG = []
+BF16_FLIPS = []   # (oracle top-2 margin / scale) of every first differing id
+
+
 def bf16_logits_close(a, b):
-    """North-star bf16 tolerance (1e-2 relative to the largest |logit|), floored at three bf16 output quanta at that
-    scale.  HF returns logits rounded to bf16; on these random-init test models max|logit| < 1, where one quantum is
-    0.4-0.8 % of the scale, so two correctly rounded results whose exact values differ by 1.6 quanta can land 2.5
-    quanta apart.  Measured: mean |diff| 0.2 % of the scale, max 1.06 % (profiles/ notes), for every kernel variant."""
+    """North-star bf16 tolerance: 1e-2 relative to the largest |logit|.  HF (and the oracle) return logits rounded to
+    bf16; on the small random-init test models max|logit| < 1, where ONE output quantum is 0.4-0.8 % of the scale, so
+    two correctly rounded results whose exact values differ by just over one quantum land two quanta apart (up to 1.6 %).
+    Such a pair is accepted up to two quanta and counted: `test_bf16_parity_summary` prints the counts and fails
+    when they grow.  The BASELINE-size tests (test_gpu_full_size.py) use the strict 1e-2 with no floor."""
     a, b = a.float().cpu(), b.float().cpu()
     scale = float(b.abs().max())
     ulp = 2.0 ** (torch.floor(torch.log2(torch.tensor(scale))).item() - 7)
-    return float((a - b).abs().max()) <= max(1e-2 * scale, 3 * ulp)
+    err = float((a - b).abs().max())
+    BF16_LOG.append((err / scale, err / ulp))
+    return err <= max(1e-2 * scale, 2.0 * ulp)
+
+
+def check_bf16_generation(ids, lg, o_ids, o_lg, o_mg):
+    """Free-running bf16 generation against the oracle's: logits are comparable while the token histories agree;
+    a first differing id must sit on an oracle top-2 margin inside bf16 resolution of the logit scale (2^-7), and is
+    counted."""
+    same_prefix = (ids == o_ids).long().cumprod(1).bool()
+    for t in range(ids.shape[1]):
+        rows = same_prefix[:, t - 1] if t else torch.ones(ids.shape[0], dtype=torch.bool)
+        if rows.any():
+            assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
+    for b in range(ids.shape[0]):
+        if not same_prefix[b].all():
+            t = int((~same_prefix[b]).float().argmax())
+            rel_margin = float(o_mg[b, t]) / float(o_lg[b, t].abs().max())
+            BF16_FLIPS.append(rel_margin)
+            assert rel_margin <= 2 ** -7, (b, t, rel_margin)
 
 
 def stream():
@@ -95,6 +121,24 @@ def test_gemv_rejects_bad_k():
     x = torch.zeros(1, 12, device="cuda", dtype=torch.bfloat16)
     rc = cabi.lib().dllm_op_gemv(0, x.data_ptr(), x.data_ptr(), None, x.data_ptr(), 1, 1, 12, 0, stream())
     assert rc != 0 and b"multiple" in cabi.lib().dllm_last_error()
+
+
+def test_handoff_peer_copy_moves_the_tile_bit_for_bit():
+    """`dllm_handoff_peer_copy` (the hand-off tile as one stream-ordered device-to-device copy): same device here, the
+    peer-to-peer form over NVLink when a second GPU is present."""
+    L = cabi.lib()
+    g = torch.Generator().manual_seed(1)
+    tile = torch.randn(2, 37, 512, generator=g).to(torch.bfloat16).cuda()
+    dst = torch.zeros_like(tile)
+    cabi.check(L.dllm_handoff_peer_copy(dst.data_ptr(), 0, tile.data_ptr(), 0, tile.numel() * 2, stream()))
+    torch.cuda.synchronize()
+    assert torch.equal(dst, tile)
+    assert L.dllm_handoff_peer_copy(None, 0, tile.data_ptr(), 0, 16, stream()) != 0      # null destination is refused
+    if torch.cuda.device_count() >= 2:
+        far = torch.zeros(tile.shape, dtype=torch.bfloat16, device="cuda:1")
+        cabi.check(L.dllm_handoff_peer_copy(far.data_ptr(), 1, tile.data_ptr(), 0, tile.numel() * 2, stream()))
+        torch.cuda.synchronize()
+        assert torch.equal(far.cpu(), tile.cpu())
 
 
 def _paged_kv(lens, KV, hd, page, dtype, gen):
@@ -221,23 +265,11 @@ def test_pipeline_matches_golden(name, tag, dtype, shards):
         err = max(rel_err(lg[:, t], g["logits"][:, t]) for t in range(lg.shape[1]))
         assert err < TOL[dtype], err
     else:
-        same = (ids == g["tokens"]).long().cumprod(1).bool()  # logits are comparable while the histories agree
-        for t in range(lg.shape[1]):
-            rows = same[:, t - 1] if t else torch.ones(ids.shape[0], dtype=torch.bool)
-            if rows.any():
-                assert bf16_logits_close(lg[rows, t], g["logits"][rows, t]), t
+        check_bf16_generation(ids, lg, g["tokens"], g["logits"], g["margins"])
     if dtype == torch.float32:
         assert torch.equal(ids, g["tokens"])  # bit-identical greedy tokens
         hf = torch.load(os.path.join(GOLD, f"hf_{name}.pt"), weights_only=True)
         assert torch.equal(ids, hf["tokens"]) and rel_err(lg, hf["logits"]) < 1e-4  # and against HF itself
-    else:
-        # bf16: identical unless the oracle's own top-2 margin is within bf16 resolution of the logit scale
-        diff = ids != g["tokens"]
-        first = diff.float().cumsum(1).clamp(max=1)  # after the first flip the continuations diverge legitimately
-        for b, t in diff.nonzero().tolist():
-            if first[b, :t].sum() == 0:
-                assert float(g["margins"][b, t]) <= 2 ** -7 * float(g["logits"][b, t].abs().max()), (b, t)
-        assert int(diff[:, 0].sum()) == 0 or float(g["margins"][:, 0].min()) <= 2 ** -7 * float(g["logits"][:, 0].abs().max())
 
 
 @pytest.mark.parametrize("name", ["llama", "gpt2"])
@@ -267,16 +299,7 @@ def test_seeded_pipeline_against_live_oracle(dtype):
         assert torch.equal(ids, o_ids)
         assert rel_err(lg, o_lg) < 1e-4
     else:
-        same_prefix = (ids == o_ids).long().cumprod(1).bool()  # compare logits while the token history agrees
-        for t in range(32):
-            rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
-            if rows.any():
-                assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
-        flips = (~same_prefix).float().argmax(1)
-        for b in range(ids.shape[0]):
-            if not same_prefix[b].all():
-                t = int(flips[b])
-                assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
+        check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
 
 
 def test_decode_loop_equals_stepwise():
@@ -291,6 +314,43 @@ def test_decode_loop_equals_stepwise():
         first = st.compute({"input_ids": prompts})["next_token"].cpu()
         rest = st.decode_loop(2, 19).cpu()
         assert torch.equal(torch.cat([first[:, None], rest], 1), ids)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_decode_loop_twice_equals_one_long_loop(dtype):
+    """decode_loop(a) followed by decode_loop(b) == decode_loop(a + b), bit for bit, with prompt + a landing on a KV
+    page boundary (the second call must start at the pending token's position, not one past it)."""
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, 2, 10, seed=2)
+    (st,) = gpu_stages(cfg, sd, 1, dtype, max_rows=32, max_seqs=2, max_context=128, page_size=16)
+    st.compute({"input_ids": prompts})
+    want = st.decode_loop(2, 6 + 11).cpu()
+    st.reset()
+    st.compute({"input_ids": prompts})
+    a = st.decode_loop(2, 6).cpu()    # 10 prompt tokens + 6 = 16 = one full page
+    b = st.decode_loop(2, 11).cpu()
+    assert torch.equal(torch.cat([a, b], 1), want)
+    c = st.decode_loop(2, 1).cpu()    # and a third call keeps going from where the second stopped
+    st.reset()
+    st.compute({"input_ids": prompts})
+    assert torch.equal(st.decode_loop(2, 18).cpu()[:, -1:], c)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_prefill_single_step_then_decode_loop(dtype):
+    """prefill (logit rows T-1, 2T-1, ...) -> one single-token forward -> decode_loop: the loop must gather its
+    positions and slots from the single-token call, not from the prefill's stale logit rows."""
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, 2, 10, seed=2)
+    (st,) = gpu_stages(cfg, sd, 1, dtype, max_rows=32, max_seqs=2, max_context=128, page_size=16)
+    ids, _ = gpu_generate([st], prompts, 12)
+    st.reset()
+    first = st.compute({"input_ids": prompts})["next_token"].cpu()
+    second = st.compute({"input_ids": first[:, None]})["next_token"].cpu()
+    rest = st.decode_loop(2, 10).cpu()
+    assert torch.equal(torch.cat([first[:, None], second[:, None], rest], 1), ids)
 
 
 def test_chunked_prefill_equals_single_call():
@@ -343,7 +403,8 @@ def test_limits_are_enforced():
 
 # ---- full-size properties (BASELINE configs[1]: TinyLlama-1.1B bf16, 512-token prompt) ---------------------------
 def test_tinyllama_full_size_properties():
-    """No CPU oracle at this size in seconds, so check what must hold at any size:
+    """Size-independent properties at the bench configuration (the oracle comparison at this size is
+    tests/test_gpu_full_size.py):
     (1) splitting the model into 2 stages does not change a single bit of the hand-off or the tokens,
     (2) the device-resident loop reproduces step-by-step decoding exactly,
     (3) a 512-token chunked prefill and token-by-token prefill agree within the bf16 tolerance."""
@@ -385,15 +446,7 @@ def test_streamed_rows_variant_matches_oracle(batch, monkeypatch):
     o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16), prompts, 12, record=True)
     stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=64, max_seqs=8, max_context=128, page_size=16)
     ids, lg = gpu_generate(stages, prompts, 12)
-    same_prefix = (ids == o_ids).long().cumprod(1).bool()
-    for t in range(12):
-        rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
-        if rows.any():
-            assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
-    for b in range(ids.shape[0]):
-        if not same_prefix[b].all():
-            t = int((~same_prefix[b]).float().argmax())
-            assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
+    check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
     # and the device-resident loop through the same variant reproduces the stepwise tokens
     stages[0].reset()
     first = stages[0].compute({"input_ids": prompts})["next_token"].cpu()
@@ -460,23 +513,15 @@ def test_long_context_decode_matches_oracle(batch, prompt_len, qt128, monkeypatc
     o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16, max_context=prompt_len + 16), prompts, n_new, record=True)
     stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=1024, max_seqs=batch, max_context=prompt_len + 16, page_size=64)
     ids, lg = gpu_generate(stages, prompts, n_new)
-    same_prefix = (ids == o_ids).long().cumprod(1).bool()
-    for t in range(n_new):
-        rows = same_prefix[:, t] if t == 0 else same_prefix[:, t - 1]
-        if rows.any():
-            assert bf16_logits_close(lg[rows, t], o_lg[rows, t]), t
-    for b in range(ids.shape[0]):
-        if not same_prefix[b].all():
-            t = int((~same_prefix[b]).float().argmax())
-            assert float(o_mg[b, t]) <= 2 ** -7 * float(o_lg[b, t].abs().max())
+    check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
 
 
 @pytest.mark.parametrize("model", ["llama3-8b", "qwen2.5-14b", "llama3-70b"])
 def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
     """Two layers at the real widths of the BASELINE configs (hidden 4096 / 5120 / 8192, GQA 4 / 5 / 8, head_dim 128,
-    full vocabulary): no CPU oracle in seconds at these sizes, so the persistent kernel (several rounds of panels per
-    CTA, the streamed-rows variant at batch 4-8) is checked against the independent per-op CUDA path, which the small
-    cases pin to the oracle.  Prefill (tcgen05 GEMMs) feeds both."""
+    full vocabulary): the persistent kernel (several rounds of panels per CTA, the streamed-rows variant at batch 4-8)
+    against the independent per-op CUDA path -- a cross-check between two implementations.  The comparison with the
+    oracle at these widths is tests/test_gpu_full_size.py::test_full_width_decode_against_oracle."""
     hf = dict(random_init.NAMED_CONFIGS[model])
     hf["num_hidden_layers"] = 2
     params = random_init.random_stage_parameters(hf, range(2), True, True, 77, torch.bfloat16, device="cuda")
@@ -501,7 +546,8 @@ def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
 def test_prefill_tile_widths_agree_bit_for_bit(monkeypatch):
     """A 4096-token prefill at Llama-3-8B width takes the 256-wide GEMM tiles (q | k | v as row segments of one
     launch); with them switched off it takes 128-wide tiles.  Both walk K in the same order, so the logits must be
-    identical -- the tile width is a scheduling choice, not a numerical one.  (No CPU oracle at this size.)"""
+    identical -- the tile width is a scheduling choice, not a numerical one.  (The same prefill against the oracle:
+    tests/test_gpu_full_size.py::test_long_prefill_against_oracle.)"""
     hf = dict(random_init.NAMED_CONFIGS["llama3-8b"])
     hf["num_hidden_layers"] = 2
     params = random_init.random_stage_parameters(hf, range(2), True, True, 5, torch.bfloat16, device="cuda")
@@ -516,3 +562,20 @@ def test_prefill_tile_widths_agree_bit_for_bit(monkeypatch):
         outs.append(sh.compute({"input_ids": prompt})["logits"].cpu())
         del sh
     assert torch.isfinite(outs[0]).all() and torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+def test_bf16_parity_summary():
+    """Runs after every bf16 comparison of this file: print how strict the parity actually was, and fail when it
+    degrades.  (Collected last in this file; run alone it has nothing to summarise.)"""
+    if not BF16_LOG:
+        pytest.skip("no bf16 comparison ran in this process")
+    n = len(BF16_LOG)
+    over = [e for e, _ in BF16_LOG if e > 1e-2]
+    worst_rel = max(e for e, _ in BF16_LOG)
+    worst_q = max(q for _, q in BF16_LOG)
+    mean_rel = sum(e for e, _ in BF16_LOG) / n
+    print(f"\n[parity] bf16, small models: {n} logit comparisons, mean rel err {mean_rel:.2e}, worst {worst_rel:.2e} "
+          f"({worst_q:.1f} output quanta); {len(over)} above the strict 1e-2 (all within two quanta of max|logit| < 1); "
+          f"{len(BF16_FLIPS)} first differing ids, oracle margin / scale there: {[round(m, 5) for m in BF16_FLIPS]}")
+    assert worst_q <= 2.0
+    assert len(over) <= max(2, n // 20), (len(over), n)   # a handful of two-quanta pairs, not a trend

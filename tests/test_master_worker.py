@@ -163,6 +163,43 @@ def test_master_two_workers_greedy_decode_matches_oracle(tmp_path, dtype):
 
 
 @pytest.mark.gpu
+def test_schedule_computation_command_over_the_socket(tmp_path):
+    """The SCHEDULE_COMPUTATION message (reference src/worker/node.py:240-261: RUN_INFERENCE with a `priority` header that
+    the reference's constant sort key turns into a no-op) sent to a worker over ZeroMQ: same RESULT as RUN_INFERENCE and as
+    the in-process `schedule_computation`, fp32, checked against the oracle."""
+    import pickle
+    from oracle.shard_oracle import ShardModelConfig, build_pipeline, pipeline_step
+    d, sd = _model_dir(tmp_path, torch.float32)
+    master, workers = _cluster(1)
+    try:
+        master.initialize_model(d, num_shards=2)
+        master.assign_shards()                       # both shards on the one worker, in pipeline order
+        master.distribute_shards(timeout=120)
+        prompt = torch.randint(0, CFG["vocab_size"], (2, 7), generator=torch.Generator().manual_seed(8))
+        worker = next(iter(master.workers.values()))
+        replies = {}
+        for cmd in ("SCHEDULE_COMPUTATION", "RUN_INFERENCE"):
+            task = f"t_{cmd}"
+            master._replies[task] = __import__("queue").Queue()
+            master._send(worker, cmd, pickle.dumps({"input_ids": prompt}),
+                         {"task_id": task, "shard_ids": [0, 1], "reset": True, "priority": 3})
+            header, payload = master._replies[task].get(timeout=60)
+            assert header["command"] == "RESULT" and not header.get("error"), header
+            replies[cmd] = pickle.loads(payload)
+        a, b = replies["SCHEDULE_COMPUTATION"], replies["RUN_INFERENCE"]
+        assert torch.equal(a["next_token"], b["next_token"]) and torch.equal(a["logits"], b["logits"])
+        workers[0].shards[0].reset(); workers[0].shards[1].reset()
+        direct = workers[0].schedule_computation({"input_ids": prompt}, [0, 1])
+        assert torch.equal(direct["logits"].cpu(), a["logits"])
+        cfg = ShardModelConfig.from_hf_dict(CFG)
+        want = pipeline_step(build_pipeline(cfg, sd, 2, torch.float32), {"input_ids": prompt})
+        assert torch.equal(a["next_token"], want["next_token"])
+        assert float((a["logits"] - want["logits"]).abs().max() / want["logits"].abs().max()) < 1e-4
+    finally:
+        _shutdown(master, workers)
+
+
+@pytest.mark.gpu
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_master_uses_the_fused_handoff_when_every_stage_has_its_own_gpu(tmp_path):
     """Two workers on two GPUs: after the prefill the master opens a mailbox on each stage, connects them into a ring

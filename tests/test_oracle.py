@@ -38,6 +38,22 @@ def test_oracle_fp32_matches_hf_golden(name, shards):
 
 
 @pytest.mark.parametrize("name", ["gpt2", "llama", "qwen2"])
+@pytest.mark.parametrize("shards", [1, 2])
+def test_oracle_bf16_matches_hf_bf16_golden(name, shards):
+    """The bf16 oracle (fp32 math, bf16 rounding at the HF op boundaries) against HF's own bf16 forward on the same
+    bf16 weights: identical greedy tokens and logits within the north star's 1e-2 relative, step by step."""
+    g = _load(f"hf_{name}_bf16.pt")
+    cfg = ShardModelConfig.from_hf_dict(g["config"])
+    sd = {k: v.to(torch.bfloat16) for k, v in make_state_dict(cfg, 1234, torch.float32, init="full").items()}
+    stages = build_pipeline(cfg, sd, shards, torch.bfloat16)
+    ids, lg, _ = greedy_generate(stages, g["prompts"], g["tokens"].shape[1], record=True)
+    assert torch.equal(ids, g["tokens"])
+    for t in range(lg.shape[1]):
+        rel = float((lg[:, t] - g["logits"][:, t]).abs().max() / g["logits"][:, t].abs().max())
+        assert rel <= 1e-2, (t, rel)
+
+
+@pytest.mark.parametrize("name", ["gpt2", "llama", "qwen2"])
 @pytest.mark.parametrize("tag,dt", [("fp32", torch.float32), ("bf16", torch.bfloat16)])
 def test_oracle_regression_pins(name, tag, dt):
     g = _load(f"oracle_{name}_{tag}.pt")

@@ -7,8 +7,8 @@ library (4 MiB per GPU), shared by all calls and never cleared between them by a
 
 This file is collected last on purpose: if it fails, a `-x` run has already executed every other test.
 The checks below call it twice in a row with different inputs (the second call sees the first one's leftovers
-in the shared area) and compare each result with the ordinary entry point, through the C ABI, within the
-tolerances the other attention tests use.  It does not depend on any other test having run.
+in the shared area) and compare each result with the ordinary entry point and with a plain fp32 reference,
+through the C ABI, within the tolerances the other attention tests use.  It does not depend on any other test having run.
 """
 import pytest
 import torch
@@ -53,7 +53,23 @@ def _run_both(dtype, lens, H, KV, hd, splits, seed, page=16):
                                                  page, pos.data_ptr(), seq.data_ptr(), R, H, KV, hd, splits,
                                                  got.data_ptr(), st))
     torch.cuda.synchronize()
-    return got.float().cpu(), want.float().cpu()
+    return got.float().cpu(), want.float().cpu(), _fp32_reference(q, kpool, vpool, bt, pos, H, KV, hd, page, dtype)
+
+
+def _fp32_reference(q, kpool, vpool, bt, pos, H, KV, hd, page, dtype):
+    """Plain fp32 attention over the gathered pages, rounded where the kernels round (scores before and after scaling):
+    the reference the ordinary entry point is held to in tests/test_gpu_parity.py."""
+    rnd = (lambda t: t.to(dtype).float())
+    q, kpool, vpool, bt, pos = (t.cpu() for t in (q, kpool, vpool, bt, pos))
+    out = torch.empty(q.shape[0], H * hd)
+    for r in range(q.shape[0]):
+        n = int(pos[r]) + 1
+        pages = bt[r, : (n + page - 1) // page].long()
+        K = kpool[pages].float().permute(0, 2, 1, 3).reshape(-1, KV, hd)[:n].repeat_interleave(H // KV, dim=1)
+        V = vpool[pages].float().permute(0, 2, 1, 3).reshape(-1, KV, hd)[:n].repeat_interleave(H // KV, dim=1)
+        sc = rnd(rnd(torch.einsum("hd,chd->hc", q[r].float(), K)) * hd ** -0.5)
+        out[r] = torch.einsum("hc,chd->hd", torch.softmax(sc, -1), V).reshape(-1)
+    return out
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
@@ -61,13 +77,16 @@ def test_static_scratch_matches_ordinary_entry_point_twice_in_a_row(dtype):
     tol = 2e-5 if dtype == torch.float32 else 1e-2
     # two different problems back to back: the second runs on the first one's leftovers in the shared area
     for seed, lens, H, KV, hd, splits in [(1, [70, 5, 200], 8, 2, 64, 6), (2, [33, 129], 4, 4, 128, 3)]:
-        got, want = _run_both(dtype, lens, H, KV, hd, splits, seed)
+        got, want, ref = _run_both(dtype, lens, H, KV, hd, splits, seed)
         assert torch.isfinite(got).all()
         err = float((got - want).abs().max() / want.abs().max())
         assert err < tol, (seed, err)
+        # and against the same fp32 reference the ordinary entry point is checked with
+        err_ref = float((got - ref).abs().max() / ref.abs().max())
+        assert err_ref < tol, (seed, err_ref)
     # and the very same problem again gives the very same bits
-    a, _ = _run_both(dtype, [70, 5, 200], 8, 2, 64, 6, seed=1)
-    b, _ = _run_both(dtype, [70, 5, 200], 8, 2, 64, 6, seed=1)
+    a, _, _ = _run_both(dtype, [70, 5, 200], 8, 2, 64, 6, seed=1)
+    b, _, _ = _run_both(dtype, [70, 5, 200], 8, 2, 64, 6, seed=1)
     assert torch.equal(a, b)
 
 
