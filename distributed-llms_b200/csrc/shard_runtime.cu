@@ -922,21 +922,38 @@ extern "C" int dllm_mailbox_destroy(dllm_mailbox* b) {
     return 0;
 }
 
+// Everything dllm_shard_decode_pipelined checks before it launches, without launching (also exported on its own: a master
+// asks every stage first and starts the loops only when all of them can run -- a stage that refuses after its neighbours
+// have started would leave them waiting for tickets that never come).
+static int pipelined_validate(const char* who, dllm_shard* s, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
+                              int32_t rows, int32_t n_steps) {
+    const std::string w(who);
+    if (!s || !inbox || !outbox) return fail(w + ": null argument");
+    const dllm_shard_config& c = s->cfg;
+    if (n_micro < 1 || rows < 1 || n_steps < 1) return fail(w + ": n_micro, rows and n_steps must be positive");
+    if ((long)n_micro * rows > c.max_rows) return fail(w + ": n_micro * rows exceeds max_rows");
+    if (!inbox->owner || inbox->device != s->device || outbox->device != s->device)
+        return fail(w + ": the inbox must be this stage's own mailbox and the outbox a view mapped on this stage's device");
+    for (const dllm_mailbox* b : {inbox, outbox})
+        if (b->n_slots < n_micro || b->rows != rows || b->hidden != c.hidden) return fail(w + ": mailbox shape does not match");
+    if (c.has_embed && (size_t)n_steps * n_micro * rows > s->tok_ring_cap) return fail(w + ": n_steps out of range");
+    if (c.n_layers < 1) return fail(w + ": the stage has no layers");
+    if (!mk_eligible(s, rows, rows, true))
+        return fail(w + ": shape not taken by the persistent kernel (bf16, <= 16 rows, fits shared memory)");
+    return 0;
+}
+
+extern "C" int dllm_shard_decode_pipelined_check(dllm_shard* s, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
+                                                 int32_t rows, int32_t n_steps) {
+    return pipelined_validate("dllm_shard_decode_pipelined_check", s, inbox, outbox, n_micro, rows, n_steps);
+}
+
 extern "C" int dllm_shard_decode_pipelined(dllm_shard* s, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
                                            int32_t rows, int32_t n_steps, uint32_t step_base, const int32_t* positions,
                                            const int32_t* seq_ids, int32_t* fed_tokens_out, void* stream) {
-    if (!s || !inbox || !outbox || !positions || !seq_ids) return fail("dllm_shard_decode_pipelined: null argument");
+    if (!positions || !seq_ids) return fail("dllm_shard_decode_pipelined: null argument");
+    if (pipelined_validate("dllm_shard_decode_pipelined", s, inbox, outbox, n_micro, rows, n_steps)) return 1;
     const dllm_shard_config& c = s->cfg;
-    if (n_micro < 1 || rows < 1 || n_steps < 1) return fail("dllm_shard_decode_pipelined: n_micro, rows and n_steps must be positive");
-    if ((long)n_micro * rows > c.max_rows)
-        return fail("dllm_shard_decode_pipelined: n_micro * rows exceeds max_rows");
-    if (!inbox->owner || inbox->device != s->device || outbox->device != s->device)
-        return fail("dllm_shard_decode_pipelined: the inbox must be this stage's own mailbox and the outbox a view mapped on this stage's device");
-    for (const dllm_mailbox* b : {inbox, outbox})
-        if (b->n_slots < n_micro || b->rows != rows || b->hidden != c.hidden) return fail("dllm_shard_decode_pipelined: mailbox shape does not match");
-    if (c.has_embed && (size_t)n_steps * n_micro * rows > s->tok_ring_cap) return fail("dllm_shard_decode_pipelined: n_steps out of range");
-    if (c.n_layers < 1) return fail("dllm_shard_decode_pipelined: the stage has no layers");
-    if (!mk_eligible(s, rows, rows, true)) return fail("dllm_shard_decode_pipelined: shape not taken by the persistent kernel (bf16, <= 16 rows, fits shared memory)");
     cudaStream_t st = (cudaStream_t)stream;
     int dev = -1;
     cudaGetDevice(&dev);

@@ -311,6 +311,20 @@ class ShardExecutor:
             cabi.check(cabi.lib().dllm_shard_decode_loop(self._handle, batch, n_steps, toks.data_ptr(), st))
         return toks.t().to(torch.int64)
 
+    def check_decode_pipelined(self, inbox, outbox, n_micro: int, rows: int, n_steps: int, positions: torch.Tensor,
+                               seq_ids: torch.Tensor) -> None:
+        """Pre-flight of `decode_pipelined`: raises what the launch would raise (shape the persistent kernel does not
+        take, mailbox mismatch, context limit, KV pool exhausted) -- and reserves the KV pages -- without launching."""
+        pos = positions.to("cpu", torch.int32).reshape(n_micro * rows)
+        seq = seq_ids.to("cpu", torch.int32).reshape(n_micro * rows)
+        if int(pos.max()) + n_steps > self.max_context:
+            raise ValueError("decode_pipelined would run past max_context")
+        with self.lock, torch.cuda.device(self.device):
+            cabi.check(cabi.lib().dllm_shard_decode_pipelined_check(self._handle, inbox.handle, outbox.handle, n_micro, rows, n_steps))
+            st = self._stream()
+            for s_, p_ in zip(seq.tolist(), pos.tolist()):
+                cabi.check(cabi.lib().dllm_shard_kv_reserve(self._handle, s_, p_ + n_steps, st))
+
     def decode_pipelined(self, inbox, outbox, n_micro: int, rows: int, n_steps: int, step_base: int,
                          positions: torch.Tensor, seq_ids: torch.Tensor) -> Optional[torch.Tensor]:
         """`n_steps` decode steps of `n_micro` micro-batches in ONE persistent launch with the hand-off fused into

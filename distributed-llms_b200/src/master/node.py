@@ -31,7 +31,7 @@ except Exception:  # pragma: no cover
     zmq = None
 
 from ..model.shard_manager import ModelShardManager
-from ..network.protocol import MessageProtocol
+from ..network.protocol import MessageProtocol, OwnedSocket
 
 
 class GreedySampler:
@@ -67,7 +67,7 @@ class MasterNode:
         self.zmq_context = zmq.Context.instance() if zmq is not None else None
         self.sampler = GreedySampler()
         self._protocol: Optional[MessageProtocol] = None
-        self._send_lock = threading.Lock()            # one ROUTER socket, several sender threads
+        self._owned: Optional[OwnedSocket] = None     # the ROUTER socket: owned by the accept thread, see OwnedSocket
         self._workers_lock = threading.Lock()
         self._replies: Dict[str, Queue] = {}          # task_id -> queue of (header, payload) from workers
         self._finished: Dict[str, Queue] = {}         # task_id -> final result for run_inference()
@@ -83,6 +83,7 @@ class MasterNode:
         self.server_socket = self._protocol.setup_zmq_socket(zmq.ROUTER, f"tcp://{self.host}:{self.port}")  # binds
         if self.port == 0:
             self.port = int(self.server_socket.getsockopt_string(zmq.LAST_ENDPOINT).rsplit(":", 1)[1])
+        self._owned = OwnedSocket(self.zmq_context, self.server_socket)
         self.running = True
         print(f"Master node listening on {self.host}:{self.port}")
         self.accept_thread = threading.Thread(target=self._accept_connections, daemon=True)
@@ -92,10 +93,13 @@ class MasterNode:
 
     def stop(self):
         self.running = False
-        time.sleep(0.05)
-        if self.server_socket is not None:
-            self.server_socket.close()
-            self.server_socket = None
+        t = getattr(self, "accept_thread", None)
+        if t is not None and t is not threading.current_thread():
+            t.join(timeout=2.0)   # the accept thread owns the socket: it must be out of its poll before the close
+        if self._owned is not None:
+            self._owned.close()
+            self._owned = None
+        self.server_socket = None
 
     # ---- model preparation (reference :54-82) ---------------------------------------------------------------
     def initialize_model(self, model_id: str, num_shards: int, cache_dir: str = "./models"):
@@ -181,8 +185,7 @@ class MasterNode:
     def _send(self, worker, command, payload=None, metadata=None) -> bool:
         md = dict(metadata or {})
         md["identity"] = worker["identity"]
-        with self._send_lock:
-            return self._protocol.send_message(self.server_socket, command, payload, md)
+        return self._owned.send(command, payload, md)  # any thread: the accept thread puts it on the wire
 
     # ---- inference (reference :117-138, :227-277) -----------------------------------------------------------------
     def run_inference(self, input_text: Union[str, Sequence[int], torch.Tensor], timeout: int = 60,
@@ -239,6 +242,15 @@ class MasterNode:
             raise RuntimeError(header["error"])
         return pickle.loads(body) if body else {}
 
+    def _drain_replies(self, task_id: str) -> None:
+        """Drop answers still queued for this task (a late RESULT must not be taken for the next request's)."""
+        q = self._replies.get(task_id)
+        while q is not None and not q.empty():
+            try:
+                q.get_nowait()
+            except Empty:
+                break
+
     def _fused_decode(self, task_id: str, first_tokens: torch.Tensor, n_steps: int, timeout: float = 300.0) -> Optional[torch.Tensor]:
         """Greedy decode of `n_steps` further tokens for the micro-batches whose prefill just ran (`first_tokens`:
         [n_micro, rows], sequence slots m * rows + r), with the hand-off fused into the stages' kernels (workers:
@@ -266,15 +278,25 @@ class MasterNode:
                 self._request(wk, task_id, "MAILBOX_CONNECT", infos[(st + 1) % len(workers)], {"stage": st})
             self._request(workers[0], task_id, "MAILBOX_POST", {"tokens": first_tokens.to(torch.int32), "ticket": 1}, {"stage": 0})
             seq = torch.arange(n_micro * rows, dtype=torch.int32)
+            loop = {"n_micro": n_micro, "rows": rows, "n_steps": n_steps, "step_base": 0}
+            # pre-flight: every stage checks shape, mailboxes, context limit and reserves its KV pages.  Nothing is
+            # launched unless all accept -- a refusal here raises RuntimeError and the caller falls back to the relay.
+            positions = []
+            for st, (wk, sid) in enumerate(zip(workers, shard_ids)):
+                ans = self._request(wk, task_id, "PREPARE_DECODE_LOOP", {"seq_ids": seq, "positions": None},
+                                    {"shard_id": sid, "stage": st, **loop})
+                positions.append(ans["positions"])
             for st, (wk, sid) in enumerate(zip(workers, shard_ids)):  # every stage starts its loop; they finish together
-                self._send(wk, "RUN_DECODE_LOOP", pickle.dumps({"seq_ids": seq, "positions": None}),
-                           {"task_id": task_id, "shard_id": sid, "n_micro": n_micro, "rows": rows, "n_steps": n_steps, "step_base": 0, "stage": st})
+                self._send(wk, "RUN_DECODE_LOOP", pickle.dumps({"seq_ids": seq, "positions": positions[st]}),
+                           {"task_id": task_id, "shard_id": sid, "stage": st, **loop})
             fed, errors = None, []
             for _ in workers:  # wait for every stage, also when one of them failed: no reply may be left in the queue
                 try:
                     header, body = self._replies[task_id].get(timeout=timeout)
                 except Empty:
-                    raise TimeoutError("a stage did not finish its decode loop")
+                    # a launched loop that never finishes: its kernels trap after 20 s without a ticket, which costs the
+                    # worker its CUDA context -- that worker has to be restarted; do not fall back onto it
+                    raise TimeoutError("a stage did not finish its decode loop (restart its worker)")
                 if header.get("error"):
                     errors.append(header["error"])
                 elif header.get("stage") == 0:
@@ -312,6 +334,7 @@ class MasterNode:
                 fused = self._fused_decode(task_id, torch.stack(first), max_new - 1)
             except RuntimeError as e:
                 print(f"fused decode unavailable ({e}); falling back to the per-step loop")
+                self._drain_replies(task_id)
         self.last_decode_path = "fused" if fused is not None else "per-step"
         if fused is not None:
             tokens = torch.cat([tokens, fused], dim=2)
@@ -335,6 +358,8 @@ class MasterNode:
             try:
                 task_id, request, max_new = self.task_queue.get(block=True, timeout=0.2)
             except Empty:
+                for w in self.evict_stale_workers():   # idle: workers whose heartbeat stopped leave the pipeline
+                    print(f"Worker {w} evicted: no heartbeat for {self.heartbeat_timeout:.0f} s")
                 continue
             done = self._finished.get(task_id)
             self._replies[task_id] = Queue()
@@ -361,8 +386,7 @@ class MasterNode:
                             fused = fused[0] if fused is not None else None
                         except RuntimeError as e:  # e.g. a shape the persistent kernel does not take: fall back below
                             print(f"fused decode unavailable ({e}); falling back to the per-step loop")
-                            while not self._replies[task_id].empty():
-                                self._replies[task_id].get_nowait()
+                            self._drain_replies(task_id)
                     self.last_decode_path = "fused" if fused is not None else "per-step"
                     if fused is not None:
                         tokens.extend(fused[:, i] for i in range(fused.shape[1]))
@@ -387,7 +411,7 @@ class MasterNode:
     def _accept_connections(self):
         while self.running:
             try:
-                header, payload = self._protocol.receive_message(self.server_socket, timeout=0.2)
+                header, payload = self._owned.receive(timeout=0.2)
             except TimeoutError:
                 continue
             except Exception as e:

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import pickle
 import socket
+import threading
 from typing import Any, Dict, Optional, Tuple
 
 try:
@@ -136,21 +137,25 @@ class MessageProtocol:
 
     # ---- ZeroMQ framing -------------------------------------------------------------------------------
     @staticmethod
+    def _zmq_frames(sock_type, command, payload, metadata) -> list:
+        header = {"command": command}
+        identity = None
+        if metadata:
+            header.update(metadata)
+            identity = header.pop("identity", None)
+        if payload is not None:
+            header["payload_size"] = len(payload)
+        frames = [pickle.dumps(header), payload if payload is not None else b""]
+        if sock_type == zmq.ROUTER:
+            if identity is None:
+                raise ValueError("ROUTER send needs metadata['identity']")
+            frames.insert(0, identity)
+        return frames
+
+    @staticmethod
     def _send_zmq(sock, command, payload, metadata) -> bool:
         try:
-            header = {"command": command}
-            identity = None
-            if metadata:
-                header.update(metadata)
-                identity = header.pop("identity", None)
-            if payload is not None:
-                header["payload_size"] = len(payload)
-            frames = [pickle.dumps(header), payload if payload is not None else b""]
-            if sock.type == zmq.ROUTER:
-                if identity is None:
-                    raise ValueError("ROUTER send needs metadata['identity']")
-                frames.insert(0, identity)
-            sock.send_multipart(frames)
+            sock.send_multipart(MessageProtocol._zmq_frames(sock.type, command, payload, metadata))
             return True
         except Exception as e:
             print(f"Error sending ZMQ message: {e}")
@@ -160,9 +165,12 @@ class MessageProtocol:
     def _receive_zmq(sock, timeout) -> Tuple[Dict[str, Any], Optional[bytes]]:
         if not sock.poll(int(timeout * 1000)):
             raise TimeoutError("Timeout while receiving ZMQ message")
-        parts = sock.recv_multipart()
+        return MessageProtocol._parse_zmq(sock.type, sock.recv_multipart())
+
+    @staticmethod
+    def _parse_zmq(sock_type, parts) -> Tuple[Dict[str, Any], Optional[bytes]]:
         identity = None
-        if sock.type == zmq.ROUTER:
+        if sock_type == zmq.ROUTER:
             identity, parts = parts[0], parts[1:]
         if not parts:
             return {}, None
@@ -178,3 +186,76 @@ class MessageProtocol:
 
     def _receive_zmq_message(self, timeout: int = 60):
         return MessageProtocol._receive_zmq(self.zmq_socket, timeout)
+
+
+class OwnedSocket:
+    """A ZeroMQ socket with ONE owning thread.  libzmq sockets are not thread-safe, and both nodes have several threads
+    that want to talk on the same socket (the reference shares its sockets between threads unguarded: heartbeat,
+    handler and task threads, src/worker/node.py:124-126,263-276, src/master/node.py:39-46).  Here the thread that
+    receives owns the socket; every other thread hands its frames to it through a thread-local inproc PUSH socket, and
+    the owner forwards them between polls -- it blocks on both at once, so a send is on the wire as soon as the owner
+    wakes up, and nothing is ever sent and received on the socket by two threads at a time."""
+
+    def __init__(self, context, sock):
+        self.context, self.sock = context, sock
+        self.endpoint = f"inproc://dllm-outbox-{id(self):x}"
+        self._pull = context.socket(zmq.PULL)
+        self._pull.setsockopt(zmq.LINGER, 0)
+        self._pull.bind(self.endpoint)
+        self._poller = zmq.Poller()
+        self._poller.register(self.sock, zmq.POLLIN)
+        self._poller.register(self._pull, zmq.POLLIN)
+        self._local = threading.local()
+        self._closed = False
+
+    def send(self, command: str, payload: Optional[bytes] = None, metadata: Optional[Dict[str, Any]] = None) -> bool:
+        """From any thread."""
+        if self._closed:
+            return False
+        try:
+            frames = MessageProtocol._zmq_frames(self.sock.type, command, payload, metadata)
+            push = getattr(self._local, "push", None)
+            if push is None:
+                push = self.context.socket(zmq.PUSH)
+                push.setsockopt(zmq.LINGER, 0)
+                push.connect(self.endpoint)
+                self._local.push = push
+            push.send_multipart(frames)
+            return True
+        except Exception as e:
+            print(f"Error sending ZMQ message: {e}")
+            return False
+
+    def _forward_outgoing(self) -> None:
+        while True:
+            try:
+                frames = self._pull.recv_multipart(zmq.NOBLOCK)
+            except zmq.Again:
+                return
+            self.sock.send_multipart(frames)
+
+    def receive(self, timeout: float = 60) -> Tuple[Dict[str, Any], Optional[bytes]]:
+        """Owning thread only.  Forwards whatever other threads queued, returns the next incoming message or raises
+        TimeoutError."""
+        import time
+        deadline = time.monotonic() + timeout
+        while True:
+            self._forward_outgoing()
+            left = deadline - time.monotonic()
+            if left <= 0:
+                raise TimeoutError("Timeout while receiving ZMQ message")
+            events = dict(self._poller.poll(int(left * 1000) + 1))
+            if self._pull in events:
+                self._forward_outgoing()
+            if self.sock in events:
+                return MessageProtocol._parse_zmq(self.sock.type, self.sock.recv_multipart())
+
+    def close(self) -> None:
+        """Owning thread (or after it has stopped)."""
+        self._closed = True
+        try:
+            self._forward_outgoing()
+        except Exception:
+            pass
+        self._pull.close()
+        self.sock.close()

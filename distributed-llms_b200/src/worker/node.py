@@ -30,7 +30,7 @@ except Exception:  # pragma: no cover
 
 from ..engine import cabi
 from ..engine.shard_exec import CONFIG_KEY, ShardExecutor, decode_config
-from ..network.protocol import MessageProtocol
+from ..network.protocol import MessageProtocol, OwnedSocket
 
 META_KEYS = ("positions", "seq_ids")
 
@@ -174,6 +174,7 @@ class WorkerNode:
         self.zmq_context = zmq.Context.instance() if zmq is not None else None
         self._shards_lock = threading.Lock()  # reference mutates self.shards from several threads unlocked
         self._protocol: Optional[MessageProtocol] = None
+        self._owned: Optional[OwnedSocket] = None  # the DEALER socket to the master: owned by the _handle_master thread
 
     # -- life cycle (reference :45-99) ------------------------------------------------------------------
     def start(self, block: bool = False):
@@ -212,8 +213,9 @@ class WorkerNode:
         self.running = False
         if self.server_socket:
             self.server_socket.close()
-        if self.master_socket:
-            self.master_socket.close()
+        t = getattr(self, "_master_thread", None)
+        if t is not None and t is not threading.current_thread():
+            t.join(timeout=3.0)   # that thread owns the master socket and closes it on its way out
 
     # -- control plane (reference :101-187) ---------------------------------------------------------------
     def _connect_to_master(self, retries: int = 3):
@@ -231,8 +233,10 @@ class WorkerNode:
                     "pid": os.getpid(),
                     "device_index": self._device_index() if torch.cuda.is_available() else -1,
                 }
-                self._protocol.send_message(self.master_socket, "REGISTER", metadata={"capabilities": capabilities})
-                threading.Thread(target=self._handle_master, daemon=True).start()
+                self._owned = OwnedSocket(self.zmq_context, self.master_socket)
+                self._owned.send("REGISTER", metadata={"capabilities": capabilities})  # on the wire once the owner polls
+                self._master_thread = threading.Thread(target=self._handle_master, daemon=True)
+                self._master_thread.start()
                 print(f"Successfully connected to master at {self.master_address}")
                 return
             except Exception as e:  # bounded retry instead of the reference's unbounded recursion (:130-136)
@@ -267,7 +271,7 @@ class WorkerNode:
         try:
             while self.running:
                 try:
-                    header, payload = self._protocol.receive_message(self.master_socket, timeout=1)
+                    header, payload = self._owned.receive(timeout=0.5)
                 except TimeoutError:
                     continue
                 if not header:
@@ -276,6 +280,10 @@ class WorkerNode:
         except Exception as e:
             if self.running:
                 print(f"Error handling master connection: {e}")
+        finally:
+            owned, self._owned, self.master_socket = self._owned, None, None
+            if owned is not None:
+                owned.close()
 
     # -- shard-execution entry point (reference :189-261) ---------------------------------------------------
     def _device_index(self) -> int:
@@ -310,7 +318,7 @@ class WorkerNode:
             for slot, toks in enumerate(args["tokens"]):
                 self._inbox.post_tokens(slot, torch.as_tensor(toks, dtype=torch.int32), int(args["ticket"]))
             return {}
-        if command == "RUN_DECODE_LOOP":
+        if command in ("PREPARE_DECODE_LOOP", "RUN_DECODE_LOOP"):
             if self._outbox is None:
                 raise RuntimeError("the mailbox of the next stage is not connected")
             ex = self.shards[header["shard_id"]].executor
@@ -320,6 +328,11 @@ class WorkerNode:
             if pos is None:  # continue every sequence where its cache ends
                 pos = torch.tensor([ex.seq_len(int(s)) for s in seq.reshape(-1)], dtype=torch.int32)
             pos = torch.as_tensor(pos, dtype=torch.int32).reshape(n_micro, rows)
+            if command == "PREPARE_DECODE_LOOP":
+                # everything that can refuse the loop is checked (and the KV pages reserved) before ANY stage starts:
+                # a stage failing after its neighbours launched would leave them waiting for tickets that never come
+                ex.check_decode_pipelined(self._inbox, self._outbox, n_micro, rows, n_steps, pos, seq)
+                return {"positions": pos}
             fed = ex.decode_pipelined(self._inbox, self._outbox, n_micro, rows, n_steps, int(header.get("step_base", 0)), pos, seq)
             torch.cuda.synchronize()
             return {"fed": fed.cpu() if fed is not None else None}
@@ -340,7 +353,12 @@ class WorkerNode:
 
     def _dispatch_command(self, sock, command, header, payload, protocol: Optional[MessageProtocol] = None):
         protocol = protocol or MessageProtocol()
-        if command.startswith("MAILBOX_") or command == "RUN_DECODE_LOOP":
+        if sock is not None and sock is self.master_socket and self._owned is not None:
+            class _ViaOwner:  # replies to the master leave through the socket's owner (OwnedSocket)
+                def send_message(_, _sock, command, payload=None, metadata=None, owned=self._owned):
+                    return owned.send(command, payload, metadata)
+            protocol = _ViaOwner()
+        if command.startswith("MAILBOX_") or command in ("RUN_DECODE_LOOP", "PREPARE_DECODE_LOOP"):
             task_id = header.get("task_id")
             md = {"task_id": task_id, "stage": header.get("stage")}
             try:
@@ -382,8 +400,8 @@ class WorkerNode:
     def _send_heartbeat(self):
         while self.running:
             try:
-                if self.master_socket is not None and self._protocol is not None:
-                    self._protocol.send_message(self.master_socket, "HEARTBEAT", metadata={"timestamp": time.time()})
+                if self._owned is not None:
+                    self._owned.send("HEARTBEAT", metadata={"timestamp": time.time()})
                 time.sleep(5)
             except Exception as e:
                 print(f"Error sending heartbeat: {e}")

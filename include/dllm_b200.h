@@ -205,6 +205,13 @@ DLLM_API int dllm_shard_decode_pipelined(dllm_shard* shard, dllm_mailbox* inbox,
                                 int32_t rows, int32_t n_steps, uint32_t step_base, const int32_t* positions,
                                 const int32_t* seq_ids, int32_t* fed_tokens_out, void* stream);
 
+/* Pre-flight of dllm_shard_decode_pipelined: the same checks, no launch, nothing enqueued.  Belongs to the master's decode
+ * loop that the reference lacks (src/master/node.py:227-277 broadcasts once): the master asks every stage first and starts
+ * the stages' loops only when all of them accept -- a stage that refused after its neighbours had started would leave them
+ * spinning on tickets that never arrive (they give up after 20 s with a device trap that costs the worker its context). */
+DLLM_API int dllm_shard_decode_pipelined_check(dllm_shard* shard, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
+                                      int32_t rows, int32_t n_steps);
+
 /* Replaces `MessageProtocol.send_message` / `receive_message` (reference
  * src/network/protocol.py:38-129) for the data plane inside one NVLink box: copy the hand-off tile
  * (`bytes` of hidden states) from this device to `dst_ptr` on device `dst_device` over NVLink
