@@ -118,8 +118,12 @@ struct PrefillAttnParams {
     const int32_t* seq_ids;
     void* out;               // [R, H*hd] bf16
     int32_t n_seqs, rows_per_seq, n_heads, n_kv_heads, head_dim;
+    int32_t num_pages;       // pages in each pool (the TMA tensor maps of the tcgen05 kernel cover the whole pool); 0 = unknown
 };
 cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st);
+// tcgen05 / TMA form (prefill_attention_tc.cu): 64-token pages, head_dim 64 or 128; launch_prefill_attn dispatches to it
+bool prefill_attn_tc_supported(const PrefillAttnParams& p);
+cudaError_t launch_prefill_attn_tc(const PrefillAttnParams& p, cudaStream_t st);
 
 // Each returns cudaGetLastError() of its launch.  dtype: 0 = bf16, 1 = fp32.
 cudaError_t gemv_init_device();  // once per device, outside stream capture

@@ -230,6 +230,7 @@ static cudaError_t launch_attn_t(const PrefillAttnParams& p, cudaStream_t st) {
 
 cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {
     if (p.n_seqs <= 0 || p.rows_per_seq <= 0 || p.n_heads % p.n_kv_heads) return cudaErrorInvalidValue;
+    if (prefill_attn_tc_supported(p)) return launch_prefill_attn_tc(p, st);  // TMA + tcgen05 (64-token pages, hd 64 / 128)
     // 128-row query tiles (8 warps share each K/V tile) once there are enough of them to fill the GPU
     const char* env = getenv("DLLM_PREFILL_QT128");  // "0": never, "1": always (tests), unset: by grid size
     const bool big = env ? env[0] == '1' : (long)((p.rows_per_seq + 127) / 128) * p.n_heads * p.n_seqs >= 296;

@@ -242,9 +242,9 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
         *it.p = s->arena + off;
         off += it.bytes;
     }
-    // zero everything that is not KV (counters must start at zero); KV pages are written before they are read
-    const size_t head_bytes = (size_t)((char*)(c.n_layers ? s->kpool[0] : (void*)(s->arena + total)) - s->arena);
-    e = cudaMemset(s->arena, 0, head_bytes);
+    // zero everything: counters must start at zero, and the tcgen05 attention multiplies whole 16-token blocks of V --
+    // rows past the end of a context meet a zero probability, which only helps if they never held NaN bit patterns
+    e = cudaMemset(s->arena, 0, total);
     if (e == cudaSuccess) e = cudaMemset(s->block_table, 0xff, (size_t)c.max_seqs * s->pages_per_seq * 4);  // -1
     std::vector<int32_t> ar(c.max_rows);
     for (int i = 0; i < c.max_rows; ++i) ar[i] = i;
@@ -637,6 +637,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
             a.q = s->qbuf; a.kv = kv; a.positions = s->pos; a.seq_ids = s->seq; a.out = s->attn_out;
             a.n_seqs = run_seqs; a.rows_per_seq = run_len; a.n_heads = c.n_heads; a.n_kv_heads = c.n_kv_heads;
             a.head_dim = c.head_dim;
+            a.num_pages = s->num_pages;
             CUDA_TRY(launch_prefill_attn(a, st));
         } else {
             AttnParams a{};

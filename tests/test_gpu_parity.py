@@ -517,6 +517,27 @@ def test_long_context_decode_matches_oracle(batch, prompt_len, qt128, monkeypatc
     check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
 
 
+@pytest.mark.parametrize("hd,H,KV", [(64, 8, 2), (128, 4, 1)])
+@pytest.mark.parametrize("batch,T,max_rows", [(1, 130, 256), (2, 300, 1024), (1, 700, 256)])
+def test_tcgen05_prefill_attention_against_oracle_and_mma_sync_kernel(hd, H, KV, batch, T, max_rows, monkeypatch):
+    """The TMA + tcgen05 prefill attention (64-token pages, head_dim 64 / 128) on ragged tile edges -- prompts that end
+    inside a 128-row query tile and inside a KV page, several sequences, a prompt fed in chunks (queries that start
+    deep inside the context) -- against the bf16 oracle, and against the mma.sync kernel it replaces."""
+    cfg = ShardModelConfig("llama", H * hd, 2, H, KV, hd, 512, 500, 1024, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 21, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, batch, T, seed=T)
+    sdd = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+    o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16, max_context=T + 8), prompts, 2, record=True)
+    outs = {}
+    for tc in ("1", "0"):
+        monkeypatch.setenv("DLLM_PREFILL_ATTN_TC", tc)
+        stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=max_rows, max_seqs=batch, max_context=T + 8, page_size=64)
+        ids, lg = gpu_generate(stages, prompts, 2)
+        check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
+        outs[tc] = lg
+    assert bf16_logits_close(outs["1"][:, 0], outs["0"][:, 0])
+
+
 @pytest.mark.parametrize("model", ["llama3-8b", "qwen2.5-14b", "llama3-70b"])
 def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
     """Two layers at the real widths of the BASELINE configs (hidden 4096 / 5120 / 8192, GQA 4 / 5 / 8, head_dim 128,
