@@ -93,6 +93,10 @@ constexpr uint32_t make_idesc(int bn) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 }
 
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
 __device__ __forceinline__ float silu_f(float g) { return g / (1.0f + expf(-g)); }
 __device__ __forceinline__ float gelu_new_f(float x) {
     return 0.5f * x * (1.0f + tanhf(0.7978845608028654f * (x + 0.044715f * x * x * x)));
@@ -187,6 +191,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16);
         bf16* out = static_cast<bf16*>(p.c) + col0;
         const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
+        // A thread owns one output row and, per tcgen05.ld, 32 consecutive columns of it: 64 bytes of bf16.  They leave
+        // as four 16-byte stores (and the residual / bias arrive as 16-byte loads): every store fills half a sector,
+        // where one bf16 pair per instruction touched 32 rows with 4 bytes each.
+        const bool vec_ok = (p.ldc % 8 == 0) && (col0 % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0) &&
+                            (!bias || (reinterpret_cast<uintptr_t>(bias) & 15) == 0);
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += 32) {
             uint32_t acc[32], acc2[32];
@@ -194,30 +203,66 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             if (kDual) tc_ld32(tbase + BN + c0, acc2);
             if (row < p.M) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 2) {
-                    const int n = n0 + c0 + j;
-                    if (n >= seg_n) break;
-                    float v0 = __uint_as_float(acc[j]), v1 = __uint_as_float(acc[j + 1]);
-                    if (EPI == GEMM_EPI_SWIGLU) {
-                        const float g0 = bf16_round(v0), g1 = bf16_round(v1);
-                        const float u0 = bf16_round(__uint_as_float(acc2[j])), u1 = bf16_round(__uint_as_float(acc2[j + 1]));
-                        v0 = bf16_round(silu_f(g0)) * u0;
-                        v1 = bf16_round(silu_f(g1)) * u1;
-                    } else {
-                        v0 = bf16_round(v0 + (bias ? __bfloat162float(bias[n]) : 0.f));
-                        v1 = bf16_round(v1 + (bias && n + 1 < seg_n ? __bfloat162float(bias[n + 1]) : 0.f));
-                        if (EPI == GEMM_EPI_RESIDUAL) {
-                            const uint32_t old = *reinterpret_cast<const uint32_t*>(out + (size_t)row * p.ldc + n);
-                            v0 += __uint_as_float(old << 16);
-                            v1 += __uint_as_float(old & 0xffff0000u);
-                        } else if (EPI == GEMM_EPI_GELU) {
-                            v0 = gelu_new_f(v0);
-                            v1 = gelu_new_f(v1);
+                for (int j8 = 0; j8 < 32; j8 += 8) {
+                    const int n8 = n0 + c0 + j8;
+                    if (n8 >= seg_n) break;
+                    bf16* dst = out + (size_t)row * p.ldc + n8;
+                    if (vec_ok && n8 + 8 <= seg_n) {
+                        float v[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(acc[j8 + j]);
+                        if (EPI == GEMM_EPI_SWIGLU) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                v[j] = bf16_round(silu_f(bf16_round(v[j]))) * bf16_round(__uint_as_float(acc2[j8 + j]));
+                        } else {
+                            if (bias) {
+                                float bf[8];
+                                unpack<bf16>(ld_u4(bias + n8), bf);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) v[j] += bf[j];
+                            }
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = bf16_round(v[j]);
+                            if (EPI == GEMM_EPI_RESIDUAL) {
+                                float of[8];
+                                unpack<bf16>(*reinterpret_cast<const uint4*>(dst), of);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) v[j] += of[j];
+                            } else if (EPI == GEMM_EPI_GELU) {
+#pragma unroll
+                                for (int j = 0; j < 8; ++j) v[j] = gelu_new_f(v[j]);
+                            }
                         }
+                        uint4 w;
+                        w.x = pack2(v[0], v[1]); w.y = pack2(v[2], v[3]); w.z = pack2(v[4], v[5]); w.w = pack2(v[6], v[7]);
+                        *reinterpret_cast<uint4*>(dst) = w;
+                        continue;
                     }
-                    // N is even for every weight shape in use; a lone last column is written alone
-                    if (n + 1 < seg_n) *reinterpret_cast<__nv_bfloat162*>(out + (size_t)row * p.ldc + n) = __floats2bfloat162_rn(v0, v1);
-                    else out[(size_t)row * p.ldc + n] = __float2bfloat16_rn(v0);
+#pragma unroll
+                    for (int j = j8; j < j8 + 8; j += 2) {   // ragged edge / unaligned output: pairs
+                        const int n = n0 + c0 + j;
+                        if (n >= seg_n) break;
+                        float v0 = __uint_as_float(acc[j]), v1 = __uint_as_float(acc[j + 1]);
+                        if (EPI == GEMM_EPI_SWIGLU) {
+                            const float g0 = bf16_round(v0), g1 = bf16_round(v1);
+                            const float u0 = bf16_round(__uint_as_float(acc2[j])), u1 = bf16_round(__uint_as_float(acc2[j + 1]));
+                            v0 = bf16_round(silu_f(g0)) * u0;
+                            v1 = bf16_round(silu_f(g1)) * u1;
+                        } else {
+                            v0 = bf16_round(v0 + (bias ? __bfloat162float(bias[n]) : 0.f));
+                            v1 = bf16_round(v1 + (bias && n + 1 < seg_n ? __bfloat162float(bias[n + 1]) : 0.f));
+                            if (EPI == GEMM_EPI_RESIDUAL) {
+                                v0 += __bfloat162float(out[(size_t)row * p.ldc + n]);
+                                if (n + 1 < seg_n) v1 += __bfloat162float(out[(size_t)row * p.ldc + n + 1]);
+                            } else if (EPI == GEMM_EPI_GELU) {
+                                v0 = gelu_new_f(v0);
+                                v1 = gelu_new_f(v1);
+                            }
+                        }
+                        out[(size_t)row * p.ldc + n] = __float2bfloat16_rn(v0);
+                        if (n + 1 < seg_n) out[(size_t)row * p.ldc + n + 1] = __float2bfloat16_rn(v1);
+                    }
                 }
             }
         }

@@ -9,6 +9,8 @@ import torch  # noqa: E402
 from src.engine import cabi  # noqa: E402
 
 SHAPES = [  # (name, M, N, K)
+    ("tinyllama qkv  M=512 ", 512, 2560, 2048), ("tinyllama o    M=512 ", 512, 2048, 2048),
+    ("tinyllama down M=512 ", 512, 2048, 5632),
     ("llama8b qkv    M=512 ", 512, 6144, 4096), ("llama8b o      M=512 ", 512, 4096, 4096),
     ("llama8b down   M=512 ", 512, 4096, 14336), ("llama8b qkv    M=4096", 4096, 6144, 4096),
     ("llama8b o      M=4096", 4096, 4096, 4096), ("llama8b down   M=4096", 4096, 4096, 14336),
