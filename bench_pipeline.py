@@ -20,7 +20,6 @@ def run_pipeline(args) -> int:
     from src.engine import cabi
     from src.engine.pipeline import ShardStepper, StagePipeline
     from src.model import random_init
-    from src.model.shard_manager import balanced_partition
     from src.network.handoff import StageLink, exchange_mailboxes, init_stage_group
     from src.worker.node import ModelShard
 
@@ -38,13 +37,21 @@ def run_pipeline(args) -> int:
     W = max(args.warmup if args.warmup >= 0 else 4, 3)
     hf = random_init.NAMED_CONFIGS[model]
     L = hf["num_hidden_layers"]
-    # the last stage also streams the lm_head: give it fewer layers (head bytes / bytes of one layer)
-    per_layer = stage_bytes_per_step(hf, 1, False, 1, 0.0)
-    head_cost = (stage_bytes_per_step(hf, 0, True, 1, 0.0)) / per_layer
-    partition = balanced_partition(L, world, head_cost)
-    layers = partition[rank]
+    # Stages are contiguous runs of BLOCKS (a layer's attention block, its MLP block): a boundary may fall inside a layer --
+    # the residual row is the hand-off either way -- and the last stage, which also streams the lm_head, gets fewer of
+    # them.  Costs = bytes one decode step streams.
+    d_, H_, KV_ = hf["hidden_size"], hf["num_attention_heads"], hf.get("num_key_value_heads", hf["num_attention_heads"])
+    hd_ = hf.get("head_dim") or d_ // H_
+    attn_cost = 2.0 * (2 * d_ * H_ * hd_ + 2 * d_ * KV_ * hd_)
+    mlp_cost = 2.0 * 3 * d_ * hf["intermediate_size"]
+    head_cost = stage_bytes_per_step(hf, 0, True, 1, 0.0)
+    from src.model.shard_manager import block_partition
+    stages_blocks = block_partition(L, world, attn_cost, mlp_cost, head_cost)
+    blocks = stages_blocks[rank]
+    block_w = {"full": 1.0, "attn": attn_cost / (attn_cost + mlp_cost), "mlp": mlp_cost / (attn_cost + mlp_cost)}
+    layers_eq = [sum(block_w[b] for _, b in st) for st in stages_blocks]   # stage sizes in layer equivalents
     first, last = rank == 0, rank == world - 1
-    params = random_init.random_stage_parameters(hf, layers, first, last, 1234, torch.bfloat16, device=str(dev))
+    params = random_init.random_stage_parameters(hf, blocks, first, last, 1234, torch.bfloat16, device=str(dev))
     max_ctx = prompt_len + 3 * (W + K) + 16
     shard = ModelShard(rank, params, config=hf, max_rows=max(128, min(batch * prompt_len, 4096)), max_seqs=n_micro * batch,
                        max_context=max_ctx, page_size=64)
@@ -264,7 +271,9 @@ def run_pipeline(args) -> int:
 
     # per-stage roofline: every stage runs n_micro * K micro-batch steps in the timed region
     ctx_mid = prompt_len + W + K / 2.0
-    my_bytes = stage_bytes_per_step(hf, len(layers), last, batch, ctx_mid)
+    n_attn = sum(1 for _, b in blocks if b != "mlp")   # layers whose KV this stage reads
+    my_bytes = (stage_bytes_per_step(hf, 1, False, 1, 0.0) * layers_eq[rank] + (head_cost if last else 0.0)
+                + n_attn * batch * ctx_mid * 2 * KV_ * hd_ * 2)
     fr = torch.zeros(world, device=dev)
     fr[rank] = my_bytes * n_micro * K / (dec_ms * 1e-3) / 1e9 / hbm_peak
     dist.all_reduce(fr)
@@ -275,7 +284,8 @@ def run_pipeline(args) -> int:
             "ms_per_step": dec_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": make_config(model, batch, prompt_len, world, L, n_micro),
-            "detail": {"layers_per_stage": [len(r) for r in partition],
+            "detail": {"layers_per_stage": [round(x, 2) for x in layers_eq],
+                       "stage_blocks": [f"{st[0][0]}{'' if st[0][1] == 'full' else ':' + st[0][1]}..{st[-1][0]}{'' if st[-1][1] == 'full' else ':' + st[-1][1]}" for st in stages_blocks],
                        "handoff": ("fused: peer stores from the down-projection epilogue into the next stage's mailbox + tickets"
                                    if fused else "NCCL send/recv per micro-batch step (batch above the persistent kernel's rows)")},
             "tokens_checked": ok, "token_check": checked,
@@ -302,8 +312,7 @@ def run_pipeline(args) -> int:
             "prefill": {"tokens_per_sec": n_micro * batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
                         # the busiest stage's flops for all micro-batches over the whole (pipelined) prefill time:
                         # includes the fill and drain bubbles of the (stages + micro-batches - 1)-slot schedule
-                        "roofline": prefill_roofline(n_micro * stage_prefill_flops(hf, max(len(r) for r in partition), False,
-                                                                                  batch, prompt_len), prefill_ms),
+                        "roofline": prefill_roofline(n_micro * stage_prefill_flops(hf, 1, False, batch, prompt_len) * max(layers_eq), prefill_ms),
                         "note": "micro-batches follow each other through the stages; tcgen05 GEMMs + flash-style attention per stage"},
         }
         print(json.dumps(line))

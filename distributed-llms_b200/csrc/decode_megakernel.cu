@@ -618,7 +618,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 if (r < R && n < ph.n0)
                     old_pref = __ldcg(reinterpret_cast<const uint32_t*>(h_m + (size_t)r * ph.n0 + n));
             }
-            const bool send_rows = piped && p.out_hidden && ph.kind == MK_DOWN && ph.layer == p.last_layer;
+            const bool send_rows = piped && p.out_hidden && phi == p.out_phase;
             ArgBest best = {-FLT_MAX, INT_MAX};
             // panels are processed in rounds of MK_ROUND_PANELS so that the partial buffer stays small however many
             // panels a CTA owns (the lm_head: ~100 per CTA); inside a round every warp takes an equal chunk of stages

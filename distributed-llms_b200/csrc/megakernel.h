@@ -79,7 +79,7 @@ struct MkParams {
     int32_t n_micro;
     uint32_t ticket_base;    // decode step number of this launch's first step
     int32_t flag_stride;     // uint32 elements between two slots' tickets
-    int32_t last_layer;      // layer whose down projection produces the stage's output
+    int32_t out_phase;       // index of the phase whose epilogue produces the stage's output rows (its last o- or down projection)
     unsigned* in_flag;       // local inbox: tickets,
     const int32_t* in_tokens;//   token ids [n_micro][R] (first stage),
     void* in_hidden;         //   hidden rows [n_micro][R][d] (other stages; used in place as the residual stream)

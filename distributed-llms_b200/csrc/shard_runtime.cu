@@ -95,7 +95,7 @@ struct dllm_shard {
     MkLayer* mk_layers = nullptr;
     unsigned* mk_sync = nullptr;  // [0] barrier, [1] done, [2] argmax ticket
     void* mk_packed = nullptr;    // streaming-layout copy of the weights (megakernel.h)
-    int mk_n_phases = 0, mk_k_max = 0, mk_part_units = 1;
+    int mk_n_phases = 0, mk_k_max = 0, mk_part_units = 1, mk_out_phase = -1;
     bool mk_enabled = false, mk_packed_ok = false;
     std::vector<void*> kpool, vpool;
     // geometry
@@ -115,6 +115,10 @@ struct dllm_shard {
 };
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// which blocks of local layer l this stage holds (a boundary may fall between a layer's attention and MLP blocks)
+static bool has_attn(const dllm_shard_config& c, int l) { return !(l == 0 && c.first_layer_mlp_only); }
+static bool has_mlp(const dllm_shard_config& c, int l) { return !(l == c.n_layers - 1 && c.last_layer_attn_only); }
 
 static int pick_splits(const dllm_shard* s, int n_rows) {
     const int H = s->cfg.n_heads;
@@ -144,6 +148,15 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
         return fail("dllm_shard_create: hidden, ffn and H*hd must be multiples of the 16-byte vector width");
     if (c.page_size < 8 || (c.page_size & (c.page_size - 1))) return fail("dllm_shard_create: page_size must be a power of two >= 8");
     if (c.max_rows <= 0 || c.max_seqs <= 0 || c.max_context <= 0) return fail("dllm_shard_create: max_rows/max_seqs/max_context must be positive");
+    if ((c.first_layer_mlp_only || c.last_layer_attn_only) && c.n_layers < 1) return fail("dllm_shard_create: a split layer needs n_layers >= 1");
+    if (c.first_layer_mlp_only && c.last_layer_attn_only && c.n_layers < 2) return fail("dllm_shard_create: one layer cannot be both MLP-only and attention-only");
+    if (c.first_layer_mlp_only && c.has_embed) return fail("dllm_shard_create: the stage with the embedding starts with a whole layer");
+    if (c.last_layer_attn_only && c.has_head) return fail("dllm_shard_create: the stage with the head ends with a whole layer");
+    for (int l = 0; l < c.n_layers; ++l) {
+        const dllm_layer_weights& w = layers[l];
+        if (has_attn(c, l) && (!w.norm1_w || !w.wq || !w.wk || !w.wv || !w.wo)) return fail("dllm_shard_create: attention weights missing");
+        if (has_mlp(c, l) && (!w.norm2_w || !w.w_up || !w.w_down)) return fail("dllm_shard_create: MLP weights missing");
+    }
     if (c.has_embed && !io->wte) return fail("dllm_shard_create: has_embed but wte is null");
     if (c.has_head && (!io->lm_head || !io->final_norm_w)) return fail("dllm_shard_create: has_head but lm_head/final_norm_w is null");
     if (c.arch != DLLM_ARCH_GPT2 && c.n_layers > 0 && (!io->rope_cos || !io->rope_sin))
@@ -223,8 +236,8 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     s->kpool.resize(c.n_layers);
     s->vpool.resize(c.n_layers);
     for (int l = 0; l < c.n_layers; ++l) {
-        add(&s->kpool[l], kv_layer);
-        add(&s->vpool[l], kv_layer);
+        add(&s->kpool[l], has_attn(c, l) ? kv_layer : 0);
+        add(&s->vpool[l], has_attn(c, l) ? kv_layer : 0);
     }
     size_t total = 0;
     for (auto& it : items) total += it.bytes;
@@ -291,15 +304,21 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
             const dllm_layer_weights& w = s->layers[l];
             ly[l] = MkLayer{w.norm1_w, w.norm1_b, w.bq, w.bk, w.bv, w.bo, w.norm2_w, w.norm2_b, w.b_up, w.b_down,
                             s->kpool[l], s->vpool[l]};
-            weight_phase(MK_QKV, l, (c.n_heads + 2 * c.n_kv_heads) * (c.head_dim / 8), c.hidden, Hd, w.wq, w.wk, w.wv);
-            plain_phase(MK_ATTN, l);
-            weight_phase(MK_OPROJ, l, c.hidden / 8, Hd, c.hidden, w.wo, nullptr, nullptr);
-            if (gpt2) weight_phase(MK_FC_GELU, l, c.ffn / 8, c.hidden, c.ffn, w.w_up, nullptr, nullptr);
-            else weight_phase(MK_GATEUP, l, c.ffn / 4, c.hidden, c.ffn, w.w_gate, w.w_up, nullptr);
-            weight_phase(MK_DOWN, l, c.hidden / 8, c.ffn, c.hidden, w.w_down, nullptr, nullptr);
+            if (has_attn(c, l)) {
+                weight_phase(MK_QKV, l, (c.n_heads + 2 * c.n_kv_heads) * (c.head_dim / 8), c.hidden, Hd, w.wq, w.wk, w.wv);
+                plain_phase(MK_ATTN, l);
+                weight_phase(MK_OPROJ, l, c.hidden / 8, Hd, c.hidden, w.wo, nullptr, nullptr);
+            }
+            if (has_mlp(c, l)) {
+                if (gpt2) weight_phase(MK_FC_GELU, l, c.ffn / 8, c.hidden, c.ffn, w.w_up, nullptr, nullptr);
+                else weight_phase(MK_GATEUP, l, c.ffn / 4, c.hidden, c.ffn, w.w_gate, w.w_up, nullptr);
+                weight_phase(MK_DOWN, l, c.hidden / 8, c.ffn, c.hidden, w.w_down, nullptr, nullptr);
+            }
         }
         if (c.has_head) weight_phase(MK_HEAD, 0, (c.vocab + 7) / 8, c.hidden, c.vocab, s->io.lm_head, nullptr, nullptr);
         s->mk_n_phases = (int)ph.size();
+        for (int i = 0; i < (int)ph.size(); ++i)
+            if (ph[i].kind == MK_OPROJ || ph[i].kind == MK_DOWN) s->mk_out_phase = i;  // the stage's rows are final here
         s->mk_part_units = MK_PART_UNITS;
         s->mk_k_max = std::max(std::max(c.hidden, Hd), c.ffn);
         if (me == cudaSuccess) me = cudaMemcpy(s->mk_phases, ph.data(), ph.size() * sizeof(MkPhase), cudaMemcpyHostToDevice);
@@ -405,7 +424,7 @@ static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advanc
     for (int l = 0; l < c.n_layers; ++l) {
         const dllm_layer_weights& w = s->layers[l];
         PagedKV kv{s->kpool[l], s->vpool[l], s->block_table, s->pages_per_seq, s->page_shift};
-        {   // K1: norm -> QKV -> bias -> rope -> paged append
+        if (has_attn(c, l)) {   // K1: norm -> QKV -> bias -> rope -> paged append
             GemvParams p{};
             p.x = s->h; p.n_rows = n_rows; p.K = c.hidden;
             p.norm = norm; p.norm_w = w.norm1_w; p.norm_b = w.norm1_b; p.eps = c.norm_eps;
@@ -417,7 +436,7 @@ static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advanc
             p.positions = s->pos; p.seq_ids = s->seq; p.kv = kv;
             CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
         }
-        {   // K2: split-K flash decoding
+        if (has_attn(c, l)) {   // K2: split-K flash decoding
             AttnParams a{};
             a.q = s->qbuf; a.kv = kv; a.positions = s->pos; a.seq_ids = s->seq;
             a.n_rows = n_rows; a.n_heads = c.n_heads; a.n_kv_heads = c.n_kv_heads; a.head_dim = c.head_dim;
@@ -425,14 +444,14 @@ static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advanc
             a.out = s->attn_out;
             CUDA_TRY(launch_attn_decode(dt, a, st));
         }
-        {   // K3: o-proj + residual
+        if (has_attn(c, l)) {   // K3: o-proj + residual
             GemvParams p{};
             p.x = s->attn_out; p.n_rows = n_rows; p.K = Hd; p.norm = NORM_NONE;
             p.w[0] = w.wo; p.b[0] = w.bo; p.n[0] = c.hidden;
             p.epi = EPI_RESIDUAL; p.y = s->h; p.accumulate = 1;
             CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
         }
-        {   // K4: norm -> gate/up -> SiLU*up   |   norm -> fc -> gelu_new
+        if (has_mlp(c, l)) {   // K4: norm -> gate/up -> SiLU*up   |   norm -> fc -> gelu_new
             GemvParams p{};
             p.x = s->h; p.n_rows = n_rows; p.K = c.hidden;
             p.norm = norm; p.norm_w = w.norm2_w; p.norm_b = w.norm2_b; p.eps = c.norm_eps;
@@ -441,7 +460,7 @@ static int enqueue_step(dllm_shard* s, int n_rows, int n_logit_rows, bool advanc
             p.y = s->act;
             CUDA_TRY(launch_gemv(dt, p, s->num_sms, st));
         }
-        {   // K5: down-proj + residual
+        if (has_mlp(c, l)) {   // K5: down-proj + residual
             GemvParams p{};
             p.x = s->act; p.n_rows = n_rows; p.K = c.ffn; p.norm = NORM_NONE;
             p.w[0] = w.w_down; p.b[0] = w.b_down; p.n[0] = c.hidden;
@@ -538,7 +557,7 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     p.n_micro = 1;
     if (pipe) {
         p.n_micro = pipe->n_micro; p.ticket_base = pipe->step_base; p.flag_stride = kFlagStride;
-        p.last_layer = c.n_layers - 1;
+        p.out_phase = s->mk_out_phase;
         p.in_flag = pipe->in->flags(); p.in_tokens = pipe->in->tokens();
         p.in_hidden = c.has_embed ? nullptr : pipe->in->hidden_rows();
         p.out_flag = pipe->out->flags(); p.out_tokens = pipe->out->tokens();
@@ -615,6 +634,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
     for (int l = 0; l < c.n_layers; ++l) {
         const dllm_layer_weights& w = s->layers[l];
         PagedKV kv{s->kpool[l], s->vpool[l], s->block_table, s->pages_per_seq, s->page_shift};
+        if (has_attn(c, l)) {
         CUDA_TRY(launch_norm_rows(s->h, w.norm1_w, w.norm1_b, s->xn, n_rows, c.hidden, norm, c.norm_eps, st));
         {   // q, k, v projections into column slices of one [R, QKVd] buffer
             GemmTcParams g{};
@@ -653,6 +673,8 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
             g.ldc = c.hidden; g.epi = GEMM_EPI_RESIDUAL;
             CUDA_TRY(launch_gemm_tc(g, st));
         }
+        }  // attention block
+        if (!has_mlp(c, l)) continue;
         CUDA_TRY(launch_norm_rows(s->h, w.norm2_w, w.norm2_b, s->xn, n_rows, c.hidden, norm, c.norm_eps, st));
         {
             GemmTcParams g{};

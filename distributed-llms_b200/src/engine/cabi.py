@@ -21,7 +21,8 @@ class ShardConfig(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("arch", "dtype", "hidden", "n_heads", "n_kv_heads", "head_dim", "ffn",
                                          "vocab", "n_layers", "has_embed", "has_head")] + \
                [("norm_eps", C.c_float)] + \
-               [(n, C.c_int32) for n in ("max_rows", "max_seqs", "max_context", "page_size", "num_pages")]
+               [(n, C.c_int32) for n in ("max_rows", "max_seqs", "max_context", "page_size", "num_pages",
+                                         "first_layer_mlp_only", "last_layer_attn_only")]
 
 
 LAYER_FIELDS = ("norm1_w", "norm1_b", "wq", "bq", "wk", "bk", "wv", "bv", "wo", "bo", "norm2_w", "norm2_b",

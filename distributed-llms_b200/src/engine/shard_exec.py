@@ -117,36 +117,58 @@ class ShardExecutor:
             return t
 
         P = parameters
+        # A stage boundary may fall inside a layer, between its attention block and its MLP block: the first layer of a
+        # stage may then hold only the MLP block, the last one only the attention block (include/dllm_b200.h).
+        attn_key = (lambda i: f"h.{i}.attn.c_attn.weight") if g.model_type == "gpt2" else (lambda i: f"layers.{i}.self_attn.q_proj.weight")
+        mlp_key = (lambda i: f"h.{i}.mlp.c_proj.weight") if g.model_type == "gpt2" else (lambda i: f"layers.{i}.mlp.down_proj.weight")
+        self.first_layer_mlp_only = bool(self.layer_ids) and attn_key(self.layer_ids[0]) not in P
+        self.last_layer_attn_only = bool(self.layer_ids) and mlp_key(self.layer_ids[-1]) not in P
+        for i in self.layer_ids:
+            whole = attn_key(i) in P and mlp_key(i) in P
+            if not whole and not ((i == self.layer_ids[0] and self.first_layer_mlp_only and mlp_key(i) in P) or
+                                  (i == self.layer_ids[-1] and self.last_layer_attn_only and attn_key(i) in P)):
+                raise ValueError(f"layer {i} is incomplete: only the first layer of a stage may lack its attention block "
+                                 "and only the last one its MLP block")
         layers = (cabi.LayerWeights * max(1, len(self.layer_ids)))()
         for n, i in enumerate(self.layer_ids):
             lw = layers[n]
+            has_attn = not (n == 0 and self.first_layer_mlp_only)
+            has_mlp = not (n == len(self.layer_ids) - 1 and self.last_layer_attn_only)
             if g.model_type == "gpt2":
                 p = f"h.{i}."
                 d = g.hidden
-                wqkv = dev(P[p + "attn.c_attn.weight"], transpose=True)  # Conv1D [in,out] -> [3d, d]
-                bqkv = dev(P[p + "attn.c_attn.bias"])
-                esz = wqkv.element_size()
-                vals = dict(
-                    norm1_w=_ptr(dev(P[p + "ln_1.weight"])), norm1_b=_ptr(dev(P[p + "ln_1.bias"])),
-                    wq=wqkv.data_ptr(), wk=wqkv.data_ptr() + d * d * esz, wv=wqkv.data_ptr() + 2 * d * d * esz,
-                    bq=bqkv.data_ptr(), bk=bqkv.data_ptr() + d * esz, bv=bqkv.data_ptr() + 2 * d * esz,
-                    wo=_ptr(dev(P[p + "attn.c_proj.weight"], True)), bo=_ptr(dev(P[p + "attn.c_proj.bias"])),
-                    norm2_w=_ptr(dev(P[p + "ln_2.weight"])), norm2_b=_ptr(dev(P[p + "ln_2.bias"])),
-                    w_gate=None, w_up=_ptr(dev(P[p + "mlp.c_fc.weight"], True)), b_up=_ptr(dev(P[p + "mlp.c_fc.bias"])),
-                    w_down=_ptr(dev(P[p + "mlp.c_proj.weight"], True)), b_down=_ptr(dev(P[p + "mlp.c_proj.bias"])))
+                vals = {}
+                if has_attn:
+                    wqkv = dev(P[p + "attn.c_attn.weight"], transpose=True)  # Conv1D [in,out] -> [3d, d]
+                    bqkv = dev(P[p + "attn.c_attn.bias"])
+                    esz = wqkv.element_size()
+                    vals.update(
+                        norm1_w=_ptr(dev(P[p + "ln_1.weight"])), norm1_b=_ptr(dev(P[p + "ln_1.bias"])),
+                        wq=wqkv.data_ptr(), wk=wqkv.data_ptr() + d * d * esz, wv=wqkv.data_ptr() + 2 * d * d * esz,
+                        bq=bqkv.data_ptr(), bk=bqkv.data_ptr() + d * esz, bv=bqkv.data_ptr() + 2 * d * esz,
+                        wo=_ptr(dev(P[p + "attn.c_proj.weight"], True)), bo=_ptr(dev(P[p + "attn.c_proj.bias"])))
+                if has_mlp:
+                    vals.update(
+                        norm2_w=_ptr(dev(P[p + "ln_2.weight"])), norm2_b=_ptr(dev(P[p + "ln_2.bias"])),
+                        w_gate=None, w_up=_ptr(dev(P[p + "mlp.c_fc.weight"], True)), b_up=_ptr(dev(P[p + "mlp.c_fc.bias"])),
+                        w_down=_ptr(dev(P[p + "mlp.c_proj.weight"], True)), b_down=_ptr(dev(P[p + "mlp.c_proj.bias"])))
             else:
                 p = f"layers.{i}."
                 opt = lambda k: _ptr(dev(P[k])) if k in P else None  # noqa: E731
-                vals = dict(
-                    norm1_w=_ptr(dev(P[p + "input_layernorm.weight"])), norm1_b=None,
-                    wq=_ptr(dev(P[p + "self_attn.q_proj.weight"])), bq=opt(p + "self_attn.q_proj.bias"),
-                    wk=_ptr(dev(P[p + "self_attn.k_proj.weight"])), bk=opt(p + "self_attn.k_proj.bias"),
-                    wv=_ptr(dev(P[p + "self_attn.v_proj.weight"])), bv=opt(p + "self_attn.v_proj.bias"),
-                    wo=_ptr(dev(P[p + "self_attn.o_proj.weight"])), bo=None,
-                    norm2_w=_ptr(dev(P[p + "post_attention_layernorm.weight"])), norm2_b=None,
-                    w_gate=_ptr(dev(P[p + "mlp.gate_proj.weight"])),
-                    w_up=_ptr(dev(P[p + "mlp.up_proj.weight"])), b_up=None,
-                    w_down=_ptr(dev(P[p + "mlp.down_proj.weight"])), b_down=None)
+                vals = {}
+                if has_attn:
+                    vals.update(
+                        norm1_w=_ptr(dev(P[p + "input_layernorm.weight"])), norm1_b=None,
+                        wq=_ptr(dev(P[p + "self_attn.q_proj.weight"])), bq=opt(p + "self_attn.q_proj.bias"),
+                        wk=_ptr(dev(P[p + "self_attn.k_proj.weight"])), bk=opt(p + "self_attn.k_proj.bias"),
+                        wv=_ptr(dev(P[p + "self_attn.v_proj.weight"])), bv=opt(p + "self_attn.v_proj.bias"),
+                        wo=_ptr(dev(P[p + "self_attn.o_proj.weight"])), bo=None)
+                if has_mlp:
+                    vals.update(
+                        norm2_w=_ptr(dev(P[p + "post_attention_layernorm.weight"])), norm2_b=None,
+                        w_gate=_ptr(dev(P[p + "mlp.gate_proj.weight"])),
+                        w_up=_ptr(dev(P[p + "mlp.up_proj.weight"])), b_up=None,
+                        w_down=_ptr(dev(P[p + "mlp.down_proj.weight"])), b_down=None)
             for k, v in vals.items():
                 setattr(lw, k, v)
 
@@ -172,7 +194,8 @@ class ShardExecutor:
             hidden=g.hidden, n_heads=g.n_heads, n_kv_heads=g.n_kv_heads, head_dim=g.head_dim, ffn=g.ffn,
             vocab=g.vocab, n_layers=len(self.layer_ids), has_embed=int(self.has_embed), has_head=int(self.has_head),
             norm_eps=g.norm_eps, max_rows=self.max_rows, max_seqs=self.max_seqs, max_context=self.max_context,
-            page_size=self.page_size, num_pages=0)
+            page_size=self.page_size, num_pages=0, first_layer_mlp_only=int(self.first_layer_mlp_only),
+            last_layer_attn_only=int(self.last_layer_attn_only))
         handle = C.c_void_p()
         with torch.cuda.device(self.device):
             cabi.check(cabi.lib().dllm_shard_create(C.byref(cfg), layers, C.byref(io), C.byref(handle)))

@@ -75,15 +75,23 @@ def end_shapes(cfg: dict, first: bool, last: bool) -> Dict[str, tuple]:
     return out
 
 
-def random_stage_parameters(cfg: dict, layers: range, first: bool, last: bool, base_seed: int = 1234,
+def block_of(key: str) -> str:
+    """"attn" or "mlp": which block of its decoder layer a tensor belongs to (norms go with the block they feed)."""
+    k = key.split(".", 2)[2]
+    return "attn" if k.startswith(("ln_1", "attn", "input_layernorm", "self_attn")) else "mlp"
+
+
+def random_stage_parameters(cfg: dict, layers, first: bool, last: bool, base_seed: int = 1234,
                             dtype: torch.dtype = torch.bfloat16, device: Optional[str] = None,
                             init: str = "hf") -> Dict[str, torch.Tensor]:
-    """Parameters of one stage.  With device=None tensors are drawn on the CPU from per-key seeded
-    generators (bit-reproducible: what parity tests use).  With a CUDA device they are drawn on that
+    """Parameters of one stage.  `layers`: layer indices, or (layer, block) pairs with block in "full" / "attn" /
+    "mlp" for a stage that starts or ends inside a layer.  With device=None tensors are drawn on the CPU from per-key
+    seeded generators (bit-reproducible: what parity tests use).  With a CUDA device they are drawn on that
     device (fast; used for throughput runs on 8B-70B models, where values only need the right scale)."""
     shapes: Dict[str, tuple] = dict(end_shapes(cfg, first, False))
-    for i in layers:
-        shapes.update(layer_shapes(cfg, i))
+    for item in layers:
+        i, block = item if isinstance(item, tuple) else (item, "full")
+        shapes.update({k: v for k, v in layer_shapes(cfg, i).items() if block == "full" or block_of(k) == block})
     shapes.update(end_shapes(cfg, False, last))
     out: Dict[str, torch.Tensor] = {}
     on_gpu = device is not None and str(device).startswith("cuda")

@@ -60,6 +60,50 @@ def balanced_partition(n_layers: int, num_shards: int, head_cost_layers: float) 
     return head + [range(n_layers - last, n_layers)]
 
 
+def block_partition(n_layers: int, num_shards: int, attn_cost: float, mlp_cost: float, head_cost: float = 0.0
+                    ) -> List[List[tuple]]:
+    """Stages as contiguous runs of BLOCKS -- (layer, "attn"), (layer, "mlp") -- so that a boundary may fall inside a
+    layer (the residual row is the hand-off either way).  Costs are the bytes a decode step streams for one block
+    (`head_cost` rides on the last stage); the split minimises the most expensive stage.  Returns per stage a list of
+    (layer, "full" | "attn" | "mlp")."""
+    units = []
+    for i in range(n_layers):
+        units += [(i, "attn", attn_cost), (i, "mlp", mlp_cost)]
+    n = len(units)
+    if num_shards > n:
+        raise ValueError("more stages than blocks")
+    prefix = [0.0]
+    for u in units:
+        prefix.append(prefix[-1] + u[2])
+    INF = float("inf")
+    # best[s][j]: smallest possible maximum over the first s stages covering units[:j]
+    best = [[INF] * (n + 1) for _ in range(num_shards + 1)]
+    cut = [[0] * (n + 1) for _ in range(num_shards + 1)]
+    best[0][0] = 0.0
+    for s_ in range(1, num_shards + 1):
+        for j in range(s_, n + 1):
+            for i in range(s_ - 1, j):
+                cost = prefix[j] - prefix[i] + (head_cost if (s_ == num_shards and j == n) else 0.0)
+                v = max(best[s_ - 1][i], cost)
+                if v < best[s_][j] - 1e-12:
+                    best[s_][j], cut[s_][j] = v, i
+    bounds, j = [n], n
+    for s_ in range(num_shards, 0, -1):
+        j = cut[s_][j]
+        bounds.append(j)
+    bounds.reverse()
+    stages: List[List[tuple]] = []
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        items: List[tuple] = []
+        for (i, blk, _) in units[a:b]:
+            if items and items[-1] == (i, "attn") and blk == "mlp":
+                items[-1] = (i, "full")
+            else:
+                items.append((i, blk))
+        stages.append(items)
+    return stages
+
+
 def partition_state_dict(state_dict: Dict[str, torch.Tensor], num_shards: int, tie_head: bool = False
                          ) -> List[Dict[str, torch.Tensor]]:
     sd = {strip_prefix(k): v for k, v in state_dict.items()}

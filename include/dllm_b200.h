@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define DLLM_ABI_VERSION 1
+#define DLLM_ABI_VERSION 2
 
 #if defined(__GNUC__)
 #define DLLM_API __attribute__((visibility("default")))
@@ -61,9 +61,16 @@ typedef struct dllm_shard_config {
     int32_t max_context;  /* tokens per sequence the KV cache and the rope tables cover            */
     int32_t page_size;    /* tokens per KV page (power of two, >= 8)                               */
     int32_t num_pages;    /* KV pages per layer; 0 = max_seqs * ceil(max_context / page_size)      */
+    /* A stage boundary may fall INSIDE a decoder layer, between the attention block (norm, q/k/v, attention, o-proj,
+     * residual) and the MLP block (norm, gate/up, down, residual): the residual row is the hand-off either way, and
+     * stages balance better -- the blocks are the units, and the last stage also streams the lm_head.  (The
+     * reference's sharder assigns whole layers, src/model/shard_manager.py:33-61.)                                  */
+    int32_t first_layer_mlp_only;   /* layers[0] holds only its MLP block (its attention block ran on the stage before) */
+    int32_t last_layer_attn_only;   /* layers[n_layers-1] holds only its attention block (its MLP runs on the next stage) */
 } dllm_shard_config;
 
-/* Device pointers to one layer's weights, all in `dtype`, row-major [out, in] (nn.Linear layout;
+/* Device pointers to one layer's weights (for a layer split between two stages: of the block this stage holds, the
+ * other block's pointers NULL), all in `dtype`, row-major [out, in] (nn.Linear layout;
  * GPT-2 Conv1D [in,out] tensors are transposed by the host before they get here).  The memory is
  * owned by the caller (reference: `ModelShard.parameters`, src/worker/node.py:16,19-22) and must
  * outlive the handle.  NULL = absent (no bias / not this architecture). */

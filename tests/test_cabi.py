@@ -3,6 +3,7 @@ import ctypes
 import os
 import re
 import subprocess
+import tempfile
 
 import pytest
 import torch
@@ -41,7 +42,7 @@ def test_no_stray_exports():
 
 def test_abi_version_and_error_string():
     lib = cabi.lib()
-    assert lib.dllm_abi_version() == 1
+    assert lib.dllm_abi_version() == 2
     assert isinstance(lib.dllm_last_error(), bytes)
     assert lib.dllm_kernel_launch_count() >= 0
 
@@ -52,8 +53,14 @@ def test_header_compiles_as_c():
 
 
 def test_struct_layouts_match_header():
-    # 11 int32 + float + 5 int32; 17 and 7 pointers
-    assert ctypes.sizeof(cabi.ShardConfig) == 17 * 4
+    # 11 int32 + float + 7 int32; 17 and 7 pointers.  The compiler's view of the header is the reference point.
+    src = '#include <stdio.h>\n#include "dllm_b200.h"\nint main(void){printf("%zu %zu %zu", sizeof(dllm_shard_config), sizeof(dllm_layer_weights), sizeof(dllm_io_weights));return 0;}'
+    exe = os.path.join(tempfile.mkdtemp(), "sz")
+    r = subprocess.run(["gcc", "-std=c99", "-I", os.path.dirname(HEADER), "-x", "c", "-", "-o", exe], input=src, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    sizes = [int(v) for v in subprocess.run([exe], capture_output=True, text=True).stdout.split()]
+    assert sizes == [ctypes.sizeof(cabi.ShardConfig), ctypes.sizeof(cabi.LayerWeights), ctypes.sizeof(cabi.IoWeights)]
+    assert ctypes.sizeof(cabi.ShardConfig) == 19 * 4
     assert ctypes.sizeof(cabi.LayerWeights) == 17 * 8
     assert ctypes.sizeof(cabi.IoWeights) == 7 * 8
 

@@ -354,6 +354,43 @@ def test_prefill_single_step_then_decode_loop(dtype):
     assert torch.equal(torch.cat([first[:, None], second[:, None], rest], 1), ids)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("arch", ["llama", "gpt2"])
+def test_stage_boundary_inside_a_layer(dtype, arch):
+    """A stage may end after a layer's attention block and the next one start with that layer's MLP block (the residual
+    row is the hand-off either way): prefill, single steps and the oracle's tokens must not notice.  Against the oracle
+    (fp32: ids identical, logits 1e-4) and, bit for bit, against the same model as one stage."""
+    from src.model.random_init import block_of
+    if arch == "llama":
+        cfg = ShardModelConfig("llama", 256, 4, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    else:
+        cfg = ShardModelConfig("gpt2", 128, 4, 4, 4, 32, 512, 211, 96, 1e-5, 10000.0, tie_head=True)
+    sd = {k: v.to(dtype) for k, v in make_state_dict(cfg, 3, torch.float32, init="full").items()}
+    (whole,) = split_state_dict(cfg, sd, 1)
+    prefix = "h." if arch == "gpt2" else "layers."
+    layer = lambda k: int(k.split(".")[1]) if k.startswith(prefix) else None
+    # stage A: embedding, layers 0-1, attention block of layer 2; stage B: MLP block of layer 2, layer 3, final norm, head
+    a = {k: v for k, v in whole.items() if (layer(k) is not None and (layer(k) < 2 or (layer(k) == 2 and block_of(k) == "attn")))
+         or k.startswith(("wte", "wpe", "embed_tokens"))}
+    b = {k: v for k, v in whole.items() if k not in a or k == "lm_head.weight"}
+    if arch == "gpt2":
+        b["lm_head.weight"] = whole["lm_head.weight"]
+        a.pop("lm_head.weight", None)
+    limits = dict(max_rows=32, max_seqs=2, max_context=64, page_size=16)
+    hf = cfg.to_hf_dict()
+    one = ModelShard(0, dict(whole), config=hf, **limits); one.to_device()
+    sa = ModelShard(0, a, config=hf, **limits); sa.to_device()
+    sb = ModelShard(1, b, config=hf, **limits); sb.to_device()
+    assert sa.executor.last_layer_attn_only and sb.executor.first_layer_mlp_only
+    prompts = make_prompts(cfg.vocab, 2, 9, seed=4)
+    ids1, lg1 = gpu_generate([one], prompts, 8)
+    ids2, lg2 = gpu_generate([sa, sb], prompts, 8)
+    assert torch.equal(ids1, ids2) and torch.equal(lg1, lg2)
+    if dtype == torch.float32:
+        o_ids, o_lg, _ = greedy_generate(build_pipeline(cfg, sd, 1, dtype), prompts, 8, record=True)
+        assert torch.equal(ids2, o_ids) and rel_err(lg2, o_lg) < 1e-4
+
+
 def test_chunked_prefill_equals_single_call():
     """max_rows smaller than the prompt -> chunked prefill; same logits (fp32 tolerance) and token."""
     cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
