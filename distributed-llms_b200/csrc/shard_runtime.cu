@@ -505,6 +505,8 @@ static bool mk_eligible(const dllm_shard* s, int n_rows, int n_logit_rows, bool 
     return mk_variant(s, n_rows, n_logit_rows, identity_rows) != 0;
 }
 
+extern "C" int dllm_handoff_peer_copy(void* dst_ptr, int dst_device, const void* src_ptr, int src_device, size_t bytes, void* stream);
+
 // mailboxes of the fused hand-off (see include/dllm_b200.h)
 struct dllm_mailbox {
     int device = 0;           // device the pointers are valid on
@@ -847,13 +849,16 @@ extern "C" int dllm_shard_decode_loop(dllm_shard* s, int32_t n_rows, int32_t n_s
 
 // ---- hand-off ---------------------------------------------------------------------------------------
 
+// rows: up to 16 for the persistent decode loop (checked again there); a prefill tile slot may hold a whole prompt chunk
+constexpr int kMailboxMaxRows = 1 << 20;
 static int mailbox_shape_ok(int n_slots, int rows, int hidden) {
-    return n_slots >= 1 && n_slots <= 64 && rows >= 1 && rows <= MK_MAX_ROWS && hidden >= 8 && hidden % 8 == 0;
+    return n_slots >= 1 && n_slots <= 64 && rows >= 1 && rows <= kMailboxMaxRows && hidden >= 8 && hidden % 8 == 0 &&
+           (size_t)n_slots * rows * hidden * 2 <= ((size_t)8 << 30);
 }
 
 extern "C" int dllm_mailbox_create(int32_t device, int32_t n_slots, int32_t rows, int32_t hidden, dllm_mailbox** out) {
     if (!out) return fail("dllm_mailbox_create: null out");
-    if (!mailbox_shape_ok(n_slots, rows, hidden)) return fail("dllm_mailbox_create: bad shape (1..64 slots, 1..16 rows, hidden % 8 == 0)");
+    if (!mailbox_shape_ok(n_slots, rows, hidden)) return fail("dllm_mailbox_create: bad shape (1..64 slots, rows >= 1, hidden % 8 == 0, at most 8 GiB)");
     if (dllm_device_count() == 0) return fail("dllm_mailbox_create: no CUDA device (this library has no CPU path)");
     CUDA_TRY(cudaSetDevice(device));
     dllm_mailbox* b = new dllm_mailbox();
@@ -930,6 +935,22 @@ extern "C" int dllm_mailbox_read_tokens(dllm_mailbox* b, int32_t slot, int32_t* 
     if (ticket_out) CUDA_TRY(cudaMemcpyAsync(ticket_out, b->flags() + (size_t)slot * kFlagStride, 4, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return 0;
+}
+
+// Prefill hand-off through a mailbox slot: the producer stage copies its [n_rows, hidden] tile straight into the next
+// stage's slot (peer memory, NVLink DMA), the consumer copies it out of its own slot.  Ordering between the two is the
+// caller's (a control message after the producer's stream has drained); no ticket is involved.
+extern "C" int dllm_mailbox_put_rows(dllm_mailbox* b, int32_t slot, const void* d_src, int32_t n_rows, void* stream) {
+    if (!b || !d_src || slot < 0 || slot >= b->n_slots || n_rows < 1 || n_rows > b->rows) return fail("dllm_mailbox_put_rows: bad argument");
+    char* dst = static_cast<char*>(b->hidden_rows()) + (size_t)slot * b->rows * b->hidden * 2;
+    // the mailbox (own, peer view or IPC mapping) is addressable from b->device: the hand-off is one device-to-device copy
+    return dllm_handoff_peer_copy(dst, b->device, d_src, b->device, (size_t)n_rows * b->hidden * 2, stream);
+}
+
+extern "C" int dllm_mailbox_get_rows(dllm_mailbox* b, int32_t slot, void* d_dst, int32_t n_rows, void* stream) {
+    if (!b || !b->owner || !d_dst || slot < 0 || slot >= b->n_slots || n_rows < 1 || n_rows > b->rows) return fail("dllm_mailbox_get_rows: bad argument");
+    const char* src = static_cast<const char*>(b->hidden_rows()) + (size_t)slot * b->rows * b->hidden * 2;
+    return dllm_handoff_peer_copy(d_dst, b->device, src, b->device, (size_t)n_rows * b->hidden * 2, stream);
 }
 
 extern "C" int dllm_mailbox_destroy(dllm_mailbox* b) {

@@ -62,6 +62,8 @@ SIGNATURES = {
     "dllm_mailbox_view": (C.c_int, [_vp, _i32, C.POINTER(C.c_void_p)]),
     "dllm_mailbox_post_tokens": (C.c_int, [_vp, _i32, _vp, C.c_uint32, _vp]),
     "dllm_mailbox_read_tokens": (C.c_int, [_vp, _i32, _vp, _vp, _vp]),
+    "dllm_mailbox_put_rows": (C.c_int, [_vp, _i32, _vp, _i32, _vp]),
+    "dllm_mailbox_get_rows": (C.c_int, [_vp, _i32, _vp, _i32, _vp]),
     "dllm_mailbox_destroy": (C.c_int, [_vp]),
     "dllm_shard_decode_pipelined": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32, C.c_uint32, _vp, _vp, _vp, _vp]),
     "dllm_op_gemv": (C.c_int, [_i32, _vp, _vp, _vp, _vp, _i32, _i32, _i32, _i32, _vp]),

@@ -75,6 +75,10 @@ class MasterNode:
         self._loaded_shards: set = set()
         self.heartbeat_timeout = 30.0
         self.use_fused_handoff = True                 # decode through peer mailboxes when every stage has its own GPU
+        self.use_direct_tiles = True                  # prefill / relay: hidden-state tiles go worker -> worker over NVLink
+        self._tile_rows = 0                           # capacity of the tile inboxes opened on the workers (0 = none)
+        self._tile_workers: List[str] = []
+        self.last_prefill_path = None                 # "tiles" | "relay": how the last prompt's hidden states travelled
         self.last_decode_path = None                  # "fused" | "per-step": how the last request was decoded
 
     # ---- life cycle (reference :29-52) -------------------------------------------------------------------
@@ -213,12 +217,54 @@ class MasterNode:
             raise RuntimeError("shard assignment is not a pipeline: a worker holds non-consecutive shards")
         return [(w, s) for _, w, s in order]
 
+    def _ensure_tiles(self, task_id: str, rows: int) -> bool:
+        """Worker-to-worker hand-off of hidden-state tiles: every stage but the first opens an inbox for `rows` rows on its
+        GPU and its predecessor maps it (CUDA IPC / peer access).  Needs one shard per worker and every worker on its
+        own GPU, like the fused decode loop; otherwise (and on any refusal) the tiles keep travelling through the
+        master as pickled RESULT payloads, which is what the reference's star topology does (src/master/node.py:256-269)."""
+        if not self.use_direct_tiles:
+            return False
+        order = self._stage_order()
+        ids = [w for w, _ in order]
+        if len(order) < 2 or any(len(s) != 1 for _, s in order):
+            return False
+        places = [(self.workers[w].get("pid"), self.workers[w].get("device_index")) for w in ids]
+        if any(p[0] is None or p[1] is None or p[1] < 0 for p in places) or len(set(places)) != len(places):
+            return False
+        if self._tile_rows >= rows and self._tile_workers == ids:
+            return True
+        try:
+            infos = {}
+            for st in range(1, len(order)):
+                infos[st] = self._request(self.workers[ids[st]], task_id, "TILE_OPEN", None, {"shard_id": order[st][1][0], "rows": rows})
+            for st in range(len(order) - 1):
+                self._request(self.workers[ids[st]], task_id, "TILE_CONNECT", infos[st + 1], {})
+        except (RuntimeError, TimeoutError) as e:
+            print(f"direct tile hand-off unavailable ({e}); hidden states go through the master")
+            self._drain_replies(task_id)
+            self._tile_rows, self._tile_workers = 0, []
+            self.use_direct_tiles = False
+            return False
+        self._tile_rows, self._tile_workers = rows, ids
+        return True
+
     def _pipeline_step(self, task_id: str, inputs: Dict[str, torch.Tensor], reset: bool, timeout: float) -> Dict[str, torch.Tensor]:
-        """One pass through all stages: each worker's RESULT (the hand-off) is forwarded to the next worker."""
+        """One pass through all stages.  The hidden states go from worker to worker over NVLink when the cluster allows
+        it (`_ensure_tiles`); else each worker's RESULT (the hand-off) is forwarded to the next worker by the master."""
         x = inputs
-        for worker_id, shard_ids in self._stage_order():
+        ids = inputs.get("input_ids")
+        rows = int(ids.shape[0]) * int(ids.shape[1]) if ids is not None and ids.dim() == 2 else 0
+        tiles = rows > 0 and self._ensure_tiles(task_id, rows)
+        self.last_prefill_path = "tiles" if tiles else "relay"
+        order = self._stage_order()
+        for i, (worker_id, shard_ids) in enumerate(order):
             worker = self.workers[worker_id]
-            self._send(worker, "RUN_INFERENCE", pickle.dumps(x), {"task_id": task_id, "shard_ids": shard_ids, "reset": reset})
+            md = {"task_id": task_id, "shard_ids": shard_ids, "reset": reset}
+            if tiles:
+                md["out_tile"] = i < len(order) - 1
+                if i > 0:
+                    md["in_tile"] = x.pop("tile_shape")
+            self._send(worker, "RUN_INFERENCE", pickle.dumps(x), md)
             try:
                 header, payload = self._replies[task_id].get(timeout=timeout)
             except Empty:

@@ -127,6 +127,21 @@ class Mailbox:
         cabi.check(cabi.lib().dllm_mailbox_read_tokens(self.handle, slot, out.data_ptr(), C.byref(ticket), st))
         return out, int(ticket.value)
 
+    def put_rows(self, slot: int, rows: torch.Tensor) -> None:
+        """Producer side: copy a [n, hidden] bf16 device tile into `slot` of this (usually another stage's) mailbox."""
+        from ..engine import cabi
+        t = rows.reshape(-1, self.hidden).contiguous()
+        st = torch.cuda.current_stream(t.device).cuda_stream
+        cabi.check(cabi.lib().dllm_mailbox_put_rows(self.handle, slot, t.data_ptr(), int(t.shape[0]), st))
+
+    def get_rows(self, slot: int, n_rows: int, dtype=torch.bfloat16) -> torch.Tensor:
+        """Owner side: the first `n_rows` rows of `slot` as a fresh [n_rows, hidden] device tensor."""
+        from ..engine import cabi
+        out = torch.empty(n_rows, self.hidden, dtype=dtype, device=torch.device("cuda", self.device))
+        st = torch.cuda.current_stream(out.device).cuda_stream
+        cabi.check(cabi.lib().dllm_mailbox_get_rows(self.handle, slot, out.data_ptr(), n_rows, st))
+        return out
+
     def close(self) -> None:
         if self.handle is not None:
             from ..engine import cabi

@@ -167,6 +167,8 @@ class WorkerNode:
         self.device = device  # CUDA device index of this worker (None: the process's current device)
         self._inbox = None    # fused hand-off: this stage's mailbox and the view of the next stage's
         self._outbox = None
+        self._tile_in = None  # prefill / relay hand-off: a one-slot mailbox that holds a whole [B*T, d] tile, and the next stage's
+        self._tile_out = None
         self.shards: Dict[int, ModelShard] = {}
         self.running = False
         self.server_socket = None
@@ -301,6 +303,24 @@ class WorkerNode:
         from ..network.handoff import Mailbox, connect_mailbox
         args = pickle.loads(payload) if payload else {}
         dev = self._device_index()
+        if command == "TILE_OPEN":   # this stage's inbox for whole hidden-state tiles (prefill, per-step relay)
+            hidden = self.shards[header["shard_id"]].executor.geom.hidden
+            if self._tile_in is not None:
+                self._tile_in.close()
+            self._tile_in = Mailbox.create(dev, 1, int(header["rows"]), hidden)
+            return {"ipc": self._tile_in.export_handle(), "pid": os.getpid(), "device_index": dev, "n_slots": 1,
+                    "rows": self._tile_in.rows, "hidden": hidden}
+        if command == "TILE_CONNECT":
+            if self._tile_out is not None and self._tile_out is not self._tile_in:
+                self._tile_out.close()
+            self._tile_out = connect_mailbox(dev, args)
+            return {}
+        if command == "TILE_CLOSE":
+            for box in (self._tile_out, self._tile_in):
+                if box is not None:
+                    box.close()
+            self._tile_in = self._tile_out = None
+            return {}
         if command == "MAILBOX_OPEN":
             shard = self.shards[header["shard_id"]]
             hidden = shard.executor.geom.hidden
@@ -358,7 +378,7 @@ class WorkerNode:
                 def send_message(_, _sock, command, payload=None, metadata=None, owned=self._owned):
                     return owned.send(command, payload, metadata)
             protocol = _ViaOwner()
-        if command.startswith("MAILBOX_") or command in ("RUN_DECODE_LOOP", "PREPARE_DECODE_LOOP"):
+        if command.startswith(("MAILBOX_", "TILE_")) or command in ("RUN_DECODE_LOOP", "PREPARE_DECODE_LOOP"):
             task_id = header.get("task_id")
             md = {"task_id": task_id, "stage": header.get("stage")}
             try:
@@ -385,12 +405,22 @@ class WorkerNode:
             shard_ids = header.get("shard_ids", [])
             try:
                 inputs = pickle.loads(payload)
+                if header.get("in_tile"):  # the hidden states are already in this GPU's tile inbox (put there over NVLink)
+                    B, T = header["in_tile"]
+                    d = self._tile_in.hidden
+                    inputs["hidden_states"] = self._tile_in.get_rows(0, int(B) * int(T)).reshape(int(B), int(T), d)
                 if header.get("reset"):
                     for sid in shard_ids:
                         if sid in self.shards:
                             self.shards[sid].reset()
                 # `priority` (reference :244-251) is a constant sort key there, i.e. a no-op; kept as such
                 results = self.schedule_computation(inputs, [s for s in shard_ids if s in self.shards])
+                if header.get("out_tile") and "hidden_states" in results:
+                    # hand-off over NVLink: the tile goes straight into the next stage's inbox; only its shape travels back
+                    h = results.pop("hidden_states")
+                    self._tile_out.put_rows(0, h)
+                    torch.cuda.current_stream(h.device).synchronize()  # the master releases the next stage on this reply
+                    results["tile_shape"] = [int(h.shape[0]), int(h.shape[1])]
                 results = {k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in results.items()}
                 protocol.send_message(sock, "RESULT", payload=pickle.dumps(results), metadata={"task_id": task_id})
             except Exception as e:  # the master's scheduler is waiting for this RESULT: tell it what went wrong

@@ -179,7 +179,7 @@ DLLM_API int dllm_shard_decode_loop(dllm_shard* shard, int32_t n_rows, int32_t n
  * No launch, no collective library call and no host involvement per token.
  *
  * A mailbox is device memory of its owner: per slot (micro-batch) a ticket, `rows` int32 token ids and
- * `rows x hidden` bf16 hidden rows.  Slot tickets count delivered inputs: the consumer of decode step G waits
+ * `rows x hidden` bf16 hidden rows (`rows` <= 16 for the decode loop; any number for a prefill tile slot).  Slot tickets count delivered inputs: the consumer of decode step G waits
  * for ticket >= G + 1.  One process per GPU: the owner exports a 64-byte IPC handle, the producer imports it. */
 typedef struct dllm_mailbox dllm_mailbox;
 #define DLLM_MAILBOX_IPC_BYTES 64
@@ -197,6 +197,15 @@ DLLM_API int dllm_mailbox_post_tokens(dllm_mailbox* box, int32_t slot, const int
 /* Owner side: copy out the token ids currently in `slot` (host or device destination) and, if `ticket_out`
  * (host) is given, the slot's ticket; synchronises `stream`. */
 DLLM_API int dllm_mailbox_read_tokens(dllm_mailbox* box, int32_t slot, int32_t* tokens_out, uint32_t* ticket_out, void* stream);
+/* Prefill hand-off through a mailbox slot (a slot may be created with as many rows as a prompt chunk has): replaces the
+ * pickled `{name: tensor}` RESULT / RUN_INFERENCE payloads that carry the hidden states from worker to worker through
+ * the master (reference src/worker/node.py:224-238, src/master/node.py:256-269).  The producer copies its
+ * [n_rows, hidden] bf16 tile (device memory) into the NEXT stage's slot -- `box` is the producer's view of that mailbox
+ * (dllm_mailbox_import / _view), so the copy is one NVLink DMA -- and the consumer copies it out of its own slot.
+ * Stream-ordered on `stream`; the two sides are ordered by the caller (a control message sent after the producer's
+ * stream has drained), not by tickets. */
+DLLM_API int dllm_mailbox_put_rows(dllm_mailbox* box, int32_t slot, const void* d_src, int32_t n_rows, void* stream);
+DLLM_API int dllm_mailbox_get_rows(dllm_mailbox* box, int32_t slot, void* d_dst, int32_t n_rows, void* stream);
 DLLM_API int dllm_mailbox_destroy(dllm_mailbox* box);
 
 /* `n_steps` decode steps of `n_micro` micro-batches of `rows` rows each in one persistent launch (bf16, rows

@@ -227,6 +227,13 @@ def test_master_uses_the_fused_handoff_when_every_stage_has_its_own_gpu(tmp_path
         again = torch.tensor(master.run_inference(prompt, timeout=180, max_new_tokens=16)["token_ids"])
         assert master.last_decode_path == "per-step"
         assert torch.equal(got, again)  # same kernels, the hand-off copies bits
+        # prefill and the per-step relay moved their hidden-state tiles worker -> worker over NVLink (mailbox tile slots);
+        # the same request with the tiles pickled through the master gives the same tokens
+        assert master.last_prefill_path == "tiles"
+        master.use_direct_tiles = False
+        relayed = torch.tensor(master.run_inference(prompt, timeout=180, max_new_tokens=16)["token_ids"])
+        assert master.last_prefill_path == "relay" and torch.equal(relayed, again)
+        master.use_direct_tiles = True
         cfg = ShardModelConfig.from_hf_dict(CFG)
         want, _, margins = greedy_generate(build_pipeline(cfg, sd, 2, torch.bfloat16), prompt, 16, record=True)
         same = (got == want).long().cumprod(1).bool()

@@ -38,6 +38,16 @@ with tempfile.TemporaryDirectory() as tmp:
         t0 = time.time(); out = master.run_inference(prompt, timeout=600, max_new_tokens=n_new); t_all = time.time() - t0
         print(f"decode path {master.last_decode_path:8s}: {(n_new - 1) / (t_all - t_pre):8.1f} tok/s "
               f"({(t_all - t_pre) / (n_new - 1) * 1e3:.2f} ms/token; prefill round trip {t_pre * 1e3:.1f} ms)")
+    # prefill hand-off: hidden-state tiles worker -> worker over NVLink (mailbox tile slots) against the pickled relay
+    # through the master, 2048-token prompt (the Qwen2.5-14B tile of BASELINE configs[3] is 20 MiB per hop)
+    long_prompt = torch.randint(0, 1000, (1, 2048), generator=torch.Generator().manual_seed(2))
+    for direct in (True, False, True):
+        master.use_direct_tiles = direct
+        master.run_inference(long_prompt, timeout=600, max_new_tokens=1)
+        t0 = time.time()
+        for _ in range(3):
+            master.run_inference(long_prompt, timeout=600, max_new_tokens=1)
+        print(f"prefill hand-off {master.last_prefill_path:6s}: {(time.time() - t0) / 3 * 1e3:8.1f} ms per 2048-token prefill round trip")
 for w in workers:
     w.stop()
 master.stop()
