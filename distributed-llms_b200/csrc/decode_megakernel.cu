@@ -39,7 +39,9 @@ using namespace mkd;
 // 256 / 128 / 64 / 32 threads (1 / 2 / <=4 / more rows) so that a single row costs one batched L2 round trip.
 
 __device__ __forceinline__ void stage_rows(const MkParams& p, const void* src, int K, int norm, const void* nw, const void* nb,
-                                           bf16* xs, int ldx, float* red) {
+                                           bf16* xs, int ldx, float* red2, unsigned& red_flip, long long* tr = nullptr) {
+    // `red2`: two buffers of kWarps floats used alternately by successive block reductions, so that one __syncthreads per
+    // reduction is enough (a buffer is rewritten two reductions later, with the barrier of the one in between in between)
     const int R = p.n_rows;
     const int tpr = R == 1 ? 256 : (R == 2 ? 128 : (R <= 4 ? 64 : 32));
     const int rows_par = kThreads / tpr, wpr = tpr >> 5;
@@ -69,10 +71,12 @@ __device__ __forceinline__ void stage_rows(const MkParams& p, const void* src, i
             if (a1) accum_stats(v1, s1, s2);
             if (a2) accum_stats(v2, s1, s2);
             if (a3) accum_stats(v3, s1, s2);
+            if (tr) tr[11] = clock64();  // row and norm weights have arrived
             auto group_sum = [&](float a) {
                 a = warp_sum(a);
                 if (wpr > 1) {
-                    __syncthreads();
+                    float* red = red2 + (red_flip & 1u) * kWarps;
+                    ++red_flip;
                     if ((threadIdx.x & 31) == 0) red[warp] = a;
                     __syncthreads();
                     a = 0.f;
@@ -101,10 +105,12 @@ __device__ __forceinline__ void stage_rows(const MkParams& p, const void* src, i
                     for (int j = 0; j < 8; ++j) sq = fmaf(f[j] - mean, f[j] - mean, sq); }
                 rstd = 1.0f / sqrtf(group_sum(sq) / (float)K + p.eps);
             }
+            if (tr) tr[12] = clock64();  // statistics reduced
             if (a0) *reinterpret_cast<uint4*>(dst + kb) = norm_vec(v0, w0, b0, norm, mean, rstd);
             if (a1) *reinterpret_cast<uint4*>(dst + k1) = norm_vec(v1, w1, b1, norm, mean, rstd);
             if (a2) *reinterpret_cast<uint4*>(dst + k2) = norm_vec(v2, w2, b2, norm, mean, rstd);
             if (a3) *reinterpret_cast<uint4*>(dst + k3) = norm_vec(v3, w3, b3, norm, mean, rstd);
+            if (tr) tr[13] = clock64();  // normalised row stored
             continue;
         }
         for (int kb = lt * 8; kb < K; kb += 4 * stride) {
@@ -125,6 +131,7 @@ __device__ __forceinline__ void stage_rows(const MkParams& p, const void* src, i
         }
         if (norm == NORM_NONE) continue;
         // row statistics: warp shuffle, then across the row's warps through shared memory
+        float* red = red2;  // (rows wider than four vectors per thread: the plain two-barrier protocol on the first buffer)
         float mean = 0.f, rstd;
         {
             float a = warp_sum(norm == NORM_RMS ? s2 : s1);
@@ -460,8 +467,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     const uint32_t ring_all = smem_u32(sp);
 
     __shared__ StepCache sc;
-    __shared__ int s_units[MK_MAX_PHASES];
-    __shared__ float red[kWarps];
+    __shared__ int s_units[MK_MAX_PHASES], s_first[MK_MAX_PHASES];
+    __shared__ float red[2 * kWarps];
+    unsigned red_flip = 0;
     __shared__ float s_val[kWarps][MK_MAX_ROWS];
     __shared__ int s_idx[kWarps][MK_MAX_ROWS];
     __shared__ int s_last;
@@ -478,6 +486,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     for (int i = threadIdx.x; i < p.n_phases; i += kThreads) {
         const MkPhase& q = p.phases[i];
         s_units[i] = is_weight_phase(q.kind) ? local_panels(q) : 0;
+        s_first[i] = panel_first(q, p.blocked);
     }
     if (threadIdx.x == 0) {
         for (int i = 0; i < kWarps * p.stages; ++i) mbar_init(full_all + i * 8, 1);
@@ -496,13 +505,15 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     if (lane < 8) s_xkey[warp][lane] = -1;
     __syncwarp();
     c.units = s_units;
+    c.first = s_first;
     c.warp = warp;
     c.lane = lane;
     c.ring = ring_all + warp * p.stages * kStageBytes;
     c.full = full_all + warp * p.stages * 8;
 
     // prime this warp's ring: the first `stages` entries of its static sequence
-    WIter prod = {0, 0, 0, 0, 0, 0, 0, nullptr, 0, 0, 0};
+    const int pstride = p.blocked ? 1 : (int)gridDim.x;
+    WIter prod = {0, 0, 0, 0, 0, 0, 0, nullptr, 0, 0, 0, 0, pstride};
     witer_seek(c, prod);
     for (int i = 0; i < p.stages && prod.step < p.n_steps; ++i) {
         issue_stage(c, prod, i);
@@ -511,6 +522,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     unsigned consumed = 0;  // stages this warp has consumed so far -> ring slot and mbarrier parity
     unsigned bar_target = 0;
     bool need_barrier = false;
+    int kv_prefetch_layer = -1;  // >= 0: prefetch this layer's old K/V rows for the attention phase at the next barrier
     // rows this lane feeds into the A fragment (rows >= R produce output rows nobody reads)
     const uint32_t xrow_lo = smem_u32(xs) + (uint32_t)(min(g, R - 1) * ldx * 2);
     const uint32_t xrow_hi = smem_u32(xs) + (uint32_t)(min(g + 8, R - 1) * ldx * 2);
@@ -528,7 +540,24 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
         for (int phi = 0; phi < p.n_phases; ++phi) {
             const MkPhase& ph = phases[phi];
             const MkLayer* L = p.layers + ph.layer;
-            if (need_barrier) grid_barrier(p.barrier, bar_target);
+            long long* tr = (p.trace && blockIdx.x == 0 && threadIdx.x == 0) ? p.trace + ((size_t)step * p.n_phases + phi) * MK_TRACE_SLOTS : nullptr;
+            if (need_barrier) {
+                grid_barrier_arrive(p.barrier, bar_target, tr);
+                if (kv_prefetch_layer >= 0) {
+                    // between this CTA's arrival and everybody's: ask for the old K/V rows of its first attention tile
+                    // (rows no CTA writes in this step -- independent of the barrier)
+                    const MkLayer& PL = p.layers[kv_prefetch_layer];
+                    kv_prefetch_layer = -1;
+                    const AttnUnit a = attn_unit(p, sc, blockIdx.x);
+                    const int tend = min(a.t1, a.t0 + kTT);
+                    const int upto = max(a.t0, min(tend, attn_safe_end(sc, a)));
+                    if (upto > a.t0) {
+                        attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, true, false);
+                        attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, false, true);
+                    }
+                }
+                grid_barrier_wait(p.barrier, bar_target, tr);
+            }
             need_barrier = true;
             c.cur_key = step * p.n_phases + phi;
             if (ph.xg) issue_deferred_rows(c, p.stages);
@@ -564,7 +593,6 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 }
                 __syncthreads();
             }
-            long long* tr = (p.trace && blockIdx.x == 0 && threadIdx.x == 0) ? p.trace + ((size_t)step * p.n_phases + phi) * 8 : nullptr;
             if (tr) tr[0] = clock64();
 
             if (ph.kind == MK_EMBED) {
@@ -596,13 +624,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             }
 
             // ---- weight-streaming phase: prologue ----
-            if (ph.kind == MK_QKV) stage_rows(p, h_m, ph.K, p.norm, L->norm1_w, L->norm1_b, xs, ldx, red);
-            else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) stage_rows(p, h_m, ph.K, p.norm, L->norm2_w, L->norm2_b, xs, ldx, red);
-            else if (ph.kind == MK_HEAD) stage_rows(p, h_m, ph.K, p.norm, p.final_norm_w, p.final_norm_b, xs, ldx, red);
+            if (ph.kind == MK_QKV) stage_rows(p, h_m, ph.K, p.norm, L->norm1_w, L->norm1_b, xs, ldx, red, red_flip, tr);
+            else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) stage_rows(p, h_m, ph.K, p.norm, L->norm2_w, L->norm2_b, xs, ldx, red, red_flip, tr);
+            else if (ph.kind == MK_HEAD) stage_rows(p, h_m, ph.K, p.norm, p.final_norm_w, p.final_norm_b, xs, ldx, red, red_flip, tr);
             else if (ph.kind == MK_DOWN) {
-                if (!ph.xg) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);
+                if (!ph.xg) stage_rows(p, p.act, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red, red_flip);
             }
-            else stage_rows(p, p.attn_out, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red);  // o-proj: merged attention rows
+            else stage_rows(p, p.attn_out, ph.K, NORM_NONE, nullptr, nullptr, xs, ldx, red, red_flip);  // o-proj: merged attention rows
             __syncthreads();
             if (tr) tr[1] = clock64();
 
@@ -614,7 +642,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             uint32_t old_pref = 0u;
             if ((ph.kind == MK_OPROJ || ph.kind == MK_DOWN) && (int)threadIdx.x < n_local * 4 * RP) {
                 const int r = threadIdx.x & (RP - 1), pi = threadIdx.x / RP;
-                const int n = (blockIdx.x + gridDim.x * (pi >> 2)) * 8 + 2 * (pi & 3);
+                const int n = (s_first[phi] + pstride * (pi >> 2)) * 8 + 2 * (pi & 3);
                 if (r < R && n < ph.n0)
                     old_pref = __ldcg(reinterpret_cast<const uint32_t*>(h_m + (size_t)r * ph.n0 + n));
             }
@@ -723,14 +751,33 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 const int pi = o / RP, pj = pi >> 2, i = pi & 3;
                 if (r >= R) continue;
                 float v0 = 0.f, v1 = 0.f;
-                const int w1 = s_wlast[pj];
-                for (int w = s_wfirst[pj]; w <= w1; ++w) {
-                    if (T < kWarps && chunk_begin(w, T) == chunk_begin(w + 1, T)) continue;  // a warp without stages
-                    const float* src = spart + (size_t)(pj + w) * kPartStride;
-                    v0 += src[(2 * i) * MK_MAX_ROWS + r];
-                    v1 += src[(2 * i + 1) * MK_MAX_ROWS + r];
+                const int w0 = s_wfirst[pj], w1 = s_wlast[pj];
+                if (T >= kWarps) {
+                    // every warp holds stages: pieces w0..w1 (at most kWarps) all exist.  All loads first, then the sum in
+                    // warp order -- the order is what makes the result reproducible, the loads need not wait for each other.
+                    float pa[kWarps], pb[kWarps];
+#pragma unroll
+                    for (int j = 0; j < kWarps; ++j) {
+                        const float* src = spart + (size_t)(pj + min(w0 + j, w1)) * kPartStride;
+                        pa[j] = src[(2 * i) * MK_MAX_ROWS + r];
+                        pb[j] = src[(2 * i + 1) * MK_MAX_ROWS + r];
+                    }
+#pragma unroll
+                    for (int j = 0; j < kWarps; ++j)
+                        if (w0 + j <= w1) {
+                            v0 += pa[j];
+                            v1 += pb[j];
+                        }
+                } else {
+                    for (int w = w0; w <= w1; ++w) {
+                        if (chunk_begin(w, T) == chunk_begin(w + 1, T)) continue;  // a warp without stages
+                        const float* src = spart + (size_t)(pj + w) * kPartStride;
+                        v0 += src[(2 * i) * MK_MAX_ROWS + r];
+                        v1 += src[(2 * i + 1) * MK_MAX_ROWS + r];
+                    }
                 }
-                const int panel = blockIdx.x + gridDim.x * (base + pj);
+                const int panel = s_first[phi] + pstride * (base + pj);
+                if (tr && o == 0 && base == 0) tr[14] = clock64();  // thread 0's pieces summed
                 if (ph.kind == MK_QKV) {
                     const int hd = p.head_dim, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
                     const int ppb = half >> 2;  // panels per head
@@ -800,23 +847,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 }
             }
 
+            if (tr && base == 0) tr[15] = clock64();  // thread 0 through its outputs of the first round
             __syncthreads();  // the partial buffer is reused by the next round
             }  // rounds
             if (send_rows) __threadfence_system();  // peer stores performed before this CTA arrives at the next barrier
 
-            if (ph.kind == MK_QKV && phi + 1 < p.n_phases && phases[phi + 1].kind == MK_ATTN) {
-                // prefetch the old K/V rows of this CTA's first attention tile before the barrier
-                const int n_units = R * p.n_kv_heads * p.n_splits;
-                if ((int)blockIdx.x < n_units) {
-                    const AttnUnit a = attn_unit(p, sc, blockIdx.x);
-                    const int tend = min(a.t1, a.t0 + kTT);
-                    const int upto = max(a.t0, min(tend, attn_safe_end(sc, a)));
-                    if (upto > a.t0) {
-                        attn_load_rows(p, *L, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, true, false);
-                        attn_load_rows(p, *L, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, false, true);
-                    }
-                }
-            }
+            if (ph.kind == MK_QKV && phi + 1 < p.n_phases && phases[phi + 1].kind == MK_ATTN &&
+                (int)blockIdx.x < R * p.n_kv_heads * p.n_splits)
+                kv_prefetch_layer = ph.layer;  // issued right after this CTA has arrived at the barrier (see the loop head)
 
             if (tr) tr[3] = clock64();
             if (ph.kind == MK_HEAD) {

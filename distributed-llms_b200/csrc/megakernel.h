@@ -11,6 +11,7 @@ constexpr int MK_STAGE_K = 256;                    // k-elements of one stage
 constexpr int MK_STAGE_BYTES = 8 * MK_STAGE_K * 2; // one stage = 8 weight rows x 256 k, bf16 = 4 KB
 constexpr int MK_MAX_ROWS = 16;
 constexpr int MK_MAX_SPLITS = 16;  // the merge loads the partials in batches of eight 16-byte vectors per thread
+constexpr int MK_TRACE_SLOTS = 16;   // clock stamps per phase in the debug trace (DLLM_MK_TRACE)
 constexpr int MK_MAX_PHASES = 512;  // 5 per layer + 2: up to 102 layers per stage
 constexpr int MK_SMEM_BUDGET = 227 * 1024 - 6 * 1024;  // dynamic shared memory: the opt-in maximum less the kernel's static arrays
 constexpr int MK_ROUND_PANELS = 13; // panels a CTA works on between two epilogues
@@ -50,6 +51,7 @@ struct MkParams {
     int32_t n_phases, n_steps, n_rows;
     int32_t hidden, n_heads, n_kv_heads, head_dim, vocab, k_max;
     int32_t norm, rope, stages, n_splits, advance, tok_base, part_units;
+    int32_t blocked;         // 1: a CTA owns a contiguous run of every phase's panels, 0: panel p belongs to CTA p % grid
     float eps;
     void* h;                 // [R, d] residual stream
     void* q;                 // [R, H*hd]

@@ -93,17 +93,30 @@ __device__ __forceinline__ uint4 ldcg_u4(const void* p) { return __ldcg(reinterp
 __device__ __forceinline__ int ldcg_i32(const int32_t* p) { return __ldcg(p); }
 
 // All CTAs of the (co-resident, cooperative) grid meet here.  `target` advances by gridDim.x per barrier.
-__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target) {
+// The barrier in two halves, so that work which does not depend on the other CTAs (cp.async prefetches of old K/V rows)
+// can be issued between this CTA's arrival and the moment everybody has arrived.
+__device__ __forceinline__ void grid_barrier_arrive(unsigned* bar, unsigned& target, long long* tr = nullptr) {
     __syncthreads();
     target += gridDim.x;
     if (threadIdx.x == 0) {
-        // release: the CTA's earlier writes (ordered before by bar.sync) become visible before the arrival;
-        // acquire: nothing after the barrier is satisfied from stale data
+        // release: the CTA's earlier writes (ordered before by bar.sync) become visible before the arrival
+        if (tr) tr[8] = clock64();
         red_release_add(bar, 1u);
+        if (tr) tr[9] = clock64();
+    }
+}
+__device__ __forceinline__ void grid_barrier_wait(const unsigned* bar, unsigned target, long long* tr = nullptr) {
+    if (threadIdx.x == 0) {
+        // acquire: nothing after the barrier is satisfied from stale data
         for (unsigned spins = 0; ld_acquire_u32(bar) < target; ++spins)
             if (spins > (1u << 26)) __trap();  // a lost arrival is a bug; do not hang the GPU
+        if (tr) tr[10] = clock64();
     }
     __syncthreads();
+}
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target, long long* tr = nullptr) {
+    grid_barrier_arrive(bar, target, tr);
+    grid_barrier_wait(bar, target, tr);
 }
 
 // ---- tickets in (peer) mailboxes: system scope, the writer may be another GPU ------------------------------
@@ -188,11 +201,21 @@ struct WIter {
     // cached at seek time so that advancing by one stage needs no division and no phase-table lookup
     const unsigned char* wp;
     int K, ns, xg;
+    int p0, pstride;        // this CTA's panel with local index i in the phase at hand: p0 + pstride * i
 };
 
 __device__ __forceinline__ int local_panels(const MkPhase& ph) {
     const int c = blockIdx.x, G = gridDim.x;
     return c < ph.n_panels ? (ph.n_panels - c + G - 1) / G : 0;
+}
+// Panels -> CTAs.  Interleaved: panel p belongs to CTA p % grid.  Blocked: CTA c owns a contiguous run of panels (the first
+// n % grid CTAs one more than the others -- the same counts as interleaved), i.e. one contiguous piece of every weight
+// matrix: its TMA stream walks 2 MB pages one after the other instead of touching every page of the matrix.
+__device__ __forceinline__ int panel_first(const MkPhase& ph, int blocked) {
+    const int c = blockIdx.x, G = gridDim.x;
+    if (!blocked) return c;
+    const int q = ph.n_panels / G, rem = ph.n_panels - q * G;
+    return c * q + min(c, rem);
 }
 
 struct Ctx {
@@ -203,6 +226,7 @@ struct Ctx {
     int* xst;               //         and its stage index (lane 0 only)
     const MkPhase* phases;  // shared-memory copy
     const int* units;       // shared: panels this CTA owns in each phase (0 = not a weight phase)
+    const int* first;       // shared: the first of them (blocked assignment) -- see panel_first()
     int warp, lane;
     uint32_t ring;          // shared address of this warp's stages
     uint32_t full;          // shared address of this warp's mbarriers
@@ -227,6 +251,7 @@ __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
                     it.wp = static_cast<const unsigned char*>(ph.wp);
                     it.K = ph.K;
                     it.xg = ph.xg;
+                    it.p0 = c.first[it.ph];
                     return;
                 }
                 it.j0 += MK_ROUND_PANELS;
@@ -243,7 +268,7 @@ __device__ __forceinline__ void issue_stage(const Ctx& c, const WIter& it, int s
     if (c.lane == 0) {
         uint32_t bytes;
         const uint32_t dst = c.ring + slot * kStageBytes, bar = c.full + slot * 8;
-        const int panel = blockIdx.x + gridDim.x * (it.j0 + it.jr);
+        const int panel = it.p0 + it.pstride * (it.j0 + it.jr);
         if (!it.xg) {
             const unsigned char* src = it.wp + mk_stage_offset(it.K, panel, it.st, kStageBytes, &bytes);
             mbar_expect_tx(bar, bytes);

@@ -557,6 +557,8 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     p.rope_cos = s->io.rope_cos; p.rope_sin = s->io.rope_sin;
     p.barrier = s->mk_sync; p.done = s->mk_sync + 1; p.arg_counter = s->mk_sync + 2;
     p.n_micro = 1;
+    p.blocked = 1;
+    if (const char* e = getenv("DLLM_MK_BLOCKED")) p.blocked = atoi(e) != 0;  // 0: panel p -> CTA p % grid (A/B measurements)
     if (pipe) {
         p.n_micro = pipe->n_micro; p.ticket_base = pipe->step_base; p.flag_stride = kFlagStride;
         p.out_phase = s->mk_out_phase;
@@ -569,7 +571,7 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     if (s->num_sms > s->arg_grid_cap) return fail("internal: argmax scratch too small for the persistent kernel");
     const char* trace_path = getenv("DLLM_MK_TRACE");
     long long* d_trace = nullptr;
-    const size_t trace_n = (size_t)n_steps * s->mk_n_phases * 8;
+    const size_t trace_n = (size_t)n_steps * s->mk_n_phases * MK_TRACE_SLOTS;
     if (trace_path && n_steps > 1) {  // debug: per-phase SM-clock stamps of CTA 0, dumped after a device sync
         CUDA_TRY(cudaMalloc((void**)&d_trace, trace_n * 8));
         CUDA_TRY(cudaMemsetAsync(d_trace, 0, trace_n * 8, st));
@@ -584,11 +586,14 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
         std::vector<MkPhase> ph(s->mk_n_phases);
         CUDA_TRY(cudaMemcpy(ph.data(), s->mk_phases, ph.size() * sizeof(MkPhase), cudaMemcpyDeviceToHost));
         if (FILE* f = fopen(trace_path, "w")) {
-            fprintf(f, "step,phase,kind,layer,t_start,t_prologue,t_main,t_epilogue,c_wait,c_mma,c_issue,n_stages\n");
+            fprintf(f, "step,phase,kind,layer,t_start,t_prologue,t_main,t_epilogue,c_wait,c_mma,c_issue,n_stages,b_enter,b_arrived,b_done,"
+                       "p_loaded,p_reduced,p_stored,e_summed,e_done\n");
             for (int i = 0; i < n_steps; ++i)
                 for (int j = 0; j < s->mk_n_phases; ++j) {
-                    const long long* t = &h[((size_t)i * s->mk_n_phases + j) * 8];
-                    fprintf(f, "%d,%d,%d,%d,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld\n", i, j, (int)ph[j].kind, (int)ph[j].layer, t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7]);
+                    const long long* t = &h[((size_t)i * s->mk_n_phases + j) * MK_TRACE_SLOTS];
+                    fprintf(f, "%d,%d,%d,%d,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld,%lld\n", i, j,
+                            (int)ph[j].kind, (int)ph[j].layer, t[0], t[1], t[2], t[3], t[4], t[5], t[6], t[7], t[8], t[9], t[10], t[11],
+                            t[12], t[13], t[14], t[15]);
                 }
             fclose(f);
         }

@@ -85,6 +85,51 @@ def check_steps(stats, what):
     return max(s[0] for s in stats), max(s[3] for s in stats), n_flip
 
 
+# ---- BASELINE configs[0]: GPT-2 small (124M), 2 layer shards, greedy decode of 32 tokens -------------------------------
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gpt2_small_two_shards_32_tokens(dtype):
+    """The reference's own CPU-runnable case at full size, on the GPU: GPT-2 small split into 2 layer shards (6 + 6 layers,
+    embeddings on shard 0, final norm + tied head on shard 1), 16-token prompt, 32 greedy tokens.  fp32: ids identical to
+    the oracle pipeline, logits within 1e-4.  bf16: every step under the oracle's history, held to the oracle's own
+    summation-order sensitivity like the other full-size cases."""
+    from oracle.shard_oracle import build_pipeline, greedy_generate, make_state_dict, split_state_dict
+    cfg = ORACLE_CONFIGS["gpt2-small"]
+    sd = {k: v.to(dtype) for k, v in make_state_dict(cfg, 1234, torch.float32).items()}
+    prompts = make_prompts(cfg.vocab, 1, 16, seed=7)
+    stages = []
+    for i, part in enumerate(split_state_dict(cfg, sd, 2)):
+        st = ModelShard(i, dict(part), config=cfg.to_hf_dict(), max_rows=64, max_seqs=1, max_context=64, page_size=16)
+        st.to_device()
+        stages.append(st)
+    if dtype == torch.float32:
+        o_ids, o_lg, _ = greedy_generate(build_pipeline(cfg, sd, 2, dtype), prompts, 32, record=True)
+        x, ids, errs = {"input_ids": prompts}, [], []
+        for t in range(32):
+            out = stages[1].compute(stages[0].compute(x))
+            ids.append(out["next_token"].cpu())
+            errs.append(rel_err(out["logits"], o_lg[:, t]))
+            x = {"input_ids": ids[-1][:, None]}
+        assert torch.equal(torch.stack(ids, 1), o_ids)
+        assert max(errs) < 1e-4, errs
+        print(f"\n[parity] gpt2-small fp32, 2 shards: 32/32 greedy ids identical, worst logit rel err {max(errs):.2e}")
+        return
+    p32 = {k: v.float() for k, v in sd.items()}
+    oracle = build_pipeline(cfg, p32, 2, dtype)
+    twin = [OracleShard(i, st.parameters, cfg, dtype, None, ksplit=2) for i, st in enumerate(oracle)]
+
+    class Chain:  # two stages behind the one-stage interface teacher_forced() drives
+        def __init__(self, parts): self.parts = parts
+        def reset(self):
+            for q in self.parts: q.reset()
+        def compute(self, x):
+            for q in self.parts: x = q.compute(x)
+            return x
+    stats, _ = teacher_forced(Chain(stages), Chain(oracle), Chain(twin), prompts, 32)
+    worst, worst_twin, n_flip = check_steps(stats, "gpt2-small")
+    print(f"\n[parity] gpt2-small bf16, 2 shards, 32 steps under the oracle's history: CUDA vs oracle worst logit rel err {worst:.2e} "
+          f"(oracle vs its twin {worst_twin:.2e}); {n_flip} of 32 ids differ")
+
+
 # ---- BASELINE configs[1]: TinyLlama-1.1B, batch 1, 512-token prompt ------------------------------------------------
 @pytest.fixture(scope="module")
 def tinyllama_weights():

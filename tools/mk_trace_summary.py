@@ -37,3 +37,32 @@ for k, a in agg.items():
     print(f"{k:8s} {n/(steps-1):6.0f} {a[1]/n:8.2f} {a[2]/n:9.2f} {a[3]/n:8.2f} {a[4]/n:9.2f}{extra}")
     tot += sum(a[1:5])
 print(f"per step: {tot/(steps-1):.1f} us")
+# fine stamps (CTA 0, thread 0): where the time inside barrier / prologue / epilogue goes
+fine = collections.defaultdict(lambda: [0] + [0.0] * 11)
+prev_end = None
+for r in rows:
+    if "b_enter" not in r:
+        break
+    t0, t1, t2, t3 = (int(r[k]) for k in ("t_start", "t_prologue", "t_main", "t_epilogue"))
+    if int(r["step"]) == 0 or prev_end is None:
+        prev_end = t3
+        continue
+    g = {k: int(r[k]) for k in ("b_enter", "b_arrived", "b_done", "p_loaded", "p_reduced", "p_stored", "e_summed", "e_done")}
+    a = fine[names[int(r["kind"])]]
+    a[0] += 1
+    if g["b_enter"]:
+        a[1] += (g["b_enter"] - prev_end) / mhz      # first __syncthreads of the barrier (waiting for this CTA's other warps)
+        a[2] += (g["b_arrived"] - g["b_enter"]) / mhz  # red.release (the CTA's stores must have been performed)
+        a[3] += (g["b_done"] - g["b_arrived"]) / mhz   # poll until every CTA has arrived
+        a[4] += (t0 - g["b_done"]) / mhz               # second __syncthreads + per-step set-up
+    if g["p_loaded"]:
+        a[5] += (g["p_loaded"] - t0) / mhz; a[6] += (g["p_reduced"] - g["p_loaded"]) / mhz; a[7] += (g["p_stored"] - g["p_reduced"]) / mhz
+        a[8] += (t1 - g["p_stored"]) / mhz
+    if g["e_summed"]:
+        a[9] += (g["e_summed"] - t2) / mhz; a[10] += (g["e_done"] - g["e_summed"]) / mhz; a[11] += (t3 - g["e_done"]) / mhz
+    prev_end = t3
+print("fine (us): barrier = sync-in | red.release | poll | sync-out ; norm prologue = loads | reduce | normalise+store | sync ; "
+      "epilogue = sum pieces | outputs of round 0 | rest")
+for k, a in fine.items():
+    n = a[0]
+    print(f"{k:8s} {a[1]/n:6.2f} {a[2]/n:6.2f} {a[3]/n:6.2f} {a[4]/n:6.2f}   ; {a[5]/n:6.2f} {a[6]/n:6.2f} {a[7]/n:6.2f} {a[8]/n:6.2f}   ; {a[9]/n:6.2f} {a[10]/n:6.2f} {a[11]/n:6.2f}")
