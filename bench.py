@@ -373,7 +373,10 @@ def run_single(args) -> int:
         "dtype": "bf16", "data": "synthetic",
         "config": make_config(model, batch, prompt_len, 1, L),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": 3 * 4 * batch, "d2h_bytes_per_step": 4 * batch,
-                "ms_per_step": e2e_ms / K},
+                "ms_per_step": e2e_ms / K,
+                "transfer": "ids / positions / slots are read from, and the sampled id written to, pinned host buffers every step "
+                            "(by the kernel, in place: dllm_shard_forward adds no copy nodes for pinned int32 buffers); the host "
+                            "synchronises the stream and feeds the id back"},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": roofline,

@@ -578,16 +578,22 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     sc.seq[threadIdx.x] = sq;
                     sc.page[threadIdx.x] = p.block_table[(size_t)sq * p.pages_per_seq + (ps >> p.page_shift)];
                     sc.off[threadIdx.x] = ps & ((1 << p.page_shift) - 1);
+                    if (p.mirror_pos && blockIdx.x == 0) {  // inputs were read in place from host memory: keep the device copies current
+                        p.mirror_pos[threadIdx.x] = ps;
+                        p.mirror_seq[threadIdx.x] = sq;
+                        if (p.mirror_ids) p.mirror_ids[threadIdx.x] = ldcg_i32(ids_m + threadIdx.x);
+                    }
                 }
+                __syncthreads();  // positions and slots are in shared memory (they may live in host memory: read them once)
                 for (int i = threadIdx.x; i < R * p.pages_per_seq; i += kThreads) {
                     const int r = i / p.pages_per_seq;
-                    sbt[i] = p.block_table[(size_t)ldcg_i32(seq_m + r) * p.pages_per_seq + (i - r * p.pages_per_seq)];
+                    sbt[i] = p.block_table[(size_t)sc.seq[r] * p.pages_per_seq + (i - r * p.pages_per_seq)];
                 }
                 if (p.rope) {
                     const int half = p.head_dim >> 1;
                     for (int i = threadIdx.x; i < R * p.head_dim; i += kThreads) {
                         const int r = i / p.head_dim, e = i - r * p.head_dim;
-                        const int ps = ldcg_i32(pos_m + r) + pos_add;
+                        const int ps = sc.pos[r];
                         srope[i] = e < half ? p.rope_cos[(size_t)ps * half + e] : p.rope_sin[(size_t)ps * half + e - half];
                     }
                 }
@@ -893,6 +899,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         }
                         if (lane == 0) {
                             p.next_token[r] = b.idx;
+                            if (p.next_token_host) p.next_token_host[r] = b.idx;  // pinned host memory: the caller reads it after the stream
                             if (piped) p.out_tokens[(size_t)m * R + r] = b.idx;  // into the first stage's inbox
                             if (p.advance) {
                                 p.ids[r] = b.idx;

@@ -74,6 +74,11 @@ struct MkParams {
     const void *wte, *wpe, *final_norm_w, *final_norm_b;
     const float *rope_cos, *rope_sin;
     unsigned *barrier, *done, *arg_counter;  // zero between launches
+    // Single steps driven by a host loop: ids / positions / slots may be read in place from pinned host memory (no copy
+    // nodes in front of the launch) and the sampled ids written there; the device copies below are then refreshed by the
+    // kernel itself, for a decode loop that may follow.
+    int32_t *mirror_ids, *mirror_pos, *mirror_seq;   // null = p.ids / p.pos / p.seq ARE the device copies
+    int32_t* next_token_host;                        // null = none
     long long* trace;        // optional [n_steps][n_phases][4] SM-clock stamps of CTA 0 (debug, DLLM_MK_TRACE)
     // ---- fused hand-off (null in_flag = off).  The kernel runs n_steps = decode steps x n_micro micro-batch steps;
     // micro-batch m = step % n_micro uses rows [m*R, (m+1)*R) of pos / seq and slot m of the mailboxes.  A slot's

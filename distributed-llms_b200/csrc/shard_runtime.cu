@@ -112,6 +112,7 @@ struct dllm_shard {
     // true after a decode loop: `pos` already holds the position of the pending token (the loops advance after
     // every step, the last one included); false after a forward: `pos` is the position of the rows just processed
     bool pos_at_pending = false;
+    int arange_rows = 0;  // logit_rows[0 .. arange_rows) currently holds 0, 1, 2, ... (skips the identity copy of single steps)
 };
 
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
@@ -528,7 +529,25 @@ struct MkPipe {
     unsigned step_base;
 };
 
-static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, cudaStream_t st, const MkPipe* pipe = nullptr) {
+// a single step whose int32 inputs are read in place (pinned host or device memory) and whose sampled ids go straight out
+struct MkHostIo {
+    const int32_t *ids, *pos, *seq;   // device-visible addresses
+    int32_t* next_token;              // device-visible address or null
+};
+
+// the address the device can use for `ptr` when it is pinned / registered host memory or device memory; null for pageable memory
+static const void* device_visible(const void* ptr) {
+    cudaPointerAttributes a{};
+    if (cudaPointerGetAttributes(&a, ptr) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    if (a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return a.devicePointer;
+    return nullptr;
+}
+
+static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, cudaStream_t st, const MkPipe* pipe = nullptr,
+                          const MkHostIo* io = nullptr) {
     const dllm_shard_config& c = s->cfg;
     const int variant = mk_variant(s, n_rows, n_rows, true);
     if (variant == 0) return fail("internal: persistent kernel not eligible");
@@ -556,6 +575,11 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     p.final_norm_w = s->io.final_norm_w; p.final_norm_b = s->io.final_norm_b;
     p.rope_cos = s->io.rope_cos; p.rope_sin = s->io.rope_sin;
     p.barrier = s->mk_sync; p.done = s->mk_sync + 1; p.arg_counter = s->mk_sync + 2;
+    if (io) {  // read in place, mirror into the handle's device copies
+        p.ids = const_cast<int32_t*>(io->ids); p.pos = const_cast<int32_t*>(io->pos); p.seq = io->seq;
+        p.mirror_ids = s->ids; p.mirror_pos = s->pos; p.mirror_seq = s->seq;
+        p.next_token_host = io->next_token;
+    }
     p.n_micro = 1;
     p.blocked = 1;
     if (const char* e = getenv("DLLM_MK_BLOCKED")) p.blocked = atoi(e) != 0;  // 0: panel p -> CTA p % grid (A/B measurements)
@@ -779,28 +803,48 @@ extern "C" int dllm_shard_forward(dllm_shard* s, const void* input, const int32_
     int dev = -1;
     cudaGetDevice(&dev);
     if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
-    if (c.has_embed) CUDA_TRY(cudaMemcpyAsync(s->ids, input, (size_t)n_rows * 4, cudaMemcpyDefault, st));
-    else CUDA_TRY(cudaMemcpyAsync(s->h, input, (size_t)n_rows * c.hidden * s->esz, cudaMemcpyDefault, st));
-    CUDA_TRY(cudaMemcpyAsync(s->pos, positions, (size_t)n_rows * 4, cudaMemcpyDefault, st));
-    CUDA_TRY(cudaMemcpyAsync(s->seq, seq_ids, (size_t)n_rows * 4, cudaMemcpyDefault, st));
     int nl = 0;
     if (c.has_head) {
         if (logit_rows) {
             if (n_logit_rows <= 0 || n_logit_rows > n_rows) return fail("dllm_shard_forward: n_logit_rows out of range");
             nl = n_logit_rows;
-            CUDA_TRY(cudaMemcpyAsync(s->logit_rows, logit_rows, (size_t)nl * 4, cudaMemcpyDefault, st));
         } else if (n_logit_rows >= 0) {
             nl = n_rows;
         }  // n_logit_rows < 0 with no row list: no logits this call (an inner chunk of a chunked prefill)
     }
     const bool use_mk = mk_eligible(s, n_rows, nl, logit_rows == nullptr);
+    // A token-by-token host loop (the master's relay, bench.py's e2e figure) pays for every copy node in front of the launch.
+    // When the stage owns the embedding and the caller's int32 buffers are pinned host (or device) memory, the persistent
+    // kernel reads them in place and writes the sampled ids straight back: the call is one launch, no copies.
+    MkHostIo io{};
+    bool in_place = false;
+    if (use_mk && c.has_embed && !hidden_out && !logits_out) {
+        io.ids = static_cast<const int32_t*>(device_visible(input));
+        io.pos = static_cast<const int32_t*>(device_visible(positions));
+        io.seq = static_cast<const int32_t*>(device_visible(seq_ids));
+        io.next_token = next_token_out ? static_cast<int32_t*>(const_cast<void*>(device_visible(next_token_out))) : nullptr;
+        in_place = io.ids && io.pos && io.seq && (!next_token_out || io.next_token);
+    }
+    if (!in_place) {
+        if (c.has_embed) CUDA_TRY(cudaMemcpyAsync(s->ids, input, (size_t)n_rows * 4, cudaMemcpyDefault, st));
+        else CUDA_TRY(cudaMemcpyAsync(s->h, input, (size_t)n_rows * c.hidden * s->esz, cudaMemcpyDefault, st));
+        CUDA_TRY(cudaMemcpyAsync(s->pos, positions, (size_t)n_rows * 4, cudaMemcpyDefault, st));
+        CUDA_TRY(cudaMemcpyAsync(s->seq, seq_ids, (size_t)n_rows * 4, cudaMemcpyDefault, st));
+    }
+    if (c.has_head && logit_rows) {
+        CUDA_TRY(cudaMemcpyAsync(s->logit_rows, logit_rows, (size_t)nl * 4, cudaMemcpyDefault, st));
+        s->arange_rows = 0;
+    }
     // every path leaves logit_rows describing this call's logit rows: a decode loop that follows gathers its
     // positions / slots through them (the persistent kernel itself takes every row's logits in place)
-    if (c.has_head && !logit_rows && nl > 0)
+    if (c.has_head && !logit_rows && nl > s->arange_rows) {
         CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)nl * 4, cudaMemcpyDeviceToDevice, st));
+        s->arange_rows = nl;  // (a shorter identity prefix is already in place)
+    }
     s->pos_at_pending = false;
     if (use_mk) {
-        if (run_megakernel(s, n_rows, 1, false, st)) return 1;
+        if (run_megakernel(s, n_rows, 1, false, st, nullptr, in_place ? &io : nullptr)) return 1;
+        if (in_place) return 0;  // the sampled ids are already where the caller wants them
     } else if (prefill_eligible(s, n_rows)) {
         int run_seqs = 0, run_len = 0;
         static const bool fa_off = [] { const char* e = getenv("DLLM_PREFILL_ATTN"); return e && e[0] == '0'; }();

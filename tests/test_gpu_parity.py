@@ -391,6 +391,38 @@ def test_stage_boundary_inside_a_layer(dtype, arch):
         assert torch.equal(ids2, o_ids) and rel_err(lg2, o_lg) < 1e-4
 
 
+def test_single_steps_on_pinned_host_buffers_read_in_place():
+    """`dllm_shard_forward` on pinned host int32 buffers (what a master's token loop passes): the persistent kernel reads
+    ids / positions / slots in place and writes the sampled id straight to host memory.  Same ids as the same steps on
+    device tensors (copy path) and as the device loop; a decode loop right after such a step continues correctly (the
+    handle's device copies were refreshed by the kernel)."""
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, 2, 10, seed=2)
+    (st,) = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=32, max_seqs=2, max_context=128, page_size=16)
+    ex = st.executor
+    first = st.compute({"input_ids": prompts})["next_token"].cpu()
+    want = st.decode_loop(2, 9).cpu()                      # 9 further ids from the device loop
+    st.reset()
+    st.compute({"input_ids": prompts})
+    for s_ in range(2):
+        ex.reserve(s_, 10 + 9 + 1)
+    ids_h = first.to(torch.int32).pin_memory()
+    pos_h = torch.full((2,), 10, dtype=torch.int32).pin_memory()
+    seq_h = torch.arange(2, dtype=torch.int32).pin_memory()
+    nxt_h = torch.zeros(2, dtype=torch.int32).pin_memory()
+    got = []
+    for _ in range(5):
+        ex.step_host(ids_h, pos_h, seq_h, next_token_out=nxt_h)
+        torch.cuda.current_stream().synchronize()
+        got.append(nxt_h.clone())
+        ids_h.copy_(nxt_h); pos_h.add_(1)
+    assert torch.equal(torch.stack(got, 1).to(torch.int64), want[:, :5])
+    ex._seq_len = {0: 15, 1: 15}
+    rest = st.decode_loop(2, 4).cpu()                      # the loop picks up from the in-place steps
+    assert torch.equal(rest, want[:, 5:])
+
+
 def test_chunked_prefill_equals_single_call():
     """max_rows smaller than the prompt -> chunked prefill; same logits (fp32 tolerance) and token."""
     cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
