@@ -458,7 +458,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     }
     sp += mk_rows_region_bytes(p);
     float* spart = reinterpret_cast<float*>(sp);
-    sp += (size_t)p.part_units * kPartStride * 4;
+    sp += mk_part_bytes(p);
     float* srope = reinterpret_cast<float*>(sp);  // [R][head_dim]: cos row then sin row of each batch row's position
     sp += (size_t)p.n_rows * p.head_dim * 4;
     int* sbt = reinterpret_cast<int*>(sp);        // [R][pages_per_seq]: block-table row of each batch row's sequence
@@ -736,14 +736,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 for (int q = 0; q < 4; ++q) acc[q] = (acc[q] + acc1[q]) + (acc2[q] + acc3[q]);
                 // C[batch g][panel rows 2*t4, 2*t4+1] (and batch g+8) -> partial buffer [jr + warp][panel row][batch]
                 // (jr and warp both grow along the round's stage sequence, so jr + warp is unique per piece)
-                float* dstp = spart + (size_t)(jr + warp) * kPartStride;
+                float* dstp = spart + (size_t)(jr + warp) * (8 * RP);
                 if (g < R) {
-                    dstp[(2 * t4) * MK_MAX_ROWS + g] = acc[0];
-                    dstp[(2 * t4 + 1) * MK_MAX_ROWS + g] = acc[1];
+                    dstp[(2 * t4) * RP + g] = acc[0];
+                    dstp[(2 * t4 + 1) * RP + g] = acc[1];
                 }
                 if (HI && g + 8 < R) {
-                    dstp[(2 * t4) * MK_MAX_ROWS + g + 8] = acc[2];
-                    dstp[(2 * t4 + 1) * MK_MAX_ROWS + g + 8] = acc[3];
+                    dstp[(2 * t4) * RP + g + 8] = acc[2];
+                    dstp[(2 * t4 + 1) * RP + g + 8] = acc[3];
                 }
                 ++jr;
                 st = 0;
@@ -764,9 +764,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     float pa[kWarps], pb[kWarps];
 #pragma unroll
                     for (int j = 0; j < kWarps; ++j) {
-                        const float* src = spart + (size_t)(pj + min(w0 + j, w1)) * kPartStride;
-                        pa[j] = src[(2 * i) * MK_MAX_ROWS + r];
-                        pb[j] = src[(2 * i + 1) * MK_MAX_ROWS + r];
+                        const float* src = spart + (size_t)(pj + min(w0 + j, w1)) * (8 * RP);
+                        pa[j] = src[(2 * i) * RP + r];
+                        pb[j] = src[(2 * i + 1) * RP + r];
                     }
 #pragma unroll
                     for (int j = 0; j < kWarps; ++j)
@@ -777,9 +777,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 } else {
                     for (int w = w0; w <= w1; ++w) {
                         if (chunk_begin(w, T) == chunk_begin(w + 1, T)) continue;  // a warp without stages
-                        const float* src = spart + (size_t)(pj + w) * kPartStride;
-                        v0 += src[(2 * i) * MK_MAX_ROWS + r];
-                        v1 += src[(2 * i + 1) * MK_MAX_ROWS + r];
+                        const float* src = spart + (size_t)(pj + w) * (8 * RP);
+                        v0 += src[(2 * i) * RP + r];
+                        v1 += src[(2 * i + 1) * RP + r];
                     }
                 }
                 const int panel = s_first[phi] + pstride * (base + pj);
@@ -987,7 +987,7 @@ size_t mk_smem_bytes(const MkParams& p, int stages) {
     size_t b = up((size_t)p.n_phases * sizeof(MkPhase));
     b += up((size_t)kWarps * stages * 8);
     b += mk_rows_region_bytes(p);
-    b += (size_t)p.part_units * kPartStride * 4;
+    b += mk_part_bytes(p);
     b += (size_t)p.n_rows * p.head_dim * 4;
     b += (size_t)((p.n_rows * p.pages_per_seq * 4 + 15) / 16) * 16;
     b = up(b) + 128;

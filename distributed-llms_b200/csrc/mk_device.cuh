@@ -412,6 +412,13 @@ __host__ __device__ inline size_t mk_attn_q_bytes(int head_dim) {
     return rows16 > f32 ? rows16 : f32;
 }
 
+// partial sums of a round: one unit per (panel, warp) piece, [8 panel rows][rows rounded up to a power of two] floats each
+__host__ __device__ inline size_t mk_part_bytes(const MkParams& p) {
+    int rp = 1;
+    while (rp < p.n_rows) rp <<= 1;
+    return ((size_t)p.part_units * 8 * rp * 4 + 127) / 128 * 128;
+}
+
 // shared region that holds the staged input rows (weight phases) or the attention tiles (attention phase)
 __host__ __device__ inline size_t mk_rows_region_bytes(const MkParams& p) {
     const size_t rows = (size_t)p.n_rows * (p.k_max + 8) * 2;
