@@ -40,6 +40,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t ok = 0;
     for (unsigned spins = 0; !ok; ++spins) {
@@ -102,41 +105,63 @@ __device__ __forceinline__ float gelu_new_f(float x) {
     return 0.5f * x * (1.0f + tanhf(0.7978845608028654f * (x + 0.044715f * x * x * x)));
 }
 
+// One tile's coordinates: which row segment of the logical weight matrix (q | k | v in one launch; BIAS epilogue only),
+// its tensor map, its first row / column.  Tiles are numbered m-fastest, so that the CTAs working side by side share a
+// weight tile (and L2 serves it once).
+struct TileCoord {
+    int seg, m0, n0, col0, seg_n;
+};
+template <int EPI, int BN>
+__device__ __forceinline__ TileCoord tile_coord(const GemmTcParams& p, int t, int tiles_m) {
+    TileCoord c;
+    c.seg = 0; c.col0 = 0; c.seg_n = p.N;
+    int tn = t / tiles_m;
+    c.m0 = (t - tn * tiles_m) * BM;
+    if (EPI != GEMM_EPI_SWIGLU) {
+        const int t0 = (p.N + BN - 1) / BN, t1 = (p.n_more[0] + BN - 1) / BN;
+        if (tn >= t0 + t1) { c.seg = 2; tn -= t0 + t1; c.col0 = p.N + p.n_more[0]; c.seg_n = p.n_more[1]; }
+        else if (tn >= t0) { c.seg = 1; tn -= t0; c.col0 = p.N; c.seg_n = p.n_more[0]; }
+    }
+    c.n0 = tn * BN;
+    return c;
+}
+
+// Persistent: one CTA per SM walks tiles t = blockIdx.x, + gridDim.x, ...  The accumulator is double-buffered in tensor
+// memory, so the MMA warp starts tile i+1 while the epilogue warps are still reading tile i out -- the epilogue
+// (tcgen05.ld, SiLU / residual arithmetic, stores) no longer sits between two main loops -- and the TMA ring never drains
+// at a tile boundary.
 template <int EPI, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
-               const __grid_constant__ CUtensorMap tm_b2, const __grid_constant__ CUtensorMap tm_b3, const GemmTcParams p) {
+               const __grid_constant__ CUtensorMap tm_b2, const __grid_constant__ CUtensorMap tm_b3, const GemmTcParams p,
+               const int n_tiles, const int tiles_m) {
     constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
     static_assert(!(kDual && BN != 128), "the dual-B tile is 128 wide");
     constexpr int kBTileBytes = BN * BK * 2;
     constexpr int kStageBytes = kTileBytes + kBTileBytes * (kDual ? 2 : 1);
-    constexpr uint32_t kTmemCols = kDual ? 256 : BN;
+    constexpr uint32_t kAccCols = kDual ? 256 : BN;       // columns of one accumulator
+    constexpr uint32_t kTmemCols = 2 * kAccCols < 32 ? 32 : 2 * kAccCols;  // two of them
     constexpr uint32_t kIdesc = make_idesc(BN);
     constexpr int kStages = gemm_stages(kStageBytes);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t bars[2 * kStages + 1];
+    __shared__ __align__(8) uint64_t bars[2 * kStages + 4];
     __shared__ uint32_t s_tmem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // row segment of the logical weight matrix this tile belongs to (q | k | v in one launch; BIAS epilogue only)
-    int seg = 0, tile = blockIdx.x, col0 = 0, seg_n = p.N;
-    if (!kDual) {
-        const int t0 = (p.N + BN - 1) / BN, t1 = (p.n_more[0] + BN - 1) / BN;
-        if (tile >= t0 + t1) { seg = 2; tile -= t0 + t1; col0 = p.N + p.n_more[0]; seg_n = p.n_more[1]; }
-        else if (tile >= t0) { seg = 1; tile -= t0; col0 = p.N; seg_n = p.n_more[0]; }
-    }
-    const CUtensorMap* map_b = seg == 0 ? &tm_b : (seg == 1 ? &tm_b2 : &tm_b3);
-    const int m0 = blockIdx.y * BM, n0 = tile * BN;
     const int num_kb = (p.K + BK - 1) / BK;
-    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages), tfull = smem_u32(bars + 2 * kStages);
+    const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
+    const uint32_t acc_full = smem_u32(bars + 2 * kStages), acc_empty = smem_u32(bars + 2 * kStages + 2);
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kStages; ++i) {
             mbar_init(full0 + i * 8, 1);
             mbar_init(empty0 + i * 8, 1);
         }
-        mbar_init(tfull, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(acc_full + i * 8, 1);
+            mbar_init(acc_empty + i * 8, 128);   // the four epilogue warps
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {  // one warp allocates tensor memory and later frees it
@@ -149,46 +174,61 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     const uint32_t tmem = s_tmem;
 
     if (warp == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer: the ring runs on across tile boundaries =====
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % kStages;
-                mbar_wait(empty0 + s * 8, ((kb / kStages) & 1) ^ 1);
-                const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
-                mbar_expect_tx(full0 + s * 8, kStageBytes);
-                tma_load_2d(dst, &tm_a, kb * BK, m0, full0 + s * 8);
-                tma_load_2d(dst + kTileBytes, map_b, kb * BK, n0, full0 + s * 8);
-                if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, kb * BK, n0, full0 + s * 8);
+            unsigned it = 0;  // k-blocks issued so far
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const TileCoord tc = tile_coord<EPI, BN>(p, t, tiles_m);
+                const CUtensorMap* map_b = tc.seg == 0 ? &tm_b : (tc.seg == 1 ? &tm_b2 : &tm_b3);
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const unsigned s = it % kStages;
+                    mbar_wait(empty0 + s * 8, ((it / kStages) & 1) ^ 1);
+                    const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
+                    mbar_expect_tx(full0 + s * 8, kStageBytes);
+                    tma_load_2d(dst, &tm_a, kb * BK, tc.m0, full0 + s * 8);
+                    tma_load_2d(dst + kTileBytes, map_b, kb * BK, tc.n0, full0 + s * 8);
+                    if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, kb * BK, tc.n0, full0 + s * 8);
+                }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) =====
+        // ===== MMA issuer (one thread): tile i+1 goes into the other accumulator while tile i is being read out =====
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % kStages;
-                mbar_wait(full0 + s * 8, (kb / kStages) & 1);
+            unsigned it = 0, lt = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+                const uint32_t acc_t = tmem + (lt & 1) * kAccCols;
+                if (lt >= 2) mbar_wait(acc_empty + (lt & 1) * 8, ((lt >> 1) & 1) ^ 1);   // the epilogue has drained this buffer
                 tc_fence_after();
-                const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
-                const uint64_t da = make_sw128_desc(base), db = make_sw128_desc(base + kTileBytes);
-                const uint64_t db2 = make_sw128_desc(base + kTileBytes + kBTileBytes);
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const unsigned s = it % kStages;
+                    mbar_wait(full0 + s * 8, (it / kStages) & 1);
+                    tc_fence_after();
+                    const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
+                    const uint64_t da = make_sw128_desc(base), db = make_sw128_desc(base + kTileBytes);
+                    const uint64_t db2 = make_sw128_desc(base + kTileBytes + kBTileBytes);
 #pragma unroll
-                for (int k = 0; k < BK / 16; ++k) {
-                    // 16 k-elements = 32 bytes further along the swizzled row: +2 in the (address >> 4) field
-                    const uint32_t acc = (kb | k) ? 1u : 0u;
-                    tc_mma(tmem, da + 2 * k, db + 2 * k, kIdesc, acc);
-                    if (kDual) tc_mma(tmem + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
+                    for (int k = 0; k < BK / 16; ++k) {
+                        // 16 k-elements = 32 bytes further along the swizzled row: +2 in the (address >> 4) field
+                        const uint32_t acc = (kb | k) ? 1u : 0u;
+                        tc_mma(acc_t, da + 2 * k, db + 2 * k, kIdesc, acc);
+                        if (kDual) tc_mma(acc_t + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
+                    }
+                    tc_commit(empty0 + s * 8);  // the slot is free once these MMAs have read it
                 }
-                tc_commit(empty0 + s * 8);  // the slot is free once these MMAs have read it
+                tc_commit(acc_full + (lt & 1) * 8);  // accumulator complete
             }
-            tc_commit(tfull);               // accumulator complete
         }
     } else {
         // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
-        mbar_wait(tfull, 0);
-        tc_fence_after();
         const int quarter = warp & 3;
-        const int row = m0 + quarter * 32 + lane;
-        const uint32_t tbase = tmem + ((uint32_t)(quarter * 32) << 16);
+        unsigned lt = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+        const TileCoord tc = tile_coord<EPI, BN>(p, t, tiles_m);
+        const int seg = tc.seg, col0 = tc.col0, seg_n = tc.seg_n, n0 = tc.n0;
+        mbar_wait(acc_full + (lt & 1) * 8, (lt >> 1) & 1);
+        tc_fence_after();
+        const int row = tc.m0 + quarter * 32 + lane;
+        const uint32_t tbase = tmem + (lt & 1) * kAccCols + ((uint32_t)(quarter * 32) << 16);
         bf16* out = static_cast<bf16*>(p.c) + col0;
         const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
         // A thread owns one output row and, per tcgen05.ld, 32 consecutive columns of it: 64 bytes of bf16.  They leave
@@ -267,6 +307,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             }
         }
         tc_fence_before();
+        mbar_arrive(acc_empty + (lt & 1) * 8);   // this accumulator may be overwritten (by the tile after next)
+        }  // tiles
     }
     __syncthreads();
     if (warp == 1) {
@@ -684,8 +726,13 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
     }
     int tiles = (p.N + BN - 1) / BN;
     if (EPI != GEMM_EPI_SWIGLU) tiles += (p.n_more[0] + BN - 1) / BN + (p.n_more[1] + BN - 1) / BN;
-    dim3 grid(tiles, (p.M + BM - 1) / BM);
-    gemm_tc_kernel<EPI, BN><<<grid, kGemmThreads, smem, st>>>(a, b, b2, b3, p);
+    const int tiles_m = (p.M + BM - 1) / BM, n_tiles = tiles * tiles_m;
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    const int n_sm = (dev >= 0 && dev < 64 && sms[dev] > 0) ? sms[dev] : 148;
+    gemm_tc_kernel<EPI, BN><<<n_tiles < n_sm ? n_tiles : n_sm, kGemmThreads, smem, st>>>(a, b, b2, b3, p, n_tiles, tiles_m);
     count_launch();
     return cudaGetLastError();
 }
