@@ -77,7 +77,8 @@ struct EmbedParams {
 
 // Prefill GEMM on tcgen05 (prefill_gemm.cu): C[M, N] = A[M, K] . W[N, K]^T, bf16 in, fp32 accumulate in TMEM.
 enum GemmEpi { GEMM_EPI_BIAS = 0, GEMM_EPI_RESIDUAL = 1, GEMM_EPI_SWIGLU = 2, GEMM_EPI_GELU = 3,
-               GEMM_EPI_LOGITS = 4 };  // LOGITS: c is fp32 [M, ldc], values rounded to bf16 (M <= 64 only)
+               GEMM_EPI_LOGITS = 4,   // LOGITS: c is fp32 [M, ldc], values rounded to bf16 (M <= 64 only)
+               GEMM_EPI_QKV = 5 };    // q | k | v segments: bias, rotary embedding, q to its buffer, k / v into the KV pages (M > 64 only)
 struct GemmTcParams {
     const void* a;      // [M, K] activations, row-major (lda = K)
     const void* w;      // [N, K] weights (nn.Linear layout)
@@ -90,6 +91,15 @@ struct GemmTcParams {
     const void* w_more[2];
     const void* bias_more[2];
     int32_t n_more[2];
+    // GEMM_EPI_QKV: the projection's epilogue is the whole K1 tail -- rotary on q and k, q rows to `q_out`, k / v rows
+    // appended to the paged cache at (seq_ids[row], positions[row]); `c` is not written
+    void* q_out;             // [M, H*hd]
+    PagedKV kv;
+    const int32_t* positions;
+    const int32_t* seq_ids;
+    const float* rope_cos;   // [max_context, hd/2] fp32, null-safe when rope == 0
+    const float* rope_sin;
+    int32_t n_heads, n_kv_heads, head_dim, rope;
 };
 struct RopeAppendParams {
     const void* qkv;    // [R, (H+2KV)*hd] projected rows (bias added)
@@ -102,6 +112,8 @@ struct RopeAppendParams {
     int32_t n_rows, n_heads, n_kv_heads, head_dim, rope;
 };
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st);
+// whether the q|k|v projection of `n_rows` rows can take GEMM_EPI_QKV (rotary + KV append in the epilogue)
+bool gemm_qkv_fusable(int n_rows, int head_dim, const void* bq, const void* bk, const void* bv);
 bool gemm_swapab_enabled();  // false under DLLM_GEMM_SWAPAB=0: M <= 64 then takes the 128-row tiles, LOGITS is unavailable
 cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
                              cudaStream_t st, const int32_t* row_map = nullptr);  // y[r] = norm(x[row_map ? row_map[r] : r])

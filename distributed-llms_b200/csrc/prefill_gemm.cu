@@ -126,6 +126,79 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmTcParams& p, int t, in
     return c;
 }
 
+// GEMM_EPI_QKV: the tail of K1 in the projection's epilogue.  A thread owns one token (row) and walks the heads of the
+// tile; it holds all HD columns of a head in registers, so both elements of every rotary pair (j, j + HD/2) are at hand.
+// Bias, rounding and rotary (q and k segments) in rope_append_kernel's order of roundings; then the head leaves as one
+// contiguous 128- or 256-byte row: q to its buffer, k / v into the KV page of (slot, position).  tcgen05.ld is
+// warp-wide, so rows past M take the loads too and skip only the arithmetic and the stores.
+template <int HD, int BN>
+__device__ __forceinline__ void qkv_tail(const GemmTcParams& p, uint32_t tbase, int row, int seg, int n0, int seg_n,
+                                         const bf16* bias) {
+    constexpr int kHalf = HD / 2;
+    const bool live = row < p.M;
+    const int pos = live ? p.positions[row] : 0;
+    const float* cs = p.rope_cos + (size_t)pos * kHalf;
+    const float* sn = p.rope_sin + (size_t)pos * kHalf;
+    bf16* kv_row = nullptr;
+    if (live && seg != 0) {
+        const int page = p.kv.block_table[(size_t)p.seq_ids[row] * p.kv.pages_per_seq + (pos >> p.kv.page_shift)];
+        const int off = pos & ((1 << p.kv.page_shift) - 1);
+        bf16* pool = static_cast<bf16*>(seg == 1 ? p.kv.kpool : p.kv.vpool);
+        kv_row = pool + ((((size_t)page * p.n_kv_heads) << p.kv.page_shift) + off) * HD;   // head 0 of that token
+    }
+    const bool rotate = p.rope && seg != 2;
+#pragma unroll 1
+    for (int h0 = 0; h0 + HD <= BN; h0 += HD) {
+        const int n = n0 + h0;            // first column of this head inside its segment (warp-uniform)
+        if (n >= seg_n) break;
+        float v[HD];
+#pragma unroll
+        for (int c0 = 0; c0 < HD; c0 += 32) {
+            uint32_t acc[32];
+            tc_ld32(tbase + h0 + c0, acc);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[c0 + j] = __uint_as_float(acc[j]);
+        }
+        if (!live) continue;
+        if (bias) {
+#pragma unroll
+            for (int j8 = 0; j8 < HD; j8 += 8) {
+                float bf[8];
+                unpack<bf16>(ld_u4(bias + n + j8), bf);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j8 + j] += bf[j];
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < HD; ++j) v[j] = bf16_round(v[j]);
+        if (rotate) {
+#pragma unroll
+            for (int j4 = 0; j4 < kHalf; j4 += 4) {
+                const float4 c4 = *reinterpret_cast<const float4*>(cs + j4), s4 = *reinterpret_cast<const float4*>(sn + j4);
+                const float cc[4] = {c4.x, c4.y, c4.z, c4.w}, ss[4] = {s4.x, s4.y, s4.z, s4.w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int j = j4 + u;
+                    const float c = bf16_round(cc[u]), s2 = bf16_round(ss[u]);
+                    const float a = v[j], b = v[j + kHalf];
+                    v[j] = bf16_round(bf16_round(a * c) + bf16_round(-b * s2));
+                    v[j + kHalf] = bf16_round(bf16_round(b * c) + bf16_round(a * s2));
+                }
+            }
+        }
+        const int head = n / HD;
+        bf16* dst = seg == 0 ? static_cast<bf16*>(p.q_out) + ((size_t)row * p.n_heads + head) * HD
+                             : kv_row + ((size_t)head << p.kv.page_shift) * HD;
+#pragma unroll
+        for (int j = 0; j < HD; j += 8) {
+            uint4 w;
+            w.x = pack2(v[j], v[j + 1]); w.y = pack2(v[j + 2], v[j + 3]);
+            w.z = pack2(v[j + 4], v[j + 5]); w.w = pack2(v[j + 6], v[j + 7]);
+            *reinterpret_cast<uint4*>(dst + j) = w;
+        }
+    }
+}
+
 // Persistent: one CTA per SM walks tiles t = blockIdx.x, + gridDim.x, ...  The accumulator is double-buffered in tensor
 // memory, so the MMA warp starts tile i+1 while the epilogue warps are still reading tile i out -- the epilogue
 // (tcgen05.ld, SiLU / residual arithmetic, stores) no longer sits between two main loops -- and the TMA ring never drains
@@ -231,6 +304,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         const uint32_t tbase = tmem + (lt & 1) * kAccCols + ((uint32_t)(quarter * 32) << 16);
         bf16* out = static_cast<bf16*>(p.c) + col0;
         const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
+        if (EPI == GEMM_EPI_QKV) {
+            if (p.head_dim == 64) qkv_tail<64, BN>(p, tbase, row, seg, n0, seg_n, bias);
+            else qkv_tail<128, BN>(p, tbase, row, seg, n0, seg_n, bias);
+        } else {
         // A thread owns one output row and, per tcgen05.ld, 32 consecutive columns of it: 64 bytes of bf16.  They leave
         // as four 16-byte stores (and the residual / bias arrive as 16-byte loads): every store fills half a sector,
         // where one bf16 pair per instruction touched 32 rows with 4 bytes each.
@@ -306,6 +383,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 }
             }
         }
+        }  // generic epilogues
         tc_fence_before();
         mbar_arrive(acc_empty + (lt & 1) * 8);   // this accumulator may be overwritten (by the tile after next)
         }  // tiles
@@ -813,10 +891,17 @@ bool gemm_swapab_enabled() {
     return !off;
 }
 
+bool gemm_qkv_fusable(int n_rows, int head_dim, const void* bq, const void* bk, const void* bv) {
+    const char* env = getenv("DLLM_QKV_FUSED");
+    if (env && env[0] == '0') return false;
+    const auto al = [](const void* b) { return (reinterpret_cast<uintptr_t>(b) & 15) == 0; };
+    return n_rows > 64 && (head_dim == 64 || head_dim == 128) && al(bq) && al(bk) && al(bv);
+}
+
 cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
     if (p.M <= 0 || p.N <= 0 || p.K <= 0 || p.K % 8 || p.ldc < p.N || (p.ldc % 2 && p.epi != GEMM_EPI_LOGITS)) return cudaErrorInvalidValue;
     const bool more = p.n_more[0] > 0 || p.n_more[1] > 0;
-    if (more && (p.epi != GEMM_EPI_BIAS || (p.n_more[1] > 0 && p.n_more[0] <= 0) || p.ldc < p.N + p.n_more[0] + p.n_more[1]))
+    if (more && ((p.epi != GEMM_EPI_BIAS && p.epi != GEMM_EPI_QKV) || (p.n_more[1] > 0 && p.n_more[0] <= 0) || p.ldc < p.N + p.n_more[0] + p.n_more[1]))
         return cudaErrorInvalidValue;
     if (small_m(p)) {
         switch (p.epi) {
@@ -829,8 +914,12 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
         return cudaErrorInvalidValue;
     }
     if (p.epi == GEMM_EPI_LOGITS) return cudaErrorInvalidValue;
+    if (p.epi == GEMM_EPI_QKV && ((p.head_dim != 64 && p.head_dim != 128) || p.N % p.head_dim || p.n_more[0] % p.head_dim ||
+                                  p.n_more[1] % p.head_dim || !p.q_out || !p.positions || !p.seq_ids || !gemm_qkv_fusable(p.M, p.head_dim, p.bias, p.bias_more[0], p.bias_more[1])))
+        return cudaErrorInvalidValue;
     CUtensorMap a, b, b2, b3;
-    const int bn = wide_tiles(p) ? 256 : (narrow_tiles(p) ? 64 : 128);
+    int bn = wide_tiles(p) ? 256 : (narrow_tiles(p) ? 64 : 128);
+    if (p.epi == GEMM_EPI_QKV && bn < p.head_dim) bn = 128;   // a tile holds whole heads
     if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, bn)) return cudaErrorNotSupported;
     b2 = b3 = b;
     if (p.epi == GEMM_EPI_SWIGLU) {
@@ -847,6 +936,7 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
         case GEMM_EPI_RESIDUAL: return DLLM_GEMM_BY_BN(GEMM_EPI_RESIDUAL);
         case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU, 128>(a, b, b2, b3, p, st);
         case GEMM_EPI_GELU: return DLLM_GEMM_BY_BN(GEMM_EPI_GELU);
+        case GEMM_EPI_QKV: return DLLM_GEMM_BY_BN(GEMM_EPI_QKV);
     }
 #undef DLLM_GEMM_BY_BN
     return cudaErrorInvalidValue;

@@ -667,16 +667,21 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
         PagedKV kv{s->kpool[l], s->vpool[l], s->block_table, s->pages_per_seq, s->page_shift};
         if (has_attn(c, l)) {
         CUDA_TRY(launch_norm_rows(s->h, w.norm1_w, w.norm1_b, s->xn, n_rows, c.hidden, norm, c.norm_eps, st));
-        {   // q, k, v projections into column slices of one [R, QKVd] buffer
+        const bool qkv_fused = s->esz == 2 && gemm_qkv_fusable(n_rows, c.head_dim, w.bq, w.bk, w.bv);
+        {   // q, k, v projections: row segments of one launch
             GemmTcParams g{};
-            g.a = s->xn; g.M = n_rows; g.K = c.hidden; g.ldc = QKVd; g.epi = GEMM_EPI_BIAS;
+            g.a = s->xn; g.M = n_rows; g.K = c.hidden; g.ldc = QKVd; g.epi = qkv_fused ? GEMM_EPI_QKV : GEMM_EPI_BIAS;
             g.w = w.wq; g.bias = w.bq; g.c = qkv; g.N = Hd;
-            // q | k | v as row segments of one launch
             g.w_more[0] = w.wk; g.bias_more[0] = w.bk; g.n_more[0] = KVd;
             g.w_more[1] = w.wv; g.bias_more[1] = w.bv; g.n_more[1] = KVd;
+            if (qkv_fused) {   // rotary and the KV append happen in the projection's epilogue; no [R, QKVd] round trip
+                g.q_out = s->qbuf; g.kv = kv; g.positions = s->pos; g.seq_ids = s->seq;
+                g.rope_cos = s->io.rope_cos; g.rope_sin = s->io.rope_sin;
+                g.n_heads = c.n_heads; g.n_kv_heads = c.n_kv_heads; g.head_dim = c.head_dim; g.rope = !gpt2;
+            }
             CUDA_TRY(launch_gemm_tc(g, st));
         }
-        {
+        if (!qkv_fused) {   // <= 64 rows (swap-AB projection) or an odd head size: separate rotary + append pass
             RopeAppendParams ra{};
             ra.qkv = qkv; ra.q = s->qbuf; ra.kv = kv; ra.positions = s->pos; ra.seq_ids = s->seq;
             ra.rope_cos = s->io.rope_cos; ra.rope_sin = s->io.rope_sin;

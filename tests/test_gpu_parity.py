@@ -607,6 +607,29 @@ def test_tcgen05_prefill_attention_against_oracle_and_mma_sync_kernel(hd, H, KV,
     assert bf16_logits_close(outs["1"][:, 0], outs["0"][:, 0])
 
 
+@pytest.mark.parametrize("arch,hd,H,KV", [("llama", 64, 8, 2), ("llama", 128, 4, 1), ("qwen2", 64, 6, 2), ("gpt2", 64, 4, 4)])
+@pytest.mark.parametrize("batch,T", [(1, 130), (3, 200)])
+def test_prefill_qkv_epilogue_with_rotary_and_kv_append_is_bit_identical_to_the_separate_pass(arch, hd, H, KV, batch, T, monkeypatch):
+    """Prefill K1 with rotary and the paged-KV append inside the projection's epilogue (GEMM_EPI_QKV) against the
+    projection followed by the separate rotary + append kernel: same roundings in the same order, so the logits of the
+    prefill AND of the decode steps that read the appended K/V back are the same bits; both against the bf16 oracle.
+    Covers rotary (llama), q/k/v biases (qwen2), no rotary + biases (gpt2), head_dim 64 / 128, tiles that end past M."""
+    cfg = ShardModelConfig(arch, H * hd, 2, H, KV, hd, 512, 500, 512, 1e-5, 10000.0, tie_head=arch == "gpt2")
+    sd = make_state_dict(cfg, 31, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, batch, T, seed=T + hd)
+    sdd = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+    o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16, max_context=T + 8), prompts, 3, record=True)
+    outs = {}
+    for fused in ("1", "0"):
+        monkeypatch.setenv("DLLM_QKV_FUSED", fused)
+        stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=1024, max_seqs=batch, max_context=T + 8, page_size=64)
+        ids, lg = gpu_generate(stages, prompts, 3)
+        check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
+        outs[fused] = (ids, lg)
+    assert torch.equal(outs["1"][0], outs["0"][0])
+    assert torch.equal(outs["1"][1], outs["0"][1])
+
+
 @pytest.mark.parametrize("model", ["llama3-8b", "qwen2.5-14b", "llama3-70b"])
 def test_full_width_layers_persistent_kernel_vs_per_op_path(model, monkeypatch):
     """Two layers at the real widths of the BASELINE configs (hidden 4096 / 5120 / 8192, GQA 4 / 5 / 8, head_dim 128,
