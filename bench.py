@@ -383,7 +383,7 @@ def run_single(args) -> int:
         "cpu_baseline": cpu,
         "prefill": {"tokens_per_sec": batch * prompt_len / (prefill_ms * 1e-3), "ms": prefill_ms,
                     "roofline": prefill_roofline(stage_prefill_flops(hf, L, True, batch, prompt_len), prefill_ms),
-                    "note": "tcgen05/TMA GEMMs for the projections, flash-style causal attention (mma.sync) over the paged cache"},
+                    "note": "persistent tcgen05/TMA GEMMs for the projections (rotary + KV append in the q|k|v epilogue, K-split tails), TMA + tcgen05 flash-style causal attention over the paged cache"},
     }
     print(json.dumps(line))
     return 0

@@ -100,7 +100,14 @@ struct GemmTcParams {
     const float* rope_cos;   // [max_context, hd/2] fp32, null-safe when rope == 0
     const float* rope_sin;
     int32_t n_heads, n_kv_heads, head_dim, rope;
+    // Optional scratch for splitting the tiles of the last, partly filled wave along K (M > 64 path): fp32 partial tiles
+    // + one ticket per split tile (zero between launches).  Null: every tile is computed whole.  One launch at a time
+    // may use a given scratch area (the shard handle owns one and runs its launches on one stream).
+    float* split_ws;
+    unsigned* split_tickets;
+    size_t split_ws_bytes;
 };
+constexpr int kGemmSplitTickets = 256;
 struct RopeAppendParams {
     const void* qkv;    // [R, (H+2KV)*hd] projected rows (bias added)
     void* q;            // [R, H*hd]

@@ -126,14 +126,91 @@ __device__ __forceinline__ TileCoord tile_coord(const GemmTcParams& p, int t, in
     return c;
 }
 
+// Work units of the persistent kernel.  Tiles of the full waves are computed whole; the tiles of the last, partly filled
+// wave (`n_tiles - whole` of them, fewer than there are SMs) are cut along K into `splits` slices, one slice per CTA, so
+// that the tail keeps every SM loading instead of a few of them for a whole tile's time -- at M = 512 a GEMM IS its
+// tail, and what bounds it is the rate at which the SMs that hold a tile can fill their shared memory.  Every slice
+// leaves its fp32 accumulator in the scratch area, waits until the tile's other slices have done so (they are running
+// at the same time: the launch is cooperative and a slice is its CTA's last unit), then adds the slices in slice order
+// -- the same sum on every run -- for ITS share of the tile's columns and runs the epilogue on them: reduction and
+// epilogue are spread over the tile's CTAs as well.
+struct UnitSched {
+    int n_units, whole, splits, kb_per;
+};
+struct Unit {
+    int tile, kb0, kb1, tail, slice;   // tail: index of the (tile, slice) pair among the split units, -1 for a whole tile
+};
+__device__ __forceinline__ Unit unit_of(const UnitSched& us, int u, int num_kb) {
+    Unit r;
+    if (u < us.whole) {
+        r.tile = u; r.kb0 = 0; r.kb1 = num_kb; r.tail = -1; r.slice = 0;
+    } else {
+        const int v = u - us.whole, tt = v / us.splits, sl = v - tt * us.splits;
+        r.tile = us.whole + tt; r.kb0 = sl * us.kb_per; r.kb1 = min(num_kb, r.kb0 + us.kb_per); r.tail = v; r.slice = sl;
+    }
+    return r;
+}
+
+// Where an epilogue thread's 32 accumulator columns come from: tensor memory, or the sum of a split tile's slices.
+// A slice in the scratch area is [32-column chunk][4-column group j4][row] float4: a warp's 32 rows are 512 contiguous
+// bytes in every access, and one chunk of one slice is one contiguous 16 KB block -- the size of a bulk copy.  The
+// CTA's share of the tile (a few chunks of every slice, <= kRedBlocks blocks) is brought into the idle operand ring
+// by bulk copies that are all in flight together; the sum then reads shared memory.
+constexpr int kRedBlockBytes = BM * 32 * 4;                  // 16 KB
+constexpr int kRedBlocks = 192 * 1024 / kRedBlockBytes;      // the ring holds 12 of them, whatever the tile width
+struct AccSrc {
+    uint32_t tbase;             // TMEM address of (lane quarter, column 0) of the accumulator
+    const unsigned char* red;   // staged blocks [chunk of the share][slice], or null: read tensor memory
+    int row;                    // this thread's row inside the tile
+    int splits;
+    int first_chunk;            // first 32-column chunk of this CTA's share of the output columns
+};
+__device__ __forceinline__ size_t ws_offset(int col32, int j4, int row) { return ((size_t)(col32 * 8 + j4) * BM + row) * 4; }
+// index of accumulator chunk `cc` among the staged chunks: out chunks in order; the dual tile keeps (gate, up) together
+template <bool kDual, int BN>
+__device__ __forceinline__ int staged_chunk(int cc, int first_chunk) {
+    constexpr int kOut = BN / 32;
+    return kDual ? ((cc % kOut) - first_chunk) * 2 + cc / kOut : cc - first_chunk;
+}
+template <bool kDual, int BN>
+__device__ __forceinline__ void acc_load32(const AccSrc& a, int col, uint32_t (&acc)[32]) {
+    if (a.red == nullptr) {   // uniform over the epilogue warps
+        tc_ld32(a.tbase + col, acc);
+        return;
+    }
+    float f[32];
+#pragma unroll
+    for (int j = 0; j < 32; ++j) f[j] = 0.f;
+    const unsigned char* blk = a.red + (size_t)staged_chunk<kDual, BN>(col >> 5, a.first_chunk) * a.splits * kRedBlockBytes + a.row * 16;
+    for (int sl = 0; sl < a.splits; ++sl, blk += kRedBlockBytes) {   // slice order: the same sum on every run
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+            const float4 v = *reinterpret_cast<const float4*>(blk + j4 * (BM * 16));
+            f[4 * j4] += v.x; f[4 * j4 + 1] += v.y; f[4 * j4 + 2] += v.z; f[4 * j4 + 3] += v.w;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 32; ++j) acc[j] = __float_as_uint(f[j]);
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
 // GEMM_EPI_QKV: the tail of K1 in the projection's epilogue.  A thread owns one token (row) and walks the heads of the
 // tile; it holds all HD columns of a head in registers, so both elements of every rotary pair (j, j + HD/2) are at hand.
 // Bias, rounding and rotary (q and k segments) in rope_append_kernel's order of roundings; then the head leaves as one
 // contiguous 128- or 256-byte row: q to its buffer, k / v into the KV page of (slot, position).  tcgen05.ld is
 // warp-wide, so rows past M take the loads too and skip only the arithmetic and the stores.
 template <int HD, int BN>
-__device__ __forceinline__ void qkv_tail(const GemmTcParams& p, uint32_t tbase, int row, int seg, int n0, int seg_n,
-                                         const bf16* bias) {
+__device__ __forceinline__ void qkv_tail(const GemmTcParams& p, const AccSrc& src, int row, int seg, int n0, int seg_n,
+                                         const bf16* bias, int c_begin, int c_end) {
     constexpr int kHalf = HD / 2;
     const bool live = row < p.M;
     const int pos = live ? p.positions[row] : 0;
@@ -148,14 +225,14 @@ __device__ __forceinline__ void qkv_tail(const GemmTcParams& p, uint32_t tbase, 
     }
     const bool rotate = p.rope && seg != 2;
 #pragma unroll 1
-    for (int h0 = 0; h0 + HD <= BN; h0 += HD) {
+    for (int h0 = c_begin; h0 + HD <= c_end; h0 += HD) {
         const int n = n0 + h0;            // first column of this head inside its segment (warp-uniform)
         if (n >= seg_n) break;
         float v[HD];
 #pragma unroll
         for (int c0 = 0; c0 < HD; c0 += 32) {
             uint32_t acc[32];
-            tc_ld32(tbase + h0 + c0, acc);
+            acc_load32<false, BN>(src, h0 + c0, acc);
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[c0 + j] = __uint_as_float(acc[j]);
         }
@@ -207,7 +284,7 @@ template <int EPI, int BN>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                const __grid_constant__ CUtensorMap tm_b2, const __grid_constant__ CUtensorMap tm_b3, const GemmTcParams p,
-               const int n_tiles, const int tiles_m) {
+               const UnitSched us, const int tiles_m) {
     constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
     static_assert(!(kDual && BN != 128), "the dual-B tile is 128 wide");
     constexpr int kBTileBytes = BN * BK * 2;
@@ -218,13 +295,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     constexpr int kStages = gemm_stages(kStageBytes);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    __shared__ __align__(8) uint64_t bars[2 * kStages + 4];
+    __shared__ __align__(8) uint64_t bars[2 * kStages + 5];
     __shared__ uint32_t s_tmem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int num_kb = (p.K + BK - 1) / BK;
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
     const uint32_t acc_full = smem_u32(bars + 2 * kStages), acc_empty = smem_u32(bars + 2 * kStages + 2);
+    const uint32_t red_bar = smem_u32(bars + 2 * kStages + 4);   // the staged slices of a split tile have landed
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kStages; ++i) {
@@ -235,6 +313,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             mbar_init(acc_full + i * 8, 1);
             mbar_init(acc_empty + i * 8, 128);   // the four epilogue warps
         }
+        mbar_init(red_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {  // one warp allocates tensor memory and later frees it
@@ -250,10 +329,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         // ===== TMA producer: the ring runs on across tile boundaries =====
         if (lane == 0) {
             unsigned it = 0;  // k-blocks issued so far
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const TileCoord tc = tile_coord<EPI, BN>(p, t, tiles_m);
+            for (int u = blockIdx.x; u < us.n_units; u += gridDim.x) {
+                const Unit un = unit_of(us, u, num_kb);
+                const TileCoord tc = tile_coord<EPI, BN>(p, un.tile, tiles_m);
                 const CUtensorMap* map_b = tc.seg == 0 ? &tm_b : (tc.seg == 1 ? &tm_b2 : &tm_b3);
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                for (int kb = un.kb0; kb < un.kb1; ++kb, ++it) {
                     const unsigned s = it % kStages;
                     mbar_wait(empty0 + s * 8, ((it / kStages) & 1) ^ 1);
                     const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
@@ -268,11 +348,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         // ===== MMA issuer (one thread): tile i+1 goes into the other accumulator while tile i is being read out =====
         if (lane == 0) {
             unsigned it = 0, lt = 0;
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
+            for (int u = blockIdx.x; u < us.n_units; u += gridDim.x, ++lt) {
+                const Unit un = unit_of(us, u, num_kb);
                 const uint32_t acc_t = tmem + (lt & 1) * kAccCols;
                 if (lt >= 2) mbar_wait(acc_empty + (lt & 1) * 8, ((lt >> 1) & 1) ^ 1);   // the epilogue has drained this buffer
                 tc_fence_after();
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                for (int kb = un.kb0; kb < un.kb1; ++kb, ++it) {
                     const unsigned s = it % kStages;
                     mbar_wait(full0 + s * 8, (it / kStages) & 1);
                     tc_fence_after();
@@ -282,7 +363,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 #pragma unroll
                     for (int k = 0; k < BK / 16; ++k) {
                         // 16 k-elements = 32 bytes further along the swizzled row: +2 in the (address >> 4) field
-                        const uint32_t acc = (kb | k) ? 1u : 0u;
+                        const uint32_t acc = (kb > un.kb0 || k) ? 1u : 0u;
                         tc_mma(acc_t, da + 2 * k, db + 2 * k, kIdesc, acc);
                         if (kDual) tc_mma(acc_t + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
                     }
@@ -295,18 +376,68 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
         const int quarter = warp & 3;
         unsigned lt = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x, ++lt) {
-        const TileCoord tc = tile_coord<EPI, BN>(p, t, tiles_m);
+        for (int u = blockIdx.x; u < us.n_units; u += gridDim.x, ++lt) {
+        const Unit un = unit_of(us, u, num_kb);
+        const TileCoord tc = tile_coord<EPI, BN>(p, un.tile, tiles_m);
         const int seg = tc.seg, col0 = tc.col0, seg_n = tc.seg_n, n0 = tc.n0;
         mbar_wait(acc_full + (lt & 1) * 8, (lt >> 1) & 1);
         tc_fence_after();
         const int row = tc.m0 + quarter * 32 + lane;
         const uint32_t tbase = tmem + (lt & 1) * kAccCols + ((uint32_t)(quarter * 32) << 16);
+        AccSrc src{tbase, nullptr, quarter * 32 + lane, 1, 0};
+        int c_begin = 0, c_end = BN;   // the output columns of the tile this CTA's epilogue covers
+        if (un.tail >= 0) {
+            // a K slice of a split tile (this CTA's last unit): the accumulator goes to the scratch area as it is; then
+            // wait for the tile's other slices and take this slice's share of the columns
+            constexpr size_t kSlice = (size_t)BM * kAccCols;
+            float* mine = p.split_ws + (size_t)un.tail * kSlice;
+#pragma unroll 1
+            for (int c0 = 0; c0 < (int)kAccCols; c0 += 32) {
+                uint32_t acc[32];
+                tc_ld32(tbase + c0, acc);
+#pragma unroll
+                for (int j4 = 0; j4 < 8; ++j4)
+                    *reinterpret_cast<uint4*>(mine + ws_offset(c0 >> 5, j4, src.row)) =
+                        make_uint4(acc[4 * j4], acc[4 * j4 + 1], acc[4 * j4 + 2], acc[4 * j4 + 3]);
+            }
+            tc_fence_before();
+            mbar_arrive(acc_empty + (lt & 1) * 8);
+            __threadfence();
+            fence_proxy_async_global();   // the slices are read back by bulk copies (async proxy)
+            asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps: every row of the slice is out
+            // shares are whole heads for the q|k|v epilogue, 32-column chunks otherwise
+            const int gcols = EPI == GEMM_EPI_QKV ? p.head_dim : 32, n_g = BN / gcols;
+            c_begin = (un.slice * n_g / us.splits) * gcols;
+            c_end = ((un.slice + 1) * n_g / us.splits) * gcols;
+            const int tt = un.tail / us.splits;
+            if (threadIdx.x == 64) {
+                unsigned* arrived = p.split_tickets + 2 * tt;
+                atomicAdd(arrived, 1u);
+                while (ld_acquire_gpu(arrived) < (unsigned)us.splits) __nanosleep(32);
+                fence_proxy_async_global();
+                // every slice of the tile is in the scratch area: this CTA's chunks of all of them into the operand ring
+                // (idle: this unit's MMAs have completed and no further loads were issued)
+                const float* tile_ws = p.split_ws + (size_t)tt * us.splits * kSlice;
+                const int n_out = (c_end - c_begin) >> 5, per_out = kDual ? 2 : 1;
+                if (n_out > 0) mbar_expect_tx(red_bar, (uint32_t)(n_out * per_out * us.splits * kRedBlockBytes));
+                for (int oc = 0; oc < n_out; ++oc)
+                    for (int h = 0; h < per_out; ++h) {
+                        const int cc = (c_begin >> 5) + oc + h * (BN / 32);   // accumulator chunk (the up half follows the gate half)
+                        for (int sl = 0; sl < us.splits; ++sl)
+                            bulk_load(smem_u32(smem) + (uint32_t)(((oc * per_out + h) * us.splits + sl) * kRedBlockBytes),
+                                      tile_ws + (size_t)sl * kSlice + ws_offset(cc, 0, 0), kRedBlockBytes, red_bar);
+                    }
+            }
+            if (c_end > c_begin) mbar_wait(red_bar, 0);
+            src.red = smem;
+            src.splits = us.splits;
+            src.first_chunk = c_begin >> 5;
+        }
         bf16* out = static_cast<bf16*>(p.c) + col0;
         const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
         if (EPI == GEMM_EPI_QKV) {
-            if (p.head_dim == 64) qkv_tail<64, BN>(p, tbase, row, seg, n0, seg_n, bias);
-            else qkv_tail<128, BN>(p, tbase, row, seg, n0, seg_n, bias);
+            if (p.head_dim == 64) qkv_tail<64, BN>(p, src, row, seg, n0, seg_n, bias, c_begin, c_end);
+            else qkv_tail<128, BN>(p, src, row, seg, n0, seg_n, bias, c_begin, c_end);
         } else {
         // A thread owns one output row and, per tcgen05.ld, 32 consecutive columns of it: 64 bytes of bf16.  They leave
         // as four 16-byte stores (and the residual / bias arrive as 16-byte loads): every store fills half a sector,
@@ -314,10 +445,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         const bool vec_ok = (p.ldc % 8 == 0) && (col0 % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0) &&
                             (!bias || (reinterpret_cast<uintptr_t>(bias) & 15) == 0);
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
+        for (int c0 = c_begin; c0 < c_end; c0 += 32) {
             uint32_t acc[32], acc2[32];
-            tc_ld32(tbase + c0, acc);
-            if (kDual) tc_ld32(tbase + BN + c0, acc2);
+            acc_load32<kDual, BN>(src, c0, acc);
+            if (kDual) acc_load32<kDual, BN>(src, BN + c0, acc2);
             if (row < p.M) {
 #pragma unroll
                 for (int j8 = 0; j8 < 32; j8 += 8) {
@@ -384,8 +515,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             }
         }
         }  // generic epilogues
-        tc_fence_before();
-        mbar_arrive(acc_empty + (lt & 1) * 8);   // this accumulator may be overwritten (by the tile after next)
+        if (un.tail < 0) {
+            tc_fence_before();
+            mbar_arrive(acc_empty + (lt & 1) * 8);   // this accumulator may be overwritten (by the tile after next)
+        } else {
+            asm volatile("bar.sync 1, 128;" ::: "memory");   // this CTA has read what it needs of the tile's slices
+            if (threadIdx.x == 64) {
+                unsigned* t = p.split_tickets + 2 * (un.tail / us.splits);
+                if (atomicAdd(t + 1, 1u) == (unsigned)us.splits - 1) {   // the last CTA to leave the tile: tickets back to zero
+                    t[0] = 0u;
+                    t[1] = 0u;
+                }
+            }
+        }
         }  // tiles
     }
     __syncthreads();
@@ -792,6 +934,11 @@ bool make_map(CUtensorMap* map, const void* base, int rows, int K, int box_rows 
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+bool gemm_split_enabled() {
+    const char* env = getenv("DLLM_GEMM_SPLIT");   // read per call: the tests compare split and whole tiles in one process
+    return !(env && env[0] == '0');
+}
+
 template <int EPI, int BN>
 cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const CUtensorMap& b3, const GemmTcParams& p,
                        cudaStream_t st) {
@@ -810,24 +957,72 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
     cudaGetDevice(&dev);
     if (dev >= 0 && dev < 64 && !sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
     const int n_sm = (dev >= 0 && dev < 64 && sms[dev] > 0) ? sms[dev] : 148;
-    gemm_tc_kernel<EPI, BN><<<n_tiles < n_sm ? n_tiles : n_sm, kGemmThreads, smem, st>>>(a, b, b2, b3, p, n_tiles, tiles_m);
+    // the last, partly filled wave is cut along K (see UnitSched)
+    constexpr size_t kSliceBytes = (size_t)BM * (EPI == GEMM_EPI_SWIGLU ? 256 : BN) * 4;
+    const int num_kb = (p.K + BK - 1) / BK;
+    UnitSched us{n_tiles, n_tiles, 1, num_kb};
+    const int rem = n_tiles % n_sm;
+    if (p.split_ws && p.split_tickets && rem > 0 && 2 * rem <= kGemmSplitTickets && gemm_split_enabled()) {
+        int s = n_sm / rem;
+        if (s > num_kb / 4) s = num_kb / 4;   // a slice keeps at least four k-blocks
+        if (s > 8) s = 8;
+        // a CTA's share of the tile (its column groups x every slice) must fit the operand ring as 16 KB blocks
+        const int gcols = EPI == GEMM_EPI_QKV ? p.head_dim : 32, n_g = BN / gcols;
+        const int blocks_per_group = (gcols / 32) * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
+        for (; s >= 2; --s) {
+            const int kb_per = (num_kb + s - 1) / s;
+            if ((num_kb + kb_per - 1) / kb_per != s) continue;   // would leave an empty slice
+            if (((n_g + s - 1) / s) * blocks_per_group * s > kRedBlocks) continue;
+            if ((size_t)rem * s * kSliceBytes > p.split_ws_bytes) continue;
+            us.whole = n_tiles - rem; us.splits = s; us.kb_per = kb_per;
+            us.n_units = us.whole + rem * s;
+            break;
+        }
+    }
+    const int grid = us.n_units < n_sm ? us.n_units : n_sm;
+    if (us.splits > 1) {
+        // the slices of a tile wait for each other: all CTAs must be resident together
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(grid);
+        cfg.blockDim = dim3(kGemmThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeCooperative;
+        attr[0].val.cooperative = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        const int tm = tiles_m;
+        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, BN>, a, b, b2, b3, p, us, tm);
+        if (e == cudaSuccess) {
+            count_launch();
+            return e;
+        }
+        cudaGetLastError();   // cannot be co-resident here: whole tiles
+        us = UnitSched{n_tiles, n_tiles, 1, num_kb};
+    }
+    gemm_tc_kernel<EPI, BN><<<n_tiles < n_sm ? n_tiles : n_sm, kGemmThreads, smem, st>>>(a, b, b2, b3, p, us, tiles_m);
     count_launch();
     return cudaGetLastError();
 }
 
-// 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give)
+// 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give); with the scratch
+// area for split tails at hand always -- the widest tile moves the fewest bytes into shared memory per flop, and the
+// split spreads however few tiles there are over the SMs
 bool wide_tiles(const GemmTcParams& p) {
     const char* env = getenv("DLLM_GEMM_BN256");  // read per call: the tests compare both tile widths in one process
     const bool off = env && env[0] == '0';
     if (off || p.epi == GEMM_EPI_SWIGLU || p.N % 256 || p.n_more[0] % 256 || p.n_more[1] % 256) return false;
+    if (p.split_ws && gemm_split_enabled()) return true;
     return (long)((p.M + BM - 1) / BM) * ((p.N + p.n_more[0] + p.n_more[1]) / 256) >= 148;
 }
 
-// 64-wide tiles when 128-wide ones would leave SMs without a tile (mid-size prompts: M = 256 .. 1024)
+// 64-wide tiles when 128-wide ones would leave SMs without a tile (mid-size prompts: M = 256 .. 1024) and there is no
+// scratch area to split tiles along K instead
 bool narrow_tiles(const GemmTcParams& p) {
     const char* env = getenv("DLLM_GEMM_BN64");
     const bool off = env && env[0] == '0';
-    if (off || p.epi == GEMM_EPI_SWIGLU) return false;
+    if (off || p.epi == GEMM_EPI_SWIGLU || (p.split_ws && gemm_split_enabled())) return false;
     const long n_all = (long)p.N + p.n_more[0] + p.n_more[1];
     return (long)((p.M + BM - 1) / BM) * ((n_all + 127) / 128) <= 74;  // at most half the SMs would get a 128-wide tile
 }

@@ -81,6 +81,9 @@ struct dllm_shard {
     void* act = nullptr;       // [max_rows, ffn]
     void* xn = nullptr;        // [max_rows, d]   normalised rows (prefill GEMM input)
     void* qkv_tmp = nullptr;   // [max_rows, (H+2KV)*hd] projected rows before rotary (prefill)
+    float* gemm_ws = nullptr;          // fp32 partial tiles of the prefill GEMMs' split tails (one slice per SM at most)
+    unsigned* gemm_tickets = nullptr;  // one per split tile, zero between launches
+    size_t gemm_ws_bytes = 0;
     int32_t *ids = nullptr, *pos = nullptr, *seq = nullptr, *logit_rows = nullptr, *arange = nullptr;
     int32_t *next_tok = nullptr, *block_table = nullptr, *tok_ring = nullptr, *step_ctr = nullptr;
     float* logits = nullptr;   // [max_logit_rows, V]
@@ -196,6 +199,9 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     const bool prefill_bufs = c.dtype == DLLM_DTYPE_BF16 && c.max_rows > 4;
     add(&s->xn, prefill_bufs ? (size_t)c.max_rows * c.hidden * s->esz : 0);
     add(&s->qkv_tmp, prefill_bufs ? (size_t)c.max_rows * (c.n_heads + 2 * c.n_kv_heads) * c.head_dim * s->esz : 0);
+    s->gemm_ws_bytes = prefill_bufs && c.max_rows > 64 ? (size_t)s->num_sms * 128 * 256 * 4 : 0;
+    add(&s->gemm_ws, s->gemm_ws_bytes);
+    add(&s->gemm_tickets, (size_t)kGemmSplitTickets * 4);
     add(&s->ids, (size_t)c.max_rows * 4);
     add(&s->pos, (size_t)c.max_rows * 4);
     add(&s->seq, (size_t)c.max_rows * 4);
@@ -670,6 +676,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
         const bool qkv_fused = s->esz == 2 && gemm_qkv_fusable(n_rows, c.head_dim, w.bq, w.bk, w.bv);
         {   // q, k, v projections: row segments of one launch
             GemmTcParams g{};
+            g.split_ws = s->gemm_ws; g.split_tickets = s->gemm_tickets; g.split_ws_bytes = s->gemm_ws_bytes;
             g.a = s->xn; g.M = n_rows; g.K = c.hidden; g.ldc = QKVd; g.epi = qkv_fused ? GEMM_EPI_QKV : GEMM_EPI_BIAS;
             g.w = w.wq; g.bias = w.bq; g.c = qkv; g.N = Hd;
             g.w_more[0] = w.wk; g.bias_more[0] = w.bk; g.n_more[0] = KVd;
@@ -705,6 +712,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
         }
         {   // o-proj + residual (in place on the residual stream)
             GemmTcParams g{};
+            g.split_ws = s->gemm_ws; g.split_tickets = s->gemm_tickets; g.split_ws_bytes = s->gemm_ws_bytes;
             g.a = s->attn_out; g.w = w.wo; g.bias = w.bo; g.c = s->h; g.M = n_rows; g.N = c.hidden; g.K = Hd;
             g.ldc = c.hidden; g.epi = GEMM_EPI_RESIDUAL;
             CUDA_TRY(launch_gemm_tc(g, st));
@@ -714,6 +722,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
         CUDA_TRY(launch_norm_rows(s->h, w.norm2_w, w.norm2_b, s->xn, n_rows, c.hidden, norm, c.norm_eps, st));
         {
             GemmTcParams g{};
+            g.split_ws = s->gemm_ws; g.split_tickets = s->gemm_tickets; g.split_ws_bytes = s->gemm_ws_bytes;
             g.a = s->xn; g.c = s->act; g.M = n_rows; g.N = c.ffn; g.K = c.hidden; g.ldc = c.ffn;
             if (gpt2) { g.w = w.w_up; g.bias = w.b_up; g.epi = GEMM_EPI_GELU; }
             else { g.w = w.w_gate; g.w2 = w.w_up; g.epi = GEMM_EPI_SWIGLU; }
@@ -721,6 +730,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
         }
         {
             GemmTcParams g{};
+            g.split_ws = s->gemm_ws; g.split_tickets = s->gemm_tickets; g.split_ws_bytes = s->gemm_ws_bytes;
             g.a = s->act; g.w = w.w_down; g.bias = w.b_down; g.c = s->h; g.M = n_rows; g.N = c.hidden; g.K = c.ffn;
             g.ldc = c.hidden; g.epi = GEMM_EPI_RESIDUAL;
             CUDA_TRY(launch_gemm_tc(g, st));
@@ -731,6 +741,7 @@ static int enqueue_prefill(dllm_shard* s, int n_rows, int n_logit_rows, int run_
         CUDA_TRY(launch_norm_rows(s->h, s->io.final_norm_w, s->io.final_norm_b, s->xn, n_logit_rows, c.hidden, norm,
                                   c.norm_eps, st, s->logit_rows));
         GemmTcParams g{};
+            g.split_ws = s->gemm_ws; g.split_tickets = s->gemm_tickets; g.split_ws_bytes = s->gemm_ws_bytes;
         g.a = s->xn; g.w = s->io.lm_head; g.c = s->logits; g.M = n_logit_rows; g.N = c.vocab; g.K = c.hidden;
         g.ldc = c.vocab; g.epi = GEMM_EPI_LOGITS;
         CUDA_TRY(launch_gemm_tc(g, st));

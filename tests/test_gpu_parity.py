@@ -667,6 +667,7 @@ def test_prefill_tile_widths_agree_bit_for_bit(monkeypatch):
     params = random_init.random_stage_parameters(hf, range(2), True, True, 5, torch.bfloat16, device="cuda")
     prompt = make_prompts(hf["vocab_size"], 1, 4096, seed=3)
     outs = []
+    monkeypatch.setenv("DLLM_GEMM_SPLIT", "0")  # whole tiles only: a K-split tail sums in another order (its own test below)
     for bn256, qt128 in (("1", None), ("0", None), ("1", "0")):
         monkeypatch.setenv("DLLM_GEMM_BN256", bn256)
         if qt128 is not None:  # the same for the attention's query tile: 128 rows by default at this size, 64 forced
@@ -676,6 +677,30 @@ def test_prefill_tile_widths_agree_bit_for_bit(monkeypatch):
         outs.append(sh.compute({"input_ids": prompt})["logits"].cpu())
         del sh
     assert torch.isfinite(outs[0]).all() and torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+
+
+@pytest.mark.parametrize("batch,T", [(1, 512), (1, 300), (2, 330)])
+def test_prefill_gemm_split_tail_against_oracle_and_whole_tiles(batch, T, monkeypatch):
+    """Mid-size prompts are all tail: fewer output tiles than SMs.  The persistent GEMM then cuts the tiles of the last
+    wave along K, parks the fp32 slices in the handle's scratch area and lets the last slice to arrive sum them in slice
+    order and run the epilogue (bias / residual / SwiGLU / rotary + KV append).  Against the bf16 oracle, against the
+    same prefill with whole tiles (another summation order: close, not identical), and twice in a row (the sum does not
+    depend on which slice arrives last: identical bits, tickets back at zero)."""
+    cfg = ShardModelConfig("llama", 1024, 2, 16, 4, 64, 2816, 500, 1024, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 41, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, batch, T, seed=T)
+    sdd = {k: v.to(torch.bfloat16) for k, v in sd.items()}
+    o_ids, o_lg, o_mg = greedy_generate(build_pipeline(cfg, sdd, 1, torch.bfloat16, max_context=T + 8), prompts, 2, record=True)
+    outs = {}
+    for split in ("1", "0", "1"):
+        monkeypatch.setenv("DLLM_GEMM_SPLIT", split)
+        stages = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=1024, max_seqs=batch, max_context=T + 8, page_size=64)
+        ids, lg = gpu_generate(stages, prompts, 2)
+        check_bf16_generation(ids, lg, o_ids, o_lg, o_mg)
+        if split == "1" and split in outs:
+            assert torch.equal(outs[split], lg)
+        outs[split] = lg
+    assert bf16_logits_close(outs["1"][:, 0], outs["0"][:, 0])
 
 
 def test_bf16_parity_summary():
