@@ -31,7 +31,8 @@ def run_pipeline(args) -> int:
     if args.prompt_len:
         prompt_len = args.prompt_len
     batch = args.batch or (wl_batch if model == "llama3-70b" else 1)
-    fused = batch <= 8  # the persistent kernel (and with it the fused hand-off) takes up to 8 rows at these widths
+    fused = batch <= 64  # the mailbox hand-off: inside the persistent kernel up to 8 rows at these widths, as wait / send kernels
+    persistent = batch <= 8  # around the step's CUDA graph above that
     n_micro = args.micro if args.micro >= world else world
     K = args.steps if args.steps > 0 else 64
     W = max(args.warmup if args.warmup >= 0 else 4, 3)
@@ -287,7 +288,10 @@ def run_pipeline(args) -> int:
             "detail": {"layers_per_stage": [round(x, 2) for x in layers_eq],
                        "stage_blocks": [f"{st[0][0]}{'' if st[0][1] == 'full' else ':' + st[0][1]}..{st[-1][0]}{'' if st[-1][1] == 'full' else ':' + st[-1][1]}" for st in stages_blocks],
                        "handoff": ("fused: peer stores from the down-projection epilogue into the next stage's mailbox + tickets"
-                                   if fused else "NCCL send/recv per micro-batch step (batch above the persistent kernel's rows)")},
+                                   if persistent else
+                                   "fused: per micro-batch step a wait kernel, the step's CUDA graph and a send kernel (peer stores into the next "
+                                   "stage's mailbox + tickets), all enqueued up front; no NCCL, no host between steps" if fused else
+                                   "NCCL send/recv per micro-batch step")},
             "tokens_checked": ok, "token_check": checked,
             "same_model_n1": ({"value": single_tps, "unit": UNIT, "scaling_efficiency": value / (world * single_tps),
                                "note": "the same model as one stage on one B200, same batch; efficiency = value / (N x this)"}
@@ -300,7 +304,7 @@ def run_pipeline(args) -> int:
                          "frac": float(fr[worst]), "traffic": None, "peak_kind": peak_kind,
                          "kernel": (f"decode_megakernel of stage {worst} (the stage with the lowest fraction: every stage takes the same step "
                                     "time in the steady state, this one moves the fewest bytes): one persistent launch for the timed loop, "
-                                    "unit = one micro-batch step of the stage") if fused else
+                                    "unit = one micro-batch step of the stage") if persistent else
                                    (f"micro-batch step of stage {worst} (the stage with the lowest fraction): CUDA graph of swap-AB tcgen05 GEMMs + "
                                     "grouped-head decode attention"),
                          "per_stage_frac": [round(float(x), 4) for x in fr]},

@@ -175,6 +175,32 @@ struct PerDeviceOnce {
 };
 
 int set_last_error(const char* msg);  // stores the message dllm_last_error() returns; always returns 1
+// Fused hand-off around a per-op decode step (pipe_ops.cu): wait for the inbox slot's ticket and set the step's inputs
+// up; afterwards store the step's rows (or sampled ids) into the next stage's mailbox and release its ticket
+struct PipeBeginParams {
+    const unsigned* in_flag;    // this slot's ticket (own memory)
+    unsigned want;
+    const int32_t* in_tokens;   // slot's ids (first stage) or null
+    const void* in_hidden;      // slot's rows (other stages) or null
+    const int32_t *pos_all, *seq_all;   // the micro-batch's positions at step 0 / KV slots
+    int32_t pos_add;
+    int32_t *ids, *pos, *seq;   // the handle's working arrays
+    void* h;
+    int32_t* tok_ring;          // where to record the fed ids, or null
+    int32_t n_rows, hidden;
+};
+struct PipeEndParams {
+    unsigned* out_flag;         // the slot's ticket in the next stage's mailbox
+    unsigned ticket;
+    int32_t* out_tokens;        // last stage: the first stage's inbox ids
+    const int32_t* next_tok;
+    void* out_hidden;           // other stages: the next stage's inbox rows (peer memory)
+    const void* h;
+    int32_t n_rows, hidden;
+};
+cudaError_t launch_pipe_begin(const PipeBeginParams& p, cudaStream_t st);
+cudaError_t launch_pipe_end(const PipeEndParams& p, cudaStream_t st);
+
 void count_launch(unsigned long long n = 1);
 unsigned long long launch_count();
 

@@ -1,6 +1,6 @@
-// Device code shared by the persistent decode kernels (decode_megakernel.cu: phases separated by grid barriers;
-// decode_flow.cu: phases chained by tagged data words): PTX wrappers, the per-warp ring of TMA bulk stages and its
-// static stage sequence, the row-normalisation vector math, and the attention unit geometry.
+// Device code of the persistent decode kernel (decode_megakernel.cu) kept apart from its phase logic, and shared with the
+// hand-off kernels of the per-op path (pipe_ops.cu): PTX wrappers, grid barrier and tickets, the per-warp ring of TMA
+// bulk stages and its static stage sequence, the row-normalisation vector math, and the attention unit geometry.
 #pragma once
 
 #include <float.h>

@@ -84,6 +84,7 @@ struct dllm_shard {
     float* gemm_ws = nullptr;          // fp32 partial tiles of the prefill GEMMs' split tails (one slice per SM at most)
     unsigned* gemm_tickets = nullptr;  // one per split tile, zero between launches
     size_t gemm_ws_bytes = 0;
+    int32_t *pipe_pos = nullptr, *pipe_seq = nullptr;   // positions / KV slots of every micro-batch of a pipelined per-op loop
     int32_t *ids = nullptr, *pos = nullptr, *seq = nullptr, *logit_rows = nullptr, *arange = nullptr;
     int32_t *next_tok = nullptr, *block_table = nullptr, *tok_ring = nullptr, *step_ctr = nullptr;
     float* logits = nullptr;   // [max_logit_rows, V]
@@ -203,6 +204,8 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->gemm_ws, s->gemm_ws_bytes);
     add(&s->gemm_tickets, (size_t)kGemmSplitTickets * 4);
     add(&s->ids, (size_t)c.max_rows * 4);
+    add(&s->pipe_pos, (size_t)c.max_rows * 4);
+    add(&s->pipe_seq, (size_t)c.max_rows * 4);
     add(&s->pos, (size_t)c.max_rows * 4);
     add(&s->seq, (size_t)c.max_rows * 4);
     add(&s->logit_rows, (size_t)c.max_rows * 4);
@@ -528,6 +531,7 @@ struct dllm_mailbox {
     }
 };
 constexpr int kFlagStride = 32;  // one ticket per 128-byte line
+constexpr int kPipeOpsMaxRows = 64;  // rows per micro-batch of the per-op pipelined loop (one CUDA graph per step)
 
 struct MkPipe {
     const dllm_mailbox *in, *out;
@@ -1047,8 +1051,43 @@ static int pipelined_validate(const char* who, dllm_shard* s, dllm_mailbox* inbo
         if (b->n_slots < n_micro || b->rows != rows || b->hidden != c.hidden) return fail(w + ": mailbox shape does not match");
     if (c.has_embed && (size_t)n_steps * n_micro * rows > s->tok_ring_cap) return fail(w + ": n_steps out of range");
     if (c.n_layers < 1) return fail(w + ": the stage has no layers");
-    if (!mk_eligible(s, rows, rows, true))
-        return fail(w + ": shape not taken by the persistent kernel (bf16, <= 16 rows, fits shared memory)");
+    if (!mk_eligible(s, rows, rows, true) && !(c.dtype == DLLM_DTYPE_BF16 && rows <= kPipeOpsMaxRows))
+        return fail(w + ": shape taken neither by the persistent kernel nor by the per-op loop (bf16, <= 64 rows)");
+    return 0;
+}
+
+// The pipelined loop for shapes the persistent kernel does not take: every micro-batch step is [wait kernel] -> the
+// step's CUDA graph (swap-AB tcgen05 GEMMs, grouped-head attention) -> [send kernel], all enqueued up front.
+static int run_pipelined_ops(dllm_shard* s, const MkPipe& pipe, int rows, int n_steps, cudaStream_t st) {
+    const dllm_shard_config& c = s->cfg;
+    const int mode = prefill_eligible(s, rows) ? 1 : 0;
+    const int nl = c.has_head ? rows : 0;
+    if (c.has_head) {
+        CUDA_TRY(cudaMemcpyAsync(s->logit_rows, s->arange, (size_t)rows * 4, cudaMemcpyDeviceToDevice, st));
+        s->arange_rows = std::max(s->arange_rows, rows);
+    }
+    for (int step = 0; step < n_steps * pipe.n_micro; ++step) {
+        const int m = step % pipe.n_micro, g = step / pipe.n_micro;
+        PipeBeginParams b{};
+        b.in_flag = pipe.in->flags() + (size_t)m * kFlagStride; b.want = pipe.step_base + g + 1;
+        b.in_tokens = c.has_embed ? pipe.in->tokens() + (size_t)m * rows : nullptr;
+        b.in_hidden = c.has_embed ? nullptr : static_cast<char*>(pipe.in->hidden_rows()) + (size_t)m * rows * c.hidden * 2;
+        b.pos_all = s->pipe_pos + (size_t)m * rows; b.seq_all = s->pipe_seq + (size_t)m * rows; b.pos_add = g;
+        b.ids = s->ids; b.pos = s->pos; b.seq = s->seq; b.h = s->h;
+        b.tok_ring = c.has_embed ? s->tok_ring + (size_t)step * rows : nullptr;
+        b.n_rows = rows; b.hidden = c.hidden;
+        CUDA_TRY(launch_pipe_begin(b, st));
+        if (run_step(s, rows, nl, false, st, mode, 0, 0)) return 1;
+        PipeEndParams e{};
+        e.out_flag = pipe.out->flags() + (size_t)m * kFlagStride;
+        e.ticket = pipe.step_base + g + (c.has_head ? 2 : 1);   // the first stage waits for step g + 1's ids
+        e.out_tokens = c.has_head ? pipe.out->tokens() + (size_t)m * rows : nullptr;
+        e.next_tok = s->next_tok;
+        e.out_hidden = c.has_head ? nullptr : static_cast<char*>(pipe.out->hidden_rows()) + (size_t)m * rows * c.hidden * 2;
+        e.h = s->h; e.n_rows = rows; e.hidden = c.hidden;
+        CUDA_TRY(launch_pipe_end(e, st));
+    }
+    s->pos_at_pending = false;
     return 0;
 }
 
@@ -1067,10 +1106,16 @@ extern "C" int dllm_shard_decode_pipelined(dllm_shard* s, dllm_mailbox* inbox, d
     int dev = -1;
     cudaGetDevice(&dev);
     if (dev != s->device) CUDA_TRY(cudaSetDevice(s->device));
-    CUDA_TRY(cudaMemcpyAsync(s->pos, positions, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
-    CUDA_TRY(cudaMemcpyAsync(s->seq, seq_ids, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
     MkPipe pipe{inbox, outbox, n_micro, step_base};
-    if (run_megakernel(s, rows, n_steps * n_micro, false, st, &pipe)) return 1;
+    if (mk_eligible(s, rows, rows, true)) {
+        CUDA_TRY(cudaMemcpyAsync(s->pos, positions, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
+        CUDA_TRY(cudaMemcpyAsync(s->seq, seq_ids, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
+        if (run_megakernel(s, rows, n_steps * n_micro, false, st, &pipe)) return 1;
+    } else {
+        CUDA_TRY(cudaMemcpyAsync(s->pipe_pos, positions, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
+        CUDA_TRY(cudaMemcpyAsync(s->pipe_seq, seq_ids, (size_t)n_micro * rows * 4, cudaMemcpyDefault, st));
+        if (run_pipelined_ops(s, pipe, rows, n_steps, st)) return 1;
+    }
     if (c.has_embed && fed_tokens_out)
         CUDA_TRY(cudaMemcpyAsync(fed_tokens_out, s->tok_ring, (size_t)n_steps * n_micro * rows * 4, cudaMemcpyDefault, st));
     return 0;

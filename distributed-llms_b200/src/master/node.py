@@ -307,7 +307,7 @@ class MasterNode:
         if first_tokens.dim() == 1:
             first_tokens = first_tokens[None, :]
         n_micro, rows = int(first_tokens.shape[0]), int(first_tokens.shape[1])
-        if n_steps < 1 or rows > 8 or any(len(s) != 1 for _, s in order):
+        if n_steps < 1 or rows > 64 or any(len(s) != 1 for _, s in order):   # the stages' pre-flight decides about the shape itself
             return None
         places = [(self.workers[w].get("pid"), self.workers[w].get("device_index")) for w, _ in order]
         if any(p[0] is None or p[1] is None or p[1] < 0 for p in places) or len(set(places)) != len(places):

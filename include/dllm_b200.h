@@ -179,8 +179,8 @@ DLLM_API int dllm_shard_decode_loop(dllm_shard* shard, int32_t n_rows, int32_t n
  * No launch, no collective library call and no host involvement per token.
  *
  * A mailbox is device memory of its owner: per slot (micro-batch) a ticket, `rows` int32 token ids and
- * `rows x hidden` bf16 hidden rows (`rows` <= 16 for the decode loop; any number for a prefill tile slot).  Slot tickets count delivered inputs: the consumer of decode step G waits
- * for ticket >= G + 1.  One process per GPU: the owner exports a 64-byte IPC handle, the producer imports it. */
+ * `rows x hidden` bf16 hidden rows (`rows` <= 64 for the decode loop; any number for a prefill tile slot).  Slot
+ * tickets count delivered inputs: the consumer of decode step G waits for ticket >= G + 1.  One process per GPU: the owner exports a 64-byte IPC handle, the producer imports it. */
 typedef struct dllm_mailbox dllm_mailbox;
 #define DLLM_MAILBOX_IPC_BYTES 64
 DLLM_API int dllm_mailbox_create(int32_t device, int32_t n_slots, int32_t rows, int32_t hidden, dllm_mailbox** out);
@@ -208,8 +208,13 @@ DLLM_API int dllm_mailbox_put_rows(dllm_mailbox* box, int32_t slot, const void* 
 DLLM_API int dllm_mailbox_get_rows(dllm_mailbox* box, int32_t slot, void* d_dst, int32_t n_rows, void* stream);
 DLLM_API int dllm_mailbox_destroy(dllm_mailbox* box);
 
-/* `n_steps` decode steps of `n_micro` micro-batches of `rows` rows each in one persistent launch (bf16, rows
- * <= 16, shapes the persistent kernel takes).  `inbox` is this stage's own mailbox, `outbox` the next stage's
+/* `n_steps` decode steps of `n_micro` micro-batches of `rows` rows each, bf16.  Shapes the persistent kernel takes
+ * (rows <= 16 and the staged rows fit shared memory: <= 8 rows at hidden 4096 and wider) run as ONE persistent launch
+ * whose epilogue does the hand-off.  Other shapes up to 64 rows run every micro-batch step as [wait kernel] -> the
+ * step's CUDA graph (swap-AB tcgen05 GEMMs, grouped-head attention) -> [send kernel], all enqueued by this call: the
+ * same mailboxes and tickets, still no host round trip and no collective library between steps -- at 8 rows and above
+ * the separate kernels reach the same fraction of the memory roofline as the persistent kernel.
+ * `inbox` is this stage's own mailbox, `outbox` the next stage's
  * (the first stage's for the last stage; for a single stage pass its own inbox twice).  `positions`, `seq_ids`
  * (host or device, int32 [n_micro * rows]): position of the token fed at this call's first step and the KV slot of
  * every row; KV pages must be reserved up to position + n_steps.  `step_base`: decode steps done by earlier calls

@@ -525,13 +525,17 @@ def test_streamed_rows_variant_matches_oracle(batch, monkeypatch):
 
 
 @pytest.mark.parametrize("arch", ["llama", "gpt2"])
-@pytest.mark.parametrize("n_micro,rows", [(1, 1), (3, 2), (2, 8)])
-def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, arch):
-    """One stage, its own mailbox as in- and outbox: the persistent kernel feeds the token ids round through the
-    mailbox tickets.  Every micro-batch must reproduce, bit for bit, what the classic device loop generates."""
+@pytest.mark.parametrize("n_micro,rows,persistent", [(1, 1, True), (3, 2, True), (2, 8, True),
+                                                     (2, 2, False), (3, 12, False), (2, 24, False)])
+def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, persistent, arch, monkeypatch):
+    """One stage, its own mailbox as in- and outbox: the token ids go round through the mailbox tickets -- inside the
+    persistent kernel, or (shapes it does not take: here it is switched off) through the wait / send kernels around every
+    step's CUDA graph.  Every micro-batch must reproduce, bit for bit, what the classic device loop generates."""
     from src.network.handoff import Mailbox
-    if os.environ.get("DLLM_MEGAKERNEL") == "0":
-        pytest.skip("the fused hand-off lives in the persistent kernel")
+    if persistent and os.environ.get("DLLM_MEGAKERNEL") == "0":
+        pytest.skip("the persistent kernel is switched off")
+    if not persistent:
+        monkeypatch.setenv("DLLM_MEGAKERNEL", "0")
     if arch == "llama":
         cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
     else:

@@ -22,7 +22,7 @@ def _free_port():
     return p
 
 
-def _prompts():
+def _prompts(B=B):
     g = torch.Generator().manual_seed(3)
     return [torch.randint(0, HF["vocab_size"], (B, PROMPT), generator=g) for _ in range(N_MICRO)]
 
@@ -97,9 +97,11 @@ def test_two_stage_pipeline_equals_single_stage():
             assert torch.equal(tok.to(torch.int32), got[m, :, t]), (m, t)
 
 
-def _fused_worker(rank, world, port, q):
-    """Same model and prompts, hand-off fused into the persistent kernels: one launch per stage for all the steps,
-    hidden rows and token ids travel through peer mailboxes (IPC handles exchanged over the process group)."""
+def _fused_worker(rank, world, port, q, B=B, megakernel="1"):
+    """Same model and prompts, hand-off through peer mailboxes (IPC handles exchanged over the process group): fused into
+    the persistent kernels -- one launch per stage for all the steps -- or, with the persistent kernel off / more rows
+    than it takes, as wait / send kernels around every step's CUDA graph."""
+    os.environ["DLLM_MEGAKERNEL"] = megakernel
     import torch.distributed as dist
     from src.model import random_init
     from src.model.shard_manager import contiguous_partition
@@ -111,10 +113,10 @@ def _fused_worker(rank, world, port, q):
     dev = torch.device("cuda", rank)
     layers = contiguous_partition(HF["num_hidden_layers"], world)[rank]
     params = random_init.random_stage_parameters(HF, layers, rank == 0, rank == world - 1, 1234, torch.bfloat16, init="full")
-    shard = ModelShard(rank, params, config=HF, max_rows=32, max_seqs=N_MICRO * B, max_context=64, page_size=16)
+    shard = ModelShard(rank, params, config=HF, max_rows=64, max_seqs=N_MICRO * B, max_context=64, page_size=16)
     shard.to_device()
     first_tokens = []
-    for m, prompts in enumerate(_prompts()):
+    for m, prompts in enumerate(_prompts(B)):
         seqs = torch.arange(m * B, (m + 1) * B, dtype=torch.int32)
         if rank == 0:
             out = shard.compute({"input_ids": prompts, "seq_ids": seqs})
@@ -152,13 +154,15 @@ def _fused_worker(rank, world, port, q):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_fused_handoff_two_stages_equals_single_stage():
+@pytest.mark.parametrize("B,megakernel", [(2, "1"), (2, "0"), (12, "0")])
+def test_fused_handoff_two_stages_equals_single_stage(B, megakernel, monkeypatch):
     from src.model import random_init
     from src.worker.node import ModelShard
+    monkeypatch.setenv("DLLM_MEGAKERNEL", megakernel)   # the single-stage run below takes the same kernels as the stages
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_fused_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_fused_worker, args=(r, 2, port, q, B, megakernel)) for r in range(2)]
     for p in procs:
         p.start()
     first, got = q.get(timeout=300)
@@ -166,9 +170,9 @@ def test_fused_handoff_two_stages_equals_single_stage():
         p.join(timeout=120)
         assert p.exitcode == 0
     params = random_init.random_stage_parameters(HF, range(HF["num_hidden_layers"]), True, True, 1234, torch.bfloat16, init="full")
-    one = ModelShard(0, params, config=HF, max_rows=32, max_seqs=N_MICRO * B, max_context=64, page_size=16)
+    one = ModelShard(0, params, config=HF, max_rows=64, max_seqs=N_MICRO * B, max_context=64, page_size=16)
     one.to_device()
-    for m, prompts in enumerate(_prompts()):
+    for m, prompts in enumerate(_prompts(B)):
         seqs = torch.arange(m * B, (m + 1) * B, dtype=torch.int32)
         tok = one.compute({"input_ids": prompts, "seq_ids": seqs})["next_token"].cpu()
         assert torch.equal(tok.to(torch.int32), first[m])
