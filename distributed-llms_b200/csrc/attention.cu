@@ -24,6 +24,8 @@ constexpr int kAttnWarps = kAttnThreads / 32;
 
 template <typename T, int HD>
 __global__ void __launch_bounds__(kAttnThreads) attn_decode_splitk_kernel(const AttnParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     using D = DT<T>;
     constexpr int EPL = HD / 32;  // elements of head_dim per lane
     const int split = blockIdx.x, h = blockIdx.y, r = blockIdx.z;
@@ -146,14 +148,15 @@ __global__ void __launch_bounds__(kAttnThreads) attn_decode_splitk_kernel(const 
 template <typename T>
 static cudaError_t launch_t(const AttnParams& p, cudaStream_t s) {
     dim3 grid(p.n_splits, p.n_heads, p.n_rows);
+    cudaError_t le = cudaSuccess;
     switch (p.head_dim) {
-        case 32: attn_decode_splitk_kernel<T, 32><<<grid, kAttnThreads, 0, s>>>(p); break;
-        case 64: attn_decode_splitk_kernel<T, 64><<<grid, kAttnThreads, 0, s>>>(p); break;
-        case 128: attn_decode_splitk_kernel<T, 128><<<grid, kAttnThreads, 0, s>>>(p); break;
+        case 32: le = launch_pdl(attn_decode_splitk_kernel<T, 32>, grid, dim3(kAttnThreads), 0, s, p); break;
+        case 64: le = launch_pdl(attn_decode_splitk_kernel<T, 64>, grid, dim3(kAttnThreads), 0, s, p); break;
+        case 128: le = launch_pdl(attn_decode_splitk_kernel<T, 128>, grid, dim3(kAttnThreads), 0, s, p); break;
         default: return cudaErrorInvalidValue;
     }
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 cudaError_t launch_attn_decode(int dtype, const AttnParams& p, cudaStream_t s) {

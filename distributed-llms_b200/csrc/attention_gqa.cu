@@ -18,6 +18,7 @@ namespace dllm {
 namespace {
 
 constexpr int kKT = 64, kThreads = 128, kWarps = 4, kRows = 16;
+constexpr int kMergeUnroll = 8;   // splits whose partials the merging CTA requests in one go
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
@@ -46,6 +47,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 
 template <int HD>
 __global__ void __launch_bounds__(kThreads) attn_decode_gqa_kernel(const AttnParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     constexpr int LD = HD + 8;            // padded rows: ldmatrix reads 8 rows x 16 bytes without bank conflicts
     constexpr int kTile = kKT * LD;       // elements of one K (or V) tile
     extern __shared__ __align__(16) unsigned char smem_dyn[];
@@ -232,14 +235,36 @@ __global__ void __launch_bounds__(kThreads) attn_decode_gqa_kernel(const AttnPar
     for (int i = threadIdx.x; i < Gq * HD; i += kThreads) {
         const int hq = i / HD, c = i - hq * HD;
         const size_t pb = ((size_t)r * H + kvh * Gq + hq) * S;
-        float Mg = -FLT_MAX;
-        for (int s2 = 0; s2 < S; ++s2) Mg = fmaxf(Mg, __ldcg(p.part_ml + (pb + s2) * 2));
-        float Lg = 0.f, acc = 0.f;
-        for (int s2 = 0; s2 < S; ++s2) {
-            const float ms = __ldcg(p.part_ml + (pb + s2) * 2);
-            const float e = ms == -FLT_MAX ? 0.f : expf(ms - Mg);
-            Lg = fmaf(__ldcg(p.part_ml + (pb + s2) * 2 + 1), e, Lg);
-            acc = fmaf(__ldcg(p.part_o + (pb + s2) * HD + c), e, acc);
+        float Mg = -FLT_MAX, Lg = 0.f, acc = 0.f;
+        if (S <= kMergeUnroll) {
+            // every (m, l, o) of this output element requested before the first is used: one L2 round trip, not 3 S
+            float ms[kMergeUnroll], ls[kMergeUnroll], os[kMergeUnroll];
+#pragma unroll
+            for (int s2 = 0; s2 < kMergeUnroll; ++s2) {
+                const bool on = s2 < S;
+                const float2 ml = on ? __ldcg(reinterpret_cast<const float2*>(p.part_ml) + pb + s2) : make_float2(-FLT_MAX, 0.f);
+                ms[s2] = ml.x;
+                ls[s2] = ml.y;
+                os[s2] = on ? __ldcg(p.part_o + (pb + s2) * HD + c) : 0.f;
+            }
+#pragma unroll
+            for (int s2 = 0; s2 < kMergeUnroll; ++s2) Mg = fmaxf(Mg, ms[s2]);
+#pragma unroll
+            for (int s2 = 0; s2 < kMergeUnroll; ++s2) {   // same order and arithmetic as the loop below
+                if (s2 < S) {
+                    const float e = ms[s2] == -FLT_MAX ? 0.f : expf(ms[s2] - Mg);
+                    Lg = fmaf(ls[s2], e, Lg);
+                    acc = fmaf(os[s2], e, acc);
+                }
+            }
+        } else {
+            for (int s2 = 0; s2 < S; ++s2) Mg = fmaxf(Mg, __ldcg(p.part_ml + (pb + s2) * 2));
+            for (int s2 = 0; s2 < S; ++s2) {
+                const float ms = __ldcg(p.part_ml + (pb + s2) * 2);
+                const float e = ms == -FLT_MAX ? 0.f : expf(ms - Mg);
+                Lg = fmaf(__ldcg(p.part_ml + (pb + s2) * 2 + 1), e, Lg);
+                acc = fmaf(__ldcg(p.part_o + (pb + s2) * HD + c), e, acc);
+            }
         }
         out[((size_t)r * H + kvh * Gq + hq) * HD + c] = __float2bfloat16_rn(Lg > 0.f ? acc / Lg : 0.f);
     }
@@ -258,9 +283,9 @@ cudaError_t launch_hd(const AttnParams& p, cudaStream_t st) {
         if (e != cudaSuccess) return e;
     }
     dim3 grid(p.n_splits, p.n_kv_heads, p.n_rows);
-    attn_decode_gqa_kernel<HD><<<grid, kThreads, smem, st>>>(p);
+    const cudaError_t le = launch_pdl(attn_decode_gqa_kernel<HD>, grid, dim3(kThreads), smem, st, p);
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 }  // namespace

@@ -9,6 +9,35 @@ namespace dllm {
 
 using bf16 = __nv_bfloat16;
 
+// ---- programmatic dependent launch ---------------------------------------------------------------------------------
+// The kernels of a step follow each other in one stream (or one CUDA graph).  Launched through launch_pdl, a kernel may
+// become resident while its predecessor is still draining: it sets its barriers and tensor memory up -- the GEMMs also
+// start streaming WEIGHTS, which no kernel of the step writes -- and only then waits (pdl_wait) for the predecessor to
+// have completed and its stores to be visible.  Everything a kernel reads that an earlier kernel of the step wrote, and
+// every global store, comes after pdl_wait.  pdl_launch_dependents lets the runtime place the NEXT kernel as soon as every
+// CTA of this one has started.  Both instructions are no-ops in a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();   // DLLM_PDL=1 switches the launch attribute on; off by default: measured slower on B200 (see its definition)
+
+// cudaLaunchKernelEx with the programmatic-serialization attribute (plus any the caller passes).  Only for kernels that
+// call pdl_wait() before they touch what their predecessors wrote.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 __device__ __forceinline__ float bf16_round(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
 
 // Per-dtype traits.  VEC = elements in one 16-byte vector.  rnd() rounds an fp32 value to the storage

@@ -20,6 +20,14 @@ namespace dllm {
 
 static std::atomic<unsigned long long> g_launches{0};
 void count_launch(unsigned long long n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+bool pdl_enabled() {
+    // Off unless DLLM_PDL=1 (read per launch).  Measured on B200, Llama-3-8B decode steps of 16 / 32 rows as CUDA graphs of
+    // these kernels, same box, alternating runs: 3.41-3.59 k / 5.63-5.71 k tokens/s without the attribute, 2.97-3.17 k /
+    // 4.46-4.54 k with it (profiles/r2b_decode_latency_experiments.md) -- every programmatic edge costs about 2 us more than
+    // a plain one here, more than the overlapped prologues give back.
+    const char* e = getenv("DLLM_PDL");
+    return e && e[0] == '1';
+}
 unsigned long long launch_count() { return g_launches.load(std::memory_order_relaxed); }
 
 constexpr int kGemvThreads = 256;
@@ -450,6 +458,8 @@ cudaError_t launch_gemv(int dtype, const GemvParams& p, int num_sms, cudaStream_
 
 template <typename T>
 __global__ void embed_kernel(const EmbedParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     using D = DT<T>;
     constexpr int VEC = D::VEC;
     const int r = blockIdx.x;
@@ -474,10 +484,10 @@ __global__ void embed_kernel(const EmbedParams p) {
 
 cudaError_t launch_embed(int dtype, const EmbedParams& p, cudaStream_t s) {
     if (p.hidden % (dtype == 0 ? 8 : 4) != 0) return cudaErrorInvalidValue;
-    if (dtype == 0) embed_kernel<bf16><<<p.n_rows, 128, 0, s>>>(p);
-    else embed_kernel<float><<<p.n_rows, 128, 0, s>>>(p);
+    const cudaError_t e = dtype == 0 ? launch_pdl(embed_kernel<bf16>, dim3(p.n_rows), dim3(128), 0, s, p)
+                                     : launch_pdl(embed_kernel<float>, dim3(p.n_rows), dim3(128), 0, s, p);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 // Decode-loop bookkeeping, on the device so that no step needs the host.
@@ -486,6 +496,8 @@ cudaError_t launch_embed(int dtype, const EmbedParams& p, cudaStream_t s) {
 //   advance: feed the sampled token back, move every position on by one, log the token
 __global__ void decode_begin_kernel(int32_t* ids, int32_t* positions, int32_t* seq_ids, const int32_t* next_token,
                                     const int32_t* logit_rows, int n, int32_t* step_ctr, int pos_add) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     const int i = threadIdx.x;
     int t = 0, ps = 0, sq = 0;
     if (i < n) {
@@ -507,13 +519,15 @@ cudaError_t launch_decode_begin(int32_t* ids, int32_t* positions, int32_t* seq_i
                                 const int32_t* logit_rows, int32_t n, int32_t* step_ctr, int32_t pos_add,
                                 cudaStream_t s) {
     if (n <= 0 || n > 1024) return cudaErrorInvalidValue;
-    decode_begin_kernel<<<1, 1024, 0, s>>>(ids, positions, seq_ids, next_token, logit_rows, n, step_ctr, pos_add);
+    const cudaError_t e = launch_pdl(decode_begin_kernel, dim3(1), dim3(1024), 0, s, ids, positions, seq_ids, next_token, logit_rows, n, step_ctr, pos_add);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 __global__ void advance_kernel(int32_t* ids, int32_t* positions, const int32_t* next_token, int32_t* tok_ring,
                                int32_t* step_ctr, int n_rows) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     const int r = threadIdx.x;
     const int step = *step_ctr;
     __syncthreads();
@@ -529,9 +543,9 @@ __global__ void advance_kernel(int32_t* ids, int32_t* positions, const int32_t* 
 cudaError_t launch_advance(int32_t* ids, int32_t* positions, const int32_t* next_token, int32_t* tok_ring,
                            int32_t* step_ctr, int32_t n_rows, cudaStream_t s) {
     if (n_rows <= 0 || n_rows > 1024) return cudaErrorInvalidValue;
-    advance_kernel<<<1, 1024, 0, s>>>(ids, positions, next_token, tok_ring, step_ctr, n_rows);
+    const cudaError_t e = launch_pdl(advance_kernel, dim3(1), dim3(1024), 0, s, ids, positions, next_token, tok_ring, step_ctr, n_rows);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 // out[m, n] = sum_k in[m, k] * param[k, n]   (reference src/worker/node.py:31, fp32)

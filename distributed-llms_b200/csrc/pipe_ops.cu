@@ -15,6 +15,8 @@ namespace {
 using namespace mkd;
 
 __global__ void __launch_bounds__(1024) pipe_begin_kernel(const PipeBeginParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     if (threadIdx.x == 0) wait_ticket(p.in_flag, p.want);
     __syncthreads();
     if ((int)threadIdx.x < p.n_rows) {
@@ -36,6 +38,8 @@ __global__ void __launch_bounds__(1024) pipe_begin_kernel(const PipeBeginParams 
 }
 
 __global__ void __launch_bounds__(1024) pipe_end_kernel(const PipeEndParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     if (p.out_hidden) {   // rows into the next stage's inbox: peer memory
         const int vecs = p.n_rows * (p.hidden >> 3);
         const uint4* src = static_cast<const uint4*>(p.h);
@@ -53,16 +57,16 @@ __global__ void __launch_bounds__(1024) pipe_end_kernel(const PipeEndParams p) {
 
 cudaError_t launch_pipe_begin(const PipeBeginParams& p, cudaStream_t st) {
     if (p.n_rows < 1 || p.n_rows > 1024 || p.hidden % 8) return cudaErrorInvalidValue;
-    pipe_begin_kernel<<<1, 1024, 0, st>>>(p);
+    const cudaError_t e = launch_pdl(pipe_begin_kernel, dim3(1), dim3(1024), 0, st, p);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 cudaError_t launch_pipe_end(const PipeEndParams& p, cudaStream_t st) {
     if (p.n_rows < 1 || p.n_rows > 1024 || p.hidden % 8) return cudaErrorInvalidValue;
-    pipe_end_kernel<<<1, 1024, 0, st>>>(p);
+    const cudaError_t e = launch_pdl(pipe_end_kernel, dim3(1), dim3(1024), 0, st, p);
     count_launch();
-    return cudaGetLastError();
+    return e;
 }
 
 }  // namespace dllm

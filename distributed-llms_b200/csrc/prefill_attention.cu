@@ -46,6 +46,8 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
 
 template <int HD, int kQT>
 __global__ void __launch_bounds__(kQT * 2) prefill_attn_kernel(const PrefillAttnParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     constexpr int kThreads = kQT * 2;  // one warp per 16 query rows
     constexpr int LD = HD + 8;  // padded rows: ldmatrix reads 8 rows x 16 bytes without bank conflicts
     extern __shared__ __align__(16) unsigned char smem_dyn[];
@@ -223,9 +225,9 @@ static cudaError_t launch_attn_t(const PrefillAttnParams& p, cudaStream_t st) {
         if (e != cudaSuccess) return e;
     }
     dim3 grid((p.rows_per_seq + QT - 1) / QT, p.n_heads, p.n_seqs);
-    prefill_attn_kernel<HD, QT><<<grid, QT * 2, smem, st>>>(p);
+    const cudaError_t le = launch_pdl(prefill_attn_kernel<HD, QT>, grid, dim3(QT * 2), smem, st, p);
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 cudaError_t launch_prefill_attn(const PrefillAttnParams& p, cudaStream_t st) {

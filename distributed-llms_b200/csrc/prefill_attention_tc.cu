@@ -165,6 +165,8 @@ prefill_attn_tc_kernel(const __grid_constant__ CUtensorMap tm_q, const __grid_co
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    pdl_launch_dependents();   // barriers and tensor memory are set up: from here on q / K / V of this step are read
+    pdl_wait();
     const uint32_t tS = tmem, tO = tmem + 256;        // S buffers at columns 0 / 128, O buffers at 256 / 256 + HD
 
     if (warp == 0) {
@@ -387,9 +389,9 @@ cudaError_t launch_t(const PrefillAttnParams& p, cudaStream_t st) {
     }
     TcAttnParams a{p.positions, p.seq_ids, p.kv.block_table, p.out, p.kv.pages_per_seq, p.n_heads, p.n_kv_heads, p.rows_per_seq};
     dim3 grid((p.rows_per_seq + QT - 1) / QT, p.n_heads, p.n_seqs);
-    prefill_attn_tc_kernel<HD><<<grid, kThreads, smem, st>>>(q, k, v, a);
+    const cudaError_t le = launch_pdl(prefill_attn_tc_kernel<HD>, grid, dim3(kThreads), smem, st, q, k, v, a);
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 }  // namespace

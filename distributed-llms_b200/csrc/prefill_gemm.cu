@@ -324,16 +324,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    pdl_launch_dependents();
+    if (threadIdx.x != 0) pdl_wait();   // (the producer thread waits after it has requested the first weight tiles)
 
     if (warp == 0) {
         // ===== TMA producer: the ring runs on across tile boundaries =====
         if (lane == 0) {
             unsigned it = 0;  // k-blocks issued so far
+            bool waited = false;
             for (int u = blockIdx.x; u < us.n_units; u += gridDim.x) {
                 const Unit un = unit_of(us, u, num_kb);
                 const TileCoord tc = tile_coord<EPI, BN>(p, un.tile, tiles_m);
                 const CUtensorMap* map_b = tc.seg == 0 ? &tm_b : (tc.seg == 1 ? &tm_b2 : &tm_b3);
-                for (int kb = un.kb0; kb < un.kb1; ++kb, ++it) {
+                int kb = un.kb0;
+                if (!waited) {
+                    // The first ring-full of WEIGHT tiles is requested before this kernel waits for its predecessor: no
+                    // kernel of the step writes weights.  The activation tiles of those stages follow the wait.
+                    const int pre = min(kStages, un.kb1 - un.kb0);
+                    for (int i = 0; i < pre; ++i) {
+                        const uint32_t dst = smem_u32(smem + (size_t)i * kStageBytes);
+                        mbar_expect_tx(full0 + i * 8, kStageBytes);
+                        tma_load_2d(dst + kTileBytes, map_b, (kb + i) * BK, tc.n0, full0 + i * 8);
+                        if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, (kb + i) * BK, tc.n0, full0 + i * 8);
+                    }
+                    pdl_wait();
+                    waited = true;
+                    for (int i = 0; i < pre; ++i)
+                        tma_load_2d(smem_u32(smem + (size_t)i * kStageBytes), &tm_a, (kb + i) * BK, tc.m0, full0 + i * 8);
+                    kb += pre;
+                    it += pre;
+                }
+                for (; kb < un.kb1; ++kb, ++it) {
                     const unsigned s = it % kStages;
                     mbar_wait(empty0 + s * 8, ((it / kStages) & 1) ^ 1);
                     const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
@@ -615,10 +636,26 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
+    pdl_launch_dependents();
+    if (threadIdx.x != 0) pdl_wait();   // (the producer thread waits after it has requested the first weight tiles)
+    float resid[EPI == GEMM_EPI_RESIDUAL ? MP : 1];
 
     if (warp == 0) {
         if (lane == 0) {
-            for (int kb = 0; kb < num_kb; ++kb) {
+            // The first ring-full of WEIGHT tiles is requested before this kernel waits for its predecessor (no kernel of
+            // the step writes weights): at a handful of rows the projection is weight streaming, and this way the stream
+            // starts while the previous kernel is still draining.  The row tiles of those stages follow the wait.
+            const int pre = min(kSt, num_kb);
+            for (int kb = 0; kb < pre; ++kb) {
+                const uint32_t dst = smem_u32(smem + (size_t)kb * kStageBytes);
+                mbar_expect_tx(full0 + kb * 8, kStageBytes);
+                tma_load_2d(dst, map_w, (kb0 + kb) * BK, n0, full0 + kb * 8);
+                if (kDual) tma_load_2d(dst + kTileBytes, &tm_w2, (kb0 + kb) * BK, n0, full0 + kb * 8);
+            }
+            pdl_wait();
+            for (int kb = 0; kb < pre; ++kb)
+                tma_load_2d(smem_u32(smem + (size_t)kb * kStageBytes) + kTileBytes * (kDual ? 2 : 1), &tm_x, (kb0 + kb) * BK, 0, full0 + kb * 8);
+            for (int kb = pre; kb < num_kb; ++kb) {
                 const int s = kb % kSt;
                 mbar_wait(empty0 + s * 8, ((kb / kSt) & 1) ^ 1);
                 const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
@@ -647,9 +684,20 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
             }
             tc_commit(tfull);
         }
-    } else if (num_kb > 0) {
-        mbar_wait(tfull, 0);  // every MMA of this CTA has read its operands: the ring is free
-        tc_fence_after();
+    } else {
+        if (EPI == GEMM_EPI_RESIDUAL && krank == 0) {
+            // the residual values this thread will add to -- one per batch row, the same output column -- requested
+            // now, all at once: they arrive while the weights stream, instead of one dependent round trip per row in
+            // the epilogue (the epilogue's own stores are the only writes to these addresses)
+            const int n = n0 + (warp & 3) * 32 + lane;
+            const bf16* y = static_cast<const bf16*>(p.c) + col0 + n;
+#pragma unroll
+            for (int j = 0; j < MP; ++j) resid[j] = (n < seg_n && j < p.M) ? __bfloat162float(y[(size_t)j * p.ldc]) : 0.f;
+        }
+        if (num_kb > 0) {
+            mbar_wait(tfull, 0);  // every MMA of this CTA has read its operands: the ring is free
+            tc_fence_after();
+        }
     }
     // 1st cluster barrier: every CTA's ring is idle, so the leader's can take the partial sums
     cluster_sync_all();
@@ -681,7 +729,9 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
         const bf16* bias = static_cast<const bf16*>(seg == 0 ? p.bias : p.bias_more[seg - 1]);
         if (n < seg_n) {
             const float bn = (bias && EPI != GEMM_EPI_SWIGLU) ? __bfloat162float(bias[n]) : 0.f;
-            for (int j = 0; j < MP && j < p.M; ++j) {
+#pragma unroll
+            for (int j = 0; j < MP; ++j) {
+                if (j >= p.M) break;
                 float v = 0.f, u = 0.f;
                 for (int k = 0; k < ksplit; ++k) {
                     v += part[((size_t)k * kCols + j) * BM + nl];
@@ -696,7 +746,7 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
                     v = bf16_round(silu_f(bf16_round(v))) * bf16_round(u);
                 } else {
                     v = bf16_round(v + bn);
-                    if (EPI == GEMM_EPI_RESIDUAL) v += __bfloat162float(*y);
+                    if (EPI == GEMM_EPI_RESIDUAL) v += resid[j];
                     else if (EPI == GEMM_EPI_GELU) v = gelu_new_f(v);
                 }
                 *y = __float2bfloat16_rn(v);
@@ -716,6 +766,8 @@ gemm_swapab_kernel(const __grid_constant__ CUtensorMap tm_w, const __grid_consta
 __global__ void __launch_bounds__(256) norm_rows_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
                                                         const bf16* __restrict__ b, bf16* __restrict__ y, int rows, int K,
                                                         int norm, float eps) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= rows) return;
     const bf16* xr = x + (size_t)row * K;
@@ -772,6 +824,8 @@ __global__ void __launch_bounds__(256) norm_rows_kernel(const bf16* __restrict__
 __global__ void __launch_bounds__(256) norm_rows_cta_kernel(const bf16* __restrict__ x, const bf16* __restrict__ w,
                                                             const bf16* __restrict__ b, bf16* __restrict__ y,
                                                             const int32_t* __restrict__ row_map, int K, int norm, float eps) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     __shared__ float red[32];
     const int row = blockIdx.x, src = row_map ? row_map[row] : row;
     const bf16* xr = x + (size_t)src * K;
@@ -833,6 +887,8 @@ __global__ void __launch_bounds__(256) norm_rows_cta_kernel(const bf16* __restri
 
 // next_token[r] = lowest index of the maximum of a row of fp32 logits (torch.argmax semantics); one CTA per row
 __global__ void __launch_bounds__(256) argmax_rows_kernel(const float* __restrict__ logits, int n, int32_t* __restrict__ next_token) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     __shared__ float s_val[8];
     __shared__ int s_idx[8];
     const float* row = logits + (size_t)blockIdx.x * n;
@@ -871,6 +927,8 @@ __global__ void __launch_bounds__(256) argmax_rows_kernel(const float* __restric
 
 // qkv [T, (H+2KV)*hd] (already bias-added and rounded) -> rotary on q and k, q to its buffer, k/v into the pages
 __global__ void __launch_bounds__(256) rope_append_kernel(const RopeAppendParams p) {
+    pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
+    pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
     const int hd = p.head_dim, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
     const int heads = H + 2 * KV;
     const int per_row = heads * half;
@@ -934,6 +992,14 @@ bool make_map(CUtensorMap* map, const void* base, int rows, int K, int box_rows 
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+int sm_count() {   // of the current device
+    static int sms[64] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
+    return (dev >= 0 && dev < 64 && sms[dev] > 0) ? sms[dev] : 148;
+}
+
 bool gemm_split_enabled() {
     const char* env = getenv("DLLM_GEMM_SPLIT");   // read per call: the tests compare split and whole tiles in one process
     return !(env && env[0] == '0');
@@ -952,11 +1018,7 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
     int tiles = (p.N + BN - 1) / BN;
     if (EPI != GEMM_EPI_SWIGLU) tiles += (p.n_more[0] + BN - 1) / BN + (p.n_more[1] + BN - 1) / BN;
     const int tiles_m = (p.M + BM - 1) / BM, n_tiles = tiles * tiles_m;
-    static int sms[64] = {0};
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !sms[dev]) cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
-    const int n_sm = (dev >= 0 && dev < 64 && sms[dev] > 0) ? sms[dev] : 148;
+    const int n_sm = sm_count();
     // the last, partly filled wave is cut along K (see UnitSched)
     constexpr size_t kSliceBytes = (size_t)BM * (EPI == GEMM_EPI_SWIGLU ? 256 : BN) * 4;
     const int num_kb = (p.K + BK - 1) / BK;
@@ -1001,9 +1063,9 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
         cudaGetLastError();   // cannot be co-resident here: whole tiles
         us = UnitSched{n_tiles, n_tiles, 1, num_kb};
     }
-    gemm_tc_kernel<EPI, BN><<<n_tiles < n_sm ? n_tiles : n_sm, kGemmThreads, smem, st>>>(a, b, b2, b3, p, us, tiles_m);
+    const cudaError_t le = launch_pdl(gemm_tc_kernel<EPI, BN>, dim3(n_tiles < n_sm ? n_tiles : n_sm), dim3(kGemmThreads), smem, st, a, b, b2, b3, p, us, tiles_m);
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 // 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give); with the scratch
@@ -1043,9 +1105,10 @@ cudaError_t launch_swapab(const GemmTcParams& p, cudaStream_t st) {
     }
     const int total_kb = (p.K + BK - 1) / BK;
     int ksplit = 1;
+    const int n_sm = sm_count();
     // one wave of CTAs: every CTA pays a fixed set-up (tensor memory, barriers, two cluster barriers, the DSMEM pass),
     // so 128 CTAs streaming twice as much each beat 256 CTAs in two waves
-    while (ksplit < Cfg::kMaxSplit && tiles * ksplit * 2 <= 160 && ksplit * 2 <= total_kb) ksplit *= 2;
+    while (ksplit < Cfg::kMaxSplit && tiles * ksplit * 2 <= n_sm + 12 && ksplit * 2 <= total_kb) ksplit *= 2;   // (clusters of 3: measured slower)
     const int kb_per_cta = (total_kb + ksplit - 1) / ksplit;
     const size_t smem = (size_t)Cfg::kStagesS * Cfg::kStageBytes + 1024;
     static PerDeviceOnce attr_once;
@@ -1058,13 +1121,15 @@ cudaError_t launch_swapab(const GemmTcParams& p, cudaStream_t st) {
     cfg.blockDim = dim3(kGemmThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 1;
     attr[0].val.clusterDim.y = ksplit;
     attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // see common.cuh: the kernel calls pdl_wait()
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = pdl_enabled() ? 2 : 1;
     cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_swapab_kernel<EPI, MP>, w, w2, w3, x, p, kb_per_cta);
     count_launch();
     return e;
@@ -1140,23 +1205,24 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
 cudaError_t launch_norm_rows(const void* x, const void* w, const void* b, void* y, int rows, int K, int norm, float eps,
                              cudaStream_t st, const int32_t* row_map) {
     if (rows <= 0 || K % 8) return cudaErrorInvalidValue;
+    cudaError_t le = cudaSuccess;
     if ((rows <= 64 || row_map) && K <= 16384) {
-        norm_rows_cta_kernel<<<rows, 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(w),
-                                                   static_cast<const bf16*>(b), static_cast<bf16*>(y), row_map, K, norm, eps);
+        le = launch_pdl(norm_rows_cta_kernel, dim3(rows), dim3(256), 0, st, static_cast<const bf16*>(x), static_cast<const bf16*>(w),
+                        static_cast<const bf16*>(b), static_cast<bf16*>(y), row_map, K, norm, eps);
     } else {
         if (row_map) return cudaErrorInvalidValue;
-        norm_rows_kernel<<<(rows + 7) / 8, 256, 0, st>>>(static_cast<const bf16*>(x), static_cast<const bf16*>(w),
-                                                         static_cast<const bf16*>(b), static_cast<bf16*>(y), rows, K, norm, eps);
+        le = launch_pdl(norm_rows_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, static_cast<const bf16*>(x), static_cast<const bf16*>(w),
+                        static_cast<const bf16*>(b), static_cast<bf16*>(y), rows, K, norm, eps);
     }
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 cudaError_t launch_argmax_rows(const float* logits, int rows, int n, int32_t* next_token, cudaStream_t st) {
     if (rows <= 0 || n <= 0) return cudaErrorInvalidValue;
-    argmax_rows_kernel<<<rows, 256, 0, st>>>(logits, n, next_token);
+    const cudaError_t le = launch_pdl(argmax_rows_kernel, dim3(rows), dim3(256), 0, st, logits, n, next_token);
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 cudaError_t launch_rope_append(const RopeAppendParams& p, cudaStream_t st) {
@@ -1164,9 +1230,9 @@ cudaError_t launch_rope_append(const RopeAppendParams& p, cudaStream_t st) {
     if (total <= 0) return cudaErrorInvalidValue;
     int blocks = (total + 255) / 256;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    rope_append_kernel<<<blocks, 256, 0, st>>>(p);
+    const cudaError_t le = launch_pdl(rope_append_kernel, dim3(blocks), dim3(256), 0, st, p);
     count_launch();
-    return cudaGetLastError();
+    return le;
 }
 
 }  // namespace dllm
