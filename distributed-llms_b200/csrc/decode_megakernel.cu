@@ -528,6 +528,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     const uint32_t xrow_hi = smem_u32(xs) + (uint32_t)(min(g + 8, R - 1) * ldx * 2);
 
     const bool piped = p.in_flag != nullptr;  // fused hand-off: inputs arrive in / outputs leave through mailboxes
+    bool ticket_ok = true;
     for (int step = 0; step < p.n_steps; ++step) {
         // micro-batch of this step and its decode step inside the launch (classic mode: m = 0, gstep = step)
         const int m = piped ? step % p.n_micro : 0;
@@ -556,7 +557,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, false, true);
                     }
                 }
-                grid_barrier_wait(p.barrier, bar_target, tr);
+                if (grid_barrier_wait(p.barrier, bar_target, tr, piped ? p.status : nullptr)) goto mk_aborted;
             }
             need_barrier = true;
             c.cur_key = step * p.n_phases + phi;
@@ -568,9 +569,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         const int pm = (step - 1) % p.n_micro, pg = (step - 1) / p.n_micro;
                         st_release_sys(p.out_flag + (size_t)pm * p.flag_stride, p.ticket_base + pg + 1);
                     }
-                    wait_ticket(p.in_flag + (size_t)m * p.flag_stride, p.ticket_base + gstep + 1);
+                    ticket_ok = wait_ticket(p.in_flag + (size_t)m * p.flag_stride, p.ticket_base + gstep + 1, p.status, p.ticket_timeout_ns);
                 }
-                if (piped) __syncthreads();
+                if (piped && __syncthreads_or(!ticket_ok)) goto mk_aborted;   // this stage's input did not arrive: leave
                 // positions / slots / KV page of every row, and the rotary rows of those positions
                 if ((int)threadIdx.x < R) {
                     const int ps = ldcg_i32(pos_m + threadIdx.x) + pos_add, sq = ldcg_i32(seq_m + threadIdx.x);
@@ -921,11 +922,16 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     }
 
     if (piped && p.out_hidden && p.n_steps > 0) {  // the last step's rows: complete once every CTA has arrived
-        grid_barrier(p.barrier, bar_target);
+        grid_barrier_arrive(p.barrier, bar_target);
+        if (grid_barrier_wait(p.barrier, bar_target, nullptr, p.status)) goto mk_aborted;
         if (blockIdx.x == 0 && threadIdx.x == 0) {
             const int pm = (p.n_steps - 1) % p.n_micro, pg = (p.n_steps - 1) / p.n_micro;
             st_release_sys(p.out_flag + (size_t)pm * p.flag_stride, p.ticket_base + pg + 1);
         }
+    }
+    if (false) {
+mk_aborted:
+        abort_drain();   // nothing is sent on; the next stage gives up in turn and the host reads the status word
     }
     // leave the barrier words at zero for the next launch: the last CTA out resets them
     __syncthreads();

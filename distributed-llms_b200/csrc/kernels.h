@@ -188,6 +188,8 @@ struct PipeBeginParams {
     void* h;
     int32_t* tok_ring;          // where to record the fed ids, or null
     int32_t n_rows, hidden;
+    int* status;                // the stage's abort word (see mk_device.cuh: wait_ticket)
+    unsigned long long timeout_ns;
 };
 struct PipeEndParams {
     unsigned* out_flag;         // the slot's ticket in the next stage's mailbox
@@ -197,6 +199,7 @@ struct PipeEndParams {
     void* out_hidden;           // other stages: the next stage's inbox rows (peer memory)
     const void* h;
     int32_t n_rows, hidden;
+    const int* status;
 };
 cudaError_t launch_pipe_begin(const PipeBeginParams& p, cudaStream_t st);
 cudaError_t launch_pipe_end(const PipeEndParams& p, cudaStream_t st);

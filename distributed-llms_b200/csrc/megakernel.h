@@ -85,6 +85,8 @@ struct MkParams {
     // ticket counts the inputs delivered to it: the consumer of decode step G waits for ticket >= G + 1.
     int32_t n_micro;
     uint32_t ticket_base;    // decode step number of this launch's first step
+    int* status;             // non-zero: a stage of this loop gave up waiting for a ticket (see wait_ticket)
+    unsigned long long ticket_timeout_ns;
     int32_t flag_stride;     // uint32 elements between two slots' tickets
     int32_t out_phase;       // index of the phase whose epilogue produces the stage's output rows (its last o- or down projection)
     unsigned* in_flag;       // local inbox: tickets,

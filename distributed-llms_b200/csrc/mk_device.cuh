@@ -105,14 +105,27 @@ __device__ __forceinline__ void grid_barrier_arrive(unsigned* bar, unsigned& tar
         if (tr) tr[9] = clock64();
     }
 }
-__device__ __forceinline__ void grid_barrier_wait(const unsigned* bar, unsigned target, long long* tr = nullptr) {
+// Returns true (to every thread of the CTA) when the launch has been aborted -- a stage gave up waiting for a ticket,
+// `status` is non-zero -- and this CTA must leave instead of waiting for arrivals that will not come.
+__device__ __forceinline__ bool grid_barrier_wait(const unsigned* bar, unsigned target, long long* tr = nullptr,
+                                                  const int* status = nullptr) {
+    int bad = 0;
     if (threadIdx.x == 0) {
         // acquire: nothing after the barrier is satisfied from stale data
-        for (unsigned spins = 0; ld_acquire_u32(bar) < target; ++spins)
+        for (unsigned spins = 0; ld_acquire_u32(bar) < target; ++spins) {
+            if (status && (spins & 0x3ffu) == 0x3ffu && *reinterpret_cast<const volatile int*>(status) != 0) {
+                bad = 1;
+                break;
+            }
             if (spins > (1u << 26)) __trap();  // a lost arrival is a bug; do not hang the GPU
+        }
         if (tr) tr[10] = clock64();
     }
-    __syncthreads();
+    if (status == nullptr) {   // classic launches: nothing can abort them
+        __syncthreads();
+        return false;
+    }
+    return __syncthreads_or(bad) != 0;
 }
 __device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned& target, long long* tr = nullptr) {
     grid_barrier_arrive(bar, target, tr);
@@ -133,15 +146,28 @@ __device__ __forceinline__ unsigned long long global_ns() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-// One thread waits until the slot's ticket reaches `want`.  The producer is another kernel (on another GPU): give
-// it 20 s -- processes start seconds apart -- then trap rather than hang the device.
-__device__ __forceinline__ void wait_ticket(const unsigned* flag, unsigned want) {
-    if ((int)(ld_acquire_sys(flag) - want) >= 0) return;
+// One thread waits until the slot's ticket reaches `want`.  The producer is another kernel (on another GPU): processes
+// start seconds apart, so the wait is long (`timeout_ns`, 20 s by default) -- but it ends: on a timeout the thread marks
+// `status` (the first one to do so names the reason) and returns false, as it does when another CTA or an earlier kernel
+// of this stage has already given up.  The caller then leaves its kernel in an orderly way; nothing traps, the context
+// stays usable and the host reads the status word (dllm_shard_pipeline_status).
+__device__ __forceinline__ bool wait_ticket(const unsigned* flag, unsigned want, int* status, unsigned long long timeout_ns) {
+    if ((int)(ld_acquire_sys(flag) - want) >= 0) return true;
     const unsigned long long t0 = global_ns();
     while ((int)(ld_acquire_sys(flag) - want) < 0) {
         __nanosleep(64);
-        if (global_ns() - t0 > 20000000000ull) __trap();
+        if (*reinterpret_cast<volatile int*>(status) != 0) return false;
+        if (global_ns() - t0 > timeout_ns) {
+            atomicCAS(status, 0, 1);
+            return false;
+        }
     }
+    return true;
+}
+// after an abort: bulk copies into this CTA's shared memory may still be in flight -- let them land before the CTA exits
+__device__ __forceinline__ void abort_drain() {
+    const unsigned long long t0 = global_ns();
+    while (global_ns() - t0 < 200000ull) __nanosleep(1000);
 }
 
 __device__ __forceinline__ uint4 pack8(const float (&in)[8]) {

@@ -17,8 +17,9 @@ using namespace mkd;
 __global__ void __launch_bounds__(1024) pipe_begin_kernel(const PipeBeginParams p) {
     pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
     pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
-    if (threadIdx.x == 0) wait_ticket(p.in_flag, p.want);
-    __syncthreads();
+    bool ok = true;
+    if (threadIdx.x == 0) ok = wait_ticket(p.in_flag, p.want, p.status, p.timeout_ns);
+    if (__syncthreads_or(!ok)) return;   // gave up (or an earlier step of this stage did): the step runs on stale rows, nothing is sent on
     if ((int)threadIdx.x < p.n_rows) {
         const int r = threadIdx.x;
         p.pos[r] = __ldcg(p.pos_all + r) + p.pos_add;
@@ -40,6 +41,7 @@ __global__ void __launch_bounds__(1024) pipe_begin_kernel(const PipeBeginParams 
 __global__ void __launch_bounds__(1024) pipe_end_kernel(const PipeEndParams p) {
     pdl_launch_dependents();   // the next kernel of the step may be placed as soon as every CTA of this one runs
     pdl_wait();                // ... and this one touches global memory only once its predecessor has completed
+    if (*reinterpret_cast<const volatile int*>(p.status) != 0) return;   // the loop has been aborted: the next stage gives up in turn
     if (p.out_hidden) {   // rows into the next stage's inbox: peer memory
         const int vecs = p.n_rows * (p.hidden >> 3);
         const uint4* src = static_cast<const uint4*>(p.h);

@@ -85,6 +85,7 @@ struct dllm_shard {
     unsigned* gemm_tickets = nullptr;  // one per split tile, zero between launches
     size_t gemm_ws_bytes = 0;
     int32_t *pipe_pos = nullptr, *pipe_seq = nullptr;   // positions / KV slots of every micro-batch of a pipelined per-op loop
+    int* pipe_status = nullptr;   // non-zero: a pipelined loop of this stage gave up waiting for a ticket
     int32_t *ids = nullptr, *pos = nullptr, *seq = nullptr, *logit_rows = nullptr, *arange = nullptr;
     int32_t *next_tok = nullptr, *block_table = nullptr, *tok_ring = nullptr, *step_ctr = nullptr;
     float* logits = nullptr;   // [max_logit_rows, V]
@@ -206,6 +207,7 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
     add(&s->ids, (size_t)c.max_rows * 4);
     add(&s->pipe_pos, (size_t)c.max_rows * 4);
     add(&s->pipe_seq, (size_t)c.max_rows * 4);
+    add(&s->pipe_status, 4);
     add(&s->pos, (size_t)c.max_rows * 4);
     add(&s->seq, (size_t)c.max_rows * 4);
     add(&s->logit_rows, (size_t)c.max_rows * 4);
@@ -533,6 +535,14 @@ struct dllm_mailbox {
 constexpr int kFlagStride = 32;  // one ticket per 128-byte line
 constexpr int kPipeOpsMaxRows = 64;  // rows per micro-batch of the per-op pipelined loop (one CUDA graph per step)
 
+// how long a stage waits for a hand-off ticket before it abandons the loop (DLLM_TICKET_TIMEOUT_MS, default 20 s:
+// the stages' processes start seconds apart)
+static unsigned long long ticket_timeout_ns() {
+    const char* e = getenv("DLLM_TICKET_TIMEOUT_MS");
+    const long ms = e ? atol(e) : 0;
+    return (unsigned long long)(ms > 0 ? ms : 20000) * 1000000ull;
+}
+
 struct MkPipe {
     const dllm_mailbox *in, *out;
     int n_micro;
@@ -595,6 +605,7 @@ static int run_megakernel(dllm_shard* s, int n_rows, int n_steps, bool advance, 
     if (const char* e = getenv("DLLM_MK_BLOCKED")) p.blocked = atoi(e) != 0;  // 0: panel p -> CTA p % grid (A/B measurements)
     if (pipe) {
         p.n_micro = pipe->n_micro; p.ticket_base = pipe->step_base; p.flag_stride = kFlagStride;
+        p.status = s->pipe_status; p.ticket_timeout_ns = ticket_timeout_ns();
         p.out_phase = s->mk_out_phase;
         p.in_flag = pipe->in->flags(); p.in_tokens = pipe->in->tokens();
         p.in_hidden = c.has_embed ? nullptr : pipe->in->hidden_rows();
@@ -1075,7 +1086,7 @@ static int run_pipelined_ops(dllm_shard* s, const MkPipe& pipe, int rows, int n_
         b.pos_all = s->pipe_pos + (size_t)m * rows; b.seq_all = s->pipe_seq + (size_t)m * rows; b.pos_add = g;
         b.ids = s->ids; b.pos = s->pos; b.seq = s->seq; b.h = s->h;
         b.tok_ring = c.has_embed ? s->tok_ring + (size_t)step * rows : nullptr;
-        b.n_rows = rows; b.hidden = c.hidden;
+        b.n_rows = rows; b.hidden = c.hidden; b.status = s->pipe_status; b.timeout_ns = ticket_timeout_ns();
         CUDA_TRY(launch_pipe_begin(b, st));
         if (run_step(s, rows, nl, false, st, mode, 0, 0)) return 1;
         PipeEndParams e{};
@@ -1084,7 +1095,7 @@ static int run_pipelined_ops(dllm_shard* s, const MkPipe& pipe, int rows, int n_
         e.out_tokens = c.has_head ? pipe.out->tokens() + (size_t)m * rows : nullptr;
         e.next_tok = s->next_tok;
         e.out_hidden = c.has_head ? nullptr : static_cast<char*>(pipe.out->hidden_rows()) + (size_t)m * rows * c.hidden * 2;
-        e.h = s->h; e.n_rows = rows; e.hidden = c.hidden;
+        e.h = s->h; e.n_rows = rows; e.hidden = c.hidden; e.status = s->pipe_status;
         CUDA_TRY(launch_pipe_end(e, st));
     }
     s->pos_at_pending = false;
@@ -1119,6 +1130,21 @@ extern "C" int dllm_shard_decode_pipelined(dllm_shard* s, dllm_mailbox* inbox, d
     if (c.has_embed && fed_tokens_out)
         CUDA_TRY(cudaMemcpyAsync(fed_tokens_out, s->tok_ring, (size_t)n_steps * n_micro * rows * 4, cudaMemcpyDefault, st));
     return 0;
+}
+
+extern "C" int dllm_shard_pipeline_status(dllm_shard* s, void* stream) {
+    if (!s) return fail("dllm_shard_pipeline_status: null shard");
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaSetDevice(s->device));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    int status = 0;
+    CUDA_TRY(cudaMemcpy(&status, s->pipe_status, 4, cudaMemcpyDeviceToHost));
+    if (status == 0) return 0;
+    CUDA_TRY(cudaMemset(s->pipe_status, 0, 4));
+    if (s->mk_sync) CUDA_TRY(cudaMemset(s->mk_sync, 0, 16));   // barrier / exit counters of the abandoned launch
+    return fail("dllm_shard_pipeline_status: the pipelined decode loop was abandoned -- a hand-off ticket did not arrive within " +
+                std::to_string(ticket_timeout_ns() / 1000000ull) + " ms (the previous stage is not running, or is itself waiting); "
+                "tokens and KV rows of that loop are incomplete: reset its sequences before reusing them");
 }
 
 extern "C" int dllm_handoff_peer_copy(void* dst_ptr, int dst_device, const void* src_ptr, int src_device,

@@ -55,6 +55,7 @@ SIGNATURES = {
     "dllm_shard_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _vp, _vp, _i32, _vp, _vp, _vp]),
     "dllm_shard_decode_loop": (C.c_int, [_vp, _i32, _i32, _vp, _vp]),
     "dllm_shard_decode_pipelined_check": (C.c_int, [_vp, _vp, _vp, _i32, _i32, _i32]),
+    "dllm_shard_pipeline_status": (C.c_int, [_vp, _vp]),
     "dllm_handoff_peer_copy": (C.c_int, [_vp, C.c_int, _vp, C.c_int, _sz, _vp]),
     "dllm_mailbox_create": (C.c_int, [_i32, _i32, _i32, _i32, C.POINTER(C.c_void_p)]),
     "dllm_mailbox_export": (C.c_int, [_vp, _vp]),

@@ -348,6 +348,12 @@ class ShardExecutor:
             for s_, p_ in zip(seq.tolist(), pos.tolist()):
                 cabi.check(cabi.lib().dllm_shard_kv_reserve(self._handle, s_, p_ + n_steps, st))
 
+    def pipeline_status(self) -> None:
+        """Waits for the pipelined loops enqueued so far and raises `DllmError` if one of them was abandoned because a
+        hand-off ticket did not arrive in time (`dllm_shard_pipeline_status`); the context stays usable either way."""
+        with self.lock, torch.cuda.device(self.device):
+            cabi.check(cabi.lib().dllm_shard_pipeline_status(self._handle, self._stream()))
+
     def decode_pipelined(self, inbox, outbox, n_micro: int, rows: int, n_steps: int, step_base: int,
                          positions: torch.Tensor, seq_ids: torch.Tensor) -> Optional[torch.Tensor]:
         """`n_steps` decode steps of `n_micro` micro-batches in ONE persistent launch with the hand-off fused into

@@ -354,7 +354,7 @@ class WorkerNode:
                 ex.check_decode_pipelined(self._inbox, self._outbox, n_micro, rows, n_steps, pos, seq)
                 return {"positions": pos}
             fed = ex.decode_pipelined(self._inbox, self._outbox, n_micro, rows, n_steps, int(header.get("step_base", 0)), pos, seq)
-            torch.cuda.synchronize()
+            ex.pipeline_status()  # waits for the loop; raises if a ticket never arrived (the RESULT then carries the error)
             return {"fed": fed.cpu() if fed is not None else None}
         if command == "MAILBOX_READ":
             got = [self._inbox.read_tokens(slot) for slot in range(self._inbox.n_slots)]

@@ -229,9 +229,17 @@ DLLM_API int dllm_shard_decode_pipelined(dllm_shard* shard, dllm_mailbox* inbox,
 /* Pre-flight of dllm_shard_decode_pipelined: the same checks, no launch, nothing enqueued.  Belongs to the master's decode
  * loop that the reference lacks (src/master/node.py:227-277 broadcasts once): the master asks every stage first and starts
  * the stages' loops only when all of them accept -- a stage that refused after its neighbours had started would leave them
- * spinning on tickets that never arrive (they give up after 20 s with a device trap that costs the worker its context). */
+ * waiting for tickets that never arrive (until they give up: dllm_shard_pipeline_status). */
 DLLM_API int dllm_shard_decode_pipelined_check(dllm_shard* shard, dllm_mailbox* inbox, dllm_mailbox* outbox, int32_t n_micro,
                                       int32_t rows, int32_t n_steps);
+
+/* Outcome of the pipelined loops enqueued on `stream` so far: waits for the stream, returns 0 when every hand-off ticket
+ * arrived.  A stage whose input ticket does not arrive within DLLM_TICKET_TIMEOUT_MS (environment, default 20000 -- the
+ * stages' processes start seconds apart) abandons its loop in an orderly way: its kernels return, nothing is sent on (so
+ * the stages after it give up in turn), the CUDA context stays usable, and this call reports the error once and clears
+ * it.  The reference has no counterpart (its master waits on a socket with a timeout, src/master/node.py:188-203); this
+ * is that timeout for the device-side hand-off. */
+DLLM_API int dllm_shard_pipeline_status(dllm_shard* shard, void* stream);
 
 /* Replaces `MessageProtocol.send_message` / `receive_message` (reference
  * src/network/protocol.py:38-129) for the data plane inside one NVLink box: copy the hand-off tile

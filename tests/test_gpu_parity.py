@@ -573,6 +573,48 @@ def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, persistent
         box.close()
 
 
+@pytest.mark.parametrize("persistent", [True, False])
+def test_pipelined_loop_gives_up_on_a_missing_ticket_and_the_stage_stays_usable(persistent, monkeypatch):
+    """A stage whose input never arrives (nobody posted the seed ids) must not hang or trap: after the time-out its loop is
+    abandoned, `pipeline_status` reports it once, and the very same handle then runs the loop correctly -- in the
+    persistent kernel (every CTA leaves, the barrier words end up clean) and in the per-op loop (wait / send kernels)."""
+    from src.network.handoff import Mailbox
+    if persistent and os.environ.get("DLLM_MEGAKERNEL") == "0":
+        pytest.skip("the persistent kernel is switched off")
+    if not persistent:
+        monkeypatch.setenv("DLLM_MEGAKERNEL", "0")
+    monkeypatch.setenv("DLLM_TICKET_TIMEOUT_MS", "300")
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 3, torch.float32, init="full")
+    rows, n_steps, T = 2, 5, 10
+    (st,) = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=64, max_seqs=rows, max_context=64, page_size=16)
+    prompts = make_prompts(cfg.vocab, rows, T, seed=20)
+    first = st.compute({"input_ids": prompts})["next_token"].cpu()
+    want = torch.cat([first[:, None], st.decode_loop(rows, n_steps).cpu()], 1)
+    st.reset()
+    seed = st.compute({"input_ids": prompts})["next_token"].to(torch.int32)
+    box = Mailbox.create(0, 1, rows, cfg.hidden)
+    try:
+        pos = torch.full((1, rows), T, dtype=torch.int32)
+        seq = torch.arange(rows, dtype=torch.int32).reshape(1, rows)
+        st.executor.decode_pipelined(box, box, 1, rows, n_steps, 0, pos, seq)   # no ids were posted: ticket 1 never comes
+        with pytest.raises(cabi.DllmError, match="abandoned"):
+            st.executor.pipeline_status()
+        st.executor.pipeline_status()          # reported once, cleared
+        # the handle, its barrier words and the CUDA context are intact: the same loop with its input
+        st.reset()
+        assert torch.equal(st.compute({"input_ids": prompts})["next_token"].to(torch.int32), seed)
+        box.post_tokens(0, seed, ticket=1)
+        fed = st.executor.decode_pipelined(box, box, 1, rows, n_steps, 0, pos, seq)
+        st.executor.pipeline_status()
+        last, ticket = box.read_tokens(0)
+        assert ticket == n_steps + 1
+        got = torch.cat([fed.cpu()[:, 0, :].t(), last[:, None]], 1).to(torch.int64)
+        assert torch.equal(got, want)
+    finally:
+        box.close()
+
+
 @pytest.mark.parametrize("qt128", ["0", "1"])
 @pytest.mark.parametrize("batch,prompt_len", [(1, 1300), (2, 2100)])
 def test_long_context_decode_matches_oracle(batch, prompt_len, qt128, monkeypatch):

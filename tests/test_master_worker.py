@@ -127,7 +127,7 @@ def test_fused_decode_is_only_tried_when_every_stage_has_its_own_gpu():
     cluster([(10, 0), (11, 0)], {"w0": [0, 1], "w1": [2]})   # a worker with two stages
     assert m._fused_decode("t", tok, 4) is None
     cluster([(10, 0), (10, 1)])
-    assert m._fused_decode("t", torch.zeros(1, 9, dtype=torch.int64), 4) is None   # more rows than the persistent kernel takes
+    assert m._fused_decode("t", torch.zeros(1, 65, dtype=torch.int64), 4) is None   # more rows than a mailbox-fed step takes
     assert m._fused_decode("t", tok, 0) is None
 
 
