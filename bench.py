@@ -352,13 +352,16 @@ def run_single(args) -> int:
     try:  # DRAM bytes per step from the committed ncu --set full capture of this workload (profiles/)
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
             t = json.load(f).get(model)
-        if t and batch == WORKLOADS[model][1]:
+        if t and batch == t.get("batch", WORKLOADS[model][1]) and not args.prompt_len:
             traffic = t["dram_bytes_per_step"]
     except Exception:
         pass
     roofline = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
                 "traffic": traffic, "peak_kind": peak_kind,
-                "kernel": "decode_megakernel: one persistent launch per decode loop; unit = one decode step of the stage",
+                "kernel": ("decode_megakernel: one persistent launch per decode loop; unit = one decode step of the stage"
+                           if launches <= 4 else
+                           f"one decode step = a CUDA graph of {int(launches) // K} kernels (swap-AB tcgen05 GEMMs, grouped-head "
+                           "attention, row norms): more rows than the persistent kernel takes at this width"),
                 "algorithmic_bytes_per_launch": algo}
 
     # ---- CPU baseline on the host cores (bounded sample) ----

@@ -25,5 +25,17 @@ DLLM_MK_TRACE=$out/${tag}_phase_trace_llama8b.csv python bench.py --workload lla
 python tools/mk_trace_summary.py $out/${tag}_phase_trace_llama8b.csv > $out/${tag}_phase_trace_llama8b_summary.txt
 # prefill launch list (tcgen05 GEMMs + flash attention): one 512-token chunk
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_ncu_prefill_launches.csv \
-    -k regex:'gemm_tc|prefill_attn|norm_rows|rope_append|embed' python bench.py --steps 4 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
-ls -la $out | tail -20
+    -k regex:'gemm_tc|gemm_swapab|prefill_attn|norm_rows|rope_append|embed|argmax' python bench.py --steps 4 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
+# Llama-3-8B: memory traffic of one persistent launch (for profiles/traffic.json), decode batches on the per-op path, prefill
+ncu --set full --clock-control none -k regex:decode_megakernel -s 1 -c 1 -o $out/${tag}_megakernel_llama8b \
+    python bench.py --workload llama3-8b --steps 8 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
+ncu -i $out/${tag}_megakernel_llama8b.ncu-rep --page raw --csv > $out/${tag}_ncu_megakernel_llama8b_raw.csv 2>/dev/null
+for b in 12 16 32 64; do
+  python bench.py --workload llama3-8b --batch $b --steps 16 --no-cpu-baseline > $out/${tag}_bench_llama8b_b$b.json 2>/dev/null
+done
+python tools/prefill_probe.py llama3-8b 4096 4096 2>/dev/null | grep prefill > $out/${tag}_prefill_probe.txt
+python tools/prefill_probe.py tinyllama-1.1b 512 512 2>/dev/null | grep prefill >> $out/${tag}_prefill_probe.txt
+python tools/prefill_probe.py qwen2.5-14b 2048 2048 2>/dev/null | grep prefill >> $out/${tag}_prefill_probe.txt
+python tools/gemm_bench.py > $out/${tag}_gemm_bench.txt 2>&1
+rm -f $out/${tag}_megakernel_llama8b.ncu-rep
+ls -la $out | tail -30
