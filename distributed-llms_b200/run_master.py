@@ -23,7 +23,7 @@ def main():
     master = MasterNode(host=a.host, port=a.port)
     master.start()
     print("Initializing and sharding model...")
-    print(f"Model initialized and sharded at: {master.initialize_model(a.model, num_shards=a.shards, cache_dir=a.cache_dir)}")
+    print(f"Model initialized and sharded at: {master.initialize_model(a.model, num_shards=a.shards, cache_dir=a.cache_dir, by_path=a.by_path)}")
     print("\nWaiting for worker connections...\nStart workers in separate terminals with: python run_worker.py")
     try:
         while True:

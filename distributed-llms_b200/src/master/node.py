@@ -106,9 +106,11 @@ class MasterNode:
         self.server_socket = None
 
     # ---- model preparation (reference :54-82) ---------------------------------------------------------------
-    def initialize_model(self, model_id: str, num_shards: int, cache_dir: str = "./models"):
-        """`model_id`: a local directory (config.json + pytorch_model.bin / model.safetensors), `random:<name>` for a
-        seeded random-init checkpoint of a known architecture (no network needed), or a Hub id (needs a network)."""
+    def initialize_model(self, model_id: str, num_shards: int, cache_dir: str = "./models", by_path: bool = False):
+        """`model_id`: a local directory (config.json + pytorch_model.bin / model.safetensors / a safetensors index),
+        `random:<name>` for a seeded random-init checkpoint of a known architecture (no network needed), or a Hub id
+        (needs a network).  `by_path=True`: the workers will read their own stages from the checkpoint
+        (`distribute_shards(by_path=True)`), so nothing is loaded or re-written here."""
         if model_id.startswith("random:"):
             self.model_path = self._materialise_random(model_id[len("random:"):], cache_dir)
         elif os.path.exists(model_id):
@@ -124,6 +126,9 @@ class MasterNode:
             self.tokenizer = None
         print(f"Sharding model into {num_shards} parts...")
         self.shard_manager = ModelShardManager(self.model_path, num_shards)
+        if by_path and any(os.path.exists(os.path.join(self.model_path, n))
+                           for n in ("model.safetensors", "model.safetensors.index.json")):
+            return self.shard_manager.plan_only()
         return self.shard_manager.shard_model()
 
     @staticmethod

@@ -214,7 +214,28 @@ class ModelShardManager:
         if os.path.exists(st):
             from safetensors.torch import load_file
             return load_file(st, device="cpu")
-        raise FileNotFoundError(f"no pytorch_model.bin or model.safetensors under {self.model_path}")
+        index = os.path.join(self.model_path, "model.safetensors.index.json")
+        if os.path.exists(index):  # multi-file checkpoints (Llama-3-8B and larger): every file the index lists
+            from safetensors.torch import load_file
+            with open(index, "r") as f:
+                files = sorted(set(json.load(f)["weight_map"].values()))
+            state: Dict[str, torch.Tensor] = {}
+            for name in files:
+                state.update(load_file(os.path.join(self.model_path, name), device="cpu"))
+            return state
+        raise FileNotFoundError(f"no pytorch_model.bin, model.safetensors or model.safetensors.index.json under {self.model_path}")
+
+    def plan_only(self):
+        """What `shard_model` records, without reading a tensor or writing a shard file: for workers that load their own
+        stage from the checkpoint (`distribute_shards(by_path=True)`), where materialising 16-140 GB on the master only to
+        rewrite it as `shards/*.pt` would be the cost the by-path route exists to avoid."""
+        with open(os.path.join(self.model_path, "config.json"), "r") as f:
+            config = json.load(f)
+        os.makedirs(self.shard_dir, exist_ok=True)
+        with open(os.path.join(self.shard_dir, "config.json"), "w") as f:
+            json.dump(config, f)
+        self.shard_info = {i: [] for i in range(self.num_shards)}
+        return self.shard_dir
 
     def shard_model(self):
         state_dict = self._load_state_dict()

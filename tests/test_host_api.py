@@ -286,3 +286,28 @@ def test_stage_loader_reads_exactly_the_partition(tmp_path, model_type, sharded)
     assert all(v.dtype == torch.bfloat16 for k, v in bf.items() if k != CONFIG_KEY)
     with pytest.raises(FileNotFoundError):
         load_stage_from_safetensors(str(tmp_path), 0, 2)
+
+
+@pytest.mark.parametrize("sharded", [False, True])
+def test_shard_manager_reads_multi_file_checkpoints_and_can_skip_the_rewrite(tmp_path, sharded):
+    """Checkpoints that come as an index of safetensors files (Llama-3-8B and larger) shard like single-file ones, and a
+    master whose workers load by path plans the partition without reading a tensor or writing `shards/*.pt`."""
+    from src.master.node import MasterNode
+    from src.model.shard_manager import ModelShardManager, partition_state_dict
+    d, cfg, full = _tiny_checkpoint(tmp_path, "llama", sharded)
+    mgr = ModelShardManager(d, 2)
+    state = mgr._load_state_dict()
+    assert set(state) == set(full) and all(torch.equal(state[k], full[k]) for k in full)
+    mgr.shard_model()
+    want = partition_state_dict(full, 2, tie_head=False)
+    for i, path in enumerate(mgr.get_shard_paths()):
+        got = torch.load(path, map_location="cpu", weights_only=True)
+        got.pop("__config__", None)
+        assert set(got) == set(want[i])
+    # by path: nothing read, nothing re-written
+    d2, _, _ = _tiny_checkpoint(tmp_path / "again", "llama", sharded)
+    m = MasterNode(host="127.0.0.1", port=0)
+    out = m.initialize_model(d2, num_shards=2, by_path=True)
+    assert os.path.exists(os.path.join(out, "config.json")) and not any(f.endswith(".pt") for f in os.listdir(out))
+    assert m.shard_manager.num_shards == 2 and len(m.shard_manager.get_shard_paths()) == 2
+
