@@ -107,7 +107,7 @@ struct GemmTcParams {
     unsigned* split_tickets;
     size_t split_ws_bytes;
 };
-constexpr int kGemmSplitTickets = 256;
+constexpr int kGemmSplitTickets = 512;
 struct RopeAppendParams {
     const void* qkv;    // [R, (H+2KV)*hd] projected rows (bias added)
     void* q;            // [R, H*hd]

@@ -17,6 +17,8 @@
 #include <stdint.h>
 #include <stdlib.h>
 
+#include <stdio.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -70,6 +72,55 @@ __device__ __forceinline__ void tc_mma(uint32_t d_tmem, uint64_t a_desc, uint64_
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// ---- CTA pairs (cta_group::2): two CTAs of a cluster on one TPC share one UMMA of M = 256 --------------------------
+// Every CTA loads its own 128 A rows and HALF of the B tile; the leader (cluster rank 0) issues the MMAs, which read the
+// operands from both CTAs' shared memory and write each CTA's 128 accumulator rows into its own tensor memory.  All TMA
+// loads are plain (no multicast) 2-D tiled loads; those of the second CTA signal the LEADER's mbarrier.
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t rank) {   // the same offset in CTA `rank`'s shared memory
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+    return remote;
+}
+__device__ __forceinline__ void mbar_expect_tx_cluster(uint32_t cluster_bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.release.cluster.shared::cluster.b64 _, [%0], %1;" ::"r"(cluster_bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar) {
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity) {   // own barrier, arrivals from the pair
+    uint32_t ok = 0;
+    for (unsigned spins = 0; !ok; ++spins) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (!ok && spins > (1u << 26)) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t cluster_bar) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+                 ::"r"(dst), "l"(map), "r"(cluster_bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint32_t bar) {   // arrives on the barrier at this offset in BOTH CTAs
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+}
+__device__ __forceinline__ void tc_mma_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_pair() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
 // 32 lanes x 32 columns of fp32 -> 32 registers per thread (thread = lane, register = column)
 __device__ __forceinline__ void tc_ld32(uint32_t taddr, uint32_t (&r)[32]) {
     asm volatile(
@@ -92,8 +143,8 @@ __device__ __forceinline__ uint64_t make_sw128_desc(uint32_t smem_addr) {
 }
 
 // Instruction descriptor: D fp32, A and B bf16, both K-major, N = bn, M = 128.
-constexpr uint32_t make_idesc(int bn) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+constexpr uint32_t make_idesc(int bn, int m = BM) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
@@ -111,12 +162,12 @@ __device__ __forceinline__ float gelu_new_f(float x) {
 struct TileCoord {
     int seg, m0, n0, col0, seg_n;
 };
-template <int EPI, int BN>
+template <int EPI, int BN, int CG = 1>
 __device__ __forceinline__ TileCoord tile_coord(const GemmTcParams& p, int t, int tiles_m) {
     TileCoord c;
     c.seg = 0; c.col0 = 0; c.seg_n = p.N;
     int tn = t / tiles_m;
-    c.m0 = (t - tn * tiles_m) * BM;
+    c.m0 = (t - tn * tiles_m) * (BM * CG);   // a CTA pair covers 256 rows
     if (EPI != GEMM_EPI_SWIGLU) {
         const int t0 = (p.N + BN - 1) / BN, t1 = (p.n_more[0] + BN - 1) / BN;
         if (tn >= t0 + t1) { c.seg = 2; tn -= t0 + t1; c.col0 = p.N + p.n_more[0]; c.seg_n = p.n_more[1]; }
@@ -280,18 +331,25 @@ __device__ __forceinline__ void qkv_tail(const GemmTcParams& p, const AccSrc& sr
 // memory, so the MMA warp starts tile i+1 while the epilogue warps are still reading tile i out -- the epilogue
 // (tcgen05.ld, SiLU / residual arithmetic, stores) no longer sits between two main loops -- and the TMA ring never drains
 // at a tile boundary.
-template <int EPI, int BN>
+// CG = 2: the CTAs come in pairs (cluster of 2, cta_group::2).  A pair owns a 256-row tile; each CTA loads its 128 A rows
+// and half of the B tile (BN / 2 weight rows), so a k-block costs a CTA 32 KB of shared-memory fill instead of 48 KB for
+// the same 128 x BN x 64 MMA work -- what bounds these kernels is that fill rate (profiles/r2_gemm_m512_ncu.md).  The
+// leader issues UMMAs of M = 256 that read both CTAs' shared memory; each CTA's epilogue warps read their own half of
+// the accumulator out of their own tensor memory.
+template <int EPI, int BN, int CG>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                const __grid_constant__ CUtensorMap tm_b2, const __grid_constant__ CUtensorMap tm_b3, const GemmTcParams p,
                const UnitSched us, const int tiles_m) {
     constexpr bool kDual = EPI == GEMM_EPI_SWIGLU;
     static_assert(!(kDual && BN != 128), "the dual-B tile is 128 wide");
-    constexpr int kBTileBytes = BN * BK * 2;
+    static_assert(CG == 1 || CG == 2, "one CTA or a pair");
+    constexpr int kBRows = BN / CG;                        // rows of a B tile this CTA loads
+    constexpr int kBTileBytes = kBRows * BK * 2;
     constexpr int kStageBytes = kTileBytes + kBTileBytes * (kDual ? 2 : 1);
     constexpr uint32_t kAccCols = kDual ? 256 : BN;       // columns of one accumulator
     constexpr uint32_t kTmemCols = 2 * kAccCols < 32 ? 32 : 2 * kAccCols;  // two of them
-    constexpr uint32_t kIdesc = make_idesc(BN);
+    constexpr uint32_t kIdesc = make_idesc(BN, BM * CG);
     constexpr int kStages = gemm_stages(kStageBytes);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* smem = reinterpret_cast<unsigned char*>(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -299,6 +357,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     __shared__ uint32_t s_tmem;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = CG == 2 ? (int)cluster_ctarank() : 0;            // 0 = the leader of the pair
+    const int unit0 = blockIdx.x / CG, unit_step = gridDim.x / CG;    // both CTAs of a pair walk the same units
     const int num_kb = (p.K + BK - 1) / BK;
     const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + kStages);
     const uint32_t acc_full = smem_u32(bars + 2 * kStages), acc_empty = smem_u32(bars + 2 * kStages + 2);
@@ -306,22 +366,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 
     if (threadIdx.x == 0) {
         for (int i = 0; i < kStages; ++i) {
-            mbar_init(full0 + i * 8, 1);
+            mbar_init(full0 + i * 8, 1);         // (pair: only the leader's is used; it expects both CTAs' bytes)
             mbar_init(empty0 + i * 8, 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(acc_full + i * 8, 1);
-            mbar_init(acc_empty + i * 8, 128);   // the four epilogue warps
+            mbar_init(acc_empty + i * 8, 128 * CG);   // the four epilogue warps (of both CTAs: the leader's MMA thread waits)
         }
         mbar_init(red_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 1) {  // one warp allocates tensor memory and later frees it
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols));
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    if (warp == 1) {  // one warp (per CTA) allocates tensor memory and later frees it
+        if (CG == 2) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s_tmem)), "r"(kTmemCols));
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+        }
     }
     tc_fence_before();
-    __syncthreads();
+    if (CG == 2) cluster_sync_pair();   // the partner's barriers are initialised before anything signals them
+    else __syncthreads();
     tc_fence_after();
     const uint32_t tmem = s_tmem;
     pdl_launch_dependents();
@@ -330,12 +396,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     if (warp == 0) {
         // ===== TMA producer: the ring runs on across tile boundaries =====
         if (lane == 0) {
+            // the barrier a stage's loads signal: this CTA's, or (pair) the leader's
+            auto full_of = [&](unsigned st) { return CG == 2 ? mapa_u32(full0 + st * 8, 0) : full0 + st * 8; };
+            // the leader expects the bytes of both CTAs' loads on its barrier (the partner's complete_tx may come first:
+            // the phase cannot complete before the leader's own arrival); no cluster-scope release per stage -- a
+            // remote arrive.expect_tx.release.cluster here cost a fence per k-block and halved the kernel's rate
+            auto arm = [&](unsigned st) {
+                if (rank == 0) mbar_expect_tx(full0 + st * 8, CG * kStageBytes);
+            };
+            auto load = [&](uint32_t dst, const CUtensorMap* map, int c0, int c1, unsigned st) {
+                if (CG == 2) tma_load_2d_pair(dst, map, c0, c1, full_of(st));
+                else tma_load_2d(dst, map, c0, c1, full0 + st * 8);
+            };
             unsigned it = 0;  // k-blocks issued so far
             bool waited = false;
-            for (int u = blockIdx.x; u < us.n_units; u += gridDim.x) {
+            for (int u = unit0; u < us.n_units; u += unit_step) {
                 const Unit un = unit_of(us, u, num_kb);
-                const TileCoord tc = tile_coord<EPI, BN>(p, un.tile, tiles_m);
+                const TileCoord tc = tile_coord<EPI, BN, CG>(p, un.tile, tiles_m);
                 const CUtensorMap* map_b = tc.seg == 0 ? &tm_b : (tc.seg == 1 ? &tm_b2 : &tm_b3);
+                const int a_row = tc.m0 + rank * BM, b_row = tc.n0 + rank * kBRows;
                 int kb = un.kb0;
                 if (!waited) {
                     // The first ring-full of WEIGHT tiles is requested before this kernel waits for its predecessor: no
@@ -343,14 +422,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                     const int pre = min(kStages, un.kb1 - un.kb0);
                     for (int i = 0; i < pre; ++i) {
                         const uint32_t dst = smem_u32(smem + (size_t)i * kStageBytes);
-                        mbar_expect_tx(full0 + i * 8, kStageBytes);
-                        tma_load_2d(dst + kTileBytes, map_b, (kb + i) * BK, tc.n0, full0 + i * 8);
-                        if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, (kb + i) * BK, tc.n0, full0 + i * 8);
+                        arm(i);
+                        load(dst + kTileBytes, map_b, (kb + i) * BK, b_row, i);
+                        if (kDual) load(dst + kTileBytes + kBTileBytes, &tm_b2, (kb + i) * BK, b_row, i);
                     }
                     pdl_wait();
                     waited = true;
                     for (int i = 0; i < pre; ++i)
-                        tma_load_2d(smem_u32(smem + (size_t)i * kStageBytes), &tm_a, (kb + i) * BK, tc.m0, full0 + i * 8);
+                        load(smem_u32(smem + (size_t)i * kStageBytes), &tm_a, (kb + i) * BK, a_row, i);
                     kb += pre;
                     it += pre;
                 }
@@ -358,25 +437,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                     const unsigned s = it % kStages;
                     mbar_wait(empty0 + s * 8, ((it / kStages) & 1) ^ 1);
                     const uint32_t dst = smem_u32(smem + (size_t)s * kStageBytes);
-                    mbar_expect_tx(full0 + s * 8, kStageBytes);
-                    tma_load_2d(dst, &tm_a, kb * BK, tc.m0, full0 + s * 8);
-                    tma_load_2d(dst + kTileBytes, map_b, kb * BK, tc.n0, full0 + s * 8);
-                    if (kDual) tma_load_2d(dst + kTileBytes + kBTileBytes, &tm_b2, kb * BK, tc.n0, full0 + s * 8);
+                    arm(s);
+                    load(dst, &tm_a, kb * BK, a_row, s);
+                    load(dst + kTileBytes, map_b, kb * BK, b_row, s);
+                    if (kDual) load(dst + kTileBytes + kBTileBytes, &tm_b2, kb * BK, b_row, s);
                 }
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread): tile i+1 goes into the other accumulator while tile i is being read out =====
-        if (lane == 0) {
+        // ===== MMA issuer (one thread; of a pair, the leader's): tile i+1 goes into the other accumulator while tile i
+        // is being read out =====
+        if (lane == 0 && rank == 0) {
             unsigned it = 0, lt = 0;
-            for (int u = blockIdx.x; u < us.n_units; u += gridDim.x, ++lt) {
+            for (int u = unit0; u < us.n_units; u += unit_step, ++lt) {
                 const Unit un = unit_of(us, u, num_kb);
                 const uint32_t acc_t = tmem + (lt & 1) * kAccCols;
-                if (lt >= 2) mbar_wait(acc_empty + (lt & 1) * 8, ((lt >> 1) & 1) ^ 1);   // the epilogue has drained this buffer
+                if (lt >= 2) {   // the epilogue (of both CTAs) has drained this buffer
+                    if (CG == 2) mbar_wait_cluster(acc_empty + (lt & 1) * 8, ((lt >> 1) & 1) ^ 1);
+                    else mbar_wait(acc_empty + (lt & 1) * 8, ((lt >> 1) & 1) ^ 1);
+                }
                 tc_fence_after();
                 for (int kb = un.kb0; kb < un.kb1; ++kb, ++it) {
                     const unsigned s = it % kStages;
-                    mbar_wait(full0 + s * 8, (it / kStages) & 1);
+                    mbar_wait(full0 + s * 8, (it / kStages) & 1);   // TMA-written operands, read by the tensor core only
                     tc_fence_after();
                     const uint32_t base = smem_u32(smem + (size_t)s * kStageBytes);
                     const uint64_t da = make_sw128_desc(base), db = make_sw128_desc(base + kTileBytes);
@@ -385,25 +468,38 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                     for (int k = 0; k < BK / 16; ++k) {
                         // 16 k-elements = 32 bytes further along the swizzled row: +2 in the (address >> 4) field
                         const uint32_t acc = (kb > un.kb0 || k) ? 1u : 0u;
-                        tc_mma(acc_t, da + 2 * k, db + 2 * k, kIdesc, acc);
-                        if (kDual) tc_mma(acc_t + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
+                        if (CG == 2) {
+                            tc_mma_pair(acc_t, da + 2 * k, db + 2 * k, kIdesc, acc);
+                            if (kDual) tc_mma_pair(acc_t + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
+                        } else {
+                            tc_mma(acc_t, da + 2 * k, db + 2 * k, kIdesc, acc);
+                            if (kDual) tc_mma(acc_t + BN, da + 2 * k, db2 + 2 * k, kIdesc, acc);
+                        }
                     }
-                    tc_commit(empty0 + s * 8);  // the slot is free once these MMAs have read it
+                    // the slot is free once these MMAs have read it (in both CTAs)
+                    if (CG == 2) tc_commit_pair(empty0 + s * 8);
+                    else tc_commit(empty0 + s * 8);
                 }
-                tc_commit(acc_full + (lt & 1) * 8);  // accumulator complete
+                if (CG == 2) tc_commit_pair(acc_full + (lt & 1) * 8);  // accumulator complete
+                else tc_commit(acc_full + (lt & 1) * 8);
             }
         }
     } else {
         // ===== epilogue: warps 2..5, TMEM lane quarter = warp % 4 =====
         const int quarter = warp & 3;
+        // where this CTA's epilogue threads report an accumulator drained: the (leader's) MMA thread's barrier
+        auto acc_drained = [&](unsigned buf) {
+            if (CG == 2) mbar_arrive_cluster(mapa_u32(acc_empty + buf * 8, 0));
+            else mbar_arrive(acc_empty + buf * 8);
+        };
         unsigned lt = 0;
-        for (int u = blockIdx.x; u < us.n_units; u += gridDim.x, ++lt) {
+        for (int u = unit0; u < us.n_units; u += unit_step, ++lt) {
         const Unit un = unit_of(us, u, num_kb);
-        const TileCoord tc = tile_coord<EPI, BN>(p, un.tile, tiles_m);
+        const TileCoord tc = tile_coord<EPI, BN, CG>(p, un.tile, tiles_m);
         const int seg = tc.seg, col0 = tc.col0, seg_n = tc.seg_n, n0 = tc.n0;
         mbar_wait(acc_full + (lt & 1) * 8, (lt >> 1) & 1);
         tc_fence_after();
-        const int row = tc.m0 + quarter * 32 + lane;
+        const int row = tc.m0 + rank * BM + quarter * 32 + lane;
         const uint32_t tbase = tmem + (lt & 1) * kAccCols + ((uint32_t)(quarter * 32) << 16);
         AccSrc src{tbase, nullptr, quarter * 32 + lane, 1, 0};
         int c_begin = 0, c_end = BN;   // the output columns of the tile this CTA's epilogue covers
@@ -411,7 +507,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             // a K slice of a split tile (this CTA's last unit): the accumulator goes to the scratch area as it is; then
             // wait for the tile's other slices and take this slice's share of the columns
             constexpr size_t kSlice = (size_t)BM * kAccCols;
-            float* mine = p.split_ws + (size_t)un.tail * kSlice;
+            const int tt = (un.tail / us.splits) * CG + rank;   // this CTA's half of the split tile is a tile of its own here
+            float* mine = p.split_ws + ((size_t)tt * us.splits + un.slice) * kSlice;
 #pragma unroll 1
             for (int c0 = 0; c0 < (int)kAccCols; c0 += 32) {
                 uint32_t acc[32];
@@ -422,7 +519,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                         make_uint4(acc[4 * j4], acc[4 * j4 + 1], acc[4 * j4 + 2], acc[4 * j4 + 3]);
             }
             tc_fence_before();
-            mbar_arrive(acc_empty + (lt & 1) * 8);
+            acc_drained(lt & 1);
             __threadfence();
             fence_proxy_async_global();   // the slices are read back by bulk copies (async proxy)
             asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps: every row of the slice is out
@@ -430,7 +527,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const int gcols = EPI == GEMM_EPI_QKV ? p.head_dim : 32, n_g = BN / gcols;
             c_begin = (un.slice * n_g / us.splits) * gcols;
             c_end = ((un.slice + 1) * n_g / us.splits) * gcols;
-            const int tt = un.tail / us.splits;
             if (threadIdx.x == 64) {
                 unsigned* arrived = p.split_tickets + 2 * tt;
                 atomicAdd(arrived, 1u);
@@ -538,11 +634,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         }  // generic epilogues
         if (un.tail < 0) {
             tc_fence_before();
-            mbar_arrive(acc_empty + (lt & 1) * 8);   // this accumulator may be overwritten (by the tile after next)
+            acc_drained(lt & 1);   // this accumulator may be overwritten (by the tile after next)
         } else {
             asm volatile("bar.sync 1, 128;" ::: "memory");   // this CTA has read what it needs of the tile's slices
             if (threadIdx.x == 64) {
-                unsigned* t = p.split_tickets + 2 * (un.tail / us.splits);
+                unsigned* t = p.split_tickets + 2 * ((un.tail / us.splits) * CG + rank);
                 if (atomicAdd(t + 1, 1u) == (unsigned)us.splits - 1) {   // the last CTA to leave the tile: tickets back to zero
                     t[0] = 0u;
                     t[1] = 0u;
@@ -551,10 +647,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         }
         }  // tiles
     }
-    __syncthreads();
+    tc_fence_before();
+    if (CG == 2) cluster_sync_pair();   // the leader's MMAs read the partner's shared memory until the very end
+    else __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols));
+        if (CG == 2) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols));
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kTmemCols));
     }
 }
 
@@ -1005,27 +1104,57 @@ bool gemm_split_enabled() {
     return !(env && env[0] == '0');
 }
 
-template <int EPI, int BN>
+bool gemm_pair_enabled() {
+    const char* env = getenv("DLLM_GEMM_CG2");   // "0": one CTA per tile everywhere (A/B measurements, tests)
+    return !(env && env[0] == '0');
+}
+
+// CG = 2: CTA pairs (clusters of 2) on 256-row tiles; the tensor maps of the weights then have boxes of BN / 2 rows.
+template <int EPI, int BN, int CG>
 cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& b2, const CUtensorMap& b3, const GemmTcParams& p,
                        cudaStream_t st) {
-    constexpr int stage = kTileBytes + BN * BK * 2 * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
+    constexpr int stage = kTileBytes + (BN / CG) * BK * 2 * (EPI == GEMM_EPI_SWIGLU ? 2 : 1);
     const size_t smem = (size_t)gemm_stages(stage) * stage + 1024;
     static PerDeviceOnce attr_once;
     if (attr_once.need()) {
-        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(gemm_tc_kernel<EPI, BN, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
     }
     int tiles = (p.N + BN - 1) / BN;
     if (EPI != GEMM_EPI_SWIGLU) tiles += (p.n_more[0] + BN - 1) / BN + (p.n_more[1] + BN - 1) / BN;
-    const int tiles_m = (p.M + BM - 1) / BM, n_tiles = tiles * tiles_m;
-    const int n_sm = sm_count();
+    const int tiles_m = (p.M + BM * CG - 1) / (BM * CG), n_tiles = tiles * tiles_m;
+    // how many CTAs (CG = 2: pairs, each on one TPC) run at once
+    int n_slots = sm_count() / CG;
+    if (CG == 2) {
+        static int pairs[64] = {0};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && !pairs[dev]) {
+            cudaLaunchConfig_t q{};
+            q.gridDim = dim3(2 * n_slots);
+            q.blockDim = dim3(kGemmThreads);
+            q.dynamicSmemBytes = smem;
+            cudaLaunchAttribute qa[1];
+            qa[0].id = cudaLaunchAttributeClusterDimension;
+            qa[0].val.clusterDim.x = 2; qa[0].val.clusterDim.y = 1; qa[0].val.clusterDim.z = 1;
+            q.attrs = qa;
+            q.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, gemm_tc_kernel<EPI, BN, CG>, &q) != cudaSuccess || n <= 0) {
+                cudaGetLastError();
+                return cudaErrorNotSupported;
+            }
+            pairs[dev] = n;
+        }
+        if (dev >= 0 && dev < 64 && pairs[dev] > 0 && pairs[dev] < n_slots) n_slots = pairs[dev];
+    }
     // the last, partly filled wave is cut along K (see UnitSched)
     constexpr size_t kSliceBytes = (size_t)BM * (EPI == GEMM_EPI_SWIGLU ? 256 : BN) * 4;
     const int num_kb = (p.K + BK - 1) / BK;
     UnitSched us{n_tiles, n_tiles, 1, num_kb};
-    const int rem = n_tiles % n_sm;
-    if (p.split_ws && p.split_tickets && rem > 0 && 2 * rem <= kGemmSplitTickets && gemm_split_enabled()) {
-        int s = n_sm / rem;
+    const int rem = n_tiles % n_slots;
+    if (p.split_ws && p.split_tickets && rem > 0 && 2 * rem * CG <= kGemmSplitTickets && gemm_split_enabled()) {
+        int s = n_slots / rem;
         if (s > num_kb / 4) s = num_kb / 4;   // a slice keeps at least four k-blocks
         if (s > 8) s = 8;
         // a CTA's share of the tile (its column groups x every slice) must fit the operand ring as 16 KB blocks
@@ -1035,37 +1164,47 @@ cudaError_t launch_epi(const CUtensorMap& a, const CUtensorMap& b, const CUtenso
             const int kb_per = (num_kb + s - 1) / s;
             if ((num_kb + kb_per - 1) / kb_per != s) continue;   // would leave an empty slice
             if (((n_g + s - 1) / s) * blocks_per_group * s > kRedBlocks) continue;
-            if ((size_t)rem * s * kSliceBytes > p.split_ws_bytes) continue;
+            if ((size_t)rem * s * CG * kSliceBytes > p.split_ws_bytes) continue;
             us.whole = n_tiles - rem; us.splits = s; us.kb_per = kb_per;
             us.n_units = us.whole + rem * s;
             break;
         }
     }
-    const int grid = us.n_units < n_sm ? us.n_units : n_sm;
-    if (us.splits > 1) {
-        // the slices of a tile wait for each other: all CTAs must be resident together
+    const int tm = tiles_m;
+    for (int attempt = 0; attempt < 2; ++attempt) {
         cudaLaunchConfig_t cfg{};
-        cfg.gridDim = dim3(grid);
+        cfg.gridDim = dim3(CG * (us.n_units < n_slots ? us.n_units : n_slots));
         cfg.blockDim = dim3(kGemmThreads);
         cfg.dynamicSmemBytes = smem;
         cfg.stream = st;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeCooperative;
-        attr[0].val.cooperative = 1;
+        cudaLaunchAttribute attr[3];
+        int na = 0;
+        if (CG == 2) {
+            attr[na].id = cudaLaunchAttributeClusterDimension;
+            attr[na].val.clusterDim.x = 2; attr[na].val.clusterDim.y = 1; attr[na].val.clusterDim.z = 1;
+            ++na;
+        }
+        if (us.splits > 1) {   // the slices of a tile wait for each other: all CTAs must be resident together
+            attr[na].id = cudaLaunchAttributeCooperative;
+            attr[na].val.cooperative = 1;
+            ++na;
+        } else if (pdl_enabled()) {
+            attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[na].val.programmaticStreamSerializationAllowed = 1;
+            ++na;
+        }
         cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        const int tm = tiles_m;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, BN>, a, b, b2, b3, p, us, tm);
+        cfg.numAttrs = na;
+        const cudaError_t e = cudaLaunchKernelEx(&cfg, gemm_tc_kernel<EPI, BN, CG>, a, b, b2, b3, p, us, tm);
         if (e == cudaSuccess) {
             count_launch();
             return e;
         }
+        if (us.splits == 1) return e;
         cudaGetLastError();   // cannot be co-resident here: whole tiles
         us = UnitSched{n_tiles, n_tiles, 1, num_kb};
     }
-    const cudaError_t le = launch_pdl(gemm_tc_kernel<EPI, BN>, dim3(n_tiles < n_sm ? n_tiles : n_sm), dim3(kGemmThreads), smem, st, a, b, b2, b3, p, us, tiles_m);
-    count_launch();
-    return le;
+    return cudaErrorUnknown;
 }
 
 // 256-wide tiles once they still give every SM a tile (and the shape has full 256-column tiles to give); with the scratch
@@ -1180,21 +1319,40 @@ cudaError_t launch_gemm_tc(const GemmTcParams& p, cudaStream_t st) {
     CUtensorMap a, b, b2, b3;
     int bn = wide_tiles(p) ? 256 : (narrow_tiles(p) ? 64 : 128);
     if (p.epi == GEMM_EPI_QKV && bn < p.head_dim) bn = 128;   // a tile holds whole heads
-    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, bn)) return cudaErrorNotSupported;
+    // CTA pairs on 256-row tiles: full-width tiles (256, or the dual 128 + 128), more than one 128-row tile of rows
+    const bool dual = p.epi == GEMM_EPI_SWIGLU;
+    // (measured: +5 % at 4096 rows -- 1.34 against 1.27 PFLOP/s on 4096 x 4096 x 14336 -- nothing at 512 rows, where the
+    // kernels are all prologue and tail; DLLM_GEMM_CG2=1 forces pairs from 129 rows on, for the tests)
+    const char* pair_env = getenv("DLLM_GEMM_CG2");
+    const int pair_min_rows = pair_env && pair_env[0] == '1' ? BM + 1 : 1024;
+    const bool pair = gemm_pair_enabled() && p.M >= pair_min_rows && (dual ? p.N % 128 == 0 : bn == 256);
+    const int box = pair ? (dual ? 64 : 128) : (dual ? BM : bn);   // weight rows one CTA loads per tile
+    if (!make_map(&a, p.a, p.M, p.K) || !make_map(&b, p.w, p.N, p.K, box)) return cudaErrorNotSupported;
     b2 = b3 = b;
-    if (p.epi == GEMM_EPI_SWIGLU) {
-        if (!make_map(&b2, p.w2, p.N, p.K)) return cudaErrorNotSupported;
+    if (dual) {
+        if (!make_map(&b2, p.w2, p.N, p.K, box)) return cudaErrorNotSupported;
     } else {
-        if (p.n_more[0] > 0 && !make_map(&b2, p.w_more[0], p.n_more[0], p.K, bn)) return cudaErrorNotSupported;
-        if (p.n_more[1] > 0 && !make_map(&b3, p.w_more[1], p.n_more[1], p.K, bn)) return cudaErrorNotSupported;
+        if (p.n_more[0] > 0 && !make_map(&b2, p.w_more[0], p.n_more[0], p.K, box)) return cudaErrorNotSupported;
+        if (p.n_more[1] > 0 && !make_map(&b3, p.w_more[1], p.n_more[1], p.K, box)) return cudaErrorNotSupported;
+    }
+    if (pair) {
+        cudaError_t e = cudaErrorNotSupported;
+        switch (p.epi) {
+            case GEMM_EPI_BIAS: e = launch_epi<GEMM_EPI_BIAS, 256, 2>(a, b, b2, b3, p, st); break;
+            case GEMM_EPI_RESIDUAL: e = launch_epi<GEMM_EPI_RESIDUAL, 256, 2>(a, b, b2, b3, p, st); break;
+            case GEMM_EPI_SWIGLU: e = launch_epi<GEMM_EPI_SWIGLU, 128, 2>(a, b, b2, b3, p, st); break;
+            case GEMM_EPI_GELU: e = launch_epi<GEMM_EPI_GELU, 256, 2>(a, b, b2, b3, p, st); break;
+            case GEMM_EPI_QKV: e = launch_epi<GEMM_EPI_QKV, 256, 2>(a, b, b2, b3, p, st); break;
+        }
+        return e;
     }
 #define DLLM_GEMM_BY_BN(E)                                                                        \
-    (bn == 256 ? launch_epi<E, 256>(a, b, b2, b3, p, st)                                          \
-               : (bn == 64 ? launch_epi<E, 64>(a, b, b2, b3, p, st) : launch_epi<E, 128>(a, b, b2, b3, p, st)))
+    (bn == 256 ? launch_epi<E, 256, 1>(a, b, b2, b3, p, st)                                       \
+               : (bn == 64 ? launch_epi<E, 64, 1>(a, b, b2, b3, p, st) : launch_epi<E, 128, 1>(a, b, b2, b3, p, st)))
     switch (p.epi) {
         case GEMM_EPI_BIAS: return DLLM_GEMM_BY_BN(GEMM_EPI_BIAS);
         case GEMM_EPI_RESIDUAL: return DLLM_GEMM_BY_BN(GEMM_EPI_RESIDUAL);
-        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU, 128>(a, b, b2, b3, p, st);
+        case GEMM_EPI_SWIGLU: return launch_epi<GEMM_EPI_SWIGLU, 128, 1>(a, b, b2, b3, p, st);
         case GEMM_EPI_GELU: return DLLM_GEMM_BY_BN(GEMM_EPI_GELU);
         case GEMM_EPI_QKV: return DLLM_GEMM_BY_BN(GEMM_EPI_QKV);
     }
