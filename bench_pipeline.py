@@ -46,8 +46,10 @@ def run_pipeline(args) -> int:
     attn_cost = 2.0 * (2 * d_ * H_ * hd_ + 2 * d_ * KV_ * hd_)
     mlp_cost = 2.0 * 3 * d_ * hf["intermediate_size"]
     head_cost = stage_bytes_per_step(hf, 0, True, 1, 0.0)
-    from src.model.shard_manager import block_partition
-    stages_blocks = block_partition(L, world, attn_cost, mlp_cost, head_cost)
+    from src.model.shard_manager import block_partition, decode_block_times
+    # balanced on estimated decode-step TIME per block (streamed bytes + the serial latency of the block's phases), not bytes
+    t_attn, t_mlp, t_head, t_first = decode_block_times(hf, batch, prompt_len)
+    stages_blocks = block_partition(L, world, t_attn, t_mlp, t_head, t_first)
     blocks = stages_blocks[rank]
     block_w = {"full": 1.0, "attn": attn_cost / (attn_cost + mlp_cost), "mlp": mlp_cost / (attn_cost + mlp_cost)}
     layers_eq = [sum(block_w[b] for _, b in st) for st in stages_blocks]   # stage sizes in layer equivalents

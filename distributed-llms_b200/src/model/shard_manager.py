@@ -60,12 +60,36 @@ def balanced_partition(n_layers: int, num_shards: int, head_cost_layers: float) 
     return head + [range(n_layers - last, n_layers)]
 
 
-def block_partition(n_layers: int, num_shards: int, attn_cost: float, mlp_cost: float, head_cost: float = 0.0
-                    ) -> List[List[tuple]]:
+def decode_block_times(config: dict, batch: int = 1, context: int = 512) -> tuple:
+    """Estimated time (us) one decode step spends in a layer's attention block, its MLP block, the final norm + lm_head
+    and the first stage's extras (embedding phase, ticket wait) inside the persistent decode kernel on a B200: the bytes
+    the block streams at the rate the weight loops reach, plus the serial latency of its phases -- barrier, prologue,
+    epilogue; the attention phase streams no weights at all.  The constants are read off the per-phase trace of Llama-3-8B
+    at batch 1 (profiles/r2_phase_trace_llama8b_summary.txt: weight loops 6.5-7.0 TB/s; QKV 5.5, attention 7.3, o-proj
+    6.0, gate/up 5.7, down 4.4, head 6.5, embedding 12 us outside the loops).  By bytes alone an attention block is
+    0.19 of a layer; by time it is 0.35 -- partitions balanced on bytes leave the stages that end in an MLP block slowest."""
+    d = config["hidden_size"] if "hidden_size" in config else config["n_embd"]
+    H = config.get("num_attention_heads", config.get("n_head"))
+    KV = config.get("num_key_value_heads", H)
+    hd = config.get("head_dim") or d // H
+    ffn = config.get("intermediate_size") or config.get("n_inner") or 4 * d
+    gated = config.get("model_type") != "gpt2"
+    rate = 6.8e6                                  # bytes per microsecond
+    qkv, o = 2.0 * d * (H + 2 * KV) * hd, 2.0 * H * hd * d
+    kv = 2.0 * batch * context * 2 * KV * hd
+    up, down = 2.0 * d * ffn * (2 if gated else 1), 2.0 * ffn * d
+    attn = (qkv + o + kv) / rate + 5.5 + 7.3 + 6.0
+    mlp = (up + down) / rate + 5.7 + 4.4
+    head = 2.0 * config["vocab_size"] * d / rate + 6.5
+    return attn, mlp, head, 12.0
+
+
+def block_partition(n_layers: int, num_shards: int, attn_cost: float, mlp_cost: float, head_cost: float = 0.0,
+                    first_cost: float = 0.0) -> List[List[tuple]]:
     """Stages as contiguous runs of BLOCKS -- (layer, "attn"), (layer, "mlp") -- so that a boundary may fall inside a
-    layer (the residual row is the hand-off either way).  Costs are the bytes a decode step streams for one block
-    (`head_cost` rides on the last stage); the split minimises the most expensive stage.  Returns per stage a list of
-    (layer, "full" | "attn" | "mlp")."""
+    layer (the residual row is the hand-off either way).  Costs are what a decode step spends on one block (bytes, or
+    better `decode_block_times`); `head_cost` rides on the last stage, `first_cost` on the first; the split minimises
+    the most expensive stage.  Returns per stage a list of (layer, "full" | "attn" | "mlp")."""
     units = []
     for i in range(n_layers):
         units += [(i, "attn", attn_cost), (i, "mlp", mlp_cost)]
@@ -83,7 +107,7 @@ def block_partition(n_layers: int, num_shards: int, attn_cost: float, mlp_cost: 
     for s_ in range(1, num_shards + 1):
         for j in range(s_, n + 1):
             for i in range(s_ - 1, j):
-                cost = prefix[j] - prefix[i] + (head_cost if (s_ == num_shards and j == n) else 0.0)
+                cost = prefix[j] - prefix[i] + (head_cost if (s_ == num_shards and j == n) else 0.0) + (first_cost if s_ == 1 else 0.0)
                 v = max(best[s_ - 1][i], cost)
                 if v < best[s_][j] - 1e-12:
                     best[s_][j], cut[s_][j] = v, i

@@ -311,3 +311,36 @@ def test_shard_manager_reads_multi_file_checkpoints_and_can_skip_the_rewrite(tmp
     assert os.path.exists(os.path.join(out, "config.json")) and not any(f.endswith(".pt") for f in os.listdir(out))
     assert m.shard_manager.num_shards == 2 and len(m.shard_manager.get_shard_paths()) == 2
 
+
+def test_block_partition_cuts_inside_layers_and_balances_the_heaviest_stage():
+    """Stages are contiguous runs of attention | MLP blocks: every block exactly once and in order, a boundary may fall
+    inside a layer, the lm_head weighs on the last stage and the embedding phase on the first, and no other contiguous
+    split has a cheaper heaviest stage (checked by brute force on a small case)."""
+    import itertools
+    from src.model import random_init
+    from src.model.shard_manager import block_partition, decode_block_times
+    a, m, h, f = decode_block_times(random_init.NAMED_CONFIGS["llama3-8b"], 1, 512)
+    assert 0.3 < a / (a + m) < 0.4 and h > a + m          # by time an attention block is a third of a layer, not 0.19
+    for n_layers, n_stages in ((32, 8), (32, 4), (6, 4), (5, 3)):
+        stages = block_partition(n_layers, n_stages, a, m, h, f)
+        flat = []
+        for st in stages:
+            for layer, blk in st:
+                flat += [(layer, "attn"), (layer, "mlp")] if blk == "full" else [(layer, blk)]
+        assert flat == [(i, b) for i in range(n_layers) for b in ("attn", "mlp")]
+        assert all(st for st in stages)
+    w = {"attn": a, "mlp": m}
+    units = [(i, b) for i in range(5) for b in ("attn", "mlp")]
+
+    def heaviest(bounds):
+        cuts = [0, *bounds, len(units)]
+        t = [sum(w[b] for _, b in units[x:y]) for x, y in zip(cuts[:-1], cuts[1:])]
+        t[0] += f
+        t[-1] += h
+        return max(t)
+    best = min(heaviest(c) for c in itertools.combinations(range(1, len(units)), 2))
+    got = block_partition(5, 3, a, m, h, f)
+    sizes = [sum(2 if blk == "full" else 1 for _, blk in st) for st in got]
+    assert abs(heaviest([sizes[0], sizes[0] + sizes[1]]) - best) < 1e-9
+    assert any(blk != "full" for st in block_partition(32, 8, a, m, h, f) for _, blk in st)   # it does cut inside layers
+
