@@ -47,9 +47,9 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
     // `red2`: two buffers of kWarps floats used alternately by successive block reductions, so that one __syncthreads per
     // reduction is enough (a buffer is rewritten two reductions later, with the barrier of the one in between in between)
     const int R = p.n_rows;
-    const int tpr = R == 1 ? 256 : (R == 2 ? 128 : (R <= 4 ? 64 : 32));
-    const int rows_par = kThreads / tpr, wpr = tpr >> 5;
-    const int sub = threadIdx.x / tpr, lt = threadIdx.x - sub * tpr;
+    const int tshift = R == 1 ? 8 : (R == 2 ? 7 : (R <= 4 ? 6 : 5)), tpr = 1 << tshift;   // threads per row: 256 / 128 / 64 / 32
+    const int rows_par = kThreads >> tshift, wpr = tpr >> 5;
+    const int sub = threadIdx.x >> tshift, lt = threadIdx.x & (tpr - 1);
     const int warp = threadIdx.x >> 5;
     const int stride = tpr * 8;
     const uint4 z = make_uint4(0u, 0u, 0u, 0u);
@@ -191,6 +191,7 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
 
 
 __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCache& sc, const int* sbt, const MkLayer& L, const AttnSmem& sm, bool prefetched,
+                                                const UnitId& my_unit,
                                                 long long* tr = nullptr) {
     __shared__ int s_attn_last;
     const int hd = p.head_dim, H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
@@ -199,7 +200,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
     const int n_units = p.n_rows * KV * S;
     bool first = true;
     for (int u = blockIdx.x; u < n_units; u += gridDim.x, first = false) {
-        const AttnUnit a = attn_unit(p, sc, u);
+        const AttnUnit a = attn_unit(p, sc, first ? my_unit : unit_id(p, u));
         if (a.t0 >= a.t1) continue;  // split past the end of the context: the merge never reads it
         // Tensor-core unit: the Gq query heads of the KV head are the (zero-padded) 16 rows of mma.sync.m16n8k16; of a
         // 64-token tile, warp w < 4 takes tokens 16 w .. 16 w + 15 and keeps its own online-softmax state (m, l) and
@@ -523,7 +524,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
         issue_stage(c, prod, i);
         witer_next(c, prod);
     }
-    unsigned consumed = 0;  // stages this warp has consumed so far -> ring slot and mbarrier parity
+    unsigned ring_slot = 0, ring_parity = 0;  // the ring slot this warp consumes next and its mbarrier parity (kept incrementally: no divisions in the loop)
     unsigned bar_target = 0;
     bool need_barrier = false;
     int kv_prefetch_layer = -1;  // >= 0: prefetch this layer's old K/V rows for the attention phase at the next barrier
@@ -532,6 +533,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     const uint32_t xrow_hi = smem_u32(xs) + (uint32_t)(min(g + 8, R - 1) * ldx * 2);
 
     const bool piped = p.in_flag != nullptr;  // fused hand-off: inputs arrive in / outputs leave through mailboxes
+    const UnitId my_unit = unit_id(p, blockIdx.x);   // this CTA's first attention unit
     bool ticket_ok = true;
     for (int step = 0; step < p.n_steps; ++step) {
         // micro-batch of this step and its decode step inside the launch (classic mode: m = 0, gstep = step)
@@ -553,7 +555,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     // (rows no CTA writes in this step -- independent of the barrier)
                     const MkLayer& PL = p.layers[kv_prefetch_layer];
                     kv_prefetch_layer = -1;
-                    const AttnUnit a = attn_unit(p, sc, blockIdx.x);
+                    const AttnUnit a = attn_unit(p, sc, my_unit);
                     const int tend = min(a.t1, a.t0 + kTT);
                     const int upto = max(a.t0, min(tend, attn_safe_end(sc, a)));
                     if (upto > a.t0) {
@@ -629,7 +631,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 continue;
             }
             if (ph.kind == MK_ATTN) {
-                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true, tr);
+                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true, my_unit, tr);
                 if (tr) tr[1] = tr[2] = tr[3] = clock64();
                 continue;
             }
@@ -652,7 +654,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
 
             // ---- main: this warp's (panel slot, k-split) units on the tensor cores ----
             const int K = ph.K, ns = ph.n_stages;
-            const int n_local = local_panels(ph);
+            const int n_local = s_units[phi];
             // the epilogue of the residual phases needs the old residual: fetch this thread's first pair now,
             // so that the L2 round trip overlaps the main loop
             uint32_t old_pref = 0u;
@@ -683,10 +685,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 float acc[4] = {0.f, 0.f, 0.f, 0.f}, acc1[4] = {0.f, 0.f, 0.f, 0.f};
                 float acc2[4] = {0.f, 0.f, 0.f, 0.f}, acc3[4] = {0.f, 0.f, 0.f, 0.f};
                 for (; x < seg_end; ++x, ++st) {
-                    const unsigned slot = consumed % (unsigned)p.stages;
+                    const unsigned slot = ring_slot;
                     long long tq0 = 0, tq1 = 0, tq2 = 0;
                     if (tr) tq0 = clock64();
-                    mbar_wait(c.full + slot * 8, (consumed / (unsigned)p.stages) & 1u);
+                    mbar_wait(c.full + slot * 8, ring_parity);
                     if (tr) tq1 = clock64();
                     const uint32_t sbase = c.ring + slot * kStageBytes + (uint32_t)(lane * 16);  // [32-k block][row g][chunk t4]
                     const int stage_k = ph.xg ? kStageK / 2 : kStageK;
@@ -729,7 +731,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     }
                     __syncwarp();
                     if (tr) tq2 = clock64();
-                    ++consumed;
+                    if (++ring_slot == (unsigned)p.stages) {
+                        ring_slot = 0;
+                        ring_parity ^= 1u;
+                    }
                     if (prod.step < p.n_steps) {  // refill the slot with the next stage of this warp's sequence
                         issue_stage(c, prod, (int)slot);
                         witer_next(c, prod);

@@ -366,12 +366,25 @@ struct AttnUnit {
     int r, kvh, split, seq, t0, t1;
 };
 
-__device__ __forceinline__ AttnUnit attn_unit(const MkParams& p, const StepCache& sc, int u) {
-    AttnUnit a;
+// (row, KV head, split) of unit u: fixed for the whole launch -- a CTA works its first unit's out once (UnitId) and only
+// the token range, which moves with the positions, is recomputed per step
+struct UnitId {
+    int r, kvh, split;
+};
+__device__ __forceinline__ UnitId unit_id(const MkParams& p, int u) {
     const int S = p.n_splits, KV = p.n_kv_heads;
-    a.r = u / (KV * S);
-    a.kvh = (u / S) % KV;
-    a.split = u % S;
+    UnitId id;
+    id.r = u / (KV * S);
+    id.kvh = (u / S) % KV;
+    id.split = u % S;
+    return id;
+}
+__device__ __forceinline__ AttnUnit attn_unit(const MkParams& p, const StepCache& sc, const UnitId& id) {
+    AttnUnit a;
+    const int S = p.n_splits;
+    a.r = id.r;
+    a.kvh = id.kvh;
+    a.split = id.split;
     const int len = sc.pos[a.r] + 1;
     a.seq = sc.seq[a.r];
     int chunk = (len + S - 1) / S;
