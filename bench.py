@@ -299,6 +299,23 @@ def run_single(args) -> int:
     torch.cuda.synchronize()
     prefill_ms = e0.elapsed_time(e1)
 
+    # ---- token check: the device-resident loop and the token-by-token host path must generate the same ids from the
+    # same prefill (a timing of a kernel that computes something else is worthless); the bench exits 3 otherwise ----
+    V = 8
+    first_tok = out["next_token"]
+    loop_ids = shard.decode_loop(batch, V).cpu()
+    shard.reset()
+    nt = shard.compute({"input_ids": prompts})["next_token"]
+    step_ids = []
+    for _ in range(V):
+        nt = shard.compute({"input_ids": nt[:, None]})["next_token"]
+        step_ids.append(nt.cpu())
+    tokens_checked = bool(torch.equal(loop_ids.to(torch.int64), torch.stack(step_ids, 1).to(torch.int64)))
+    shard.reset()
+    out = shard.compute({"input_ids": prompts})
+    assert torch.equal(out["next_token"].cpu(), first_tok.cpu())
+    torch.cuda.synchronize()
+
     # ---- decode, device-resident (value) ----
     shard.decode_loop(batch, W)
     torch.cuda.synchronize()
@@ -381,6 +398,7 @@ def run_single(args) -> int:
                             "(by the kernel, in place: dllm_shard_forward adds no copy nodes for pinned int32 buffers); the host "
                             "synchronises the stream and feeds the id back"},
         "gpu_launches": int(launches),
+        "tokens_checked": tokens_checked,
         "clocks": clocks,
         "roofline": roofline,
         "cpu_baseline": cpu,
@@ -389,7 +407,7 @@ def run_single(args) -> int:
                     "note": "persistent tcgen05/TMA GEMMs for the projections (rotary + KV append in the q|k|v epilogue, K-split tails), TMA + tcgen05 flash-style causal attention over the paged cache"},
     }
     print(json.dumps(line))
-    return 0
+    return 0 if tokens_checked else 3
 
 
 def main() -> int:
