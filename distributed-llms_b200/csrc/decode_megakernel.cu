@@ -40,13 +40,13 @@ using namespace mkd;
 
 // (not inlined: it has five call sites, and the kernel's code size is what the instruction caches feel -- 15.7 k -> 12.2 k
 // SASS instructions, +1 % tokens/s; TR: per-phase time stamps compiled in)
-template <bool TR>
+template <bool TR, int RK>   // RK = 1: the launch has exactly one row (the row loops and row masks fold away)
 __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int K, int norm, const void* nw, const void* nb,
                                         bf16* xs, int ldx, float* red2, unsigned& red_flip, long long* tr_in = nullptr) {
     long long* const tr = TR ? tr_in : nullptr;
     // `red2`: two buffers of kWarps floats used alternately by successive block reductions, so that one __syncthreads per
     // reduction is enough (a buffer is rewritten two reductions later, with the barrier of the one in between in between)
-    const int R = p.n_rows;
+    const int R = RK == 1 ? 1 : p.n_rows;
     const int tshift = R == 1 ? 8 : (R == 2 ? 7 : (R <= 4 ? 6 : 5)), tpr = 1 << tshift;   // threads per row: 256 / 128 / 64 / 32
     const int rows_par = kThreads >> tshift, wpr = tpr >> 5;
     const int sub = threadIdx.x >> tshift, lt = threadIdx.x & (tpr - 1);
@@ -437,7 +437,8 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 // ---- the kernel ----------------------------------------------------------------------------------------
 
 
-template <bool HI, bool TR>  // HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps compiled in
+template <bool HI, bool TR, int RK>  // HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
+                                      // compiled in; RK = 1: one row (batch 1 -- R and RP are the constant 1), 0: any
 __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
     const int ldx = p.k_max + 8;  // padded row stride of xs: rows land in different banks
@@ -483,9 +484,10 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t4 = lane & 3;  // mma fragment coordinates
-    const int R = p.n_rows;
+    const int R = RK == 1 ? 1 : p.n_rows;
     int RP = 1;
-    while (RP < R) RP <<= 1;
+    if (RK != 1)
+        while (RP < R) RP <<= 1;
     for (int i = threadIdx.x; i < p.n_phases * (int)(sizeof(MkPhase) / 4); i += kThreads)
         reinterpret_cast<uint32_t*>(phases)[i] = reinterpret_cast<const uint32_t*>(p.phases)[i];
     for (int i = threadIdx.x; i < p.n_phases; i += kThreads) {
@@ -647,7 +649,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 else if (ph.kind == MK_HEAD) { nw = p.final_norm_w; nb = p.final_norm_b; }
                 else if (ph.kind == MK_DOWN) { rows = p.act; nk = NORM_NONE; stage = !ph.xg; }
                 else { rows = p.attn_out; nk = NORM_NONE; }   // o-proj: merged attention rows
-                if (stage) stage_rows<TR>(p, rows, ph.K, nk, nw, nb, xs, ldx, red, red_flip, tr);
+                if (stage) stage_rows<TR, RK>(p, rows, ph.K, nk, nw, nb, xs, ldx, red, red_flip, tr);
             }
             __syncthreads();
             if (tr) tr[1] = clock64();
@@ -1023,9 +1025,9 @@ static int mk_pick_stages(const MkParams& p) {
     return 0;
 }
 
-template <bool HI, bool TR>
+template <bool HI, bool TR, int RK>
 static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
@@ -1037,7 +1039,7 @@ static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStr
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR>, p);
+    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK>, p);
     count_launch();
     return e;
 }
@@ -1050,8 +1052,9 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
     p.stages = mk_pick_stages(p);
     if (p.stages == 0) return cudaErrorInvalidValue;
     const size_t smem = mk_smem_bytes(p, p.stages);
-    if (p.trace) return p.n_rows > 8 ? mk_launch_t<true, true>(p, num_sms, smem, st) : mk_launch_t<false, true>(p, num_sms, smem, st);
-    return p.n_rows > 8 ? mk_launch_t<true, false>(p, num_sms, smem, st) : mk_launch_t<false, false>(p, num_sms, smem, st);
+    if (p.n_rows > 8) return mk_launch_t<true, false, 0>(p, num_sms, smem, st);   // (no time stamps in this variant)
+    if (p.n_rows == 1) return p.trace ? mk_launch_t<false, true, 1>(p, num_sms, smem, st) : mk_launch_t<false, false, 1>(p, num_sms, smem, st);
+    return p.trace ? mk_launch_t<false, true, 0>(p, num_sms, smem, st) : mk_launch_t<false, false, 0>(p, num_sms, smem, st);
 }
 
 int mk_max_splits(int n_rows, int n_heads, int head_dim) {
