@@ -40,7 +40,8 @@ using namespace mkd;
 
 // (not inlined: it has five call sites, and the kernel's code size is what the instruction caches feel -- 15.7 k -> 12.2 k
 // SASS instructions, +1 % tokens/s; TR: per-phase time stamps compiled in)
-template <bool TR, int RK>   // RK = 1: the launch has exactly one row (the row loops and row masks fold away)
+template <bool TR, int RK, bool LL>   // RK = 1: the launch has exactly one row (the row loops and row masks fold away);
+                                       // LL: the model normalises with RMSNorm (no LayerNorm code)
 __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int K, int norm, const void* nw, const void* nb,
                                         bf16* xs, int ldx, float* red2, unsigned& red_flip, long long* tr_in = nullptr) {
     long long* const tr = TR ? tr_in : nullptr;
@@ -67,10 +68,10 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
             const bf16* bq = static_cast<const bf16*>(nb);
             const bool a0 = active && kb < K, a1 = active && k1 < K, a2 = active && k2 < K, a3 = active && k3 < K;
             uint4 v0 = z, v1 = z, v2 = z, v3 = z, w0 = z, w1 = z, w2 = z, w3 = z, b0 = z, b1 = z, b2 = z, b3 = z;
-            if (a0) { v0 = ldcg_u4(xr + kb); w0 = ld_u4(wq + kb); if (norm == NORM_LAYER) b0 = ld_u4(bq + kb); }
-            if (a1) { v1 = ldcg_u4(xr + k1); w1 = ld_u4(wq + k1); if (norm == NORM_LAYER) b1 = ld_u4(bq + k1); }
-            if (a2) { v2 = ldcg_u4(xr + k2); w2 = ld_u4(wq + k2); if (norm == NORM_LAYER) b2 = ld_u4(bq + k2); }
-            if (a3) { v3 = ldcg_u4(xr + k3); w3 = ld_u4(wq + k3); if (norm == NORM_LAYER) b3 = ld_u4(bq + k3); }
+            if (a0) { v0 = ldcg_u4(xr + kb); w0 = ld_u4(wq + kb); if ((!LL && norm == NORM_LAYER)) b0 = ld_u4(bq + kb); }
+            if (a1) { v1 = ldcg_u4(xr + k1); w1 = ld_u4(wq + k1); if ((!LL && norm == NORM_LAYER)) b1 = ld_u4(bq + k1); }
+            if (a2) { v2 = ldcg_u4(xr + k2); w2 = ld_u4(wq + k2); if ((!LL && norm == NORM_LAYER)) b2 = ld_u4(bq + k2); }
+            if (a3) { v3 = ldcg_u4(xr + k3); w3 = ld_u4(wq + k3); if ((!LL && norm == NORM_LAYER)) b3 = ld_u4(bq + k3); }
             if (a0) accum_stats(v0, s1, s2);
             if (a1) accum_stats(v1, s1, s2);
             if (a2) accum_stats(v2, s1, s2);
@@ -90,7 +91,7 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
                 return a;
             };
             float mean = 0.f, rstd;
-            if (norm == NORM_RMS) {
+            if (LL || norm == NORM_RMS) {
                 rstd = 1.0f / sqrtf(group_sum(s2) / (float)K + p.eps);
             } else {
                 mean = group_sum(s1) / (float)K;
@@ -150,7 +151,7 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
             if (norm == NORM_RMS) rstd = 1.0f / sqrtf(a / (float)K + p.eps);  // HF LlamaRMSNorm: fp32 variance
             else mean = a / (float)K;
         }
-        if (norm == NORM_LAYER) {
+        if ((!LL && norm == NORM_LAYER)) {
             float sq = 0.f;
             if (active)
                 for (int k = lt * 8; k < K; k += stride) {
@@ -177,7 +178,7 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
             if (active) {
                 uint4 w0 = ld_u4(wp + kb), w1 = z, b0 = z, b1 = z;
                 if (k1 < K) w1 = ld_u4(wp + k1);
-                if (norm == NORM_LAYER) {
+                if ((!LL && norm == NORM_LAYER)) {
                     b0 = ld_u4(bp + kb);
                     if (k1 < K) b1 = ld_u4(bp + k1);
                 }
@@ -437,7 +438,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 // ---- the kernel ----------------------------------------------------------------------------------------
 
 
-template <bool HI, bool TR, int RK>  // HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
+template <bool HI, bool TR, int RK, bool LL>  // LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
                                       // compiled in; RK = 1: one row (batch 1 -- R and RP are the constant 1), 0: any
 __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -598,7 +599,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     const int r = i / p.pages_per_seq;
                     sbt[i] = p.block_table[(size_t)sc.seq[r] * p.pages_per_seq + (i - r * p.pages_per_seq)];
                 }
-                if (p.rope) {
+                if (LL || p.rope) {
                     const int half = p.head_dim >> 1;
                     for (int i = threadIdx.x; i < R * p.head_dim; i += kThreads) {
                         const int r = i / p.head_dim, e = i - r * p.head_dim;
@@ -619,7 +620,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     if (piped && v == 0) p.tok_ring[(size_t)step * R + r] = id;  // the ids this stage fed, step-major
                     id = min(max(id, 0), p.vocab - 1);
                     uint4 val = ld_u4(static_cast<const bf16*>(p.wte) + (size_t)id * p.hidden + v * 8);
-                    if (p.wpe) {
+                    if (!LL && p.wpe) {
                         float a[8], b[8];
                         unpack<bf16>(val, a);
                         unpack<bf16>(ld_u4(static_cast<const bf16*>(p.wpe) + (size_t)sc.pos[r] * p.hidden + v * 8), b);
@@ -642,14 +643,14 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             {   // one call site: which rows, which norm
                 const void* rows = h_m;
                 const void *nw = nullptr, *nb = nullptr;
-                int nk = p.norm;
+                int nk = LL ? (int)NORM_RMS : p.norm;
                 bool stage = true;
                 if (ph.kind == MK_QKV) { nw = L->norm1_w; nb = L->norm1_b; }
                 else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) { nw = L->norm2_w; nb = L->norm2_b; }
                 else if (ph.kind == MK_HEAD) { nw = p.final_norm_w; nb = p.final_norm_b; }
                 else if (ph.kind == MK_DOWN) { rows = p.act; nk = NORM_NONE; stage = !ph.xg; }
                 else { rows = p.attn_out; nk = NORM_NONE; }   // o-proj: merged attention rows
-                if (stage) stage_rows<TR, RK>(p, rows, ph.K, nk, nw, nb, xs, ldx, red, red_flip, tr);
+                if (stage) stage_rows<TR, RK, LL>(p, rows, ph.K, nk, nw, nb, xs, ldx, red, red_flip, tr);
             }
             __syncthreads();
             if (tr) tr[1] = clock64();
@@ -811,7 +812,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     const void* bias = m == 0 ? L->bq : (m == 1 ? L->bk : L->bv);
                     v0 = bf16_round(v0 + (bias ? ldf(bias, row0) : 0.f));
                     v1 = bf16_round(v1 + (bias ? ldf(bias, row0 + half) : 0.f));
-                    if (p.rope && m != 2) {
+                    if ((LL || p.rope) && m != 2) {
                         const float cs = bf16_round(srope[r * hd + jj]);
                         const float sn = bf16_round(srope[r * hd + half + jj]);
                         const float o0 = bf16_round(bf16_round(v0 * cs) + bf16_round(-v1 * sn));
@@ -840,7 +841,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     const int n = panel * 8 + 2 * i;  // rows n, n+1
                     if (n >= ph.n0) continue;
                     const bool valid1 = n + 1 < ph.n0;
-                    if (ph.kind == MK_FC_GELU) {
+                    if (!LL && ph.kind == MK_FC_GELU) {
                         bf16* y = static_cast<bf16*>(p.act) +
                                   (p.act_xlayout ? ((size_t)(n >> 5) * 8 + r) * 32 + (n & 31) : (size_t)r * ph.n0 + n);
                         y[0] = __float2bfloat16_rn(gelu_new_f(bf16_round(v0 + (L->b_up ? ldf(L->b_up, n) : 0.f))));
@@ -1025,9 +1026,9 @@ static int mk_pick_stages(const MkParams& p) {
     return 0;
 }
 
-template <bool HI, bool TR, int RK>
+template <bool HI, bool TR, int RK, bool LL>
 static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
@@ -1039,7 +1040,7 @@ static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStr
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK>, p);
+    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL>, p);
     count_launch();
     return e;
 }
@@ -1052,9 +1053,11 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
     p.stages = mk_pick_stages(p);
     if (p.stages == 0) return cudaErrorInvalidValue;
     const size_t smem = mk_smem_bytes(p, p.stages);
-    if (p.n_rows > 8) return mk_launch_t<true, false, 0>(p, num_sms, smem, st);   // (no time stamps in this variant)
-    if (p.n_rows == 1) return p.trace ? mk_launch_t<false, true, 1>(p, num_sms, smem, st) : mk_launch_t<false, false, 1>(p, num_sms, smem, st);
-    return p.trace ? mk_launch_t<false, true, 0>(p, num_sms, smem, st) : mk_launch_t<false, false, 0>(p, num_sms, smem, st);
+    const bool ll = p.norm == NORM_RMS && p.rope && p.wpe == nullptr;   // Llama / Qwen2 (GPT-2: LayerNorm, learned positions, gelu)
+    if (p.n_rows > 8) return mk_launch_t<true, false, 0, false>(p, num_sms, smem, st);   // (no time stamps in this variant)
+    if (p.trace) return p.n_rows == 1 ? mk_launch_t<false, true, 1, false>(p, num_sms, smem, st) : mk_launch_t<false, true, 0, false>(p, num_sms, smem, st);
+    if (p.n_rows == 1) return ll ? mk_launch_t<false, false, 1, true>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, false>(p, num_sms, smem, st);
+    return ll ? mk_launch_t<false, false, 0, true>(p, num_sms, smem, st) : mk_launch_t<false, false, 0, false>(p, num_sms, smem, st);
 }
 
 int mk_max_splits(int n_rows, int n_heads, int head_dim) {
