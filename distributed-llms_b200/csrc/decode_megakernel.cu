@@ -192,10 +192,10 @@ __device__ __noinline__ void stage_rows(const MkParams& p, const void* src, int 
 
 
 __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCache& sc, const int* sbt, const MkLayer& L, const AttnSmem& sm, bool prefetched,
-                                                const UnitId& my_unit,
+                                                const UnitId& my_unit, const int hd,
                                                 long long* tr = nullptr) {
     __shared__ int s_attn_last;
-    const int hd = p.head_dim, H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
+    const int H = p.n_heads, KV = p.n_kv_heads, S = p.n_splits, Gq = H / KV, ld = hd + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const float scale = rsqrtf((float)hd);
     const int n_units = p.n_rows * KV * S;
@@ -220,8 +220,8 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
                 // before them was being multiplied)
                 int from = tile0;
                 if (first && prefetched) from = max(tile0, min(tend, attn_safe_end(sc, a)));
-                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, true, false);
-                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, false, true);
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, true, false, hd);
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0, from, tend, false, true, hd);
                 // q of the Gq heads -> 16 bf16 rows in shared memory (rows past Gq zero): one 16-byte L2 load per
                 // thread, in flight together with the K/V copies above
                 const int vpr = hd >> 3;  // 16-byte vectors per row
@@ -253,7 +253,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
             __syncthreads();  // every warp is done with the K tile
             if (tr) tr[6] = clock64();  // scores done
             if (has_next) {  // the K buffer is free: request the next tile's K rows, then wait for this tile's V rows
-                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), true, false);
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), true, false, hd);
                 cp_async_wait_but_one();
             } else {
                 cp_async_wait_all();
@@ -316,7 +316,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
             }
             __syncthreads();  // the V buffer is free
             if (has_next)
-                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), false, true);
+                attn_load_rows(p, L, sm, sbt + a.r * p.pages_per_seq, a.kvh, tile0 + kTT, tile0 + kTT, min(a.t1, tile0 + 2 * kTT), false, true, hd);
             if (tr) tr[7] = clock64();  // softmax + P.V done
         }
         // merge the four token slices (fixed order) through shared memory: the K/V tile buffers are free now
@@ -438,7 +438,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 // ---- the kernel ----------------------------------------------------------------------------------------
 
 
-template <bool HI, bool TR, int RK, bool LL>  // LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
+template <bool HI, bool TR, int RK, bool LL, int HD>  // HD: head_dim as a compile-time constant (0: run-time); LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
                                       // compiled in; RK = 1: one row (batch 1 -- R and RP are the constant 1), 0: any
 __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -485,6 +485,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t4 = lane & 3;  // mma fragment coordinates
+    const int HDv = HD ? HD : p.head_dim;
     const int R = RK == 1 ? 1 : p.n_rows;
     int RP = 1;
     if (RK != 1)
@@ -562,8 +563,8 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     const int tend = min(a.t1, a.t0 + kTT);
                     const int upto = max(a.t0, min(tend, attn_safe_end(sc, a)));
                     if (upto > a.t0) {
-                        attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, true, false);
-                        attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, false, true);
+                        attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, true, false, HDv);
+                        attn_load_rows(p, PL, at, sbt + a.r * p.pages_per_seq, a.kvh, a.t0, a.t0, upto, false, true, HDv);
                     }
                 }
                 if (grid_barrier_wait(p.barrier, bar_target, tr, piped ? p.status : nullptr)) goto mk_aborted;
@@ -600,9 +601,9 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     sbt[i] = p.block_table[(size_t)sc.seq[r] * p.pages_per_seq + (i - r * p.pages_per_seq)];
                 }
                 if (LL || p.rope) {
-                    const int half = p.head_dim >> 1;
-                    for (int i = threadIdx.x; i < R * p.head_dim; i += kThreads) {
-                        const int r = i / p.head_dim, e = i - r * p.head_dim;
+                    const int half = HDv >> 1;
+                    for (int i = threadIdx.x; i < R * HDv; i += kThreads) {
+                        const int r = i / HDv, e = i - r * HDv;
                         const int ps = sc.pos[r];
                         srope[i] = e < half ? p.rope_cos[(size_t)ps * half + e] : p.rope_sin[(size_t)ps * half + e - half];
                     }
@@ -634,7 +635,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 continue;
             }
             if (ph.kind == MK_ATTN) {
-                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true, my_unit, tr);
+                attention_phase(p, sc, sbt, *L, at, /*prefetched=*/true, my_unit, HDv, tr);
                 if (tr) tr[1] = tr[2] = tr[3] = clock64();
                 continue;
             }
@@ -803,7 +804,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 const int panel = s_first[phi] + pstride * (base + pj);
                 if (tr && o == 0 && base == 0) tr[14] = clock64();  // thread 0's pieces summed
                 if (ph.kind == MK_QKV) {
-                    const int hd = p.head_dim, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
+                    const int hd = HDv, half = hd >> 1, H = p.n_heads, KV = p.n_kv_heads;
                     const int ppb = half >> 2;  // panels per head
                     const int head = panel / ppb, jj = (panel - head * ppb) * 4 + i;
                     const int m = head < H ? 0 : (head < H + KV ? 1 : 2);
@@ -1026,9 +1027,9 @@ static int mk_pick_stages(const MkParams& p) {
     return 0;
 }
 
-template <bool HI, bool TR, int RK, bool LL>
+template <bool HI, bool TR, int RK, bool LL, int HD>
 static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
@@ -1040,7 +1041,7 @@ static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStr
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL>, p);
+    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL, HD>, p);
     count_launch();
     return e;
 }
@@ -1054,10 +1055,17 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
     if (p.stages == 0) return cudaErrorInvalidValue;
     const size_t smem = mk_smem_bytes(p, p.stages);
     const bool ll = p.norm == NORM_RMS && p.rope && p.wpe == nullptr;   // Llama / Qwen2 (GPT-2: LayerNorm, learned positions, gelu)
-    if (p.n_rows > 8) return mk_launch_t<true, false, 0, false>(p, num_sms, smem, st);   // (no time stamps in this variant)
-    if (p.trace) return p.n_rows == 1 ? mk_launch_t<false, true, 1, false>(p, num_sms, smem, st) : mk_launch_t<false, true, 0, false>(p, num_sms, smem, st);
-    if (p.n_rows == 1) return ll ? mk_launch_t<false, false, 1, true>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, false>(p, num_sms, smem, st);
-    return ll ? mk_launch_t<false, false, 0, true>(p, num_sms, smem, st) : mk_launch_t<false, false, 0, false>(p, num_sms, smem, st);
+    // Variants: one generic kernel per (more than 8 rows | time stamps | one row | several rows), and for the shapes that
+    // matter most -- Llama-style models, no time stamps -- specialised ones: a single row with head_dim 64 / 128 as
+    // compile-time constants (the headline decode and the default pipeline bench), several rows with a run-time head_dim.
+    if (p.n_rows > 8) return mk_launch_t<true, false, 0, false, 0>(p, num_sms, smem, st);   // (no time stamps in this variant)
+    if (p.trace) return p.n_rows == 1 ? mk_launch_t<false, true, 1, false, 0>(p, num_sms, smem, st) : mk_launch_t<false, true, 0, false, 0>(p, num_sms, smem, st);
+    if (p.n_rows == 1) {
+        if (ll && p.head_dim == 64) return mk_launch_t<false, false, 1, true, 64>(p, num_sms, smem, st);
+        if (ll && p.head_dim == 128) return mk_launch_t<false, false, 1, true, 128>(p, num_sms, smem, st);
+        return mk_launch_t<false, false, 1, false, 0>(p, num_sms, smem, st);
+    }
+    return ll ? mk_launch_t<false, false, 0, true, 0>(p, num_sms, smem, st) : mk_launch_t<false, false, 0, false, 0>(p, num_sms, smem, st);
 }
 
 int mk_max_splits(int n_rows, int n_heads, int head_dim) {

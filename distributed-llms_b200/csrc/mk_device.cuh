@@ -341,8 +341,8 @@ struct AttnSmem {
 // cp.async the K and V rows of tokens [a, b) of (seq, kvh) into tile rows (token - tile0)
 // (inlined at its six call sites: as a real call it spills the attention accumulators around every call -- measured 3 % slower)
 __device__ __forceinline__ void attn_load_rows(const MkParams& p, const MkLayer& L, const AttnSmem& sm, const int* bt,
-                                               int kvh, int tile0, int a, int b, bool load_k, bool load_v) {
-    const int hd = p.head_dim, vecs = hd >> 3, ld = hd + 8;
+                                               int kvh, int tile0, int a, int b, bool load_k, bool load_v, int hd) {
+    const int vecs = hd >> 3, ld = hd + 8;   // hd: p.head_dim, a compile-time constant in the specialised kernels
     const int vshift = 31 - __clz(vecs);   // head_dim is 32 / 64 / 128: vecs is a power of two
     const int mask = (1 << p.page_shift) - 1;
     for (int i = threadIdx.x; i < (b - a) * vecs; i += kThreads) {
