@@ -438,7 +438,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 // ---- the kernel ----------------------------------------------------------------------------------------
 
 
-template <bool HI, bool TR, int RK, bool LL, int HD>  // HD: head_dim as a compile-time constant (0: run-time); LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
+template <bool HI, bool TR, int RK, bool LL, int HD, int PP>  // PP: fused hand-off off (0) / on (1) / decided at run time (2); HD: head_dim as a compile-time constant (0: run-time); LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
                                       // compiled in; RK = 1: one row (batch 1 -- R and RP are the constant 1), 0: any
 __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -536,7 +536,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     const uint32_t xrow_lo = smem_u32(xs) + (uint32_t)(min(g, R - 1) * ldx * 2);
     const uint32_t xrow_hi = smem_u32(xs) + (uint32_t)(min(g + 8, R - 1) * ldx * 2);
 
-    const bool piped = p.in_flag != nullptr;  // fused hand-off: inputs arrive in / outputs leave through mailboxes
+    const bool piped = PP == 2 ? p.in_flag != nullptr : PP == 1;  // fused hand-off: inputs arrive in / outputs leave through mailboxes
     const UnitId my_unit = unit_id(p, blockIdx.x);   // this CTA's first attention unit
     bool ticket_ok = true;
     for (int step = 0; step < p.n_steps; ++step) {
@@ -1027,9 +1027,9 @@ static int mk_pick_stages(const MkParams& p) {
     return 0;
 }
 
-template <bool HI, bool TR, int RK, bool LL, int HD>
+template <bool HI, bool TR, int RK, bool LL, int HD, int PP>
 static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL, HD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL, HD, PP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
@@ -1041,7 +1041,7 @@ static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStr
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL, HD>, p);
+    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL, HD, PP>, p);
     count_launch();
     return e;
 }
@@ -1057,15 +1057,19 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
     const bool ll = p.norm == NORM_RMS && p.rope && p.wpe == nullptr;   // Llama / Qwen2 (GPT-2: LayerNorm, learned positions, gelu)
     // Variants: one generic kernel per (more than 8 rows | time stamps | one row | several rows), and for the shapes that
     // matter most -- Llama-style models, no time stamps -- specialised ones: a single row with head_dim 64 / 128 as
-    // compile-time constants (the headline decode and the default pipeline bench), several rows with a run-time head_dim.
-    if (p.n_rows > 8) return mk_launch_t<true, false, 0, false, 0>(p, num_sms, smem, st);   // (no time stamps in this variant)
-    if (p.trace) return p.n_rows == 1 ? mk_launch_t<false, true, 1, false, 0>(p, num_sms, smem, st) : mk_launch_t<false, true, 0, false, 0>(p, num_sms, smem, st);
+    // compile-time constants and the fused hand-off compiled in or out (the headline decode and the default pipeline
+    // bench), several rows with a run-time head_dim.
+    if (p.n_rows > 8) return mk_launch_t<true, false, 0, false, 0, 2>(p, num_sms, smem, st);   // (no time stamps in this variant)
+    if (p.trace) return p.n_rows == 1 ? mk_launch_t<false, true, 1, false, 0, 2>(p, num_sms, smem, st) : mk_launch_t<false, true, 0, false, 0, 2>(p, num_sms, smem, st);
     if (p.n_rows == 1) {
-        if (ll && p.head_dim == 64) return mk_launch_t<false, false, 1, true, 64>(p, num_sms, smem, st);
-        if (ll && p.head_dim == 128) return mk_launch_t<false, false, 1, true, 128>(p, num_sms, smem, st);
-        return mk_launch_t<false, false, 1, false, 0>(p, num_sms, smem, st);
+        const bool piped = p.in_flag != nullptr;
+        if (ll && p.head_dim == 64)
+            return piped ? mk_launch_t<false, false, 1, true, 64, 1>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, true, 64, 0>(p, num_sms, smem, st);
+        if (ll && p.head_dim == 128)
+            return piped ? mk_launch_t<false, false, 1, true, 128, 1>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, true, 128, 0>(p, num_sms, smem, st);
+        return mk_launch_t<false, false, 1, false, 0, 2>(p, num_sms, smem, st);
     }
-    return ll ? mk_launch_t<false, false, 0, true, 0>(p, num_sms, smem, st) : mk_launch_t<false, false, 0, false, 0>(p, num_sms, smem, st);
+    return ll ? mk_launch_t<false, false, 0, true, 0, 2>(p, num_sms, smem, st) : mk_launch_t<false, false, 0, false, 0, 2>(p, num_sms, smem, st);
 }
 
 int mk_max_splits(int n_rows, int n_heads, int head_dim) {
