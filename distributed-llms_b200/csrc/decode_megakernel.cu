@@ -438,7 +438,7 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
 // ---- the kernel ----------------------------------------------------------------------------------------
 
 
-template <bool HI, bool TR, int RK, bool LL, int HD, int PP>  // PP: fused hand-off off (0) / on (1) / decided at run time (2); HD: head_dim as a compile-time constant (0: run-time); LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
+template <bool HI, bool TR, int RK, bool LL, int HD, int PP, bool XG>  // XG: the phase table may hold a streamed-rows phase; PP: fused hand-off off (0) / on (1) / decided at run time (2); HD: head_dim as a compile-time constant (0: run-time); LL: Llama-style model (RMSNorm, rotary, gated MLP): the GPT-2 paths are compiled out; HI: more than 8 batch rows (second half of the mma M dimension in use); TR: time stamps
                                       // compiled in; RK = 1: one row (batch 1 -- R and RP are the constant 1), 0: any
 __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_constant__ MkParams p) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -525,7 +525,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
     WIter prod = {0, 0, 0, 0, 0, 0, 0, nullptr, 0, 0, 0, 0, pstride};
     witer_seek(c, prod);
     for (int i = 0; i < p.stages && prod.step < p.n_steps; ++i) {
-        issue_stage(c, prod, i);
+        issue_stage<XG>(c, prod, i);
         witer_next(c, prod);
     }
     unsigned ring_slot = 0, ring_parity = 0;  // the ring slot this warp consumes next and its mbarrier parity (kept incrementally: no divisions in the loop)
@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             }
             need_barrier = true;
             c.cur_key = step * p.n_phases + phi;
-            if (ph.xg) issue_deferred_rows(c, p.stages);
+            if (XG && ph.xg) issue_deferred_rows(c, p.stages);
             if (phi == 0) {
                 if (piped && threadIdx.x == 0) {
                     // every CTA is past the barrier: the previous step's rows are complete in the next stage's inbox
@@ -649,7 +649,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                 if (ph.kind == MK_QKV) { nw = L->norm1_w; nb = L->norm1_b; }
                 else if (ph.kind == MK_GATEUP || ph.kind == MK_FC_GELU) { nw = L->norm2_w; nb = L->norm2_b; }
                 else if (ph.kind == MK_HEAD) { nw = p.final_norm_w; nb = p.final_norm_b; }
-                else if (ph.kind == MK_DOWN) { rows = p.act; nk = NORM_NONE; stage = !ph.xg; }
+                else if (ph.kind == MK_DOWN) { rows = p.act; nk = NORM_NONE; stage = !(XG && ph.xg); }
                 else { rows = p.attn_out; nk = NORM_NONE; }   // o-proj: merged attention rows
                 if (stage) stage_rows<TR, RK, LL>(p, rows, ph.K, nk, nw, nb, xs, ldx, red, red_flip, tr);
             }
@@ -695,13 +695,13 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     mbar_wait(c.full + slot * 8, ring_parity);
                     if (tr) tq1 = clock64();
                     const uint32_t sbase = c.ring + slot * kStageBytes + (uint32_t)(lane * 16);  // [32-k block][row g][chunk t4]
-                    const int stage_k = ph.xg ? kStageK / 2 : kStageK;
+                    const int stage_k = (XG && ph.xg) ? kStageK / 2 : kStageK;
                     const int k0 = st * stage_k;
                     const int nkb = min(stage_k, K - k0) >> 5;  // 32-k blocks in this stage
                     // input rows: from the shared-memory copy (row-major), or from the second half of the stage
                     // (fragment layout: [32-k block][row g][chunk t4], 512 bytes per block)
-                    const uint32_t xstep = ph.xg ? 512u : 64u;
-                    const uint32_t xlo = ph.xg ? c.ring + slot * kStageBytes + kStageBytes / 2 + (uint32_t)(lane * 16)
+                    const uint32_t xstep = (XG && ph.xg) ? 512u : 64u;
+                    const uint32_t xlo = (XG && ph.xg) ? c.ring + slot * kStageBytes + kStageBytes / 2 + (uint32_t)(lane * 16)
                                                : xrow_lo + (uint32_t)((k0 + t4 * 8) * 2);
                     const uint32_t xhi = xrow_hi + (uint32_t)((k0 + t4 * 8) * 2);
                     // lane (g, t4) holds 8 consecutive k of weight row g and of batch row g: two mma k-steps per block
@@ -740,7 +740,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                         ring_parity ^= 1u;
                     }
                     if (prod.step < p.n_steps) {  // refill the slot with the next stage of this warp's sequence
-                        issue_stage(c, prod, (int)slot);
+                        issue_stage<XG>(c, prod, (int)slot);
                         witer_next(c, prod);
                     }
                     if (tr) {
@@ -1027,9 +1027,9 @@ static int mk_pick_stages(const MkParams& p) {
     return 0;
 }
 
-template <bool HI, bool TR, int RK, bool LL, int HD, int PP>
+template <bool HI, bool TR, int RK, bool LL, int HD, int PP, bool XG = true>
 static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStream_t st) {
-    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL, HD, PP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(decode_megakernel<HI, TR, RK, LL, HD, PP, XG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
@@ -1041,7 +1041,7 @@ static cudaError_t mk_launch_t(const MkParams& p, int grid, size_t smem, cudaStr
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL, HD, PP>, p);
+    e = cudaLaunchKernelEx(&cfg, decode_megakernel<HI, TR, RK, LL, HD, PP, XG>, p);
     count_launch();
     return e;
 }
@@ -1063,10 +1063,11 @@ cudaError_t launch_decode_megakernel(const MkParams& p_in, int num_sms, cudaStre
     if (p.trace) return p.n_rows == 1 ? mk_launch_t<false, true, 1, false, 0, 2>(p, num_sms, smem, st) : mk_launch_t<false, true, 0, false, 0, 2>(p, num_sms, smem, st);
     if (p.n_rows == 1) {
         const bool piped = p.in_flag != nullptr;
-        if (ll && p.head_dim == 64)
-            return piped ? mk_launch_t<false, false, 1, true, 64, 1>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, true, 64, 0>(p, num_sms, smem, st);
-        if (ll && p.head_dim == 128)
-            return piped ? mk_launch_t<false, false, 1, true, 128, 1>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, true, 128, 0>(p, num_sms, smem, st);
+        const bool plain = ll && !p.act_xlayout;   // (a single row never needs the streamed-rows variant; DLLM_MK_XG=1 can force it)
+        if (plain && p.head_dim == 64)
+            return piped ? mk_launch_t<false, false, 1, true, 64, 1, false>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, true, 64, 0, false>(p, num_sms, smem, st);
+        if (plain && p.head_dim == 128)
+            return piped ? mk_launch_t<false, false, 1, true, 128, 1, false>(p, num_sms, smem, st) : mk_launch_t<false, false, 1, true, 128, 0, false>(p, num_sms, smem, st);
         return mk_launch_t<false, false, 1, false, 0, 2>(p, num_sms, smem, st);
     }
     return ll ? mk_launch_t<false, false, 0, true, 0, 2>(p, num_sms, smem, st) : mk_launch_t<false, false, 0, false, 0, 2>(p, num_sms, smem, st);

@@ -243,12 +243,14 @@ __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
     }
 }
 
+// XG = false: the launch has no streamed-rows phase (the variant's code is compiled out)
+template <bool XG = true>
 __device__ __forceinline__ void issue_stage(const Ctx& c, const WIter& it, int slot) {
     if (c.lane == 0) {
         uint32_t bytes;
         const uint32_t dst = c.ring + slot * kStageBytes, bar = c.full + slot * 8;
         const int panel = it.p0 + it.pstride * (it.j0 + it.jr);
-        if (!it.xg) {
+        if (!XG || !it.xg) {
             const unsigned char* src = it.wp + mk_stage_offset(it.K, panel, it.st, kStageBytes, &bytes);
             mbar_expect_tx(bar, bytes);
             bulk_g2s(dst, src, bytes, bar);
