@@ -576,6 +576,27 @@ def test_fused_handoff_single_stage_equals_decode_loop(n_micro, rows, persistent
         box.close()
 
 
+@pytest.mark.parametrize("batch", [1, 3])
+def test_time_stamped_kernel_variant_generates_the_same_ids(batch, tmp_path, monkeypatch):
+    """DLLM_MK_TRACE selects the persistent kernel's variants with per-phase time stamps compiled in (their own template
+    instantiations, generic in everything else): same ids as the specialised kernels, and the trace file is written."""
+    if os.environ.get("DLLM_MEGAKERNEL") == "0":
+        pytest.skip("the persistent kernel is switched off")
+    cfg = ShardModelConfig("llama", 256, 2, 4, 2, 64, 512, 500, 128, 1e-5, 10000.0)
+    sd = make_state_dict(cfg, 5, torch.float32, init="full")
+    prompts = make_prompts(cfg.vocab, batch, 9, seed=batch)
+    ids = {}
+    for traced in (False, True):
+        if traced:
+            monkeypatch.setenv("DLLM_MK_TRACE", str(tmp_path / "trace.csv"))
+        (st,) = gpu_stages(cfg, sd, 1, torch.bfloat16, max_rows=64, max_seqs=batch, max_context=64, page_size=16)
+        first = st.compute({"input_ids": prompts})["next_token"].cpu()
+        ids[traced] = torch.cat([first[:, None], st.decode_loop(batch, 6).cpu()], 1)
+    assert torch.equal(ids[True], ids[False])
+    lines = open(tmp_path / "trace.csv").read().splitlines()
+    assert lines[0].startswith("step,phase,kind") and len(lines) > 6
+
+
 @pytest.mark.parametrize("persistent", [True, False])
 def test_pipelined_loop_gives_up_on_a_missing_ticket_and_the_stage_stays_usable(persistent, monkeypatch):
     """A stage whose input never arrives (nobody posted the seed ids) must not hang or trap: after the time-out its loop is
