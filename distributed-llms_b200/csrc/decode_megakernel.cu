@@ -208,7 +208,9 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
         // output fragment; the four warps are merged once, after the last tile.  P is rounded to bf16 where HF rounds it.
         const int g = lane >> 2, t4 = lane & 3;
         bf16* sQ = reinterpret_cast<bf16*>(sm.q);  // [16][ld]
-        float m_lo = -FLT_MAX, m_hi = -FLT_MAX, l_lo = 0.f, l_hi = 0.f;  // heads g and g + 8, this warp's tokens only
+        // (a group has at most kMaxGq = 8 query heads: MMA rows 8..15 are padding, their half of every fragment is never used)
+        static_assert(kMaxGq <= 8, "the upper half of the MMA rows is assumed to be padding");
+        float m_lo = -FLT_MAX, l_lo = 0.f;  // head g, this warp's tokens only
         float o[16][4];  // [hd / 8 column tiles][C fragment]; head_dim 32 / 64 use the first 4 / 8
 #pragma unroll
         for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
@@ -261,54 +263,44 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
             __syncthreads();
             if (my_tokens) {
                 // scale, mask the tokens past the end of the tile, online softmax over this warp's 16 tokens
-                float mx_lo = -FLT_MAX, mx_hi = -FLT_MAX;
+                float mx_lo = -FLT_MAX;
 #pragma unroll
                 for (int n2 = 0; n2 < 2; ++n2) {
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const int key = warp * 16 + n2 * 8 + 2 * t4 + (e & 1);
+                    for (int e = 0; e < 2; ++e) {
+                        const int key = warp * 16 + n2 * 8 + 2 * t4 + e;
                         float v = bf16_round(bf16_round(s[n2][e]) * scale);
                         if (key >= nt) v = -FLT_MAX;
                         s[n2][e] = v;
                     }
                     mx_lo = fmaxf(mx_lo, fmaxf(s[n2][0], s[n2][1]));
-                    mx_hi = fmaxf(mx_hi, fmaxf(s[n2][2], s[n2][3]));
                 }
                 mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 1));
                 mx_lo = fmaxf(mx_lo, __shfl_xor_sync(0xffffffffu, mx_lo, 2));
-                mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 1));
-                mx_hi = fmaxf(mx_hi, __shfl_xor_sync(0xffffffffu, mx_hi, 2));
-                const float mn_lo = fmaxf(m_lo, mx_lo), mn_hi = fmaxf(m_hi, mx_hi);
-                const float c_lo = expf(m_lo - mn_lo), c_hi = expf(m_hi - mn_hi);
-                float sum_lo = 0.f, sum_hi = 0.f;
+                const float mn_lo = fmaxf(m_lo, mx_lo);
+                const float c_lo = expf(m_lo - mn_lo);
+                float sum_lo = 0.f;
                 uint32_t pf[4];  // P as the A fragment of one 16-token k-step
 #pragma unroll
                 for (int n2 = 0; n2 < 2; ++n2) {
                     const float p0 = s[n2][0] == -FLT_MAX ? 0.f : expf(s[n2][0] - mn_lo);
                     const float p1 = s[n2][1] == -FLT_MAX ? 0.f : expf(s[n2][1] - mn_lo);
-                    const float p2 = s[n2][2] == -FLT_MAX ? 0.f : expf(s[n2][2] - mn_hi);
-                    const float p3 = s[n2][3] == -FLT_MAX ? 0.f : expf(s[n2][3] - mn_hi);
                     sum_lo += p0 + p1;
-                    sum_hi += p2 + p3;
                     pf[n2 * 2 + 0] = pack_bf16(p0, p1);
-                    pf[n2 * 2 + 1] = pack_bf16(p2, p3);
+                    pf[n2 * 2 + 1] = 0u;   // rows 8..15 of P
                 }
                 sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 1);
                 sum_lo += __shfl_xor_sync(0xffffffffu, sum_lo, 2);
-                sum_hi += __shfl_xor_sync(0xffffffffu, sum_hi, 1);
-                sum_hi += __shfl_xor_sync(0xffffffffu, sum_hi, 2);
                 l_lo = l_lo * c_lo + sum_lo;
-                l_hi = l_hi * c_hi + sum_hi;
                 m_lo = mn_lo;
-                m_hi = mn_hi;
                 // O = O * corr + P V : V[token][col] is read transposed
 #pragma unroll
                 for (int ct = 0; ct < 16; ct += 2) {
                     if (ct * 8 < hd) {
                         uint32_t vb[4];
                         ldsm_x4_trans(vb, smem_u32(sm.v + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ld + ct * 8 + (lane >> 4) * 8));
-                        o[ct][0] *= c_lo; o[ct][1] *= c_lo; o[ct][2] *= c_hi; o[ct][3] *= c_hi;
-                        o[ct + 1][0] *= c_lo; o[ct + 1][1] *= c_lo; o[ct + 1][2] *= c_hi; o[ct + 1][3] *= c_hi;
+                        o[ct][0] *= c_lo; o[ct][1] *= c_lo;
+                        o[ct + 1][0] *= c_lo; o[ct + 1][1] *= c_lo;
                         mma_bf16(o[ct], pf[0], pf[1], pf[2], pf[3], vb[0], vb[1]);
                         mma_bf16(o[ct + 1], pf[0], pf[1], pf[2], pf[3], vb[2], vb[3]);
                     }
@@ -324,15 +316,14 @@ __device__ __forceinline__ void attention_phase(const MkParams& p, const StepCac
         float* mm = sm.s;                            // [4][16] maxima, then [4][16] sums
         if (warp < 4) {
             if (t4 == 0) {
-                mm[warp * 16 + g] = m_lo; mm[warp * 16 + g + 8] = m_hi;
-                mm[64 + warp * 16 + g] = l_lo; mm[64 + warp * 16 + g + 8] = l_hi;
+                mm[warp * 16 + g] = m_lo;
+                mm[64 + warp * 16 + g] = l_lo;
             }
 #pragma unroll
             for (int ct = 0; ct < 16; ++ct) {
                 if (ct * 8 < hd) {
                     float* d = mo + ((size_t)warp * 16 + g) * hd + ct * 8 + 2 * t4;  // rows past Gq are padding
                     if (g < Gq) *reinterpret_cast<float2*>(d) = make_float2(o[ct][0], o[ct][1]);
-                    if (g + 8 < Gq) *reinterpret_cast<float2*>(d + 8 * hd) = make_float2(o[ct][2], o[ct][3]);
                 }
             }
         }
