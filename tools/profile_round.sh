@@ -10,9 +10,8 @@ python bench.py --steps 8 --warmup 3 --no-cpu-baseline > $out/${tag}_bench_8step
 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $out/${tag}_ncu_launches.csv \
     python bench.py --steps 8 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_launches.log 2>&1
-# the timed launch (8 steps) is the second decode_megakernel launch of that command with more than one step:
-# launches in order: prefill-side single-step launches (none for a 512-row chunk), warm-up loop (3 steps), timed loop (8)
-ncu --set full --clock-control none --import-source on -k regex:decode_megakernel -s 1 -c 1 -o $out/${tag}_megakernel \
+# the first decode_megakernel launch of the command is the 8-step loop of bench.py's token check (right after the prefill)
+ncu --set full --clock-control none --import-source on -k regex:decode_megakernel -s 0 -c 1 -o $out/${tag}_megakernel \
     python bench.py --steps 8 --warmup 3 --no-cpu-baseline > $out/${tag}_ncu_full.log 2>&1
 ncu -i $out/${tag}_megakernel.ncu-rep --page raw --csv > $out/${tag}_ncu_megakernel_raw.csv 2>/dev/null
 DLLM_MK_TRACE=$out/${tag}_phase_trace.csv python bench.py --steps 6 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
@@ -27,7 +26,7 @@ python tools/mk_trace_summary.py $out/${tag}_phase_trace_llama8b.csv > $out/${ta
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_ncu_prefill_launches.csv \
     -k regex:'gemm_tc|gemm_swapab|prefill_attn|norm_rows|rope_append|embed|argmax' python bench.py --steps 4 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
 # Llama-3-8B: memory traffic of one persistent launch (for profiles/traffic.json), decode batches on the per-op path, prefill
-ncu --set full --clock-control none -k regex:decode_megakernel -s 1 -c 1 -o $out/${tag}_megakernel_llama8b \
+ncu --set full --clock-control none -k regex:decode_megakernel -s 0 -c 1 -o $out/${tag}_megakernel_llama8b \
     python bench.py --workload llama3-8b --steps 8 --warmup 3 --no-cpu-baseline > /dev/null 2>&1
 ncu -i $out/${tag}_megakernel_llama8b.ncu-rep --page raw --csv > $out/${tag}_ncu_megakernel_llama8b_raw.csv 2>/dev/null
 for b in 12 16 32 64; do
