@@ -672,7 +672,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
             }
             int x = chunk_begin(warp, T);
             const int x_end = chunk_begin(warp + 1, T);
-            int jr = x < x_end ? x / ns : 0;
+            int jr = x < x_end ? div_stages(x, ph) : 0;
             int st = x - jr * ns;
             while (x < x_end) {
                 const int seg_end = min(x_end, (jr + 1) * ns);

@@ -32,13 +32,18 @@ struct MkPhase {
     int32_t n0;          // logical output rows (un-padded)
     int16_t kind;        // MkKind
     int16_t layer;
-    int16_t ksplit;      // unused (the kernel cuts a round's stages into equal per-warp chunks)
     int16_t n_stages;    // ceil(K / 256); K / 128 when xg
     int16_t xg;          // 1: the input rows are streamed from global memory with the weights (half-size stages:
                          //    2 KB of weights + 2 KB of rows in fragment layout) instead of being staged in shared
                          //    memory by the prologue -- used for the down projection when R x ffn does not fit
-    int16_t pad_;
+    float inv_ns;        // 1 / n_stages: the kernel divides stage indices by multiplying (mk_set_stages)
 };
+static_assert(sizeof(MkPhase) == 32, "MkPhase is copied to shared memory word by word");
+
+inline void mk_set_stages(MkPhase& q, int n_stages) {
+    q.n_stages = (int16_t)n_stages;
+    q.inv_ns = 1.0f / (float)(n_stages > 0 ? n_stages : 1);
+}
 
 struct MkLayer {
     const void *norm1_w, *norm1_b, *bq, *bk, *bv, *bo, *norm2_w, *norm2_b, *b_up, *b_down;

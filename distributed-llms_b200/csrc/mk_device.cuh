@@ -213,6 +213,9 @@ struct Ctx {
 
 // chunk of warp w in a round of T stages: [w * T / kWarps, (w + 1) * T / kWarps)
 __device__ __forceinline__ int chunk_begin(int w, int T) { return (w * T) / kWarps; }
+// x / ph.n_stages without an integer division: x is a stage index of a round (< 2^16), so (x + 0.5) * (1 / ns) is at
+// least 0.5 / ns away from every integer -- far more than the rounding error of the product
+__device__ __forceinline__ int div_stages(int x, const MkPhase& ph) { return (int)(((float)x + 0.5f) * ph.inv_ns); }
 
 __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
     while (it.step < c.n_steps) {
@@ -225,7 +228,7 @@ __device__ __forceinline__ void witer_seek(const Ctx& c, WIter& it) {
                 it.x_end = chunk_begin(c.warp + 1, T);
                 if (it.x < it.x_end) {
                     it.ns = ph.n_stages;
-                    it.jr = it.x / it.ns;
+                    it.jr = div_stages(it.x, ph);
                     it.st = it.x - it.jr * it.ns;
                     it.wp = static_cast<const unsigned char*>(ph.wp);
                     it.K = ph.K;

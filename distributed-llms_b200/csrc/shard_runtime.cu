@@ -301,14 +301,13 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
             if (me == cudaSuccess) me = launch_pack(job, 0);
             MkPhase q{};
             q.wp = pk; q.n_panels = n_panels; q.K = K; q.n0 = n0; q.kind = (int16_t)kind; q.layer = (int16_t)layer;
-            q.n_stages = (int16_t)((K + MK_STAGE_K - 1) / MK_STAGE_K);
-            q.ksplit = 1;
+            mk_set_stages(q, (K + MK_STAGE_K - 1) / MK_STAGE_K);
             ph.push_back(q);
             pk += align_up(mk_packed_bytes(n_panels, K), 256);
         };
         auto plain_phase = [&](int kind, int layer) {
             MkPhase q{};
-            q.kind = (int16_t)kind; q.layer = (int16_t)layer; q.ksplit = 1; q.n_stages = 1;
+            q.kind = (int16_t)kind; q.layer = (int16_t)layer; mk_set_stages(q, 1);
             ph.push_back(q);
         };
         if (c.has_embed) plain_phase(MK_EMBED, 0);
@@ -343,7 +342,7 @@ extern "C" int dllm_shard_create(const dllm_shard_config* cfg, const dllm_layer_
             for (auto& q : px) {
                 if (q.kind == MK_DOWN) {
                     q.xg = 1;
-                    q.n_stages = (int16_t)(q.K / (MK_STAGE_K / 2));
+                    mk_set_stages(q, q.K / (MK_STAGE_K / 2));
                 }
             }
             s->mk_part_units_xg = MK_PART_UNITS;
