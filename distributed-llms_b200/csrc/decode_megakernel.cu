@@ -580,6 +580,7 @@ __global__ void __launch_bounds__(kThreads, 1) decode_megakernel(const __grid_co
                     sc.seq[threadIdx.x] = sq;
                     sc.page[threadIdx.x] = p.block_table[(size_t)sq * p.pages_per_seq + (ps >> p.page_shift)];
                     sc.off[threadIdx.x] = ps & ((1 << p.page_shift) - 1);
+                    step_cache_splits(sc, threadIdx.x, p.n_splits);
                     if (p.mirror_pos && blockIdx.x == 0) {  // inputs were read in place from host memory: keep the device copies current
                         p.mirror_pos[threadIdx.x] = ps;
                         p.mirror_seq[threadIdx.x] = sq;

@@ -165,7 +165,18 @@ struct StepCache {
     int seq[MK_MAX_ROWS];
     int page[MK_MAX_ROWS];   // KV page that holds position pos[r] of sequence seq[r]
     int off[MK_MAX_ROWS];    // offset of pos[r] inside that page
+    // the split geometry of each row's context, the same in every layer of the step: tokens per split (whole 64-token
+    // tiles) and how many splits own a token -- worked out once per step, not per attention phase
+    int chunk[MK_MAX_ROWS];
+    int n_act[MK_MAX_ROWS];
 };
+__device__ __forceinline__ void step_cache_splits(StepCache& sc, int r, int n_splits) {
+    const int len = sc.pos[r] + 1;
+    int chunk = (len + n_splits - 1) / n_splits;
+    chunk = (chunk + 63) / 64 * 64;   // kTT
+    sc.chunk[r] = chunk;
+    sc.n_act[r] = (len + chunk - 1) / chunk;
+}
 
 // ---- a warp's static sequence of stages -------------------------------------------------------------------
 // Panel p belongs to CTA p % grid (local index p / grid).  A CTA works through its panels in rounds of up to
@@ -325,12 +336,7 @@ __device__ __forceinline__ uint4 norm_vec(const uint4& x, const uint4& w, const 
 }
 
 // number of splits of row r that own at least one token (the others never run and are never read)
-__device__ __forceinline__ int attn_active_splits(const MkParams& p, const StepCache& sc, int r) {
-    const int S = p.n_splits, len = sc.pos[r] + 1;
-    int chunk = (len + S - 1) / S;
-    chunk = (chunk + kTT - 1) / kTT * kTT;
-    return (len + chunk - 1) / chunk;
-}
+__device__ __forceinline__ int attn_active_splits(const MkParams&, const StepCache& sc, int r) { return sc.n_act[r]; }
 
 __device__ __forceinline__ float4 ldcg_f4(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
 
@@ -386,14 +392,12 @@ __device__ __forceinline__ UnitId unit_id(const MkParams& p, int u) {
 }
 __device__ __forceinline__ AttnUnit attn_unit(const MkParams& p, const StepCache& sc, const UnitId& id) {
     AttnUnit a;
-    const int S = p.n_splits;
     a.r = id.r;
     a.kvh = id.kvh;
     a.split = id.split;
     const int len = sc.pos[a.r] + 1;
     a.seq = sc.seq[a.r];
-    int chunk = (len + S - 1) / S;
-    chunk = (chunk + kTT - 1) / kTT * kTT;  // whole tiles per split: no one-token tail tiles
+    const int chunk = sc.chunk[a.r];  // whole tiles per split: no one-token tail tiles
     a.t0 = min(len, a.split * chunk);
     a.t1 = min(len, a.t0 + chunk);
     return a;
